@@ -1,0 +1,145 @@
+// Shared device/host helpers for libhpcodec_sm100a.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <math.h>
+
+#include "../../include/hpcodec.h"
+
+// ---------------------------------------------------------------------------------------
+// error convention: every export returns int, message via hpc_last_error()
+// ---------------------------------------------------------------------------------------
+extern thread_local char g_hpc_err[512];
+
+#define HPC_FAIL(code, ...)                                   \
+  do {                                                        \
+    snprintf(g_hpc_err, sizeof(g_hpc_err), __VA_ARGS__);      \
+    return (code);                                            \
+  } while (0)
+
+#define HPC_REQUIRE(cond, code, ...) \
+  do {                               \
+    if (!(cond)) HPC_FAIL(code, __VA_ARGS__); \
+  } while (0)
+
+#define HPC_CUDA(expr)                                                                 \
+  do {                                                                                 \
+    cudaError_t _e = (expr);                                                           \
+    if (_e != cudaSuccess)                                                             \
+      HPC_FAIL(HPC_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e),   \
+               __FILE__, __LINE__);                                                    \
+  } while (0)
+
+#define HPC_LAUNCH_CHECK()                                                             \
+  do {                                                                                 \
+    cudaError_t _e = cudaGetLastError();                                               \
+    if (_e != cudaSuccess)                                                             \
+      HPC_FAIL(HPC_ERR_CUDA, "kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), \
+               __FILE__, __LINE__);                                                    \
+  } while (0)
+
+static inline bool hpc_aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+// number of SMs of the current device (cached per thread)
+int hpc_num_sms();
+
+// ---------------------------------------------------------------------------------------
+// low-precision element access (T = float or __nv_bfloat16)
+// ---------------------------------------------------------------------------------------
+template <typename T> __device__ __forceinline__ float ld_as_float(const T* p, size_t i);
+template <> __device__ __forceinline__ float ld_as_float<float>(const float* p, size_t i) { return p[i]; }
+template <> __device__ __forceinline__ float ld_as_float<__nv_bfloat16>(const __nv_bfloat16* p, size_t i) {
+  return __bfloat162float(p[i]);
+}
+template <typename T> __device__ __forceinline__ void st_from_float(T* p, size_t i, float v);
+template <> __device__ __forceinline__ void st_from_float<float>(float* p, size_t i, float v) { p[i] = v; }
+template <> __device__ __forceinline__ void st_from_float<__nv_bfloat16>(__nv_bfloat16* p, size_t i, float v) {
+  p[i] = __float2bfloat16_rn(v);
+}
+
+// ---------------------------------------------------------------------------------------
+// reductions
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Sum over the block (blockDim.x*blockDim.y*blockDim.z threads, multiple of 32, <= 1024).
+// Result valid in thread 0.  `sm` must hold 32 floats.
+__device__ __forceinline__ float block_sum(float v, float* sm) {
+  const int tid = threadIdx.x + blockDim.x * (threadIdx.y + blockDim.y * threadIdx.z);
+  const int nthreads = blockDim.x * blockDim.y * blockDim.z;
+  v = warp_sum(v);
+  __syncthreads();  // protect sm reuse across successive calls
+  if ((tid & 31) == 0) sm[tid >> 5] = v;
+  __syncthreads();
+  if (tid < 32) {
+    float t = (tid < (nthreads + 31) / 32) ? sm[tid] : 0.f;
+    t = warp_sum(t);
+    v = t;
+  }
+  return v;
+}
+
+// Deterministic cross-block sum: every block stores its partial; the last block to arrive
+// (atomic ticket) adds the partials in index order in double and writes out[0].
+// counter must be zero before the launch and is reset to zero by the last block.
+__device__ __forceinline__ void finalize_partials(float partial, float* partials, int nblocks, int block_id,
+                                                  unsigned int* counter, float* out, float scale) {
+  __shared__ bool is_last;
+  const int tid = threadIdx.x + blockDim.x * (threadIdx.y + blockDim.y * threadIdx.z);
+  if (tid == 0) {
+    partials[block_id] = partial;
+    __threadfence();
+    unsigned int t = atomicAdd(counter, 1u);
+    is_last = (t == (unsigned int)nblocks - 1);
+  }
+  __syncthreads();
+  if (is_last && tid < 32) {
+    __threadfence();
+    double s = 0.0;
+    for (int i = tid; i < nblocks; i += 32) s += (double)((volatile float*)partials)[i];
+    s = warp_sum_d(s);
+    if (tid == 0) {
+      out[0] = (float)(s * (double)scale);
+      *counter = 0;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// Philox4x32-10 counter RNG (in-kernel uniform noise; key = seed, counter = (offset,idx))
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    uint32_t hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
+    uint32_t hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
+    ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+    key.x += W0;
+    key.y += W1;
+  }
+  return ctr;
+}
+// U[0,1) with 24 bits, like torch.rand for fp32 (multiples of 2^-24, never 1.0)
+__device__ __forceinline__ float u01_from_bits(uint32_t b) { return (float)(b >> 8) * (1.0f / 16777216.0f); }
+
+// one uniform for flat element index i
+__device__ __forceinline__ float philox_uniform(uint64_t seed, uint64_t offset, uint64_t i) {
+  uint4 ctr = make_uint4((uint32_t)(i >> 2), (uint32_t)(i >> 34), (uint32_t)offset, (uint32_t)(offset >> 32));
+  uint2 key = make_uint2((uint32_t)seed, (uint32_t)(seed >> 32));
+  uint4 r = philox4x32_10(ctr, key);
+  uint32_t w = (i & 3) == 0 ? r.x : (i & 3) == 1 ? r.y : (i & 3) == 2 ? r.z : r.w;
+  return u01_from_bits(w);
+}

@@ -1,0 +1,646 @@
+"""Host-side orchestration of the sm_100a kernels: layer plans, forward and hand-scheduled
+backward of every block on the scale-hyperprior hot path.
+
+Nothing here does arithmetic on tensors with torch ops: torch is used for device memory
+(torch.empty / zeros), streams and autograd plumbing only; every value is produced by a
+kernel of libhpcodec_sm100a.so (include/hpcodec.h).
+
+Layout: activations are contiguous (N,H,W,C) tensors ("NHWC"); module boundaries expose
+them as (N,C,H,W)-shaped views (torch channels_last), see `as_nchw` / `to_nhwc`.
+"""
+import ctypes
+import math
+from ctypes import byref, c_double, c_float, c_int
+
+import torch
+
+from . import _lib
+from ._lib import (BF16, DIST_GAUSS, DIST_LAPLACE, ENGINE_SIMT, ENGINE_UMMA, EPI_EXP_CLAMP, EPI_GDN, EPI_GDN_BWD,
+                   EPI_IGDN, EPI_IGDN_BWD, EPI_LINEAR, EPI_RELU, EPI_RELU_MASK, EPI_SIGN_ADD, F32, check, lib, ptr,
+                   stream)
+
+# ----------------------------------------------------------------------------------------
+# compute mode
+# ----------------------------------------------------------------------------------------
+_MODES = {
+    # name: (activation dtype, igemm engine)
+    "bf16": (torch.bfloat16, ENGINE_UMMA),       # product path: tcgen05/TMEM/TMA, bf16 operands, fp32 accumulate
+    "fp32": (torch.float32, ENGINE_SIMT),        # exact-parity path: CUDA-core fp32 (checker for the bf16 path)
+    "bf16_simt": (torch.bfloat16, ENGINE_SIMT),  # bf16 operands on CUDA cores (isolates tcgen05 bugs from rounding)
+}
+_mode = "bf16"
+
+
+def set_compute_mode(mode):
+    global _mode
+    if mode not in _MODES:
+        raise KeyError(f"compute mode {mode!r} not in {sorted(_MODES)}")
+    _mode = mode
+
+
+def get_compute_mode():
+    return _mode
+
+
+def lp_dtype():
+    return _MODES[_mode][0]
+
+
+def engine():
+    return _MODES[_mode][1]
+
+
+class compute_mode:
+    """Context manager: `with compute_mode("fp32"): ...`"""
+
+    def __init__(self, mode):
+        self.mode = mode
+
+    def __enter__(self):
+        self.prev = get_compute_mode()
+        set_compute_mode(self.mode)
+
+    def __exit__(self, *a):
+        set_compute_mode(self.prev)
+
+
+# ----------------------------------------------------------------------------------------
+# small utilities
+# ----------------------------------------------------------------------------------------
+_scratch = {}
+
+
+def reduce_scratch(device):
+    key = ("reduce", device)
+    if key not in _scratch:
+        _scratch[key] = torch.zeros(lib().hpc_reduce_scratch_bytes(), dtype=torch.uint8, device=device)
+    return _scratch[key]
+
+
+def sse_scratch(device, n):
+    key = ("sse", device)
+    need = 4096 + 4 * 64 * max(n, 1)
+    if key not in _scratch or _scratch[key].numel() < need:
+        _scratch[key] = torch.zeros(need, dtype=torch.uint8, device=device)
+    return _scratch[key]
+
+
+def to_nhwc(x, dtype=None):
+    """(N,C,H,W)-shaped tensor (any strides) -> contiguous (N,H,W,C) tensor of `dtype`."""
+    _lib.require_cuda(x)
+    dtype = dtype or x.dtype
+    v = x.permute(0, 2, 3, 1)
+    if v.is_contiguous():
+        if v.dtype == dtype:
+            return v
+        out = torch.empty(v.shape, dtype=dtype, device=x.device)
+        check(lib().hpc_cast(ptr(v), _lib.dtype_code(v), ptr(out), _lib.dtype_code(out), v.numel(), stream()))
+        return out
+    xc = x.contiguous()
+    N, C, H, W = xc.shape
+    if xc.dtype != torch.float32:
+        xf = torch.empty(xc.shape, dtype=torch.float32, device=x.device)
+        check(lib().hpc_cast(ptr(xc), _lib.dtype_code(xc), ptr(xf), F32, xc.numel(), stream()))
+        xc = xf
+    out = torch.empty((N, H, W, C), dtype=dtype, device=x.device)
+    check(lib().hpc_nchw_to_nhwc(ptr(xc), ptr(out), _lib.dtype_code(out), N, C, H, W, stream()))
+    return out
+
+
+def as_nchw(x_nhwc):
+    """zero-copy (N,C,H,W) view of an NHWC tensor (== torch channels_last)."""
+    return x_nhwc.permute(0, 3, 1, 2)
+
+
+def cast(x, dtype):
+    if x.dtype == dtype:
+        return x
+    out = torch.empty(x.shape, dtype=dtype, device=x.device)
+    check(lib().hpc_cast(ptr(x), _lib.dtype_code(x), ptr(out), _lib.dtype_code(out), x.numel(), stream()))
+    return out
+
+
+def contiguous_f32(x):
+    """fp32 contiguous copy/view of a tensor (module-boundary hygiene; uses the cast kernel)."""
+    if x.dtype == torch.float32 and x.is_contiguous():
+        return x
+    if not x.is_contiguous():
+        x = x.contiguous()
+    return cast(x, torch.float32)
+
+
+# ----------------------------------------------------------------------------------------
+# tap tables
+# ----------------------------------------------------------------------------------------
+def conv_type_taps(k, s, p):
+    """Conv2d(k,s,p) as one dense phase: input pixel = out*s + (kh-p)."""
+    taps = [(kh - p, kw - p, kh * k + kw) for kh in range(k) for kw in range(k)]
+    return taps, [(len(taps), 0, 0, 0)]
+
+
+def deconv_type_taps(k, s, p):
+    """ConvTranspose2d(k,s,p): one phase per output-pixel parity (a,b); out = i*s+a reads in[i+dh],
+    dh = (a+p-kh)/s for the kh with (a+p-kh) % s == 0."""
+    taps, phases = [], []
+    for a in range(s):
+        for b in range(s):
+            begin = len(taps)
+            for kh in range(k):
+                if (a + p - kh) % s:
+                    continue
+                for kw in range(k):
+                    if (b + p - kw) % s:
+                        continue
+                    taps.append(((a + p - kh) // s, (b + p - kw) // s, kh * k + kw))
+            phases.append((len(taps) - begin, begin, a, b))
+    return taps, phases
+
+
+def _fill_taps(P, taps, phases):
+    P.nphases = len(phases)
+    for i, (nt, begin, a, b) in enumerate(phases):
+        P.phase[i].ntaps, P.phase[i].tap_begin, P.phase[i].oh_off, P.phase[i].ow_off = nt, begin, a, b
+    for i, (dh, dw, _) in enumerate(taps):
+        P.dh[i], P.dw[i] = dh, dw
+
+
+_pack_cache = {}
+
+
+def pack_weight(w, taps, rows, cols, stride_r, stride_c, dtype, cache=True):
+    """Packed (ntaps, rows, cols) copy of a reference-layout weight in `dtype` (hpc_pack_weight).
+    Cached on (storage, version) so evaluation loops do not repack unchanged weights."""
+    key = (w.data_ptr(), w._version, rows, cols, stride_r, stride_c, dtype, tuple(t[2] for t in taps))
+    if cache:
+        hit = _pack_cache.get(key)
+        if hit is not None:
+            return hit
+    out = torch.empty((len(taps), rows, cols), dtype=dtype, device=w.device)
+    src = (c_int * len(taps))(*[t[2] for t in taps])
+    check(lib().hpc_pack_weight(ptr(w), ptr(out), _lib.dtype_code(out), len(taps), rows, cols, stride_r, stride_c,
+                                src, stream()))
+    if cache:
+        if len(_pack_cache) > 256:
+            _pack_cache.clear()
+        _pack_cache[key] = out
+    return out
+
+
+def unpack_wgrad(gw_packed, grad_out, taps, rows, cols, stride_r, stride_c):
+    src = (c_int * len(taps))(*[t[2] for t in taps])
+    check(lib().hpc_unpack_wgrad(ptr(gw_packed), ptr(grad_out), len(taps), rows, cols, stride_r, stride_c, src, 0,
+                                 stream()))
+
+
+# ----------------------------------------------------------------------------------------
+# implicit GEMM wrappers
+# ----------------------------------------------------------------------------------------
+def igemm_fwd(x, w_packed, taps, phases, grid_hw, is_, os_, out_hw, Co, epi=EPI_LINEAR, bias=None, aux0=None,
+              aux1=None, aux2=None, want_f32=False, want_lp=True, want_sq=False, want_abs=False, want_nrm=False):
+    """x: NHWC lp tensor.  Returns dict with the requested outputs (NHWC)."""
+    N, H, W, Ci = x.shape
+    OH, OW = out_hw
+    P = _lib.IgemmFwdParams()
+    P.engine, P.dtype = engine(), _lib.dtype_code(x)
+    P.x, P.w = ptr(x), ptr(w_packed)
+    P.N, P.H, P.W, P.Ci = N, H, W, Ci
+    P.GH, P.GW = grid_hw
+    P.is_, P.os = is_, os_
+    P.OH, P.OW, P.Co = OH, OW, Co
+    _fill_taps(P, taps, phases)
+    P.epi = epi
+    P.bias, P.aux0, P.aux1, P.aux2 = ptr(bias), ptr(aux0), ptr(aux1), ptr(aux2)
+    outs = {}
+    shape = (N, OH, OW, Co)
+    if want_f32:
+        outs["f32"] = torch.empty(shape, dtype=torch.float32, device=x.device)
+    if want_lp:
+        outs["lp"] = torch.empty(shape, dtype=x.dtype, device=x.device)
+    if want_sq:
+        outs["sq"] = torch.empty(shape, dtype=x.dtype, device=x.device)
+    if want_abs:
+        outs["abs"] = torch.empty(shape, dtype=x.dtype, device=x.device)
+    if want_nrm:
+        outs["nrm"] = torch.empty(shape, dtype=x.dtype, device=x.device)
+    P.out_f32, P.out_lp = ptr(outs.get("f32")), ptr(outs.get("lp"))
+    P.out_sq_lp, P.out_abs_lp, P.out_nrm_lp = ptr(outs.get("sq")), ptr(outs.get("abs")), ptr(outs.get("nrm"))
+    check(lib().hpc_igemm_fwd(byref(P), stream()))
+    return outs
+
+
+def igemm_wgrad(lo, hi, taps, phases, hs, scale=1.0):
+    """Returns packed gw (ntaps, R, Cc) fp32."""
+    N, GH, GW, R = lo.shape
+    _, HH, HW, Cc = hi.shape
+    P = _lib.IgemmWgradParams()
+    P.engine, P.dtype = engine(), _lib.dtype_code(lo)
+    P.lo, P.hi = ptr(lo), ptr(hi)
+    P.N, P.GH, P.GW, P.R = N, GH, GW, R
+    P.HH, P.HW, P.Cc, P.hs = HH, HW, Cc, hs
+    _fill_taps(P, taps, phases)
+    P.scale = scale
+    gw = torch.empty((len(taps), R, Cc), dtype=torch.float32, device=lo.device)
+    P.gw_f32 = ptr(gw)
+    wsb = lib().hpc_igemm_wgrad_workspace_bytes(byref(P))
+    ws = torch.empty(max(wsb, 1), dtype=torch.uint8, device=lo.device) if wsb else None
+    P.workspace, P.workspace_bytes = ptr(ws), wsb
+    check(lib().hpc_igemm_wgrad(byref(P), stream()))
+    return gw
+
+
+def colsum(x2d_like, scale=1.0):
+    """sum over all leading dims -> (C,) fp32."""
+    C = x2d_like.shape[-1]
+    P = x2d_like.numel() // C
+    out = torch.empty((C,), dtype=torch.float32, device=x2d_like.device)
+    nb = lib().hpc_colsum_scratch_bytes(P, C)
+    sc = torch.empty(nb, dtype=torch.uint8, device=x2d_like.device)
+    check(lib().hpc_colsum(ptr(x2d_like), _lib.dtype_code(x2d_like), P, C, scale, ptr(out), ptr(sc), nb, stream()))
+    return out
+
+
+# ----------------------------------------------------------------------------------------
+# conv / deconv layers (forward, and backward = dgrad + wgrad + bias grad)
+# ----------------------------------------------------------------------------------------
+class ConvSpec:
+    """Geometry of one nn.Conv2d / nn.ConvTranspose2d of the reference (analysis.py:55,
+    synthesis.py:55-57, prior_analysis.py:54-56, prior_synthesis.py:54-56)."""
+
+    def __init__(self, transposed, cin, cout, k, s):
+        self.transposed, self.cin, self.cout, self.k, self.s = transposed, cin, cout, k, s
+        self.p = k // 2
+        self.K = k * k
+        self.conv_taps = conv_type_taps(k, s, self.p)
+        self.deconv_taps = deconv_type_taps(k, s, self.p)
+
+    def out_hw(self, H, W):
+        k, s, p = self.k, self.s, self.p
+        if self.transposed:
+            return (H - 1) * s - 2 * p + k + (s - 1), (W - 1) * s - 2 * p + k + (s - 1)
+        return (H + 2 * p - k) // s + 1, (W + 2 * p - k) // s + 1
+
+    # ---- forward -------------------------------------------------------------------
+    def forward(self, x, weight, bias, epi=EPI_LINEAR, **wants):
+        N, H, W, Ci = x.shape
+        assert Ci == self.cin, (Ci, self.cin)
+        OH, OW = self.out_hw(H, W)
+        K, Ci_, Co = self.K, self.cin, self.cout
+        if self.transposed:   # weight (Ci,Co,k,k); rows=Co cols=Ci
+            taps, phases = self.deconv_taps
+            wp = pack_weight(weight, taps, Co, Ci_, K, Co * K, x.dtype)
+            return igemm_fwd(x, wp, taps, phases, (H, W), 1, self.s, (OH, OW), Co, epi, bias, **wants)
+        taps, phases = self.conv_taps  # weight (Co,Ci,k,k)
+        wp = pack_weight(weight, taps, Co, Ci_, Ci_ * K, K, x.dtype)
+        return igemm_fwd(x, wp, taps, phases, (OH, OW), self.s, 1, (OH, OW), Co, epi, bias, **wants)
+
+    # ---- backward ------------------------------------------------------------------
+    def dgrad(self, g, weight, in_hw, epi=EPI_LINEAR, **kw):
+        """g: NHWC lp gradient wrt this layer's output -> gradient wrt its input."""
+        N, GH_, GW_, _ = g.shape
+        H, W = in_hw
+        K, Ci, Co = self.K, self.cin, self.cout
+        if self.transposed:   # conv-type over the input grid; rows=Ci cols=Co from W[ci][co][k]
+            taps, phases = self.conv_taps
+            wp = pack_weight(weight, taps, Ci, Co, Co * K, K, g.dtype)
+            return igemm_fwd(g, wp, taps, phases, (H, W), self.s, 1, (H, W), Ci, epi, None, **kw)
+        taps, phases = self.deconv_taps  # rows=Ci cols=Co from W[co][ci][k]
+        wp = pack_weight(weight, taps, Ci, Co, K, Ci * K, g.dtype)
+        return igemm_fwd(g, wp, taps, phases, (GH_, GW_), 1, self.s, (H, W), Ci, epi, None, **kw)
+
+    def wgrad(self, x, g, weight_shape_like):
+        """x: layer input (NHWC lp), g: gradient wrt layer output (NHWC lp) -> grad in the
+        reference weight layout (fp32)."""
+        K, Ci, Co = self.K, self.cin, self.cout
+        taps, phases = self.deconv_taps
+        gw_ref = torch.empty(weight_shape_like.shape, dtype=torch.float32, device=x.device)
+        if self.transposed:   # lo = x (rows=Ci), hi = g (cols=Co); W[ci][co][k]
+            gw = igemm_wgrad(x, g, taps, phases, self.s)
+            unpack_wgrad(gw, gw_ref, taps, Ci, Co, Co * K, K)
+        else:                 # lo = g (rows=Co), hi = x (cols=Ci); W[co][ci][k]
+            gw = igemm_wgrad(g, x, taps, phases, self.s)
+            unpack_wgrad(gw, gw_ref, taps, Co, Ci, Ci * K, K)
+        return gw_ref
+
+
+# ----------------------------------------------------------------------------------------
+# GDN (modelling/layers/gdn.py:65-88)
+# ----------------------------------------------------------------------------------------
+_ONE_TAP = ([(0, 0, 0)], [(1, 0, 0, 0)])
+PEDESTAL = float(2 ** -18) ** 2                      # gdn.py:50
+GAMMA_BOUND = float((0.0 + PEDESTAL ** 2) ** 0.5)    # gdn.py:53 (pedestal squared again: SURVEY 3.5.1)
+
+
+def beta_bound(beta_min=1e-6):
+    # computed like the reference: float32 tensor arithmetic (gdn.py:52-53)
+    ped = torch.tensor(PEDESTAL)
+    return float((float(beta_min) + ped.clone() ** 2) ** 0.5)
+
+
+def nonneg_fwd(param, bound, pedestal=PEDESTAL):
+    out = torch.empty_like(param)
+    check(lib().hpc_nonneg_fwd(ptr(param), ptr(out), param.numel(), bound, pedestal, stream()))
+    return out
+
+
+def nonneg_bwd(param, gout, bound, scale=1.0):
+    g = torch.empty_like(param)
+    check(lib().hpc_nonneg_bwd(ptr(param), ptr(gout), ptr(g), param.numel(), bound, scale, stream()))
+    return g
+
+
+def square(x, relu=False):
+    out = torch.empty_like(x)
+    ro = torch.empty_like(x) if relu else None
+    check(lib().hpc_square(ptr(x), ptr(out), _lib.dtype_code(x), x.numel(), int(relu), ptr(ro), stream()))
+    return out, ro
+
+
+def gdn_forward(x, xsq, gamma_eff, beta_eff, inverse=False):
+    """x, xsq: NHWC lp; gamma_eff (C,C,1,1) fp32, beta_eff (C,) fp32 -> (y, nrm) NHWC lp."""
+    N, H, W, C = x.shape
+    wp = pack_weight(gamma_eff, _ONE_TAP[0], C, C, C, 1, x.dtype, cache=False)
+    o = igemm_fwd(xsq, wp, _ONE_TAP[0], _ONE_TAP[1], (H, W), 1, 1, (H, W), C, EPI_IGDN if inverse else EPI_GDN,
+                  beta_eff, aux0=x, want_nrm=True)
+    return o["lp"], o["nrm"]
+
+
+def gdn_backward(g, x, xsq, nrm, gamma_eff, inverse=False, need_dx=True):
+    """SURVEY A.4.  Returns (dx lp, dgamma_eff (C,C,1,1) fp32, dbeta_eff (C,) fp32)."""
+    N, H, W, C = x.shape
+    t = torch.empty_like(x)
+    check(lib().hpc_gdn_bwd_t(ptr(g), ptr(x), ptr(nrm), ptr(t), _lib.dtype_code(x), x.numel(), int(inverse),
+                              stream()))
+    dx = None
+    if need_dx:
+        wp = pack_weight(gamma_eff, _ONE_TAP[0], C, C, 1, C, x.dtype, cache=False)  # rows=k, cols=i: gamma[i][k]
+        dx = igemm_fwd(t, wp, _ONE_TAP[0], _ONE_TAP[1], (H, W), 1, 1, (H, W), C,
+                       EPI_IGDN_BWD if inverse else EPI_GDN_BWD, None, aux0=g, aux1=x, aux2=nrm)["lp"]
+    sgn = 0.5 if inverse else -0.5
+    dgamma = igemm_wgrad(t, xsq, _ONE_TAP[0], _ONE_TAP[1], 1, sgn).view(C, C, 1, 1)
+    dbeta = colsum(t, sgn)
+    return dx, dgamma, dbeta
+
+
+# ----------------------------------------------------------------------------------------
+# thin-channel layers
+# ----------------------------------------------------------------------------------------
+def conv_c3_forward(x_nchw, weight, bias, want_sq=True, want_f32=False):
+    """Conv2d(3->C,5,2,2) on an NCHW fp32 image -> NHWC lp (+ squares)."""
+    N, Cs, H, W = x_nchw.shape
+    Cw = weight.shape[0]
+    dt = lp_dtype()
+    shape = (N, H // 2, W // 2, Cw)
+    out = torch.empty(shape, dtype=dt, device=x_nchw.device)
+    sq = torch.empty(shape, dtype=dt, device=x_nchw.device) if want_sq else None
+    of = torch.empty(shape, dtype=torch.float32, device=x_nchw.device) if want_f32 else None
+    check(lib().hpc_conv_c3_fwd(ptr(x_nchw), ptr(weight), Cs * 25, 25, ptr(bias), N, Cs, H, W, Cw, ptr(of), ptr(out),
+                                ptr(sq), _lib.dtype_code(dt), stream()))
+    return out, sq, of
+
+
+def wgrad_c3(wide_nhwc, thin_nchw, Cw, Cs):
+    """gw (Cw,Cs,5,5) = sum wide[n,i,j,cw]*thin[n,cs,2i-2+kh,2j-2+kw]."""
+    N, H, W, _ = wide_nhwc.shape
+    gw = torch.empty((Cw, Cs, 5, 5), dtype=torch.float32, device=wide_nhwc.device)
+    nb = lib().hpc_wgrad_c3_scratch_bytes(N, Cw, Cs, H, W)
+    sc = torch.empty(nb, dtype=torch.uint8, device=wide_nhwc.device)
+    check(lib().hpc_wgrad_c3(ptr(wide_nhwc), _lib.dtype_code(wide_nhwc), ptr(thin_nchw), N, Cw, Cs, H, W, ptr(gw),
+                             Cs * 25, 25, ptr(sc), nb, stream()))
+    return gw
+
+
+def deconv_c3_forward(x_nhwc, weight, bias):
+    """ConvTranspose2d(C->3,5,2,2,1): NHWC lp -> NCHW fp32 image."""
+    N, H, W, Cw = x_nhwc.shape
+    Cs = weight.shape[1]
+    out = torch.empty((N, Cs, 2 * H, 2 * W), dtype=torch.float32, device=x_nhwc.device)
+    check(lib().hpc_deconv_c3_fwd(ptr(x_nhwc), _lib.dtype_code(x_nhwc), ptr(weight), Cs * 25, 25, ptr(bias), N, Cw, H,
+                                  W, Cs, ptr(out), stream()))
+    return out
+
+
+def deconv_c3_backward(g_nchw, x_nhwc, weight, need_dx=True):
+    """g: (N,3,2H,2W) fp32.  dgrad = Conv2d(3->C) with the same weight layout; wgrad; bias grad."""
+    N, Cs, H2, W2 = g_nchw.shape
+    Cw = weight.shape[0]
+    dt = x_nhwc.dtype
+    dx = None
+    if need_dx:
+        dx = torch.empty((N, H2 // 2, W2 // 2, Cw), dtype=dt, device=g_nchw.device)
+        check(lib().hpc_conv_c3_fwd(ptr(g_nchw), ptr(weight), Cs * 25, 25, None, N, Cs, H2, W2, Cw, None, ptr(dx), None,
+                                    _lib.dtype_code(dt), stream()))
+    gw = wgrad_c3(x_nhwc, g_nchw, Cw, Cs)
+    gb = torch.empty((Cs,), dtype=torch.float32, device=g_nchw.device)
+    check(lib().hpc_nchw_channel_sum(ptr(g_nchw), N, Cs, H2 * W2, ptr(gb), stream()))
+    return dx, gw, gb
+
+
+# ----------------------------------------------------------------------------------------
+# entropy models
+# ----------------------------------------------------------------------------------------
+def _cdf_struct(tensors):
+    """tensors: dict with w0..w3, b0..b3, f0..f2 (reference layouts, fp32 contiguous)."""
+    s = _lib.CdfParams()
+    for i in range(4):
+        s.w[i] = ptr(tensors[f"w{i}"])
+        s.b[i] = ptr(tensors[f"b{i}"])
+    for i in range(3):
+        s.f[i] = ptr(tensors[f"f{i}"])
+    return s
+
+
+def _check_cdf_dims(t):
+    ok = (t["w0"].shape[2:] == (3, 1) and t["w1"].shape[2:] == (3, 3) and t["w2"].shape[2:] == (3, 3)
+          and t["w3"].shape[2:] == (1, 3))
+    if not ok:
+        raise NotImplementedError("the factorised-prior kernel is specialised for ENTROPY_MODEL.DIMS == [3,3,3] "
+                                  "(utils/config.py:66); got " + str([tuple(t[f'w{i}'].shape) for i in range(4)]))
+
+
+def next_seed():
+    """(seed, offset) for the in-kernel Philox stream, drawn from torch's CPU generator so that
+    torch.manual_seed() makes runs reproducible (no device sync)."""
+    v = torch.randint(0, 2 ** 62, (2,), dtype=torch.int64)
+    return int(v[0]), int(v[1])
+
+
+def factorized_forward(z, cdf, training, noise=None, bin_=1.0, want_probs=True, want_lp=False):
+    """z: NHWC fp32 (N,h,w,C).  Returns z_tilde f32, z_tilde lp|None, probs|None, bits (1,)."""
+    _check_cdf_dims(cdf)
+    C = z.shape[-1]
+    P = z.numel() // C
+    zt = torch.empty_like(z)
+    ztl = torch.empty(z.shape, dtype=lp_dtype(), device=z.device) if want_lp else None
+    probs = torch.empty_like(z) if want_probs else None
+    bits = torch.empty((1,), dtype=torch.float32, device=z.device)
+    seed, off = (0, 0) if (noise is not None or not training) else next_seed()
+    s = _cdf_struct(cdf)
+    check(lib().hpc_factorized_fwd(ptr(z), ptr(noise), byref(s), P, C, int(training), bin_, seed, off, ptr(zt),
+                                   ptr(ztl), _lib.dtype_code(lp_dtype()), ptr(probs), ptr(bits),
+                                   ptr(reduce_scratch(z.device)), stream()))
+    return zt, ztl, probs, bits
+
+
+def factorized_backward(zt, cdf, training, g_bits, g_scale, g_probs=None, g_zt=None, bin_=1.0):
+    """Returns (gz fp32, dict of parameter grads in the reference layouts)."""
+    C = zt.shape[-1]
+    P = zt.numel() // C
+    gz = torch.empty_like(zt)
+    grads = {k: torch.zeros_like(v) for k, v in cdf.items()}
+    s, gs = _cdf_struct(cdf), _cdf_struct(grads)
+    check(lib().hpc_factorized_bwd(ptr(zt), byref(s), P, C, int(training), bin_, ptr(g_bits), g_scale, ptr(g_probs),
+                                   ptr(g_zt), ptr(gz), byref(gs), stream()))
+    return gz, grads
+
+
+def conditional_forward(y, scale, dist, training, noise=None, bin_=1.0, mean=0.0, want_probs=True, want_lp=False):
+    n = y.numel()
+    yt = torch.empty_like(y)
+    ytl = torch.empty(y.shape, dtype=lp_dtype(), device=y.device) if want_lp else None
+    probs = torch.empty_like(y) if want_probs else None
+    bits = torch.empty((1,), dtype=torch.float32, device=y.device)
+    seed, off = (0, 0) if (noise is not None or not training) else next_seed()
+    check(lib().hpc_conditional_fwd(ptr(y), ptr(scale), ptr(noise), n, dist, int(training), bin_, mean, seed, off,
+                                    ptr(yt), ptr(ytl), _lib.dtype_code(lp_dtype()), ptr(probs), ptr(bits),
+                                    ptr(reduce_scratch(y.device)), stream()))
+    return yt, ytl, probs, bits
+
+
+def conditional_backward(yt, scale, dist, training, g_bits, g_scale, g_probs=None, g_yt=None, fuse_exp_clamp=False,
+                         want_gs_f32=True, want_gs_lp=False, bin_=1.0, mean=0.0):
+    n = yt.numel()
+    gy = torch.empty_like(yt)
+    gs = torch.empty_like(scale) if want_gs_f32 else None
+    gsl = torch.empty(scale.shape, dtype=lp_dtype(), device=yt.device) if want_gs_lp else None
+    check(lib().hpc_conditional_bwd(ptr(yt), ptr(scale), n, dist, int(training), bin_, mean, ptr(g_bits), g_scale,
+                                    ptr(g_probs), ptr(g_yt), _lib.dtype_code(g_yt) if g_yt is not None else F32,
+                                    int(fuse_exp_clamp), ptr(gy), ptr(gs), ptr(gsl), _lib.dtype_code(lp_dtype()),
+                                    stream()))
+    return gy, gs, gsl
+
+
+# ----------------------------------------------------------------------------------------
+# distortion
+# ----------------------------------------------------------------------------------------
+def clamp01_sse(x, raw, scale=1.0, do_clamp=True, want_xt=True):
+    """x, raw: (N,...) fp32 contiguous.  Returns (x_tilde|None, sse_per_image (N,))."""
+    N = x.shape[0]
+    per = x.numel() // N
+    xt = torch.empty_like(raw) if want_xt else None
+    sse = torch.empty((N,), dtype=torch.float32, device=x.device)
+    check(lib().hpc_clamp01_sse_fwd(ptr(x), ptr(raw), ptr(xt), N, per, scale, int(do_clamp), ptr(sse),
+                                    ptr(sse_scratch(x.device, N)), stream()))
+    return xt, sse
+
+
+def clamp01_backward(raw, x, g_xt, mse_coef, mse_coef_dev=None, do_clamp=True):
+    g = torch.empty_like(raw)
+    check(lib().hpc_clamp01_bwd(ptr(raw), ptr(x), ptr(g_xt), raw.numel(), mse_coef, ptr(mse_coef_dev), int(do_clamp),
+                                ptr(g), stream()))
+    return g
+
+
+def relu_mask(g, x):
+    out = torch.empty_like(g)
+    check(lib().hpc_relu_mask(ptr(g), ptr(x), ptr(out), _lib.dtype_code(g), g.numel(), stream()))
+    return out
+
+
+_filters = {}
+
+
+def gauss_filter_1d(size, sigma, device):
+    """1-D factor g of the reference window softmax2D(-(x^2+y^2)/2s^2) = g (x) g  (loss.py:113-121,
+    SURVEY A.5).  Tiny host computation, cached per device."""
+    key = (size, sigma, device)
+    if key not in _filters:
+        r = [i + 0.5 - size / 2 for i in range(size)]
+        e = [math.exp(-(v * v) / (2.0 * sigma * sigma)) for v in r]
+        s = sum(e)
+        _filters[key] = torch.tensor([v / s for v in e], dtype=torch.float32).to(device)
+    return _filters[key]
+
+
+class SsimPyramid:
+    """Forward state of an L-level (MS-)SSIM evaluation (K7)."""
+
+    def __init__(self, img1, img2, levels, fs, sigma, c1, c2, in_scale):
+        N, C, H, W = img1.shape
+        self.N, self.C, self.levels, self.fs, self.c1, self.c2, self.in_scale = N, C, levels, fs, c1, c2, in_scale
+        self.filt = gauss_filter_1d(fs, sigma, img1.device)
+        self.imgs = [(img1, img2, H, W, in_scale)]
+        self.sums = torch.empty((levels, 2, N), dtype=torch.float32, device=img1.device)
+        self.counts = []
+        a, b, h, w, sc = img1, img2, H, W, in_scale
+        for l in range(levels):
+            if h < fs or w < fs:
+                raise ValueError(f"(MS-)SSIM level {l}: image {h}x{w} smaller than the {fs}-tap window "
+                                 "(the reference's F.conv2d raises here too)")
+            check(lib().hpc_ssim_level_fwd(ptr(a), ptr(b), N, C, h, w, ptr(self.filt), fs, sc, c1, c2,
+                                           ptr(self.sums[l, 0]), ptr(self.sums[l, 1]), None, stream()))
+            self.counts.append(float(C * (h - fs + 1) * (w - fs + 1)))
+            if l < levels - 1:
+                oh, ow = (h + 1) // 2, (w + 1) // 2
+                a2 = torch.empty((N, C, oh, ow), dtype=torch.float32, device=img1.device)
+                b2 = torch.empty((N, C, oh, ow), dtype=torch.float32, device=img1.device)
+                # level 0 is stored unscaled; the pooled level carries the x255 scale from here on
+                check(lib().hpc_avgpool2_fwd(ptr(a), ptr(a2), N * C, h, w, sc, stream()))
+                check(lib().hpc_avgpool2_fwd(ptr(b), ptr(b2), N * C, h, w, sc, stream()))
+                a, b, h, w, sc = a2, b2, oh, ow, 1.0
+                self.imgs.append((a, b, h, w, sc))
+
+    def combine(self, kind, flags, eps, weights):
+        L, N = self.levels, self.N
+        n_out = N if kind in (_lib.MSSSIM_METRIC, _lib.SSIM_METRIC) or (kind == _lib.SSIM_LOSS and flags & 1) else 1
+        out = torch.empty((n_out,), dtype=torch.float32, device=self.sums.device)
+        cnt = (c_double * L)(*self.counts)
+        wts = (c_float * L)(*[float(w) for w in weights])
+        check(lib().hpc_msssim_combine_fwd(ptr(self.sums), cnt, L, N, wts, kind, flags, eps, ptr(out), stream()))
+        return out
+
+    def backward(self, kind, flags, eps, weights, g_out, g_scale=1.0):
+        """gradient wrt img2 (level-0, unscaled units); upstream = g_out (device) * g_scale."""
+        L, N, C = self.levels, self.N, self.C
+        g_sums = torch.empty_like(self.sums)
+        cnt = (c_double * L)(*self.counts)
+        wts = (c_float * L)(*[float(w) for w in weights])
+        check(lib().hpc_msssim_combine_bwd(ptr(self.sums), cnt, L, N, wts, kind, flags, eps, ptr(g_out), g_scale, ptr(g_sums),
+                                           stream()))
+        g_next = None  # gradient wrt the images of level l+1
+        for l in range(L - 1, -1, -1):
+            a, b, h, w, sc = self.imgs[l]
+            oh, ow = h - self.fs + 1, w - self.fs + 1
+            g = torch.empty((N, C, h, w), dtype=torch.float32, device=a.device)
+            acc = 0
+            if g_next is not None:
+                # pooled level = sc_l * avgpool(level l)  -> scatter back
+                check(lib().hpc_avgpool2_bwd(ptr(g_next), ptr(g), N * C, h, w, sc, 0, stream()))
+                acc = 1
+            maps = torch.empty((3, N * C, oh, ow), dtype=torch.float32, device=a.device)
+            check(lib().hpc_ssim_level_bwd(ptr(a), ptr(b), N, C, h, w, ptr(self.filt), self.fs, sc, self.c1, self.c2,
+                                           ptr(g_sums[l, 0]), ptr(g_sums[l, 1]), ptr(maps), ptr(g), acc, stream()))
+            g_next = g
+        return g_next
+
+
+def psnr_from_sse(sse, per_image, max_val):
+    out = torch.empty_like(sse)
+    check(lib().hpc_psnr_from_sse(ptr(sse), sse.numel(), per_image, max_val, ptr(out), stream()))
+    return out
+
+
+def rd_combine(z_bits, y_bits, terms, lmbda, inv_num_pixels):
+    """terms: list of (tensor, scale).  Returns (8,) fp32: z_entropy, y_entropy, bpp, total, d0..d3."""
+    out = torch.empty((8,), dtype=torch.float32, device=z_bits.device)
+    T = _lib.DistTerms()
+    T.n_terms = len(terms)
+    for i, (t, sc) in enumerate(terms):
+        T.dist[i], T.n[i], T.scale[i] = ptr(t), t.numel(), sc
+    check(lib().hpc_rd_combine(ptr(z_bits), ptr(y_bits), byref(T), lmbda, inv_num_pixels, ptr(out), stream()))
+    return out
+
+
+def exp_clamp_backward(sigma, g_sigma):
+    out = torch.empty(sigma.shape, dtype=lp_dtype(), device=sigma.device)
+    check(lib().hpc_exp_clamp_bwd(ptr(sigma), ptr(g_sigma), ptr(out), _lib.dtype_code(out), sigma.numel(), stream()))
+    return out

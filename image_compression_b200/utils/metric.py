@@ -1,0 +1,53 @@
+"""Evaluation metrics on the GPU kernels K6/K7, with the reference's call surface
+(utils/metric.py:26-138): `psnr(img1,img2,max_val)`, `SSIM(...)(a,b)`, `MS_SSIM(...)(a,b)`.
+Inputs are (N,C,H,W) CUDA tensors already scaled to [0,max_val] (engine/monitor.py:122-123)."""
+import torch
+
+from .. import _lib
+from .. import hotpath as hp
+
+MS_SSIM_DEFAULT_WEIGHTS = [0.0448, 0.2856, 0.3001, 0.2363, 0.1333]  # utils/metric.py:103
+
+
+def psnr(img1, img2, max_val=255.):
+    """per-image 10*(2*log10(max_val) - ln(mse)/ln10)   (utils/metric.py:26-36)"""
+    _lib.require_cuda(img1, img2)
+    a, b = hp.contiguous_f32(img1), hp.contiguous_f32(img2)
+    N = a.shape[0]
+    _, sse = hp.clamp01_sse(a.reshape(N, -1), b.reshape(N, -1), 1.0, do_clamp=False, want_xt=False)
+    return hp.psnr_from_sse(sse, a.numel() // N, max_val)
+
+
+class SSIM:
+    """utils/metric.py:39-97.  `device` is accepted for signature parity; the filter lives on the
+    device of the inputs (the reference's default builds it on "cuda" at import, monitor.py:50)."""
+
+    def __init__(self, max_val=255., filter_size=11, filter_sigma=1.5, k1=0.01, k2=0.03, device="cuda",
+                 in_dB=False, non_negative=False):
+        self.filter_size, self.filter_sigma = filter_size, filter_sigma
+        self.c1, self.c2 = (k1 * max_val) ** 2, (k2 * max_val) ** 2
+        self.non_negative, self.in_dB = non_negative, in_dB
+
+    def _pyramid(self, img1, img2, levels):
+        _lib.require_cuda(img1, img2)
+        a, b = hp.contiguous_f32(img1), hp.contiguous_f32(img2)
+        return hp.SsimPyramid(a, b, levels, self.filter_size, self.filter_sigma, self.c1, self.c2, 1.0)
+
+    def __call__(self, img1, img2):
+        with torch.no_grad():
+            flags = (1 if self.in_dB else 0) | (2 if self.non_negative else 0)
+            return self._pyramid(img1, img2, 1).combine(_lib.SSIM_METRIC, flags, 0.0, (1.0,))
+
+
+class MS_SSIM(SSIM):
+    """utils/metric.py:100-138 (clamp_min 0 on every level, product of powers, optional dB)."""
+
+    def __init__(self, max_val=255., filter_size=11, filter_sigma=1.5, k1=0.01, k2=0.03, device="cuda",
+                 in_dB=True, weights=MS_SSIM_DEFAULT_WEIGHTS):
+        super().__init__(max_val, filter_size, filter_sigma, k1, k2, device, non_negative=True, in_dB=False)
+        self.in_dB, self.weights = in_dB, list(weights)
+
+    def __call__(self, img1, img2):
+        with torch.no_grad():
+            pyr = self._pyramid(img1, img2, len(self.weights))
+            return pyr.combine(_lib.MSSSIM_METRIC, 1 if self.in_dB else 0, 0.0, self.weights)

@@ -1,0 +1,361 @@
+/*
+ * hpcodec.h -- C ABI of libhpcodec_sm100a.so: the B200-native (sm_100a) kernels behind the
+ * scale-hyperprior codec hot path of hieu1999210/image_compression.
+ *
+ * The reference has no FFI of its own: every arithmetic op on the path is a stock torch call
+ * inside its nn.Modules.  This header is the native seam one level below
+ * that module surface; each entry cites the reference code (path:line under the reference
+ * repository root) whose arithmetic it replaces.  The Python modules in
+ * image_compression_b200/modelling bind these through ctypes.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; all pointers are DEVICE pointers unless stated otherwise
+ *  - every call enqueues work on `stream` (a cudaStream_t) and returns without synchronising
+ *  - return value: HPC_OK or an HPC_ERR_* code; text via hpc_last_error() (thread local)
+ *  - activations are NHWC ("channels last"): element (n,h,w,c) at ((n*H+h)*W+w)*C+c
+ *  - `lp` ("low precision") tensors have element type `dtype`: HPC_F32 or HPC_BF16; tensors
+ *    named *_f32 are always float
+ *  - the library never allocates device memory; scratch is passed in by the caller
+ */
+#ifndef HPCODEC_H_
+#define HPCODEC_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HPC_VERSION 100
+
+#define HPC_OK 0
+#define HPC_ERR_BAD_SHAPE 1
+#define HPC_ERR_BAD_ALIGNMENT 2
+#define HPC_ERR_UNSUPPORTED 3
+#define HPC_ERR_CUDA 4
+
+#define HPC_F32 0
+#define HPC_BF16 1
+
+typedef void* hpc_stream_t; /* cudaStream_t */
+
+int hpc_version(void);
+const char* hpc_last_error(void);
+/* 1 when the current device is compute capability 10.x (tcgen05/TMEM/TMA kernels usable) */
+int hpc_device_is_sm100(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Bounds and the GDN non-negative reparameterisation
+ * ---------------------------------------------------------------------------------------- */
+
+/* LowerBound / UpperBound forward: y = max(x,bound) or min(x,bound).
+ * Replaces modelling/layers/bound.py:30-33 and :47-50. */
+int hpc_bound_fwd(const float* x, float* y, int64_t n, float bound, int is_upper, hpc_stream_t stream);
+/* backward: gx = g where (x>=bound or g<0) [lower] / (x<=bound or g>0) [upper], else 0.
+ * Replaces modelling/layers/bound.py:36-42 and :53-59. */
+int hpc_bound_bwd(const float* x, const float* gy, float* gx, int64_t n, float bound, int is_upper,
+                  hpc_stream_t stream);
+
+/* NonNegativeParam.forward: out = max(param,bound)^2 - pedestal.
+ * Replaces modelling/layers/gdn.py:59-62 (bound/pedestal as built at :51-53). */
+int hpc_nonneg_fwd(const float* param, float* out, int64_t n, float bound, float pedestal, hpc_stream_t stream);
+/* backward: gparam = m * 2*max(param,bound) * gout, m = (param>=bound) or (2*val*gout < 0).
+ * `scale` multiplies gout first (GDN kernels hand over -1/2-free sums; see hpc_igemm_wgrad). */
+int hpc_nonneg_bwd(const float* param, const float* gout, float* gparam, int64_t n, float bound, float scale,
+                   hpc_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Factorised prior (EntropyModel + CDFEstimator, DIMS=[3,3,3]) -- kernel K4
+ * ---------------------------------------------------------------------------------------- */
+
+/* The 11 parameter tensors of the per-channel cumulative MLP 1->3->3->3->1, in the reference's
+ * own memory layout (entropy_model.py:54-65): weight (1,C,out,in), bias (1,C,out,1),
+ * factor (1,C,out,1).  The same struct carries the gradient pointers in the backward call. */
+typedef struct {
+  float* w[4]; /* (C,3,1) (C,3,3) (C,3,3) (C,1,3) */
+  float* b[4]; /* (C,3) (C,3) (C,3) (C,1) */
+  float* f[3]; /* (C,3) x3 */
+} hpc_cdf_params;
+
+/* EntropyModel.forward: quantise, pmf = s*(sigmoid(s*u)-sigmoid(s*l)), bits.
+ * Replaces modelling/blocks/entropy_model.py:204-214 (_quantize :216-236, _prob_mass :259-269,
+ * CDFLayer.forward :67-78, CDFEstimator.forward :101-114, _ce_loss :185).
+ *   z            (P,C) NHWC rows, float
+ *   mode         0 = "quantize" (round half to even), 1 = "noise"
+ *   noise        optional (P,C) U[0,1) tensor; when NULL in mode 1 Philox(seed,offset) is used
+ *   z_tilde_f32  (P,C) out;  z_tilde_lp optional copy in `lp_dtype` (feeds h_s)
+ *   probs        optional (P,C) out (NHWC; the reference's (N,W,C,H) result is a view of it)
+ *   bits_out     1 float: sum of clamp(-log2(p+1e-10),0,50); deterministic reduction
+ *   scratch      >= hpc_reduce_scratch_bytes() bytes, zero-initialised once by the caller */
+int hpc_factorized_fwd(const float* z, const float* noise, const hpc_cdf_params* params, int64_t P, int C,
+                       int mode, float bin, uint64_t seed, uint64_t offset, float* z_tilde_f32,
+                       void* z_tilde_lp, int lp_dtype, float* probs, float* bits_out, void* scratch,
+                       hpc_stream_t stream);
+/* backward of the above (autograd in the reference).  g_bits: device scalar dL/dbits (may be
+ * NULL), g_probs: optional (P,C) dL/dprobs, g_zt: optional (P,C) dL/dz_tilde (float).
+ * gz (P,C) out; gparams accumulated with atomics into caller-zeroed buffers.  g_scale
+ * multiplies *g_bits (e.g. 1/num_pixels). */
+int hpc_factorized_bwd(const float* z_tilde, const hpc_cdf_params* params, int64_t P, int C, int mode,
+                       float bin, const float* g_bits, float g_scale, const float* g_probs, const float* g_zt,
+                       float* gz, const hpc_cdf_params* gparams, hpc_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Conditional (scale-only) Laplace / Gauss likelihood -- kernel K5
+ * ---------------------------------------------------------------------------------------- */
+#define HPC_DIST_LAPLACE 0
+#define HPC_DIST_GAUSS 1
+
+/* SymmetricConditionalModel.forward: p = cdf((bin/2-|y~-mean|)/s) - cdf((-bin/2-|y~-mean|)/s).
+ * Replaces modelling/blocks/entropy_model.py:280-295, :319-339, :341-352, :362 / :375 and the
+ * bit count of :185 (called from modelling/meta_arch/bmshl2018.py:76-77).
+ * n elements, any layout (pure pointwise).  Outputs as in hpc_factorized_fwd. */
+int hpc_conditional_fwd(const float* y, const float* scale, const float* noise, int64_t n, int dist, int mode,
+                        float bin, float mean, uint64_t seed, uint64_t offset, float* y_tilde_f32,
+                        void* y_tilde_lp, int lp_dtype, float* probs, float* bits_out, void* scratch,
+                        hpc_stream_t stream);
+/* backward: gy = gp*dp/dy~ + g_yt ; gscale = gp*dp/dscale, gp = *g_bits*g_scale*dbits/dp + g_probs.
+ * g_yt optional, dtype g_yt_dtype (the dgrad of g_s arrives in bf16).  If fuse_exp_clamp != 0
+ * the scale gradient is chained through sigma = clamp(exp(pre),1e-10,1e10)
+ * (modelling/blocks/prior_synthesis.py:72): gscale_out = gscale*sigma*[1e-10<=sigma<=1e10].
+ * gscale_f32 and/or gscale_lp may be NULL. */
+int hpc_conditional_bwd(const float* y_tilde, const float* scale, int64_t n, int dist, int mode, float bin,
+                        float mean, const float* g_bits, float g_scale, const float* g_probs, const void* g_yt,
+                        int g_yt_dtype, int fuse_exp_clamp, float* gy, float* gscale_f32, void* gscale_lp,
+                        int lp_dtype, hpc_stream_t stream);
+
+/* backward of sigma = clamp(exp(pre),1e-10,1e10) (modelling/blocks/prior_synthesis.py:72) for the
+ * stand-alone HyperpriorSynthesisTransform: g_pre = g_sigma*sigma*[1e-10<=sigma<=1e10] (lp out). */
+int hpc_exp_clamp_bwd(const float* sigma, const float* g_sigma, void* g_pre_lp, int lp_dtype, int64_t n,
+                      hpc_stream_t stream);
+
+/* BaseEntropyModel._ce_loss standalone: bits = sum clamp(-log(p+1e-10)/ln2,0,50).
+ * Replaces modelling/blocks/entropy_model.py:171-185. */
+int hpc_bits_fwd(const float* probs, int64_t n, float* bits_out, void* scratch, hpc_stream_t stream);
+int hpc_bits_bwd(const float* probs, const float* g_bits, int64_t n, float* g_probs, hpc_stream_t stream);
+
+size_t hpc_reduce_scratch_bytes(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Clamp + MSE / PSNR -- kernel K6.  Images are NCHW float (the user-facing layout).
+ * ---------------------------------------------------------------------------------------- */
+
+/* x~ = LowerBound(UpperBound(raw,1),0) and per-image sum of squared error against x.
+ * Replaces modelling/meta_arch/bmshl2018.py:80-81 + modelling/loss.py:25 (nn.MSELoss) and, with
+ * scale=255, utils/metric.py:26-36 (psnr).  raw/x/xt: (N, per_image) floats; xt may alias raw or
+ * be NULL; sse_per_image (N) out = sum((scale*(x - x~))^2).  grid-deterministic. */
+int hpc_clamp01_sse_fwd(const float* x, const float* raw, float* xt, int N, int64_t per_image, float scale,
+                        int do_clamp, float* sse_per_image, void* scratch, hpc_stream_t stream);
+/* g_raw = bounds_bwd( g_xt + mse_coef * 2*(x~ - x) ), masks per bound.py:36-42,:53-59.
+ * g_xt may be NULL (no extra upstream gradient), x may be NULL (no MSE term);
+ * mse_coef_dev: optional device scalar multiplied into mse_coef (upstream dL/dloss).
+ * do_clamp=0 skips the bounds (plain nn.MSELoss backward wrt its target, modelling/loss.py:25). */
+int hpc_clamp01_bwd(const float* raw, const float* x, const float* g_xt, int64_t n, float mse_coef,
+                    const float* mse_coef_dev, int do_clamp, float* g_raw, hpc_stream_t stream);
+/* psnr_n = 10*(2*log10(max_val) - ln(sse_n/per_image)/ln10); utils/metric.py:26-36 */
+int hpc_psnr_from_sse(const float* sse_per_image, int N, int64_t per_image, float max_val, float* psnr,
+                      hpc_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (MS-)SSIM -- kernel K7.  Planes are NCHW float.
+ * ---------------------------------------------------------------------------------------- */
+
+/* One SSIM level: valid 11x11 (size `fs`<=15) Gaussian moments, cs and ssim maps, per-image sums.
+ * Replaces modelling/loss.py:75-91,103-121 and utils/metric.py:56-72,79-97.
+ *   img1,img2 (N,C,H,W); in_scale multiplies both on load (the x255 of loss.py:67-68)
+ *   filt1d    fs floats on the device (the 2-D softmax window is exactly g (x) g)
+ *   ssim_sum, cs_sum (N) out: sums over (C,H',W'), H'=H-fs+1 (caller divides)       */
+int hpc_ssim_level_fwd(const float* img1, const float* img2, int N, int C, int H, int W, const float* filt1d,
+                       int fs, float in_scale, float c1, float c2, float* ssim_sum, float* cs_sum,
+                       void* scratch, hpc_stream_t stream);
+/* backward wrt img2: g_ssim, g_cs (N) are dL/d(sum) per image (already divided by the map size).
+ * maps: scratch of 3*N*C*H'*W' floats.  g_img2 (N,C,H,W): if accumulate!=0 adds to the
+ * existing content (the pyramid's upsampled gradient), else overwrites.  The result is
+ * multiplied by in_scale (chain rule of the load scaling). */
+int hpc_ssim_level_bwd(const float* img1, const float* img2, int N, int C, int H, int W, const float* filt1d,
+                       int fs, float in_scale, float c1, float c2, const float* g_ssim, const float* g_cs,
+                       float* maps, float* g_img2, int accumulate, hpc_stream_t stream);
+/* 2x2 average pool with reflect padding of odd edges; out = scale*avg.
+ * Replaces modelling/loss.py:176-188 and utils/metric.py:126-138. */
+int hpc_avgpool2_fwd(const float* in, float* out, int NC, int H, int W, float scale, hpc_stream_t stream);
+/* gin (+)= scale * pooled-gradient scatter (accumulate flag as above). */
+int hpc_avgpool2_bwd(const float* gout, float* gin, int NC, int H, int W, float scale, int accumulate,
+                     hpc_stream_t stream);
+
+#define HPC_MSSSIM_LOSS_LOG 0   /* MS_SSIMLoss._log_forward  modelling/loss.py:141-156 */
+#define HPC_MSSSIM_LOSS_PLAIN 1 /* MS_SSIMLoss._forward      modelling/loss.py:158-174 */
+#define HPC_MSSSIM_METRIC 2     /* utils/metric.py:110-124 (clamp_min 0, optional dB)   */
+#define HPC_SSIM_LOSS 3         /* SSIMLoss.forward          modelling/loss.py:65-73     */
+#define HPC_SSIM_METRIC 4       /* SSIM.__call__             utils/metric.py:52-54       */
+/* Per-image level means -> loss / metric.  sums: (L,2,N) floats = [level][0:ssim,1:cs][n] sums,
+ * counts (L) map sizes C*H'*W' (host array).  out: 1 float for losses, N floats for metrics
+ * (SSIM_LOSS with log_scale returns N values: loss.py:72 returns -ssim unreduced).
+ * flags: bit0 = log_scale (SSIM_LOSS), bit0 = in_dB (metrics), bit1 = non_negative (SSIM metric) */
+int hpc_msssim_combine_fwd(const float* sums, const double* counts_host, int L, int N, const float* weights_host,
+                           int kind, int flags, float eps, float* out, hpc_stream_t stream);
+/* backward of the loss kinds: g_out device scalar (or N values for SSIM_LOSS log), multiplied by
+ * the host scalar g_scale (lambda); g_sums (L,2,N) out = dL/d(sum) per level/image. */
+int hpc_msssim_combine_bwd(const float* sums, const double* counts_host, int L, int N, const float* weights_host,
+                           int kind, int flags, float eps, const float* g_out, float g_scale, float* g_sums,
+                           hpc_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Convolution family as implicit GEMM -- kernels K1/K2/K3/K8
+ * ---------------------------------------------------------------------------------------- */
+#define HPC_MAX_TAPS 25
+#define HPC_MAX_PHASES 4
+
+#define HPC_ENGINE_SIMT 0 /* CUDA-core fp32-accumulate reference engine (any channel count) */
+#define HPC_ENGINE_UMMA 1 /* tcgen05/TMEM/TMA engine (bf16 operands, Ci%64==0, Co%16==0, Co<=256) */
+
+#define HPC_EPI_LINEAR 0     /* out = acc + bias */
+#define HPC_EPI_RELU 1       /* out = max(acc+bias,0)                         prior_analysis.py:66, prior_synthesis.py:64 */
+#define HPC_EPI_EXP_CLAMP 2  /* out = clamp(exp(acc+bias),1e-10,1e10)         prior_synthesis.py:72 */
+#define HPC_EPI_GDN 3        /* n=acc+bias; out = aux0*rsqrt(n); nrm=rsqrt(n) gdn.py:84-86 (aux0 = x, A = x^2) */
+#define HPC_EPI_IGDN 4       /* out = aux0*sqrt(n); nrm=rsqrt(n)              gdn.py:86 inverse */
+#define HPC_EPI_GDN_BWD 5    /* out = aux0*aux2 - aux1*acc   (g*nrm - x*u)    SURVEY A.4 */
+#define HPC_EPI_IGDN_BWD 6   /* out = aux0/aux2 + aux1*acc                    SURVEY A.4 */
+#define HPC_EPI_RELU_MASK 7  /* out = acc * [aux0 > 0]                        autograd of ReLU */
+#define HPC_EPI_SIGN_ADD 8   /* out = acc*sign(aux0_f32) + aux1_f32           autograd of abs, bmshl2018.py:72 */
+
+/* One dense stride-1 sub-problem of the implicit GEMM (a stride-2 transposed convolution is four
+ * of them, one per output-pixel parity). */
+typedef struct {
+  int ntaps;     /* taps of this phase */
+  int tap_begin; /* first tap: index into dh/dw and into the packed weights [tap][Co][Ci] */
+  int oh_off, ow_off; /* output pixel of grid point (i,j) = (i*os+oh_off, j*os+ow_off) */
+} hpc_igemm_phase;
+
+/* out[n, i*os+oh_off, j*os+ow_off, co] = epi( sum_{t in phase} sum_ci
+ *        x[n, i*is+dh[t], j*is+dw[t], ci] * w[t][co][ci] )          (x = 0 outside the image)
+ * Conv2d(k,s=is,p):   one phase, taps (kh-p, kw-p), os=1, grid = output size
+ * ConvTranspose2d(5,2,2,1): four phases over the INPUT grid, is=1, os=2
+ * Replaces the nn.Conv2d / nn.ConvTranspose2d calls at modelling/blocks/analysis.py:55,
+ * synthesis.py:55-57, prior_analysis.py:54-56, prior_synthesis.py:54-56, the 1x1 gamma
+ * contraction of modelling/layers/gdn.py:84, and (with transposed packing) their autograd dgrads. */
+typedef struct {
+  int engine;   /* HPC_ENGINE_* */
+  int dtype;    /* element type of x, w and the lp outputs / lp aux inputs */
+  const void* x; /* (N,H,W,Ci) */
+  const void* w; /* packed (ntaps_total, Co, Ci) */
+  int N, H, W, Ci;
+  int GH, GW;   /* iteration grid per image */
+  int is, os;
+  int OH, OW, Co;
+  int nphases;
+  hpc_igemm_phase phase[HPC_MAX_PHASES];
+  int dh[HPC_MAX_TAPS], dw[HPC_MAX_TAPS];
+  /* epilogue */
+  int epi;
+  const float* bias;  /* (Co) or NULL */
+  const void* aux0;   /* see HPC_EPI_*; lp (N,OH,OW,Co) unless stated float */
+  const void* aux1;
+  const void* aux2;
+  float* out_f32;     /* optional (N,OH,OW,Co) */
+  void* out_lp;       /* optional */
+  void* out_sq_lp;    /* optional out^2 (the A operand of the following GDN) */
+  void* out_abs_lp;   /* optional |out| (input of h_a, bmshl2018.py:72) */
+  void* out_nrm_lp;   /* GDN/IGDN: rsqrt(n), saved for backward */
+} hpc_igemm_fwd_params;
+
+int hpc_igemm_fwd(const hpc_igemm_fwd_params* p, hpc_stream_t stream);
+
+/* Weight gradient as implicit GEMM over pixels:
+ * gw[t][r][c] = scale * sum_{n,i,j} lo[n, i+dh[t], j+dw[t], r] * hi[n, i*hs+oh_off, j*hs+ow_off, c]
+ * for every tap t of every phase ("lo" = tensor on the iteration grid, "hi" = strided tensor).
+ *   Conv2d(k,s=2) wgrad:            lo = dy (grid GH x GW), hi = x, phases = input-pixel parities
+ *   ConvTranspose2d(5,2) wgrad:     lo = x, hi = dy
+ *   stride-1 conv / GDN gamma grad: one phase, hs = 1
+ * Output gw_f32 (ntaps_total, R, Cc) float in the packed tap order (hpc_unpack_wgrad maps it to
+ * the reference layout).  Replaces autograd's convolution_backward weight path. */
+typedef struct {
+  int engine, dtype;
+  const void* lo; /* (N,GH,GW,R) */
+  const void* hi; /* (N,HH,HW,Cc) */
+  int N, GH, GW, R;
+  int HH, HW, Cc;
+  int hs;
+  int nphases;
+  hpc_igemm_phase phase[HPC_MAX_PHASES];
+  int dh[HPC_MAX_TAPS], dw[HPC_MAX_TAPS];
+  float scale;
+  float* gw_f32;
+  void* workspace;        /* UMMA engine split-K partials; >= hpc_igemm_wgrad_workspace_bytes() */
+  size_t workspace_bytes;
+} hpc_igemm_wgrad_params;
+
+int hpc_igemm_wgrad(const hpc_igemm_wgrad_params* p, hpc_stream_t stream);
+size_t hpc_igemm_wgrad_workspace_bytes(const hpc_igemm_wgrad_params* p);
+
+/* Weight (un)packing between the reference layouts and the packed (tap, row, col) layout.
+ * src element (r, c, k) of a weight with K taps (k = kh*KW+kw) sits at r*stride_r + c*stride_c + k:
+ *   Conv2d weight (Co,Ci,kh,kw), rows=Co, cols=Ci:          stride_r = Ci*K, stride_c = K
+ *   ConvTranspose2d weight (Ci,Co,kh,kw), rows=Co, cols=Ci: stride_r = K,    stride_c = Co*K
+ * dst[t][r][c] = src(r, c, tap_src[t]) converted to `dtype`.  tap_src: host array (ntaps). */
+int hpc_pack_weight(const float* src, void* dst, int dtype, int ntaps, int rows, int cols, int64_t stride_r,
+                    int64_t stride_c, const int* tap_src_host, hpc_stream_t stream);
+/* inverse for gradients: dst(r,c,tap_src[t]) (+)= src[t][r][c]; float both sides. */
+int hpc_unpack_wgrad(const float* src, float* dst, int ntaps, int rows, int cols, int64_t stride_r,
+                     int64_t stride_c, const int* tap_src_host, int accumulate, hpc_stream_t stream);
+
+/* out[c] = scale * sum_p x[p][c]  (bias gradients; GDN beta gradient).  x (P,C) lp. */
+int hpc_colsum(const void* x, int dtype, int64_t P, int C, float scale, float* out, void* scratch,
+               size_t scratch_bytes, hpc_stream_t stream);
+size_t hpc_colsum_scratch_bytes(int64_t P, int C);
+
+/* GDN helpers (elementwise, NHWC lp tensors of n elements).
+ * hpc_square: out = x^2 (optionally relu first: gdn.py:80-81); used when the producer did not
+ * emit x^2 itself.  hpc_gdn_bwd_t: t = g*x*nrm^3 (GDN) or g*x*nrm (IGDN), SURVEY A.4. */
+int hpc_square(const void* x, void* out, int dtype, int64_t n, int relu, void* relu_out, hpc_stream_t stream);
+int hpc_gdn_bwd_t(const void* g, const void* x, const void* nrm, void* t, int dtype, int64_t n, int inverse,
+                  hpc_stream_t stream);
+
+/* out = g * [x > 0]  (autograd of F.relu in the stand-alone relu-GDN, gdn.py:80-81) */
+int hpc_relu_mask(const void* g, const void* x, void* out, int dtype, int64_t n, hpc_stream_t stream);
+
+/* Layout / dtype conversion: NCHW float <-> NHWC lp (module boundaries). */
+int hpc_nchw_to_nhwc(const float* src, void* dst, int dtype, int N, int C, int H, int W, hpc_stream_t stream);
+int hpc_nhwc_to_nchw(const void* src, int dtype, float* dst, int N, int C, int H, int W, hpc_stream_t stream);
+/* elementwise cast between float and lp (n elements) */
+int hpc_cast(const void* src, int src_dtype, void* dst, int dst_dtype, int64_t n, hpc_stream_t stream);
+
+/* Thin-channel layers (Cin=3 head of g_a, Cout=3 tail of g_s): K=75 is memory-bound.
+ * conv_c3_fwd:   Conv2d(Cs->Cw,5,s2,p2): x NCHW float (N,Cs,H,W), w float (Cw,Cs,5,5) with
+ *                strides (w_sr, w_sc) for (Cw,Cs) so the same kernel serves the dgrad of the tail
+ *                deconv (weight (Cw,Cs,5,5) read transposed).  out NHWC (N,H/2,W/2,Cw).
+ * deconv_c3_fwd: ConvTranspose2d(Cw->Cs,5,s2,p2,op1): x NHWC lp (N,H,W,Cw) -> out NCHW float
+ *                (N,Cs,2H,2W) (+bias).
+ * wgrad_c3:      gw(Cw,Cs,5,5)-strided float = sum_pixels wide[n,i,j,cw]*thin[n,cs,2i-2+kh,2j-2+kw]
+ *                (serves Conv2d(3->C) weight grads and ConvTranspose2d(C->3) weight grads). */
+int hpc_conv_c3_fwd(const float* x_nchw, const float* w, int64_t w_sr, int64_t w_sc, const float* bias, int N,
+                    int Cs, int H, int W, int Cw, float* out_f32, void* out_lp, void* out_sq_lp, int lp_dtype,
+                    hpc_stream_t stream);
+int hpc_deconv_c3_fwd(const void* x_nhwc, int lp_dtype, const float* w, int64_t w_sr, int64_t w_sc,
+                      const float* bias, int N, int Cw, int H, int W, int Cs, float* out_nchw,
+                      hpc_stream_t stream);
+int hpc_wgrad_c3(const void* wide_nhwc, int lp_dtype, const float* thin_nchw, int N, int Cw, int Cs, int H, int W,
+                 float* gw, int64_t w_sr, int64_t w_sc, void* scratch, size_t scratch_bytes,
+                 hpc_stream_t stream);
+size_t hpc_wgrad_c3_scratch_bytes(int N, int Cw, int Cs, int H, int W);
+/* per-channel sum of an NCHW float tensor (bias grad of the tail deconv) */
+int hpc_nchw_channel_sum(const float* x, int N, int C, int64_t HW, float* out, hpc_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Rate-distortion combine (bmshl2018.py:84-96): device scalars in, device scalars out, no sync
+ *   out[0]=z_entropy out[1]=y_entropy out[2]=bpp out[3]=total_loss out[4+i]=distortion term i
+ * term i = scale[i] * sum(dist[i][0..n[i]))   (scale = 1/(N*3*H*W) turns per-image SSEs into the
+ * MSE of modelling/loss.py:25); total = lambda * sum_i term_i + bpp. */
+#define HPC_MAX_DIST_TERMS 4
+typedef struct {
+  const float* dist[HPC_MAX_DIST_TERMS];
+  int n[HPC_MAX_DIST_TERMS];
+  float scale[HPC_MAX_DIST_TERMS];
+  int n_terms;
+} hpc_dist_terms;
+int hpc_rd_combine(const float* z_bits, const float* y_bits, const hpc_dist_terms* terms, float lambda,
+                   float inv_num_pixels, float* out8, hpc_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HPCODEC_H_ */
