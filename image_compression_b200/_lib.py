@@ -16,7 +16,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(_HERE, "libhpcodec_sm100a.so")
 SOURCES = ["hpc_api.cu", "entropy_kernels.cu", "loss_kernels.cu", "igemm_simt.cu", "thin_kernels.cu",
-           "igemm_umma.cu"]
+           "igemm_umma.cu", "misc_kernels.cu"]
 # no --use_fast_math: IEEE division / sqrt / expf are part of the parity contract
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC"]
@@ -124,6 +124,9 @@ _SIGNATURES = {
                                    c_void_p]),
     "hpc_factorized_bwd": (c_int, [c_void_p, POINTER(CdfParams), c_int64, c_int, c_int, c_float, c_void_p,
                                    c_float, c_void_p, c_void_p, c_void_p, POINTER(CdfParams), c_void_p]),
+    "hpc_cdf_logits_fwd": (c_int, [c_void_p, POINTER(CdfParams), c_int64, c_int, c_void_p, c_void_p]),
+    "hpc_cdf_logits_bwd": (c_int, [c_void_p, POINTER(CdfParams), c_int64, c_int, c_void_p, c_void_p,
+                                   POINTER(CdfParams), c_void_p]),
     "hpc_conditional_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_float, c_float,
                                     c_uint64, c_uint64, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
                                     c_void_p]),
@@ -138,6 +141,8 @@ _SIGNATURES = {
                                     c_void_p, c_void_p]),
     "hpc_clamp01_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_float, c_void_p, c_int, c_void_p,
                                 c_void_p]),
+    "hpc_abs_fwd": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
+    "hpc_abs_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
     "hpc_relu_mask": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_void_p]),
     "hpc_psnr_from_sse": (c_int, [c_void_p, c_int, c_int64, c_float, c_void_p, c_void_p]),
     "hpc_ssim_level_fwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int, c_float,

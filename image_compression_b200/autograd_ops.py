@@ -446,7 +446,7 @@ class Compressor2018Fn(torch.autograd.Function):
         m = meta
         x = _f32c(x)
         N, C, H, W = x.shape
-        save = torch.is_grad_enabled() and any(p.requires_grad for p in params)
+        save = any(ctx.needs_input_grad)  # forward() itself always runs under no_grad
         i = 0
         ga_convs, ga_gdns = _split_ga(params[i:i + m.n_ga], len(m.strides)); i += m.n_ga
         ha_convs = _split_h(params[i:i + m.n_ha], m.ha_bias); i += m.n_ha
@@ -518,3 +518,62 @@ class Compressor2018Fn(torch.autograd.Function):
         grads = (_join_ga(ga_cg, ga_gg) + _join_h(ha_cg, m.ha_bias) + _join_h(hs_cg, [True] * len(hs_cg)) +
                  _join_ga(gs_cg, gs_gg) + [cdf_grads[k] for k in CDF_KEYS])
         return (None, None, None, None, None, *grads)
+
+
+class CdfLogitsFn(torch.autograd.Function):
+    """CDFEstimator.forward stand-alone (entropy_model.py:101-114)."""
+
+    @staticmethod
+    def forward(ctx, x, *cdf_params):
+        _lib.require_cuda(x, *cdf_params)
+        cdf = {k: v.contiguous() for k, v in zip(CDF_KEYS, cdf_params)}
+        hp._check_cdf_dims(cdf)
+        idx = _channel_last_index(x.dim())
+        xl = _f32c(x.permute(*idx))
+        C = xl.shape[-1]
+        out = torch.empty_like(xl)
+        s = hp._cdf_struct(cdf)
+        check(lib().hpc_cdf_logits_fwd(ptr(xl), _lib.byref(s), xl.numel() // C, C, ptr(out), stream()))
+        ctx.save_for_backward(xl, *cdf.values())
+        ctx.idx = idx
+        return out.permute(*idx)   # the reference re-applies idx as its "inverse" (entropy_model.py:113)
+
+    @staticmethod
+    def backward(ctx, g):
+        xl, *vals = ctx.saved_tensors
+        cdf = dict(zip(CDF_KEYS, vals))
+        inv = [ctx.idx.index(i) for i in range(len(ctx.idx))]
+        gl = _f32c(g.permute(*inv))
+        C = xl.shape[-1]
+        gx = torch.empty_like(xl)
+        grads = {k: torch.zeros_like(v) for k, v in cdf.items()}
+        s, gs = hp._cdf_struct(cdf), hp._cdf_struct(grads)
+        check(lib().hpc_cdf_logits_bwd(ptr(xl), _lib.byref(s), xl.numel() // C, C, ptr(gl), ptr(gx), _lib.byref(gs),
+                                       stream()))
+        return (gx.permute(*inv), *[grads[k] for k in CDF_KEYS])
+
+
+class AbsFn(torch.autograd.Function):
+    """torch.abs(y) of bmshl2018.py:72 (composed path)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        _lib.require_cuda(x)
+        dense = x.dtype == torch.float32 and (x.is_contiguous() or (
+            x.dim() == 4 and x.is_contiguous(memory_format=torch.channels_last)))
+        xc = x if dense else _f32c(x)
+        y = torch.empty_like(xc)
+        check(lib().hpc_abs_fwd(ptr(xc), ptr(y), xc.numel(), stream()))
+        ctx.save_for_backward(xc)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        (x,) = ctx.saved_tensors
+        if g.dtype != torch.float32 or g.stride() != x.stride():
+            g2 = torch.empty_like(x)
+            g2.copy_(g)
+            g = g2
+        gx = torch.empty_like(x)
+        check(lib().hpc_abs_bwd(ptr(x), ptr(g), ptr(gx), x.numel(), stream()))
+        return gx

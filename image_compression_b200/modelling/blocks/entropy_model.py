@@ -1,0 +1,109 @@
+"""Factorised prior and conditional (scale-only) likelihood models with the reference's class
+names, registry entries, parameter names and return conventions
+(modelling/blocks/entropy_model.py:47-378); arithmetic in kernels K4/K5."""
+import numpy as np
+import torch
+import torch.nn as nn
+
+from ... import _lib
+from ...autograd_ops import BitsFn, CdfLogitsFn, ConditionalFn, EntropyModelFn
+from .build import ENTROPY_MODEL_REGISTRY
+
+
+class CDFLayer(nn.Module):
+    """Parameter container of one MLP layer: weight (1,C,out,in) = log(expm1(1/scale/out)),
+    bias ~ U(-.5,.5), factor = 0 (entropy_model.py:51-65)."""
+
+    def __init__(self, channels, in_dim, out_dim, init_scale, act=True):
+        super().__init__()
+        self.act = act
+        w0 = float(np.log(np.expm1(1 / init_scale / out_dim)))
+        self.weight = nn.Parameter(nn.init.constant_(torch.empty(1, channels, out_dim, in_dim), w0))
+        self.bias = nn.Parameter(nn.init.uniform_(torch.empty(1, channels, out_dim, 1), -0.5, 0.5))
+        if act:
+            self.factor = nn.Parameter(nn.init.zeros_(torch.empty(1, channels, out_dim, 1)))
+
+    def forward(self, x):
+        raise NotImplementedError("CDFLayer is evaluated inside the fused per-channel MLP kernel; call "
+                                  "CDFEstimator / EntropyModel instead")
+
+
+class CDFEstimator(nn.Module):
+    def __init__(self, channels, dims=[3, 3, 3], init_scale=10.):
+        super().__init__()
+        dims = [1] + list(dims) + [1]        # the reference mutates its argument here; we copy
+        n = len(dims) - 1
+        scale = init_scale ** (1 / n)
+        self.layers = nn.Sequential(*[CDFLayer(channels, dims[i], dims[i + 1], scale, act=i < n - 1)
+                                      for i in range(n)])
+
+    def flat_params(self):
+        """order of autograd_ops.CDF_KEYS: w0,b0,f0, w1,b1,f1, w2,b2,f2, w3,b3"""
+        if len(self.layers) != 4:
+            raise NotImplementedError("kernel K4 is specialised for ENTROPY_MODEL.DIMS == [3,3,3]")
+        out = []
+        for l in self.layers:
+            out += [l.weight, l.bias] + ([l.factor] if l.act else [])
+        return out
+
+    def forward(self, x):
+        return CdfLogitsFn.apply(x, *self.flat_params())
+
+
+class BaseEntropyModel(nn.Module):
+    def _ce_loss(self, probs):
+        """sum clamp(-log2(p+1e-10),0,50)  (entropy_model.py:171-185)"""
+        return BitsFn.apply(probs)
+
+    def compress(self, x):
+        raise NotImplementedError()
+
+    def decompress(self, x):
+        raise NotImplementedError()
+
+    def _dequantize(self, x):
+        raise NotImplementedError()
+
+
+@ENTROPY_MODEL_REGISTRY.register()
+class EntropyModel(BaseEntropyModel):
+    """forward(x) -> (x_tilde, probs, bits); probs comes back in the reference's (N,W,C,H) layout for
+    4-D input.  `noise` (U[0,1), shape of x) may be injected for parity tests;
+    otherwise the kernel draws Philox noise seeded from torch's generator."""
+
+    def __init__(self, in_channels, cfg):
+        super().__init__()
+        em = cfg.MODEL.ENTROPY_MODEL
+        self._cdf_estimator = CDFEstimator(in_channels, em.DIMS, em.INIT_SCALE)
+        self.bin = em.BIN
+
+    def forward(self, x, noise=None):
+        return EntropyModelFn.apply(x, float(self.bin), bool(self.training), noise,
+                                    *self._cdf_estimator.flat_params())
+
+    def _logit_cumulative(self, x):
+        return self._cdf_estimator(x)
+
+
+class SymmetricConditionalModel(BaseEntropyModel):
+    DIST = None
+
+    def __init__(self, cfg):
+        super().__init__()
+        self.bin = cfg.MODEL.ENTROPY_MODEL.BIN
+
+    def forward(self, x, scale, mean=0, noise=None):
+        if isinstance(mean, torch.Tensor):
+            raise NotImplementedError("tensor-valued mean: the reference only ever passes mean=0 "
+                                      "(bmshl2018.py:76)")
+        return ConditionalFn.apply(x, scale, float(mean), float(self.bin), bool(self.training), self.DIST, noise)
+
+
+@ENTROPY_MODEL_REGISTRY.register()
+class GaussianConditionalModel(SymmetricConditionalModel):
+    DIST = _lib.DIST_GAUSS
+
+
+@ENTROPY_MODEL_REGISTRY.register()
+class LaplacianConditionalModel(SymmetricConditionalModel):
+    DIST = _lib.DIST_LAPLACE

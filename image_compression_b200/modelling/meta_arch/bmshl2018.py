@@ -1,0 +1,99 @@
+"""Compressor2018: the scale-hyperprior codec (Balle et al. 2018) training/evaluation simulator with
+the reference's module surface (modelling/meta_arch/bmshl2018.py:49-110): same sub-module names (so
+state_dict keys match the reference's 50 keys), `forward(x) -> (x_tilde.detach(), losses)`,
+`loss_names`.
+
+Two execution paths, both on the hand-written kernels only:
+  * fused (default): the whole forward is ONE autograd node with a hand-scheduled backward
+    (autograd_ops.Compressor2018Fn);
+  * composed: the reference's forward line by line over the block modules -- used for loss
+    configurations the fused node does not cover, and by the parity tests as a cross-check.
+"""
+import torch.nn as nn
+
+from ...autograd_ops import Compressor2018Fn, ModelMeta
+from ..blocks import (ENTROPY_MODEL_REGISTRY, AnalysisTransform, HyperpriorAnalysisTransform,
+                      HyperpriorSynthesisTransform, SynthesisTransform)
+from ..layers import LowerBound, UpperBound
+from ..loss import get_loss_dict
+from .build import META_ARCH_REGISTRY
+
+
+@META_ARCH_REGISTRY.register()
+class Compressor2018(nn.Module):
+    def __init__(self, cfg):
+        super().__init__()
+        m = cfg.MODEL
+        # construction order fixes the init RNG stream (bmshl2018.py:56-63)
+        self.analysis_transform = AnalysisTransform(cfg)
+        self.prior_analysis = HyperpriorAnalysisTransform(cfg)
+        self.prior_synthesis = HyperpriorSynthesisTransform(cfg)
+        self.synthesis_transform = SynthesisTransform(cfg)
+        self.entropy_model = ENTROPY_MODEL_REGISTRY.get("EntropyModel")(m.LATENT_CHANNELS, cfg)
+        self.conditional_model = ENTROPY_MODEL_REGISTRY.get(m.ENTROPY_MODEL.CONDITIONAL_MODEL)(cfg)
+        self.distortion_loss_fns = get_loss_dict(cfg, m.LOSS.DISTORTION_LOSS_NAMES)
+        self.distortion_loss_weight = m.LOSS.DISTORTION_LOSS_WEIGHT
+        self.loss_names = ["y_entropy", "z_entropy", "bpp"] + list(self.distortion_loss_fns.keys())
+        self._meta = ModelMeta(m.CONV_KERNEL, m.STRIDES, m.HYPER_PRIOR.KERNELS, m.HYPER_PRIOR.STRIDES,
+                               self.conditional_model.DIST, m.ENTROPY_MODEL.BIN, self.distortion_loss_weight,
+                               list(self.distortion_loss_fns.keys()), getattr(m.LOSS, "REDUCTION", "mean"),
+                               m.LOSS.SSIM)
+        self.fused = True
+
+    # ------------------------------------------------------------------------------
+    def _flat_params(self):
+        return (self.analysis_transform.flat_params() + self.prior_analysis.flat_params() +
+                self.prior_synthesis.flat_params() + self.synthesis_transform.flat_params() +
+                self.entropy_model._cdf_estimator.flat_params())
+
+    def forward(self, x, noise_z=None, noise_y=None):
+        """noise_z / noise_y: optional U[0,1) tensors shaped like z / y (NCHW) replacing the in-kernel
+        Philox noise of training mode (parity tests inject the reference's draws here)."""
+        if self.fused and self._meta.fusable():
+            return self._forward_fused(x, noise_z, noise_y)
+        return self._forward_composed(x, noise_z, noise_y)
+
+    def _forward_fused(self, x, noise_z, noise_y):
+        self._meta.lmbda = float(self.distortion_loss_weight)
+        x_tilde, out = Compressor2018Fn.apply(x, self._meta, bool(self.training), noise_z, noise_y,
+                                              *self._flat_params())
+        det = out.detach()
+        losses = {"z_entropy": det[0], "y_entropy": det[1], "bpp": det[2], "total_loss": out[3]}
+        for i, name in enumerate(self.distortion_loss_fns.keys()):
+            losses[name] = det[4 + i]
+        return x_tilde.detach(), losses
+
+    def _forward_composed(self, x, noise_z=None, noise_y=None):
+        N, C, H, W = x.size()
+        num_pixels = N * H * W
+        y = self.analysis_transform(x)
+        z = self.prior_analysis(_abs(y))
+        z_tilde, z_probs, z_ce_loss = self.entropy_model(z, noise_z)
+        sigma = self.prior_synthesis(z_tilde)
+        y_tilde, y_probs = self.conditional_model(y, sigma, noise=noise_y)
+        y_ce_loss = self.conditional_model._ce_loss(y_probs)
+        x_tilde = self.synthesis_transform(y_tilde)
+        x_tilde = UpperBound.apply(x_tilde, 1.)
+        x_tilde = LowerBound.apply(x_tilde, 0.)
+        distortion_losses = self.distortion_loss(x, x_tilde)
+        total_distortion = sum(distortion_losses.values())
+        entropy_loss = (z_ce_loss + y_ce_loss) / num_pixels
+        total_loss = self.distortion_loss_weight * total_distortion + entropy_loss
+        losses = {"z_entropy": z_ce_loss.detach() / num_pixels, "y_entropy": y_ce_loss.detach() / num_pixels,
+                  "bpp": entropy_loss.detach(), "total_loss": total_loss}
+        losses.update({k: v.detach() for k, v in distortion_losses.items()})
+        return x_tilde.detach(), losses
+
+    def distortion_loss(self, img1, img2):
+        return {name: fn(img1, img2) for name, fn in self.distortion_loss_fns.items()}
+
+    def compress(self, x):   # stubs in the reference too (bmshl2018.py:106-110)
+        pass
+
+    def decompress(self, x):
+        pass
+
+
+def _abs(y):
+    from ...autograd_ops import AbsFn
+    return AbsFn.apply(y)

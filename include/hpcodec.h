@@ -100,6 +100,13 @@ int hpc_factorized_bwd(const float* z_tilde, const hpc_cdf_params* params, int64
                        float bin, const float* g_bits, float g_scale, const float* g_probs, const float* g_zt,
                        float* gz, const hpc_cdf_params* gparams, hpc_stream_t stream);
 
+/* CDFEstimator.forward stand-alone: logits of the per-channel MLP at x (P,C) (entropy_model.py:101-114)
+ * and its backward (g (P,C) upstream; gx may be NULL; gparams accumulated into zeroed buffers). */
+int hpc_cdf_logits_fwd(const float* x, const hpc_cdf_params* params, int64_t P, int C, float* out,
+                       hpc_stream_t stream);
+int hpc_cdf_logits_bwd(const float* x, const hpc_cdf_params* params, int64_t P, int C, const float* g, float* gx,
+                       const hpc_cdf_params* gparams, hpc_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------
  * Conditional (scale-only) Laplace / Gauss likelihood -- kernel K5
  * ---------------------------------------------------------------------------------------- */
@@ -309,6 +316,10 @@ size_t hpc_colsum_scratch_bytes(int64_t P, int C);
 int hpc_square(const void* x, void* out, int dtype, int64_t n, int relu, void* relu_out, hpc_stream_t stream);
 int hpc_gdn_bwd_t(const void* g, const void* x, const void* nrm, void* t, int dtype, int64_t n, int inverse,
                   hpc_stream_t stream);
+
+/* |x| and its autograd (torch.abs at modelling/meta_arch/bmshl2018.py:72), float, n elements */
+int hpc_abs_fwd(const float* x, float* y, int64_t n, hpc_stream_t stream);
+int hpc_abs_bwd(const float* x, const float* g, float* gx, int64_t n, hpc_stream_t stream);
 
 /* out = g * [x > 0]  (autograd of F.relu in the stand-alone relu-GDN, gdn.py:80-81) */
 int hpc_relu_mask(const void* g, const void* x, void* out, int dtype, int64_t n, hpc_stream_t stream);

@@ -1,0 +1,89 @@
+"""CPU tests of the host-side plans: tap tables, phase decomposition, weight packing."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+import igemm_emulator as E
+from image_compression_b200 import hotpath as hp
+
+torch.manual_seed(0)
+CASES = [(False, 5, 2), (False, 3, 1), (True, 5, 2), (True, 3, 1)]
+
+
+def _ref(transposed, x, w, k, s):
+    if transposed:
+        return F.conv_transpose2d(x, w, None, stride=s, padding=k // 2, output_padding=s - 1)
+    return F.conv2d(x, w, None, stride=s, padding=k // 2)
+
+
+@pytest.mark.parametrize("transposed,k,s", CASES)
+def test_forward_dgrad_wgrad_plans(transposed, k, s):
+    ci, co, N, H, W = 3, 4, 2, 6, 8
+    x = torch.randn(N, ci, H, W, dtype=torch.float64, requires_grad=True)
+    w = torch.randn((ci, co, k, k) if transposed else (co, ci, k, k), dtype=torch.float64, requires_grad=True)
+    y = _ref(transposed, x, w, k, s)
+    g = torch.randn_like(y)
+    gx_ref, gw_ref = torch.autograd.grad(y, (x, w), g)
+    spec = hp.ConvSpec(transposed, ci, co, k, s)
+    K = k * k
+    OH, OW = spec.out_hw(H, W)
+    assert (OH, OW) == tuple(y.shape[2:])
+    xn, gn = x.detach().permute(0, 2, 3, 1), g.permute(0, 2, 3, 1)
+    wd = w.detach()
+    # forward (ConvSpec.forward)
+    if transposed:
+        taps, phases = spec.deconv_taps
+        wp = E.pack_weight(wd, taps, co, ci, K, co * K)
+        out = E.igemm_fwd(xn, wp, taps, phases, (H, W), 1, s, (OH, OW), co)
+    else:
+        taps, phases = spec.conv_taps
+        wp = E.pack_weight(wd, taps, co, ci, ci * K, K)
+        out = E.igemm_fwd(xn, wp, taps, phases, (OH, OW), s, 1, (OH, OW), co)
+    assert torch.allclose(out.permute(0, 3, 1, 2), y.detach(), atol=1e-10)
+    # dgrad (ConvSpec.dgrad)
+    if transposed:
+        taps, phases = spec.conv_taps
+        wp = E.pack_weight(wd, taps, ci, co, co * K, K)
+        gx = E.igemm_fwd(gn, wp, taps, phases, (H, W), s, 1, (H, W), ci)
+    else:
+        taps, phases = spec.deconv_taps
+        wp = E.pack_weight(wd, taps, ci, co, K, ci * K)
+        gx = E.igemm_fwd(gn, wp, taps, phases, (OH, OW), 1, s, (H, W), ci)
+    assert torch.allclose(gx.permute(0, 3, 1, 2), gx_ref, atol=1e-10)
+    # wgrad (ConvSpec.wgrad)
+    taps, phases = spec.deconv_taps
+    if transposed:
+        gw = E.igemm_wgrad(xn, gn, taps, phases, s)
+        gw = E.unpack_wgrad(gw, w.shape, taps, ci, co, co * K, K)
+    else:
+        gw = E.igemm_wgrad(gn, xn, taps, phases, s)
+        gw = E.unpack_wgrad(gw, w.shape, taps, co, ci, ci * K, K)
+    assert torch.allclose(gw, gw_ref, atol=1e-10)
+
+
+def test_phase_tap_counts():
+    taps, phases = hp.deconv_type_taps(5, 2, 2)
+    assert [p[0] for p in phases] == [9, 6, 6, 4] and len(taps) == 25
+    taps, phases = hp.conv_type_taps(5, 2, 2)
+    assert len(taps) == 25 and phases == [(25, 0, 0, 0)]
+
+
+def test_gdn_bounds_match_reference_quirk():
+    assert hp.PEDESTAL == 2.0 ** -36
+    assert hp.GAMMA_BOUND == 2.0 ** -36          # sqrt(0 + pedestal^2): gdn.py:53
+    assert abs(hp.beta_bound(1e-6) - 1e-3) < 1e-6
+
+
+def test_gauss_filter_is_the_separable_factor():
+    import sys
+    from oracle import hyperprior_oracle as O
+    g2 = O.gauss_filter_2d(11, 1.5)[0, 0]
+    g1 = hp.gauss_filter_1d(11, 1.5, "cpu")
+    assert torch.allclose(torch.outer(g1, g1), g2, atol=1e-8)
+
+
+def test_cpu_tensor_is_rejected_loudly():
+    import image_compression_b200 as pkg
+    m = pkg.build_model(pkg.get_recipe_cfg("psnr_256"))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        m(torch.rand(1, 3, 64, 64))
