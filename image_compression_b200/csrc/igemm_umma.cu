@@ -1,5 +1,396 @@
-// placeholder until the tcgen05 engine lands
-#include "hpc_common.cuh"
-int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) { HPC_FAIL(HPC_ERR_UNSUPPORTED, "umma engine not built"); }
-int hpc_igemm_wgrad_umma(const hpc_igemm_wgrad_params* p, hpc_stream_t stream) { HPC_FAIL(HPC_ERR_UNSUPPORTED, "umma engine not built"); }
-size_t hpc_igemm_wgrad_umma_workspace_bytes(const hpc_igemm_wgrad_params* p) { return 0; }
+// tcgen05 / TMEM / TMA engine of the implicit-GEMM convolution family (sm_100a).
+//
+// Forward kernel (conv, transposed-conv phases, dgrads, the GDN gamma contraction):
+//   one persistent CTA per SM, 192 threads = warp 0 TMA producer, warp 1 MMA issuer + TMEM owner,
+//   warps 2-5 epilogue.  An M tile is a (nb x th x tw) = 128-pixel patch of the iteration grid; for
+//   every tap t and 64-channel slice c the producer issues ONE 4-D TMA box over the NHWC input
+//   (elementStrides = input stride, out-of-bounds = zero fill == the convolution padding) that lands
+//   as a canonical K-major SWIZZLE_128B [128 x 64] bf16 operand, plus a [BLOCK_N x 64] weight box.
+//   Accumulators (128 lanes x BLOCK_N fp32 columns) are double-buffered in TMEM so the epilogue of
+//   tile i overlaps the MMAs of tile i+1.
+#include <cuda.h>
+
+#include "igemm_epilogue.cuh"
+#include "umma_ptx.cuh"
+
+using namespace umma;
+
+// ---------------------------------------------------------------------------------------
+// driver entry point for tensor-map encoding (no link-time dependency on libcuda)
+// ---------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+// bf16 tensor map of rank `rank` (dims innermost first), SWIZZLE_128B, zero OOB fill
+static int make_tmap(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                     const uint32_t* box, const uint32_t* estr) {
+  EncodeTiledFn fn = get_encode_fn();
+  HPC_REQUIRE(fn, HPC_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), dims, strides_bytes,
+                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  HPC_REQUIRE(r == CUDA_SUCCESS, HPC_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return HPC_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// forward kernel
+// ---------------------------------------------------------------------------------------
+constexpr int FW_THREADS = 192;
+constexpr int FW_BM = 128;   // pixels per tile (UMMA M)
+constexpr int FW_BK = 64;    // channels per stage (one 128-byte swizzle row of bf16)
+
+struct FwdKParams {
+  int N, GH, GW, is, os, OH, OW, Co, Ci;
+  int tw, th, nb;            // tile shape, tw*th*nb == 128
+  int tiles_w, tiles_h, tiles_n, tiles_per_phase, total_tiles;
+  int nphases;
+  hpc_igemm_phase phase[HPC_MAX_PHASES];
+  int dh[HPC_MAX_TAPS], dw[HPC_MAX_TAPS];
+  int kchunks;               // Ci / 64
+  EpiArgs epi;
+};
+
+template <int BLOCK_N>
+struct FwdCfg {
+  static constexpr int A_BYTES = FW_BM * FW_BK * 2;        // 16 KB
+  static constexpr int B_BYTES = BLOCK_N * FW_BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (200 * 1024 / STAGE_BYTES) > 8 ? 8 : (200 * 1024 / STAGE_BYTES);
+  static constexpr int ACC_STRIDE = BLOCK_N <= 32 ? 32 : (BLOCK_N <= 64 ? 64 : (BLOCK_N <= 128 ? 128 : 256));
+  static constexpr int TMEM_COLS = 2 * ACC_STRIDE;          // 64..512, power of two
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+};
+
+__device__ __forceinline__ void tile_coords(const FwdKParams& p, int tile, int& ph, int& n0, int& i0, int& j0) {
+  ph = tile / p.tiles_per_phase;
+  int r = tile - ph * p.tiles_per_phase;
+  const int tj = r % p.tiles_w; r /= p.tiles_w;
+  const int ti = r % p.tiles_h; r /= p.tiles_h;
+  n0 = r * p.nb; i0 = ti * p.th; j0 = tj * p.tw;
+}
+
+// epilogue for 8 consecutive channels of one output pixel (bf16 lp tensors)
+__device__ __forceinline__ void load8_bf16(const void* base, int64_t o, float* f) {
+  const uint4 u = *reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(base) + o);
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float2 t = __bfloat1622float2(h[i]);
+    f[2 * i] = t.x; f[2 * i + 1] = t.y;
+  }
+}
+__device__ __forceinline__ void store8_bf16(void* base, int64_t o, const float* f) {
+  uint4 u;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+  *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(base) + o) = u;
+}
+__device__ __forceinline__ void load8_f32(const void* base, int64_t o, float* f) {
+  const float4 a = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(base) + o);
+  const float4 b = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(base) + o + 4);
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+__device__ __forceinline__ void store8_f32(float* base, int64_t o, const float* f) {
+  *reinterpret_cast<float4*>(base + o) = make_float4(f[0], f[1], f[2], f[3]);
+  *reinterpret_cast<float4*>(base + o + 4) = make_float4(f[4], f[5], f[6], f[7]);
+}
+
+__device__ __forceinline__ void epilogue8(const EpiArgs& e, const float* acc, int64_t o, int c0) {
+  float v[8], nrm[8];
+  if (e.bias) {
+    float b[8];
+    load8_f32(e.bias, c0, b);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] = acc[i] + b[i];
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] = acc[i];
+  }
+  switch (e.epi) {
+    case HPC_EPI_RELU:
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.f);
+      break;
+    case HPC_EPI_EXP_CLAMP:
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = fminf(fmaxf(expf(v[i]), 1e-10f), 1e10f);
+      break;
+    case HPC_EPI_GDN: case HPC_EPI_IGDN: {
+      float x[8];
+      load8_bf16(e.aux0, o, x);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float r = rsqrtf(v[i]);
+        nrm[i] = r;
+        v[i] = (e.epi == HPC_EPI_GDN) ? x[i] * r : x[i] * (v[i] * r);
+      }
+      break;
+    }
+    case HPC_EPI_GDN_BWD: case HPC_EPI_IGDN_BWD: {
+      float g[8], x[8], r[8];
+      load8_bf16(e.aux0, o, g);
+      load8_bf16(e.aux1, o, x);
+      load8_bf16(e.aux2, o, r);
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        v[i] = (e.epi == HPC_EPI_GDN_BWD) ? (g[i] * r[i] - x[i] * v[i]) : (g[i] / r[i] + x[i] * v[i]);
+      break;
+    }
+    case HPC_EPI_RELU_MASK: {
+      float x[8];
+      load8_bf16(e.aux0, o, x);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = x[i] > 0.f ? v[i] : 0.f;
+      break;
+    }
+    case HPC_EPI_SIGN_ADD: {
+      float y[8], a[8];
+      load8_f32(e.aux0, o, y);
+      load8_f32(e.aux1, o, a);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = (y[i] > 0.f ? v[i] : (y[i] < 0.f ? -v[i] : 0.f)) + a[i];
+      break;
+    }
+    default: break;
+  }
+  if (e.out_f32) store8_f32(e.out_f32, o, v);
+  if (e.out_lp) store8_bf16(e.out_lp, o, v);
+  if (e.out_sq_lp) {
+    float s[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s[i] = v[i] * v[i];
+    store8_bf16(e.out_sq_lp, o, s);
+  }
+  if (e.out_abs_lp) {
+    float s[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s[i] = fabsf(v[i]);
+    store8_bf16(e.out_abs_lp, o, s);
+  }
+  if (e.out_nrm_lp && (e.epi == HPC_EPI_GDN || e.epi == HPC_EPI_IGDN)) store8_bf16(e.out_nrm_lp, o, nrm);
+}
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(FW_THREADS, 1)
+igemm_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                      const __grid_constant__ FwdKParams p) {
+  using Cfg = FwdCfg<BLOCK_N>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;                                  // STAGES x 16 KB
+  uint8_t* smem_b = smem + Cfg::STAGES * Cfg::A_BYTES;     // STAGES x B_BYTES (multiples of 1 KB)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
+  uint64_t* full_bar = bars;                    // [STAGES]  TMA -> MMA
+  uint64_t* empty_bar = bars + Cfg::STAGES;     // [STAGES]  MMA -> TMA
+  uint64_t* tfull_bar = bars + 2 * Cfg::STAGES; // [2]       MMA -> epilogue
+  uint64_t* tempty_bar = tfull_bar + 2;         // [2]       epilogue -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    for (int s = 0; s < Cfg::STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&tfull_bar[s], 1); mbar_init(&tempty_bar[s], 4); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================================ TMA producer ================================
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+        int ph, n0, i0, j0;
+        tile_coords(p, tile, ph, n0, i0, j0);
+        const hpc_igemm_phase P = p.phase[ph];
+        for (int t = P.tap_begin; t < P.tap_begin + P.ntaps; ++t) {
+          const int cw = j0 * p.is + p.dw[t], chh = i0 * p.is + p.dh[t];
+          for (int c = 0; c < p.kchunks; ++c) {
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+            tma_load_4d(smem_a + stage * Cfg::A_BYTES, &tmA, &full_bar[stage], c * FW_BK, cw, chh, n0);
+            tma_load_2d(smem_b + stage * Cfg::B_BYTES, &tmB, &full_bar[stage], c * FW_BK, t * p.Co);
+            if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer ==================================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(FW_BM, BLOCK_N, 0, 0);
+      int stage = 0; uint32_t phase = 0;
+      int acc = 0; uint32_t acc_phase = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+        int ph, n0, i0, j0;
+        tile_coords(p, tile, ph, n0, i0, j0);
+        const int ksteps = p.phase[ph].ntaps * p.kchunks;
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);     // epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * Cfg::ACC_STRIDE;
+        for (int ks = 0; ks < ksteps; ++ks) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem_a + stage * Cfg::A_BYTES);
+          const uint32_t b_addr = smem_u32(smem_b + stage * Cfg::B_BYTES);
+#pragma unroll
+          for (int k = 0; k < FW_BK / 16; ++k) {
+            const uint64_t ad = make_smem_desc_sw128(a_addr + k * 32, 16, 1024);
+            const uint64_t bd = make_smem_desc_sw128(b_addr + k * 32, 16, 1024);
+            mma_bf16_ss(d_tmem, ad, bd, idesc, (ks | k) != 0);
+          }
+          mma_commit(&empty_bar[stage]);                // frees the smem stage when these MMAs retire
+          if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+        }
+        mma_commit(&tfull_bar[acc]);                    // accumulator complete -> epilogue
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else {
+    // ================================ epilogue (4 warps) ==========================
+    const int q = warp & 3;                 // TMEM lane quarter this warp may access
+    const int row = q * 32 + lane;          // tile row == TMEM lane
+    int acc = 0; uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+      int ph, n0, i0, j0;
+      tile_coords(p, tile, ph, n0, i0, j0);
+      const hpc_igemm_phase P = p.phase[ph];
+      const int jl = row % p.tw, il = (row / p.tw) % p.th, nl = row / (p.tw * p.th);
+      const int n = n0 + nl, i = i0 + il, j = j0 + jl;
+      const int oh = i * p.os + P.oh_off, ow = j * p.os + P.ow_off;
+      const bool valid = (n < p.N) && (i < p.GH) && (j < p.GW) && (oh < p.OH) && (ow < p.OW);
+      const int64_t obase = (((int64_t)n * p.OH + oh) * p.OW + ow) * p.Co;
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + acc * Cfg::ACC_STRIDE + ((uint32_t)(q * 32) << 16);
+#pragma unroll 1
+      for (int c0 = 0; c0 < BLOCK_N; c0 += 16) {
+        float v[16];
+        tmem_ld16(taddr + c0, v);
+        tmem_ld_wait();
+        if (valid) {
+          epilogue8(p.epi, v, obase + c0, c0);
+          epilogue8(p.epi, v + 8, obase + c0 + 8, c0 + 8);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+}
+
+// ---------------------------------------------------------------------------------------
+// host side of the forward kernel
+// ---------------------------------------------------------------------------------------
+static int pow2_floor(int v) { int r = 1; while (r * 2 <= v) r *= 2; return r; }
+
+template <int BLOCK_N>
+static int launch_fwd(const CUtensorMap& tmA, const CUtensorMap& tmB, const FwdKParams& kp, cudaStream_t st) {
+  using Cfg = FwdCfg<BLOCK_N>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    HPC_CUDA(cudaFuncSetAttribute(igemm_fwd_umma_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  int grid = kp.total_tiles < hpc_num_sms() ? kp.total_tiles : hpc_num_sms();
+  igemm_fwd_umma_kernel<BLOCK_N><<<grid, FW_THREADS, Cfg::SMEM_BYTES, st>>>(tmA, tmB, kp);
+  HPC_LAUNCH_CHECK();
+  return HPC_OK;
+}
+
+int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
+  HPC_REQUIRE(p->dtype == HPC_BF16, HPC_ERR_UNSUPPORTED, "umma engine: operands must be bf16");
+  HPC_REQUIRE(p->Ci % FW_BK == 0, HPC_ERR_UNSUPPORTED, "umma engine: Ci=%d must be a multiple of 64", p->Ci);
+  HPC_REQUIRE(p->Co == 64 || p->Co == 128 || p->Co == 192 || p->Co == 256, HPC_ERR_UNSUPPORTED,
+              "umma engine: Co=%d not in {64,128,192,256}", p->Co);
+  HPC_REQUIRE(p->is >= 1 && p->is <= 8, HPC_ERR_UNSUPPORTED, "umma engine: input stride %d not in [1,8]", p->is);
+  HPC_REQUIRE(hpc_aligned16(p->x) && hpc_aligned16(p->w), HPC_ERR_BAD_ALIGNMENT, "umma engine: x/w must be 16B aligned");
+  const void* outs[] = {p->out_f32, p->out_lp, p->out_sq_lp, p->out_abs_lp, p->out_nrm_lp, p->aux0, p->aux1, p->aux2,
+                        p->bias};
+  for (const void* q : outs) HPC_REQUIRE(hpc_aligned16(q), HPC_ERR_BAD_ALIGNMENT, "umma engine: epilogue pointers must be 16B aligned");
+
+  FwdKParams kp;
+  memset(&kp, 0, sizeof(kp));
+  kp.N = p->N; kp.GH = p->GH; kp.GW = p->GW; kp.is = p->is; kp.os = p->os; kp.OH = p->OH; kp.OW = p->OW;
+  kp.Co = p->Co; kp.Ci = p->Ci;
+  kp.tw = pow2_floor(p->GW < 16 ? p->GW : 16);
+  kp.th = pow2_floor(p->GH < FW_BM / kp.tw ? p->GH : FW_BM / kp.tw);
+  kp.nb = FW_BM / (kp.tw * kp.th);
+  kp.tiles_w = (p->GW + kp.tw - 1) / kp.tw;
+  kp.tiles_h = (p->GH + kp.th - 1) / kp.th;
+  kp.tiles_n = (p->N + kp.nb - 1) / kp.nb;
+  kp.tiles_per_phase = kp.tiles_w * kp.tiles_h * kp.tiles_n;
+  kp.nphases = p->nphases;
+  kp.total_tiles = kp.tiles_per_phase * p->nphases;
+  memcpy(kp.phase, p->phase, sizeof(kp.phase));
+  memcpy(kp.dh, p->dh, sizeof(kp.dh));
+  memcpy(kp.dw, p->dw, sizeof(kp.dw));
+  kp.kchunks = p->Ci / FW_BK;
+  kp.epi = make_epi_args(p);
+  int ntaps_total = 0;
+  for (int i = 0; i < p->nphases; ++i) {
+    int e = p->phase[i].tap_begin + p->phase[i].ntaps;
+    if (e > ntaps_total) ntaps_total = e;
+  }
+
+  CUtensorMap tmA, tmB;
+  {
+    uint64_t dims[4] = {(uint64_t)p->Ci, (uint64_t)p->W, (uint64_t)p->H, (uint64_t)p->N};
+    uint64_t strides[3] = {(uint64_t)p->Ci * 2, (uint64_t)p->W * p->Ci * 2, (uint64_t)p->H * p->W * p->Ci * 2};
+    uint32_t box[4] = {(uint32_t)FW_BK, (uint32_t)(kp.tw * p->is), (uint32_t)(kp.th * p->is), (uint32_t)kp.nb};
+    uint32_t estr[4] = {1, (uint32_t)p->is, (uint32_t)p->is, 1};
+    int rc = make_tmap(&tmA, p->x, 4, dims, strides, box, estr);
+    if (rc) return rc;
+  }
+  {
+    uint64_t dims[2] = {(uint64_t)p->Ci, (uint64_t)ntaps_total * p->Co};
+    uint64_t strides[1] = {(uint64_t)p->Ci * 2};
+    uint32_t box[2] = {(uint32_t)FW_BK, (uint32_t)p->Co};
+    uint32_t estr[2] = {1, 1};
+    int rc = make_tmap(&tmB, p->w, 2, dims, strides, box, estr);
+    if (rc) return rc;
+  }
+  auto st = (cudaStream_t)stream;
+  switch (p->Co) {
+    case 64: return launch_fwd<64>(tmA, tmB, kp, st);
+    case 128: return launch_fwd<128>(tmA, tmB, kp, st);
+    case 192: return launch_fwd<192>(tmA, tmB, kp, st);
+    default: return launch_fwd<256>(tmA, tmB, kp, st);
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// weight gradient: tcgen05 kernel pending; until it lands the SIMT engine serves this entry
+// ---------------------------------------------------------------------------------------
+size_t hpc_igemm_wgrad_umma_workspace_bytes(const hpc_igemm_wgrad_params* p) { (void)p; return 0; }
+int hpc_igemm_wgrad_umma(const hpc_igemm_wgrad_params* p, hpc_stream_t stream) {
+  hpc_igemm_wgrad_params q = *p;
+  q.engine = HPC_ENGINE_SIMT;
+  return hpc_igemm_wgrad(&q, stream);
+}

@@ -1,0 +1,97 @@
+"""tcgen05 engine against the CUDA-core engine on IDENTICAL bf16 operands: both accumulate in fp32, so
+fp32 outputs agree to summation-order round-off (1e-4 relative to the output scale) -- any descriptor,
+swizzle, TMA-coordinate or pipeline bug shows up as an O(1) error here, separated from bf16 rounding."""
+import pytest
+import torch
+
+import image_compression_b200 as pkg
+from image_compression_b200 import _lib
+from image_compression_b200 import hotpath as hp
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _both(fn):
+    with pkg.compute_mode("bf16_simt"):
+        ref = fn()
+    with pkg.compute_mode("bf16"):
+        out = fn()
+    return out, ref
+
+
+def _cmp(out, ref, tol=2e-4):
+    for k in ref:
+        a, b = out[k].float(), ref[k].float()
+        scale = float(b.abs().max()) + 1e-20
+        err = float((a - b).abs().max()) / scale
+        lim = tol if k == "f32" else 1e-2        # bf16 outputs may differ by one rounding step
+        assert err < lim, (k, err)
+
+
+@pytest.mark.parametrize("transposed,k,s", [(False, 5, 2), (True, 5, 2), (False, 3, 1), (True, 3, 1)])
+@pytest.mark.parametrize("N,H,W,C", [(2, 32, 32, 192), (3, 8, 8, 192), (5, 4, 4, 192), (1, 16, 24, 192),
+                                     (2, 8, 12, 64), (1, 6, 10, 128)])
+def test_forward_and_dgrad(transposed, k, s, N, H, W, C):
+    torch.manual_seed(0)
+    spec = hp.ConvSpec(transposed, C, C, k, s)
+    x = torch.randn(N, H, W, C, device=DEV).to(torch.bfloat16)
+    w = (torch.randn(C, C, k, k, device=DEV) / (C * k * k) ** 0.5)
+    b = torch.randn(C, device=DEV)
+    out, ref = _both(lambda: spec.forward(x, w, b, _lib.EPI_LINEAR, want_f32=True, want_sq=True, want_abs=True))
+    _cmp(out, ref)
+    OH, OW = spec.out_hw(H, W)
+    g = torch.randn(N, OH, OW, C, device=DEV).to(torch.bfloat16)
+    out, ref = _both(lambda: spec.dgrad(g, w, (H, W), want_f32=True))
+    _cmp(out, ref)
+
+
+@pytest.mark.parametrize("epi", ["relu", "exp_clamp", "relu_mask", "sign_add"])
+def test_epilogues(epi):
+    torch.manual_seed(1)
+    C, N, H, W = 192, 2, 16, 16
+    spec = hp.ConvSpec(False, C, C, 3, 1)
+    x = torch.randn(N, H, W, C, device=DEV).to(torch.bfloat16)
+    w = torch.randn(C, C, 3, 3, device=DEV) / (C * 9) ** 0.5
+    b = 0.1 * torch.randn(C, device=DEV)
+    aux_lp = torch.randn(N, H, W, C, device=DEV).to(torch.bfloat16)
+    y32, a32 = torch.randn(N, H, W, C, device=DEV), torch.randn(N, H, W, C, device=DEV)
+    if epi == "relu":
+        f = lambda: spec.forward(x, w, b, _lib.EPI_RELU, want_f32=True)
+    elif epi == "exp_clamp":
+        f = lambda: spec.forward(x, w, b, _lib.EPI_EXP_CLAMP, want_f32=True, want_lp=False)
+    elif epi == "relu_mask":
+        f = lambda: spec.dgrad(x, w, (H, W), _lib.EPI_RELU_MASK, aux0=aux_lp, want_f32=True)
+    else:
+        f = lambda: spec.dgrad(x, w, (H, W), _lib.EPI_SIGN_ADD, aux0=y32, aux1=a32, want_f32=True)
+    out, ref = _both(f)
+    _cmp(out, ref)
+
+
+@pytest.mark.parametrize("inverse", [False, True])
+def test_gdn_forward_backward_engines(inverse):
+    torch.manual_seed(2)
+    C, N, H, W = 192, 2, 16, 24
+    x = torch.randn(N, H, W, C, device=DEV).to(torch.bfloat16)
+    g = torch.randn(N, H, W, C, device=DEV).to(torch.bfloat16)
+    gamma = (0.1 * torch.eye(C, device=DEV) + 0.01 * torch.rand(C, C, device=DEV)).view(C, C, 1, 1)
+    beta = 1 + torch.rand(C, device=DEV)
+
+    def run():
+        xsq, _ = hp.square(x)
+        y, nrm = hp.gdn_forward(x, xsq, gamma, beta, inverse)
+        dx, dg, db = hp.gdn_backward(g, x, xsq, nrm, gamma, inverse)
+        return {"y": y, "nrm": nrm, "dx": dx, "dg": dg, "db": db}
+    out, ref = _both(run)
+    for k in ref:
+        a, b = out[k].float(), ref[k].float()
+        err = float((a - b).abs().max()) / (float(b.abs().max()) + 1e-20)
+        assert err < 2e-2, (k, err)
+
+
+def test_rejects_unsupported_shapes_loudly():
+    x = torch.randn(1, 8, 8, 48, device=DEV).to(torch.bfloat16)
+    w = torch.randn(48, 48, 3, 3, device=DEV)
+    with pkg.compute_mode("bf16"):
+        with pytest.raises(_lib.HpcError, match="multiple of 64"):
+            hp.ConvSpec(False, 48, 48, 3, 1).forward(x, w, None)
