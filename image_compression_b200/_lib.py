@@ -115,6 +115,7 @@ _SIGNATURES = {
     "hpc_version": (c_int, []),
     "hpc_last_error": (c_char_p, []),
     "hpc_device_is_sm100": (c_int, []),
+    "hpc_launch_count": (ctypes.c_ulonglong, []),
     "hpc_bound_fwd": (c_int, [c_void_p, c_void_p, c_int64, c_float, c_int, c_void_p]),
     "hpc_bound_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_float, c_int, c_void_p]),
     "hpc_nonneg_fwd": (c_int, [c_void_p, c_void_p, c_int64, c_float, c_float, c_void_p]),

@@ -3,6 +3,9 @@
 
 thread_local char g_hpc_err[512] = "";
 
+unsigned long long g_hpc_launches = 0;
+unsigned long long hpc_launch_count(void) { return __atomic_load_n(&g_hpc_launches, __ATOMIC_RELAXED); }
+
 int hpc_version(void) { return HPC_VERSION; }
 const char* hpc_last_error(void) { return g_hpc_err; }
 

@@ -13,6 +13,7 @@
 // error convention: every export returns int, message via hpc_last_error()
 // ---------------------------------------------------------------------------------------
 extern thread_local char g_hpc_err[512];
+extern unsigned long long g_hpc_launches;  // kernels launched by this library (bench.py's gpu_launches)
 
 #define HPC_FAIL(code, ...)                                   \
   do {                                                        \
@@ -35,6 +36,7 @@ extern thread_local char g_hpc_err[512];
 
 #define HPC_LAUNCH_CHECK()                                                             \
   do {                                                                                 \
+    __atomic_fetch_add(&g_hpc_launches, 1ull, __ATOMIC_RELAXED);                       \
     cudaError_t _e = cudaGetLastError();                                               \
     if (_e != cudaSuccess)                                                             \
       HPC_FAIL(HPC_ERR_CUDA, "kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), \

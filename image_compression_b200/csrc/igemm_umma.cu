@@ -386,11 +386,251 @@ int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
 }
 
 // ---------------------------------------------------------------------------------------
-// weight gradient: tcgen05 kernel pending; until it lands the SIMT engine serves this entry
+// weight gradient kernel ("wgrad"): gw[t][r][c] = sum_pixels lo[p+d_t][r] * hi[p'][c]
+//
+// GEMM view per phase: M = (tap, r) rows, N = c columns, K = pixels.  Both operands come straight from
+// the NHWC tensors as MN-major SWIZZLE_128B tiles ([64 pixels] x [64 channels] per TMA box = one UMMA
+// "atom"); shifting `lo` by the tap offset is a TMA coordinate, so no im2col is ever materialised.
+// A CTA owns one "unit" of 4 consecutive atoms of the phase's (tap, r-chunk) list = two 128-row
+// accumulators in TMEM (2 x Cc fp32 columns) and one slice of the pixel range (split-K); it writes its
+// partial to the workspace and a second kernel reduces the slices in a fixed order (deterministic).
 // ---------------------------------------------------------------------------------------
-size_t hpc_igemm_wgrad_umma_workspace_bytes(const hpc_igemm_wgrad_params* p) { (void)p; return 0; }
+constexpr int WG_THREADS = 192;
+constexpr int WG_P = 64;                       // pixels per stage (K block)
+constexpr int WG_ATOM_BYTES = WG_P * 128;      // 8 KB: 64 pixels x 64 bf16
+constexpr int WG_STAGES = 3;
+constexpr int WG_MAX_UNITS = 32;
+
+struct WgUnit { int phase, atom_begin, natoms; };   // atoms index the phase's (tap, r-chunk) list
+
+struct WgKParams {
+  int N, GH, GW, R, HH, HW, Cc, hs;
+  int tw, th, nb, tiles_w, tiles_h, tiles_n, kblocks;
+  int nunits, nsplits, rchunks, cchunks, ntaps;
+  hpc_igemm_phase phase[HPC_MAX_PHASES];
+  int dh[HPC_MAX_TAPS], dw[HPC_MAX_TAPS];
+  WgUnit unit[WG_MAX_UNITS];
+  float* ws;                                   // [nsplits][ntaps][R][Cc]
+};
+
+__global__ void __launch_bounds__(WG_THREADS, 1)
+igemm_wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmLo, const __grid_constant__ CUtensorMap tmHi,
+                        const __grid_constant__ WgKParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int stage_bytes = (4 + p.cchunks) * WG_ATOM_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + WG_STAGES * stage_bytes);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + WG_STAGES;
+  uint64_t* done_bar = bars + 2 * WG_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done_bar + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int unit_id = blockIdx.x % p.nunits, split = blockIdx.x / p.nunits;
+  const WgUnit U = p.unit[unit_id];
+  const hpc_igemm_phase P = p.phase[U.phase];
+  const int kb0 = (int)(((int64_t)split * p.kblocks) / p.nsplits);
+  const int kb1 = (int)(((int64_t)(split + 1) * p.kblocks) / p.nsplits);
+  const int nkb = kb1 - kb0;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmLo);
+    prefetch_tmap(&tmHi);
+    for (int s = 0; s < WG_STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    mbar_init(done_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      const uint32_t tx = (uint32_t)(U.natoms + p.cchunks) * WG_ATOM_BYTES;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        int r = kb;
+        const int tj = r % p.tiles_w; r /= p.tiles_w;
+        const int ti = r % p.tiles_h; r /= p.tiles_h;
+        const int n0 = r * p.nb, i0 = ti * p.th, j0 = tj * p.tw;
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        mbar_arrive_expect_tx(&full_bar[stage], tx);
+        uint8_t* sa = smem + stage * stage_bytes;
+        uint8_t* sb = sa + 4 * WG_ATOM_BYTES;
+        for (int a = 0; a < U.natoms; ++a) {
+          const int atom = U.atom_begin + a;
+          const int t = P.tap_begin + atom / p.rchunks, rc = atom % p.rchunks;
+          tma_load_4d(sa + a * WG_ATOM_BYTES, &tmLo, &full_bar[stage], rc * 64, j0 + p.dw[t], i0 + p.dh[t], n0);
+        }
+        for (int c = 0; c < p.cchunks; ++c)
+          tma_load_4d(sb + c * WG_ATOM_BYTES, &tmHi, &full_bar[stage], c * 64, j0 * p.hs + P.ow_off,
+                      i0 * p.hs + P.oh_off, n0);
+        if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(128, p.Cc, 1, 1);   // both operands MN-major
+      const int nmma = (U.natoms + 1) / 2;
+      int stage = 0; uint32_t phase = 0;
+      for (int kb = 0; kb < nkb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem + stage * stage_bytes);
+        const uint32_t b_addr = a_addr + 4 * WG_ATOM_BYTES;
+#pragma unroll
+        for (int ks = 0; ks < WG_P / 16; ++ks) {
+          const uint64_t bd = make_smem_desc_sw128(b_addr + ks * 2048, WG_ATOM_BYTES, 1024);
+          for (int m = 0; m < nmma; ++m) {
+            const uint64_t ad = make_smem_desc_sw128(a_addr + m * 2 * WG_ATOM_BYTES + ks * 2048, WG_ATOM_BYTES, 1024);
+            mma_bf16_ss(tmem_base + m * 256, ad, bd, idesc, (kb | ks) != 0);
+          }
+        }
+        mma_commit(&empty_bar[stage]);
+        if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
+      }
+      mma_commit(done_bar);
+    }
+  } else {
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    mbar_wait(done_bar, 0);
+    tc_fence_after();
+    const int nmma = (U.natoms + 1) / 2;
+    for (int m = 0; m < nmma; ++m) {
+      const int a = 2 * m + row / 64;
+      const bool valid = a < U.natoms;
+      const int atom = U.atom_begin + a;
+      const int t = P.tap_begin + atom / p.rchunks, r = (atom % p.rchunks) * 64 + (row & 63);
+      float* dst = p.ws + (((int64_t)split * p.ntaps + t) * p.R + r) * p.Cc;
+      const uint32_t taddr = tmem_base + m * 256 + ((uint32_t)(q * 32) << 16);
+      for (int c0 = 0; c0 < p.Cc; c0 += 16) {
+        float v[16];
+        if (nkb > 0) {
+          tmem_ld16(taddr + c0, v);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = 0.f;
+        }
+        if (valid) {
+          store8_f32(dst, c0, v);
+          store8_f32(dst, c0 + 8, v + 8);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+__global__ void wgrad_reduce_kernel(const float* __restrict__ ws, int nsplits, int64_t n, float scale,
+                                    float* __restrict__ gw) {
+  for (int64_t i = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) * 4; i < n; i += (int64_t)gridDim.x * blockDim.x * 4) {
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int s = 0; s < nsplits; ++s) {
+      const float4 v = *reinterpret_cast<const float4*>(ws + (int64_t)s * n + i);
+      a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+    }
+    *reinterpret_cast<float4*>(gw + i) = make_float4(a.x * scale, a.y * scale, a.z * scale, a.w * scale);
+  }
+}
+
+static int wgrad_plan(const hpc_igemm_wgrad_params* p, WgKParams* kp) {
+  memset(kp, 0, sizeof(*kp));
+  kp->N = p->N; kp->GH = p->GH; kp->GW = p->GW; kp->R = p->R; kp->HH = p->HH; kp->HW = p->HW; kp->Cc = p->Cc;
+  kp->hs = p->hs;
+  kp->tw = pow2_floor(p->GW < 8 ? p->GW : 8);
+  kp->th = pow2_floor(p->GH < WG_P / kp->tw ? p->GH : WG_P / kp->tw);
+  kp->nb = WG_P / (kp->tw * kp->th);
+  kp->tiles_w = (p->GW + kp->tw - 1) / kp->tw;
+  kp->tiles_h = (p->GH + kp->th - 1) / kp->th;
+  kp->tiles_n = (p->N + kp->nb - 1) / kp->nb;
+  kp->kblocks = kp->tiles_w * kp->tiles_h * kp->tiles_n;
+  kp->rchunks = p->R / 64; kp->cchunks = p->Cc / 64;
+  memcpy(kp->phase, p->phase, sizeof(kp->phase));
+  memcpy(kp->dh, p->dh, sizeof(kp->dh));
+  memcpy(kp->dw, p->dw, sizeof(kp->dw));
+  int nu = 0, nt = 0;
+  for (int ph = 0; ph < p->nphases; ++ph) {
+    const int natoms = p->phase[ph].ntaps * kp->rchunks;
+    for (int a = 0; a < natoms; a += 4) {
+      HPC_REQUIRE(nu < WG_MAX_UNITS, HPC_ERR_UNSUPPORTED, "umma wgrad: too many work units");
+      kp->unit[nu].phase = ph; kp->unit[nu].atom_begin = a; kp->unit[nu].natoms = natoms - a < 4 ? natoms - a : 4;
+      ++nu;
+    }
+    nt += p->phase[ph].ntaps;
+  }
+  kp->nunits = nu; kp->ntaps = nt;
+  int ns = hpc_num_sms() / nu;
+  if (ns < 1) ns = 1;
+  if (ns > kp->kblocks) ns = kp->kblocks;
+  kp->nsplits = ns;
+  return HPC_OK;
+}
+
+static int wgrad_check(const hpc_igemm_wgrad_params* p) {
+  HPC_REQUIRE(p->dtype == HPC_BF16, HPC_ERR_UNSUPPORTED, "umma wgrad: operands must be bf16");
+  HPC_REQUIRE(p->R % 64 == 0 && p->R <= 256 * 4, HPC_ERR_UNSUPPORTED, "umma wgrad: R=%d must be a multiple of 64", p->R);
+  HPC_REQUIRE(p->Cc % 64 == 0 && p->Cc >= 64 && p->Cc <= 256, HPC_ERR_UNSUPPORTED,
+              "umma wgrad: Cc=%d must be a multiple of 64 in [64,256]", p->Cc);
+  HPC_REQUIRE(p->hs >= 1 && p->hs <= 8, HPC_ERR_UNSUPPORTED, "umma wgrad: hs=%d not in [1,8]", p->hs);
+  HPC_REQUIRE(hpc_aligned16(p->lo) && hpc_aligned16(p->hi) && hpc_aligned16(p->gw_f32), HPC_ERR_BAD_ALIGNMENT,
+              "umma wgrad: pointers must be 16B aligned");
+  return HPC_OK;
+}
+
+size_t hpc_igemm_wgrad_umma_workspace_bytes(const hpc_igemm_wgrad_params* p) {
+  WgKParams kp;
+  if (wgrad_check(p) || wgrad_plan(p, &kp)) return 0;
+  return (size_t)kp.nsplits * kp.ntaps * p->R * p->Cc * sizeof(float);
+}
+
 int hpc_igemm_wgrad_umma(const hpc_igemm_wgrad_params* p, hpc_stream_t stream) {
-  hpc_igemm_wgrad_params q = *p;
-  q.engine = HPC_ENGINE_SIMT;
-  return hpc_igemm_wgrad(&q, stream);
+  int rc = wgrad_check(p);
+  if (rc) return rc;
+  WgKParams local;
+  rc = wgrad_plan(p, &local);
+  if (rc) return rc;
+  const size_t need = (size_t)local.nsplits * local.ntaps * p->R * p->Cc * sizeof(float);
+  HPC_REQUIRE(p->workspace && p->workspace_bytes >= need, HPC_ERR_BAD_SHAPE,
+              "umma wgrad: workspace too small (%zu < %zu)", p->workspace_bytes, need);
+  HPC_REQUIRE(hpc_aligned16(p->workspace), HPC_ERR_BAD_ALIGNMENT, "umma wgrad: workspace must be 16B aligned");
+  local.ws = (float*)p->workspace;
+  CUtensorMap tmLo, tmHi;
+  {
+    uint64_t dims[4] = {(uint64_t)p->R, (uint64_t)p->GW, (uint64_t)p->GH, (uint64_t)p->N};
+    uint64_t strides[3] = {(uint64_t)p->R * 2, (uint64_t)p->GW * p->R * 2, (uint64_t)p->GH * p->GW * p->R * 2};
+    uint32_t box[4] = {64, (uint32_t)local.tw, (uint32_t)local.th, (uint32_t)local.nb};
+    uint32_t estr[4] = {1, 1, 1, 1};
+    rc = make_tmap(&tmLo, p->lo, 4, dims, strides, box, estr);
+    if (rc) return rc;
+  }
+  {
+    uint64_t dims[4] = {(uint64_t)p->Cc, (uint64_t)p->HW, (uint64_t)p->HH, (uint64_t)p->N};
+    uint64_t strides[3] = {(uint64_t)p->Cc * 2, (uint64_t)p->HW * p->Cc * 2, (uint64_t)p->HH * p->HW * p->Cc * 2};
+    uint32_t box[4] = {64, (uint32_t)(local.tw * p->hs), (uint32_t)(local.th * p->hs), (uint32_t)local.nb};
+    uint32_t estr[4] = {1, (uint32_t)p->hs, (uint32_t)p->hs, 1};
+    rc = make_tmap(&tmHi, p->hi, 4, dims, strides, box, estr);
+    if (rc) return rc;
+  }
+  const int smem_bytes = WG_STAGES * (4 + local.cchunks) * WG_ATOM_BYTES + 1024 + 256;
+  static bool attr_set = false;
+  if (!attr_set) {
+    HPC_CUDA(cudaFuncSetAttribute(igemm_wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  WG_STAGES * 8 * WG_ATOM_BYTES + 1024 + 256));
+    attr_set = true;
+  }
+  auto st = (cudaStream_t)stream;
+  igemm_wgrad_umma_kernel<<<local.nunits * local.nsplits, WG_THREADS, smem_bytes, st>>>(tmLo, tmHi, local);
+  HPC_LAUNCH_CHECK();
+  const int64_t n = (int64_t)local.ntaps * p->R * p->Cc;
+  int grid = (int)((n / 4 + 255) / 256);
+  if (grid > 148 * 8) grid = 148 * 8;
+  wgrad_reduce_kernel<<<grid, 256, 0, st>>>(local.ws, local.nsplits, n, p->scale, p->gw_f32);
+  HPC_LAUNCH_CHECK();
+  return HPC_OK;
 }

@@ -42,6 +42,8 @@ typedef void* hpc_stream_t; /* cudaStream_t */
 
 int hpc_version(void);
 const char* hpc_last_error(void);
+/* number of kernels this library has launched so far in this process (monotonic) */
+unsigned long long hpc_launch_count(void);
 /* 1 when the current device is compute capability 10.x (tcgen05/TMEM/TMA kernels usable) */
 int hpc_device_is_sm100(void);
 

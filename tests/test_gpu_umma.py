@@ -95,3 +95,17 @@ def test_rejects_unsupported_shapes_loudly():
     with pkg.compute_mode("bf16"):
         with pytest.raises(_lib.HpcError, match="multiple of 64"):
             hp.ConvSpec(False, 48, 48, 3, 1).forward(x, w, None)
+
+
+@pytest.mark.parametrize("transposed,k,s", [(False, 5, 2), (True, 5, 2), (False, 3, 1), (True, 3, 1)])
+@pytest.mark.parametrize("N,H,W,C", [(2, 16, 16, 192), (3, 8, 8, 192), (5, 4, 4, 192), (1, 16, 24, 192),
+                                     (2, 8, 12, 64), (1, 6, 10, 128)])
+def test_wgrad(transposed, k, s, N, H, W, C):
+    torch.manual_seed(3)
+    spec = hp.ConvSpec(transposed, C, C, k, s)
+    OH, OW = spec.out_hw(H, W)
+    x = torch.randn(N, H, W, C, device=DEV).to(torch.bfloat16)
+    g = torch.randn(N, OH, OW, C, device=DEV).to(torch.bfloat16)
+    w = torch.empty(C, C, k, k, device=DEV)
+    out, ref = _both(lambda: {"f32": spec.wgrad(x, g, w)})
+    _cmp(out, ref, tol=1e-3)
