@@ -10,6 +10,7 @@ them as (N,C,H,W)-shaped views (torch channels_last), see `as_nchw` / `to_nhwc`.
 """
 import ctypes
 import math
+import weakref
 from ctypes import byref, c_double, c_float, c_int
 
 import torch
@@ -170,11 +171,13 @@ _pack_cache = {}
 def pack_weight(w, taps, rows, cols, stride_r, stride_c, dtype, cache=True):
     """Packed (ntaps, rows, cols) copy of a reference-layout weight in `dtype` (hpc_pack_weight).
     Cached on (storage, version) so evaluation loops do not repack unchanged weights."""
-    key = (w.data_ptr(), w._version, rows, cols, stride_r, stride_c, dtype, tuple(t[2] for t in taps))
+    key = (id(w), rows, cols, stride_r, stride_c, dtype, tuple(t[2] for t in taps))
     if cache:
         hit = _pack_cache.get(key)
-        if hit is not None:
-            return hit
+        # valid only for the very same live tensor object at the same version and storage: ids and
+        # device addresses are both recycled after a model is freed
+        if hit is not None and hit[0]() is w and hit[1] == w._version and hit[2] == w.data_ptr():
+            return hit[3]
     out = torch.empty((len(taps), rows, cols), dtype=dtype, device=w.device)
     src = (c_int * len(taps))(*[t[2] for t in taps])
     check(lib().hpc_pack_weight(ptr(w), ptr(out), _lib.dtype_code(out), len(taps), rows, cols, stride_r, stride_c,
@@ -182,7 +185,7 @@ def pack_weight(w, taps, rows, cols, stride_r, stride_c, dtype, cache=True):
     if cache:
         if len(_pack_cache) > 256:
             _pack_cache.clear()
-        _pack_cache[key] = out
+        _pack_cache[key] = (weakref.ref(w), w._version, w.data_ptr(), out)
     return out
 
 

@@ -1,0 +1,80 @@
+"""Product path (bf16 operands on tcgen05, fp32 accumulate) against the fp32 CPU oracle on identical
+inputs, weights and noise.  Tolerances are BASELINE.json's: per-image bpp within 1e-3 relative, PSNR
+within 0.01 dB, rounded symbols bit-exact wherever the pre-rounding values agree; for loss and gradients
+the stated bf16 tolerance is: total loss 2e-3 relative, every parameter gradient cosine >= 0.995 and
+relative L2 <= 8e-2 against the fp32 oracle (bf16 has 8 mantissa bits: 2^-9 = 2e-3 per rounding)."""
+import pytest
+import torch
+
+import image_compression_b200 as pkg
+from image_compression_b200 import utils as U
+from oracle import hyperprior_oracle as O
+from util import cosine, make_pair, perturb, rel_l2
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+@pytest.fixture(autouse=True)
+def _bf16_mode():
+    with pkg.compute_mode("bf16"):
+        yield
+
+
+@pytest.mark.parametrize("recipe,hw,N", [("psnr_256", (128, 128), 2), ("ssim_64", (192, 192), 1),
+                                          ("psnr_8192", (256, 256), 1)])
+def test_train_step_bf16(recipe, hw, N):
+    model, params, ocfg = make_pair(recipe, 192)
+    params = perturb(params)
+    model.load_state_dict(params)
+    model.train()
+    torch.manual_seed(21)
+    x = torch.rand(N, 3, *hw)
+    nz = torch.rand(N, 192, hw[0] // 64, hw[1] // 64)
+    ny = torch.rand(N, 192, hw[0] // 16, hw[1] // 16)
+    xt, losses = model(x.to(DEV), nz.to(DEV), ny.to(DEV))
+    pl = O.leaf_params(params)
+    xto, lo = O.compressor2018_forward(pl, x, ocfg, True, nz, ny)
+    rep = {k: (float(losses[k]), float(lo[k])) for k in lo}
+    print(rep)
+    assert abs(rep["bpp"][0] - rep["bpp"][1]) <= 1e-3 * rep["bpp"][1], rep
+    assert abs(rep["total_loss"][0] - rep["total_loss"][1]) <= 2e-3 * abs(rep["total_loss"][1]), rep
+    p1 = U.psnr(xt * 255, x.to(DEV) * 255).cpu()
+    p0 = O.psnr(xto * 255, x * 255)
+    assert float((p1 - p0).abs().max()) <= 0.01, (p1, p0)
+    losses["total_loss"].backward()
+    lo["total_loss"].backward()
+    worst_c, worst_r = 1.0, 0.0
+    for k, p in model.named_parameters():
+        c, r = cosine(p.grad, pl[k].grad), rel_l2(p.grad, pl[k].grad)
+        worst_c, worst_r = min(worst_c, c), max(worst_r, r)
+        assert c >= 0.995 and r <= 8e-2, (k, c, r)
+    print("worst cosine", worst_c, "worst rel-L2", worst_r)
+
+
+def test_eval_bf16_bpp_psnr_symbols():
+    model, params, ocfg = make_pair("psnr_256", 192)
+    model.eval()
+    torch.manual_seed(22)
+    x = torch.rand(2, 3, 192, 256)
+    with torch.no_grad():
+        xt, losses = model(x.to(DEV))
+        xto, lo, inter = O.compressor2018_forward(params, x, ocfg, False, return_intermediates=True)
+        assert abs(float(losses["bpp"]) - float(lo["bpp"])) <= 1e-3 * float(lo["bpp"])
+        p1 = U.psnr(xt * 255, x.to(DEV) * 255).cpu()
+        p0 = O.psnr(xto * 255, x * 255)
+        assert float((p1 - p0).abs().max()) <= 0.01, (p1, p0)
+        m1 = U.MS_SSIM(device=DEV)(xt * 255, x.to(DEV) * 255).cpu()
+        m0 = O.ms_ssim_metric(xto * 255, x * 255)
+        assert float((m1 - m0).abs().max()) <= 0.02, (m1, m0)
+        # symbols: y from the bf16 analysis transform, rounded by K5, against the oracle's
+        y = model.analysis_transform(x.to(DEV))
+        yt, _ = model.conditional_model(y, inter["sigma"].to(DEV))
+        mism = yt.cpu() != inter["y_tilde"]
+        rate = float(mism.float().mean())
+        # a mismatch is only allowed where the two pre-rounding values straddle a .5 boundary
+        d = (y.cpu() - inter["y"]).abs()
+        frac = (inter["y"] - inter["y"].floor() - 0.5).abs()
+        assert bool((frac[mism] <= d[mism] + 1e-6).all())
+        print("symbol mismatch rate", rate, "max |dy|", float(d.max()))
+        assert rate < 0.02
