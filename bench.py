@@ -1,0 +1,426 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the scale-hyperprior hot path on B200.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload train|train_ssim|eval]
+
+Own arm (default): one "step" = one pass of the hot path over one batch of synthetic input:
+  train       psnr_256 training step = Compressor2018 forward (noise quantisation) + RD loss + backward
+              (+ gradient all-reduce when N>1), 64 crops of 256x256 per GPU, bf16 operands / fp32 accumulate
+              (BASELINE.json configs[1], the configuration the metric is quoted on)
+  train_ssim  the same with the ssim_64 recipe (MS_SSIMLoss, log scale)  (configs[3])
+  eval        forward in rounding mode + bpp / PSNR / MS-SSIM(dB) on 768x512 images, sharded per image (configs[4])
+`value` is whole-job throughput with inputs resident in HBM; `e2e` is the same metric through the public
+module API with HOST (pinned) inputs copied in every step and the loss read back every step.
+
+Reference arm (--impl reference): the reference's CPU implementation of the same step, timed on this box's
+host cores with all threads.  The reference is pure Python/torch and is not present on the GPU box, so the
+arm runs the oracle port (oracle/hyperprior_oracle.py, pinned bit-exactly to the reference modules by
+tests/golden/make_golden.py) -- kind "port".
+
+One JSON line on stdout (rank 0).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = {"train": "train crops/s (256x256, fwd+bwd)", "train_ssim": "train crops/s (256x256, fwd+bwd)",
+          "eval": "768x512 eval images/s"}
+UNIT = {"train": "crops/s", "train_ssim": "crops/s", "eval": "images/s"}
+RECIPE = {"train": "psnr_256", "train_ssim": "ssim_64", "eval": "psnr_256"}
+L2_BYTES = 126 * 1024 * 1024
+
+# algorithmic GEMM flops per 256x256 crop: forward 24.567 GFLOP, train step 73.23 GFLOP
+TRAIN_GFLOP_PER_CROP = 73.23
+EVAL_GFLOP_PER_IMAGE = 147.40
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="train", choices=list(METRIC))
+    ap.add_argument("--batch", type=int, default=None, help="crops (images) per GPU per step")
+    ap.add_argument("--size", type=int, nargs=2, default=None, metavar=("H", "W"))
+    ap.add_argument("--mode", default="bf16", choices=["bf16", "fp32", "bf16_simt"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-sample", type=int, default=8, help="crops per CPU-baseline step")
+    return ap.parse_args()
+
+
+def workload_shape(args):
+    if args.workload == "eval":
+        return (args.batch or 3), tuple(args.size or (512, 768))
+    return (args.batch or 64), tuple(args.size or (256, 256))
+
+
+# ------------------------------------------------------------------------------------------
+# clocks: sampled DURING the timed region (B200_PROFILING.md "clocks line")
+# ------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0, period=0.1):
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._th = None
+        self._nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nvml = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        except Exception:
+            self._nvml = None
+
+    def _sample_nvml(self):
+        n = self._nvml
+        self.samples.append(float(n.nvmlDeviceGetClockInfo(self._h, n.NVML_CLOCK_SM)))
+        if self.max_mhz is None:
+            self.max_mhz = float(n.nvmlDeviceGetMaxClockInfo(self._h, n.NVML_CLOCK_SM))
+        r = n.nvmlDeviceGetCurrentClocksEventReasons(self._h) if hasattr(
+            n, "nvmlDeviceGetCurrentClocksEventReasons") else n.nvmlDeviceGetCurrentClocksThrottleReasons(self._h)
+        for name, bit in (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20),
+                          ("sw_power_cap", 0x4)):
+            if r & bit:
+                self.reasons.add(name)
+
+    def _sample_smi(self):
+        out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
+                              str(self.index)], capture_output=True, text=True, timeout=10).stdout.strip()
+        f = [v.strip() for v in out.split(",")]
+        self.samples.append(float(f[0]))
+        self.max_mhz = float(f[1])
+        for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[2:6]):
+            if v.lower().startswith("active"):
+                self.reasons.add(name)
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                self._sample_nvml() if self._nvml else self._sample_smi()
+            except Exception:
+                pass
+            self._stop.wait(self.period)
+
+    def __enter__(self):
+        self._th = threading.Thread(target=self._run, daemon=True)
+        self._th.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._th.join(timeout=15)
+
+    def summary(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"],
+                "bf16_tflops_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "source": "measured"}
+    # B200_PROFILING.md fallback
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1590.0, "source": "fallback"}
+
+
+def ncu_traffic(kernel_key):
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture
+    (profiles/traffic.json, written by scripts/ncu_summarise.py), or None."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(p):
+        return None
+    try:
+        with open(p) as f:
+            return json.load(f).get(kernel_key)
+    except Exception:
+        return None
+
+
+# ------------------------------------------------------------------------------------------
+# CPU legs: the reference's own arithmetic on the host cores (oracle port; checker/baseline only)
+# ------------------------------------------------------------------------------------------
+def cpu_step_fn(workload, n, hw):
+    """Returns (step callable, units per step).  train*: forward + RD loss + backward of `n` crops in fp32
+    (what engine/trainer.py:179-188 times); eval: forward in rounding mode + psnr + MS-SSIM of `n` images."""
+    import torch
+    from oracle import hyperprior_oracle as O
+    torch.manual_seed(0)
+    if workload == "train_ssim":
+        cfg = O.default_cfg(lmbda=64.0, loss_names=("MS_SSIMLoss",), log_scale=True)
+    else:
+        cfg = O.default_cfg(lmbda=256.0)
+    params = O.leaf_params(O.init_params(cfg, seed=0))
+    H, W = hw
+    x = torch.rand(n, 3, H, W)
+
+    def train_step():
+        for p in params.values():
+            p.grad = None
+        _, losses = O.compressor2018_forward(params, x, cfg, True)
+        losses["total_loss"].backward()
+        return float(losses["total_loss"].detach())
+
+    def eval_step():
+        with torch.no_grad():
+            xt, losses = O.compressor2018_forward(params, x, cfg, False)
+            ps = O.psnr(xt * 255, x * 255)
+            ms = O.ms_ssim_metric(xt * 255, x * 255)
+        return float(losses["bpp"]) + float(ps.sum()) + float(ms.sum())
+
+    return (eval_step if workload == "eval" else train_step), n
+
+
+def time_cpu(workload, n, hw, steps, warmup):
+    import torch
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    fn, units = cpu_step_fn(workload, n, hw)
+    for _ in range(warmup):
+        fn()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        fn()
+    dt = time.perf_counter() - t0
+    return {"value": units * steps / dt, "ms_per_step": 1e3 * dt / steps, "cores": torch.get_num_threads(),
+            "units": units}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path (oracle port) on this box's host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return  # rank 0 alone runs it
+    _, hw = workload_shape(args)
+    n = args.cpu_sample if args.workload != "eval" else 1
+    steps, warmup = args.steps, max(1, min(args.warmup, 2))
+    # bound the run: a step of 8 crops costs seconds on a host; cap the timed steps to keep it within minutes
+    probe = time_cpu(args.workload, n, hw, 1, 1)
+    budget_s = 120.0
+    max_steps = max(1, int(budget_s / max(probe["ms_per_step"] / 1e3, 1e-3)))
+    steps_run = min(steps, max_steps)
+    r = time_cpu(args.workload, n, hw, steps_run, warmup)
+    sample = (f"{steps_run} step(s) of {n} x {hw[0]}x{hw[1]} synthetic "
+              f"{'crops fwd+loss+bwd' if args.workload != 'eval' else 'image fwd+metrics'} in fp32, torch-CPU, "
+              f"{r['cores']} threads, after {warmup} warm-up")
+    line = {
+        "impl": "reference", "metric": METRIC[args.workload], "value": r["value"], "unit": UNIT[args.workload],
+        "n_gpus": args.gpus, "steps": steps_run, "warmup": warmup, "ms_per_step": r["ms_per_step"],
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": config_dict(args, per_gpu=workload_shape(args)[0],
+                              note=f"CPU reference arm: each step is a bounded sample of {n} unit(s) of this workload"),
+        "cpu_baseline": {"value": r["value"], "unit": UNIT[args.workload], "cores": r["cores"], "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": r["value"], "unit": UNIT[args.workload], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def config_dict(args, per_gpu, note=None):
+    _, hw = workload_shape(args)
+    names = {"train": "psnr_256 training step (fwd+bwd, noise quantisation), 256x256 synthetic crops",
+             "train_ssim": "ssim_64 MS-SSIM-distortion training step (fwd+bwd), 256x256 synthetic crops",
+             "eval": "eval sweep: 768x512 Kodak-shaped synthetic images, rounding quantisation, bpp/PSNR/MS-SSIM"}
+    d = {"workload": names[args.workload], "recipe": RECIPE[args.workload], "per_gpu_batch": per_gpu,
+         "global_batch": per_gpu * args.gpus, "height": hw[0], "width": hw[1], "channels": 192,
+         "parallelism": f"dp{args.gpus}" if args.workload != "eval" else f"per-image x{args.gpus}"}
+    if note:
+        d["note"] = note
+    return d
+
+
+# ------------------------------------------------------------------------------------------
+# own arm
+# ------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import image_compression_b200 as pkg
+    from image_compression_b200 import _lib, sharding
+    from image_compression_b200.utils.metric import image_metrics
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the hot path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.lib()  # fail loudly here if the extension is missing
+    pkg.set_compute_mode(args.mode)
+
+    B, (H, W) = workload_shape(args)
+    training = args.workload != "eval"
+    torch.manual_seed(0)                       # identical random-init weights on every rank
+    model = pkg.build_model(pkg.get_recipe_cfg(RECIPE[args.workload])).to(dev)
+    model.train(training)
+    sharding.broadcast_parameters(model)
+    torch.manual_seed(1000 + rank)             # per-rank inputs and in-kernel Philox noise streams
+    n_rot = max(2, -(-int(1.6 * L2_BYTES) // (B * 3 * H * W * 4)))   # resident input batches: > L2 in total
+    host = [torch.rand(B, 3, H, W).pin_memory() for _ in range(n_rot)]
+    resident = [h.to(dev) for h in host]
+    fg = sharding.FlatGradients(model.parameters(), dev) if training else None
+    stage = torch.empty(B, 3, H, W, device=dev)
+    loss_host = torch.empty(1 + 2 * B, dtype=torch.float32).pin_memory()
+
+    def step(x):
+        if training:
+            fg.zero()
+            _, losses = model(x)
+            losses["total_loss"].backward()
+            fg.all_reduce_mean()
+            return losses["total_loss"]
+        with torch.no_grad():
+            xt, losses = model(x)
+            ps, ms = image_metrics(xt, x)
+        return losses["bpp"], ps, ms
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        """EXACTLY `steps` calls bracketed by barrier+synchronize; device time, max over ranks."""
+        sync_all()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            fn(i)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        sync_all()
+        return float(ms)
+
+    # ---- resident-input throughput (`value`) ------------------------------------------------
+    for i in range(args.warmup):
+        step(resident[i % n_rot])
+    with ClockSampler(local) as clocks:
+        n0 = _lib.lib().hpc_launch_count()
+        _lib.prof_enable(True)
+        ms_total = timed(lambda i: step(resident[i % n_rot]), args.steps)
+        _lib.prof_enable(False)
+        launches = _lib.lib().hpc_launch_count() - n0
+    prof = {name: _lib.prof_read(c) for c, name in enumerate(_lib.PROF_NAMES)}
+    units = B * world * args.steps
+    value = units / (ms_total / 1e3)
+
+    # ---- end to end through the module API with host inputs (`e2e`) --------------------------
+    def e2e_step(i):
+        stage.copy_(host[i % n_rot], non_blocking=True)          # H2D of this step's inputs (pinned)
+        out = step(stage)
+        if training:
+            loss_host[:1].copy_(out.detach().reshape(1), non_blocking=False)   # D2H read of the loss
+        else:
+            bpp, ps, ms = out
+            loss_host[:1].copy_(bpp.reshape(1), non_blocking=True)      # D2H read of bpp + per-image metrics
+            loss_host[1:1 + B].copy_(ps, non_blocking=True)
+            loss_host[1 + B:1 + 2 * B].copy_(ms, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+    for i in range(max(2, args.warmup // 2)):
+        e2e_step(i)
+    e2e_ms = timed(e2e_step, args.steps)
+    e2e_value = units / (e2e_ms / 1e3)
+    h2d = B * 3 * H * W * 4
+    d2h = 4 if training else 4 * (1 + 2 * B)
+    return dict(rank=rank, world=world, B=B, H=H, W=W, ms_total=ms_total, value=value, launches=launches, prof=prof,
+                clocks=clocks.summary(), e2e_value=e2e_value, e2e_ms=e2e_ms, h2d=h2d, d2h=d2h, n_rot=n_rot,
+                grad_bytes=fg.nbytes() if fg else 0)
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return run_reference(args)
+    r = run_ours(args)
+    if r["rank"] != 0:
+        return
+    peaks = measured_peaks()
+    wl = args.workload
+    B, H, W, world = r["B"], r["H"], r["W"], r["world"]
+    ms_per_step = r["ms_total"] / args.steps
+    # dominant kernel: the tcgen05 implicit-GEMM forward kernel (conv / deconv phases / dgrads / GDN contractions)
+    ms, n, flops = r["prof"]["igemm_fwd_umma"]
+    roofline = None
+    if n:
+        ach = flops / (ms * 1e-3) / 1e12
+        peak = peaks["bf16_tflops_sustained"]   # kernel timed inside a long step -> sustained figure
+        roofline = {"bound": "tensor", "kernel": "igemm_fwd_umma_kernel", "achieved": ach, "peak": peak,
+                    "unit": "TFLOP/s", "frac": ach / peak, "traffic": ncu_traffic("igemm_fwd_umma_kernel"),
+                    "peak_source": f"{peaks['source']} (bf16 sustained)", "launches": n,
+                    "avg_launch_ms": ms / n, "share_of_step": ms / r["ms_total"],
+                    "algorithmic_flops_per_launch": flops / n}
+    kernels = {}
+    for name, (kms, kn, work) in r["prof"].items():
+        if not kn:
+            continue
+        gemm = name.startswith("igemm")
+        rate = work / (kms * 1e-3) / (1e12 if gemm else 1e9)
+        pk = peaks["bf16_tflops_sustained"] if gemm else peaks["hbm_gbs"]
+        kernels[name] = {"ms_per_step": kms / args.steps, "launches_per_step": kn / args.steps,
+                         "achieved": rate, "unit": "TFLOP/s" if gemm else "GB/s", "frac": rate / pk,
+                         "share_of_step": kms / r["ms_total"]}
+    gflop_unit = TRAIN_GFLOP_PER_CROP if wl != "eval" else EVAL_GFLOP_PER_IMAGE
+    if (H, W) != ((256, 256) if wl != "eval" else (512, 768)):
+        gflop_unit *= (H * W) / ((256 * 256) if wl != "eval" else (512 * 768))
+    step_tflops = r["value"] / world * gflop_unit / 1e3
+    line = {
+        "metric": METRIC[wl], "value": r["value"], "unit": UNIT[wl], "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": {"bf16": "bf16", "fp32": "f32", "bf16_simt": "bf16"}[args.mode],
+        "data": "synthetic (torch.rand images, random-init weights of the reference architecture)",
+        "config": dict(config_dict(args, per_gpu=B),
+                       l2="inputs rotate over %d resident batches (%.0f MB > 126 MB L2); one step streams >1 GB of "
+                          "activations" % (r["n_rot"], r["n_rot"] * r["h2d"] / 1e6),
+                       timing="CUDA events on the launching stream, max over ranks",
+                       optimizer="excluded (SURVEY 8d); gradient all-reduce included for N>1"),
+        "clocks": r["clocks"],
+        "e2e": {"value": r["e2e_value"], "unit": UNIT[wl], "h2d_bytes_per_step": r["h2d"],
+                "d2h_bytes_per_step": r["d2h"], "ms_per_step": r["e2e_ms"] / args.steps},
+        "gpu_launches": int(r["launches"]),
+        "roofline": roofline,
+        "kernels": kernels,
+        "step_gemm_tflops_per_gpu": step_tflops,
+        "step_frac_of_tensor_peak": step_tflops / peaks["bf16_tflops_sustained"],
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        n = args.cpu_sample if wl != "eval" else 1
+        probe = time_cpu(wl, n, (H, W), 1, 1)
+        steps = max(1, min(5, int(20.0 / max(probe["ms_per_step"] / 1e3, 1e-3))))
+        c = time_cpu(wl, n, (H, W), steps, 0)
+        line["cpu_baseline"] = {
+            "value": c["value"], "unit": UNIT[wl], "cores": c["cores"], "kind": "port",
+            "sample": f"{steps} step(s) of {n} x {H}x{W} synthetic "
+                      f"{'crops, fwd+loss+bwd' if wl != 'eval' else 'image, fwd+metrics'}, fp32 torch-CPU oracle port of "
+                      f"the reference modules, {c['cores']} threads, after 2 warm-up steps"}
+    print(json.dumps(line), flush=True)
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized():
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

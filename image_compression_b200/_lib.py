@@ -28,6 +28,8 @@ MAX_TAPS, MAX_PHASES = 25, 4
 (EPI_LINEAR, EPI_RELU, EPI_EXP_CLAMP, EPI_GDN, EPI_IGDN, EPI_GDN_BWD, EPI_IGDN_BWD, EPI_RELU_MASK,
  EPI_SIGN_ADD) = range(9)
 DIST_LAPLACE, DIST_GAUSS = 0, 1
+(PROF_IGEMM_FWD, PROF_IGEMM_WGRAD, PROF_CONDITIONAL, PROF_FACTORIZED, PROF_THIN, PROF_DISTORTION) = range(6)
+PROF_NAMES = ("igemm_fwd_umma", "igemm_wgrad_umma", "conditional", "factorized", "thin_c3", "distortion")
 MSSSIM_LOSS_LOG, MSSSIM_LOSS_PLAIN, MSSSIM_METRIC, SSIM_LOSS, SSIM_METRIC = range(5)
 
 
@@ -116,6 +118,8 @@ _SIGNATURES = {
     "hpc_last_error": (c_char_p, []),
     "hpc_device_is_sm100": (c_int, []),
     "hpc_launch_count": (ctypes.c_ulonglong, []),
+    "hpc_prof_enable": (c_int, [c_int]),
+    "hpc_prof_read": (c_int, [c_int, POINTER(c_double), POINTER(ctypes.c_ulonglong), POINTER(c_double)]),
     "hpc_bound_fwd": (c_int, [c_void_p, c_void_p, c_int64, c_float, c_int, c_void_p]),
     "hpc_bound_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_float, c_int, c_void_p]),
     "hpc_nonneg_fwd": (c_int, [c_void_p, c_void_p, c_int64, c_float, c_float, c_void_p]),
@@ -211,6 +215,17 @@ def check(rc):
     if rc != 0:
         msg = lib().hpc_last_error()
         raise HpcError(f"hpcodec error {rc}: {msg.decode() if msg else '?'}")
+
+
+def prof_enable(on):
+    check(lib().hpc_prof_enable(int(on)))
+
+
+def prof_read(cls):
+    """(ms_total, launches, work_total) of one kernel class since prof_enable(True)."""
+    ms, n, w = c_double(), ctypes.c_ulonglong(), c_double()
+    check(lib().hpc_prof_read(cls, byref(ms), byref(n), byref(w)))
+    return ms.value, n.value, w.value
 
 
 def ptr(t):

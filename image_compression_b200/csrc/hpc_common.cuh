@@ -43,6 +43,22 @@ extern unsigned long long g_hpc_launches;  // kernels launched by this library (
                __FILE__, __LINE__);                                                    \
   } while (0)
 
+// kernel-class timing (hpc_prof_* in hpcodec.h).  Usage inside an export:
+//   HpcProfScope prof(HPC_PROF_IGEMM_FWD, flops, stream);  ... launches ...   (the destructor records the end event)
+extern int g_hpc_prof_on;
+int hpc_prof_begin_(int cls, double work, cudaStream_t st);
+void hpc_prof_end_(int slot, cudaStream_t st);
+struct HpcProfScope {
+  int slot;
+  cudaStream_t st;
+  HpcProfScope(int cls, double work, void* stream) : slot(-1), st((cudaStream_t)stream) {
+    if (g_hpc_prof_on) slot = hpc_prof_begin_(cls, work, st);
+  }
+  ~HpcProfScope() {
+    if (slot >= 0) hpc_prof_end_(slot, st);
+  }
+};
+
 static inline bool hpc_aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 // number of SMs of the current device (cached per thread)

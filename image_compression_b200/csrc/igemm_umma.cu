@@ -324,6 +324,12 @@ static int launch_fwd(const CUtensorMap& tmA, const CUtensorMap& tmB, const FwdK
   return HPC_OK;
 }
 
+static int ntaps_total_all(const hpc_igemm_fwd_params* p) {
+  int n = 0;
+  for (int i = 0; i < p->nphases; ++i) n += p->phase[i].ntaps;
+  return n;
+}
+
 int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
   HPC_REQUIRE(p->dtype == HPC_BF16, HPC_ERR_UNSUPPORTED, "umma engine: operands must be bf16");
   HPC_REQUIRE(p->Ci % FW_BK == 0, HPC_ERR_UNSUPPORTED, "umma engine: Ci=%d must be a multiple of 64", p->Ci);
@@ -377,6 +383,10 @@ int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
     if (rc) return rc;
   }
   auto st = (cudaStream_t)stream;
+  // algorithmic flops: every grid pixel sees every tap of its phase once (zero taps of the
+  // stride-2 transposed conv are never counted because the phases only hold the live taps)
+  HpcProfScope prof(HPC_PROF_IGEMM_FWD,
+                    2.0 * p->N * p->GH * p->GW * (double)ntaps_total_all(p) * p->Ci * p->Co, stream);
   switch (p->Co) {
     case 64: return launch_fwd<64>(tmA, tmB, kp, st);
     case 128: return launch_fwd<128>(tmA, tmB, kp, st);
@@ -625,6 +635,7 @@ int hpc_igemm_wgrad_umma(const hpc_igemm_wgrad_params* p, hpc_stream_t stream) {
     attr_set = true;
   }
   auto st = (cudaStream_t)stream;
+  HpcProfScope prof(HPC_PROF_IGEMM_WGRAD, 2.0 * p->N * p->GH * p->GW * (double)local.ntaps * p->R * p->Cc, stream);
   igemm_wgrad_umma_kernel<<<local.nunits * local.nsplits, WG_THREADS, smem_bytes, st>>>(tmLo, tmHi, local);
   HPC_LAUNCH_CHECK();
   const int64_t n = (int64_t)local.ntaps * p->R * p->Cc;

@@ -93,6 +93,7 @@ int hpc_clamp01_sse_fwd(const float* x, const float* raw, float* xt, int N, int6
   if (bpi < 1) bpi = 1;
   unsigned int* counters = (unsigned int*)scratch;
   float* partials = (float*)((char*)scratch + 4096);
+  HpcProfScope prof(HPC_PROF_DISTORTION, (double)N * per_image * (8 + (xt ? 4 : 0)), stream);
   clamp01_sse_kernel<<<dim3(bpi, N), 256, 0, (cudaStream_t)stream>>>(x, raw, xt, per_image, scale, do_clamp,
                                                                    sse_per_image, counters, partials);
   HPC_LAUNCH_CHECK();
@@ -119,6 +120,7 @@ __global__ void clamp01_bwd_kernel(const float* __restrict__ raw, const float* _
 int hpc_clamp01_bwd(const float* raw, const float* x, const float* g_xt, int64_t n, float mse_coef,
                     const float* mse_coef_dev, int do_clamp, float* g_raw, hpc_stream_t stream) {
   if (n <= 0) return HPC_OK;
+  HpcProfScope prof(HPC_PROF_DISTORTION, (double)n * (8 + (x ? 4 : 0) + (g_xt ? 4 : 0)), stream);
   clamp01_bwd_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(raw, x, g_xt, n, mse_coef, mse_coef_dev,
                                                                        do_clamp, g_raw);
   HPC_LAUNCH_CHECK();

@@ -66,6 +66,8 @@ conv_c3_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, int
   }
 }
 
+static thread_local double g_thin_work = 0.0;
+
 int hpc_conv_c3_fwd(const float* x_nchw, const float* w, int64_t w_sr, int64_t w_sc, const float* bias, int N,
                     int Cs, int H, int W, int Cw, float* out_f32, void* out_lp, void* out_sq_lp, int lp_dtype,
                     hpc_stream_t stream) {
@@ -80,6 +82,12 @@ int hpc_conv_c3_fwd(const float* x_nchw, const float* w, int64_t w_sr, int64_t w
   int gx = (int)(ntiles < 148 * 6 ? ntiles : 148 * 6);
   dim3 grid(gx, gy);
   auto st = (cudaStream_t)stream;
+  {
+    const int lpb = lp_dtype == HPC_BF16 ? 2 : 4;
+    const double opix = (double)N * (H / 2) * (W / 2) * Cw;
+    g_thin_work = (double)N * Cs * H * W * 4 + opix * ((out_f32 ? 4 : 0) + (out_lp ? lpb : 0) + (out_sq_lp ? lpb : 0));
+  }
+  HpcProfScope prof(HPC_PROF_THIN, g_thin_work, stream);
 #define LAUNCH(T, CS_)                                                                                            \
   conv_c3_fwd_kernel<T, CS_><<<grid, threads, 0, st>>>(x_nchw, w, w_sr, w_sc, bias, N, H, W, Cw, out_f32,         \
                                                         (T*)out_lp, (T*)out_sq_lp)
@@ -179,6 +187,8 @@ int hpc_deconv_c3_fwd(const void* x_nhwc, int lp_dtype, const float* w, int64_t 
   const int64_t npix = (int64_t)N * H * W;
   int grid = (int)((npix + 7) / 8 < 148 * 4 ? (npix + 7) / 8 : 148 * 4);
   auto st = (cudaStream_t)stream;
+  HpcProfScope prof(HPC_PROF_THIN,
+                    (double)npix * Cw * (lp_dtype == HPC_BF16 ? 2 : 4) + (double)npix * 4 * Cs * 4, stream);
 #define LAUNCH(T, CS_)                                                                                             \
   do {                                                                                                             \
     HPC_CUDA(cudaFuncSetAttribute(deconv_c3_fwd_kernel<T, CS_>, cudaFuncAttributeMaxDynamicSharedMemorySize,       \
@@ -283,6 +293,8 @@ int hpc_wgrad_c3(const void* wide_nhwc, int lp_dtype, const float* thin_nchw, in
   int nblocks = wgrad_c3_blocks(N, H, W);
   dim3 grid(nblocks, gy);
   auto st = (cudaStream_t)stream;
+  HpcProfScope prof(HPC_PROF_THIN,
+                    (double)N * H * W * Cw * (lp_dtype == HPC_BF16 ? 2 : 4) + (double)N * Cs * 4 * H * W * 4, stream);
 #define LAUNCH(T, CS_) \
   wgrad_c3_stage1<T, CS_><<<grid, threads, 0, st>>>((const T*)wide_nhwc, thin_nchw, N, Cw, H, W, (float*)scratch)
 #define LAUNCH_T(CS_) do { if (lp_dtype == HPC_BF16) LAUNCH(__nv_bfloat16, CS_); else LAUNCH(float, CS_); } while (0)

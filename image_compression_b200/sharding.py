@@ -1,0 +1,93 @@
+"""Batch-sharded training and per-image-sharded evaluation, one process per GPU.
+
+The reference's only parallelism is a single-process `nn.DataParallel` (engine/trainer.py:256-259):
+replicas see a slice of the batch, each normalises its loss by its LOCAL pixel count
+(bmshl2018.py:70,88) and the trainer averages the replica losses (engine/trainer.py:180), i.e. the
+global gradient is the MEAN of the replica gradients.  Here every rank is such a replica and the mean
+is ONE NCCL all-reduce (SUM, then x 1/world) over a flat fp32 buffer that the `.grad` tensors alias,
+so there is no pack/unpack pass.  Evaluation has no coupling at all: image i goes to rank
+i % world and the per-image metrics are all-gathered at the end.
+
+torch.distributed is plumbing only (NCCL on the GPU box, gloo in the CPU tests).
+"""
+import torch
+import torch.distributed as dist
+
+
+class FlatGradients:
+    """Flat fp32 gradient buffer aliased by every parameter's `.grad` (state_dict order).
+
+    usage per step:   fg.zero();  loss.backward();  fg.all_reduce_mean()
+    """
+
+    def __init__(self, params, device=None):
+        self.params = [p for p in params if p.requires_grad]
+        if not self.params:
+            raise ValueError("FlatGradients: no trainable parameters")
+        device = device or self.params[0].device
+        for p in self.params:
+            if p.dtype != torch.float32:
+                raise TypeError("FlatGradients: parameters must be fp32 (the reference trains in fp32)")
+        # 16-byte aligned slots so vectorised kernels may write the views directly
+        offs, n = [], 0
+        for p in self.params:
+            offs.append(n)
+            n += (p.numel() + 3) // 4 * 4
+        self.flat = torch.zeros(n, dtype=torch.float32, device=device)
+        self.numel = sum(p.numel() for p in self.params)
+        for p, o in zip(self.params, offs):
+            p.grad = self.flat[o:o + p.numel()].view(p.shape)
+
+    def zero(self):
+        self.flat.zero_()
+
+    def all_reduce_mean(self, group=None, async_op=False):
+        """Mean over ranks of the whole gradient (no-op without an initialised process group)."""
+        if not (dist.is_available() and dist.is_initialized()):
+            return None
+        world = dist.get_world_size(group)
+        if world == 1:
+            return None
+        if dist.get_backend(group) == "nccl":
+            return dist.all_reduce(self.flat, op=dist.ReduceOp.AVG, group=group, async_op=async_op)
+        work = dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group, async_op=False)
+        self.flat.mul_(1.0 / world)
+        return work
+
+    def nbytes(self):
+        return self.flat.numel() * 4
+
+
+def shard_indices(n_items, rank, world):
+    """Indices of the evaluation images owned by `rank` (round-robin: i % world == rank)."""
+    if not (0 <= rank < world):
+        raise ValueError(f"rank {rank} not in [0,{world})")
+    return list(range(rank, n_items, world))
+
+
+def gather_per_image(values, n_items, rank, world, group=None):
+    """values: (len(shard_indices(n_items, rank, world)), K) tensor of this rank's per-image metrics.
+    Returns the (n_items, K) table in image order on every rank."""
+    values = values.reshape(len(shard_indices(n_items, rank, world)), -1)
+    K = values.shape[1]
+    if world == 1:
+        return values
+    per = (n_items + world - 1) // world
+    pad = torch.zeros((per, K), dtype=values.dtype, device=values.device)
+    pad[:values.shape[0]] = values
+    bufs = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(bufs, pad, group=group)
+    out = torch.empty((n_items, K), dtype=values.dtype, device=values.device)
+    for r in range(world):
+        idx = shard_indices(n_items, r, world)
+        out[idx] = bufs[r][:len(idx)]
+    return out
+
+
+def broadcast_parameters(module, src=0, group=None):
+    """Make every rank start from rank `src`'s weights (the reference replicates module state the
+    same way each step through DataParallel's Broadcast)."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return
+    for p in module.parameters():
+        dist.broadcast(p.data, src=src, group=group)

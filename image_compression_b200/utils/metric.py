@@ -51,3 +51,19 @@ class MS_SSIM(SSIM):
         with torch.no_grad():
             pyr = self._pyramid(img1, img2, len(self.weights))
             return pyr.combine(_lib.MSSSIM_METRIC, 1 if self.in_dB else 0, 0.0, self.weights)
+
+
+def image_metrics(preds, targets, max_val=255., weights=MS_SSIM_DEFAULT_WEIGHTS):
+    """What engine/monitor.py:113-125 computes per batch -- psnr(preds*255, targets*255) and
+    MS_SSIM()(preds*255, targets*255) in dB -- with the x255 folded into the kernels (no scaled copies).
+    preds/targets: (N,C,H,W) CUDA tensors in [0,1].  Returns (psnr (N,), ms_ssim_dB (N,))."""
+    _lib.require_cuda(preds, targets)
+    with torch.no_grad():
+        a, b = hp.contiguous_f32(preds), hp.contiguous_f32(targets)
+        N = a.shape[0]
+        _, sse = hp.clamp01_sse(a.reshape(N, -1), b.reshape(N, -1), float(max_val), do_clamp=False, want_xt=False)
+        ps = hp.psnr_from_sse(sse, a.numel() // N, max_val)
+        c1, c2 = (0.01 * max_val) ** 2, (0.03 * max_val) ** 2
+        pyr = hp.SsimPyramid(a, b, len(weights), 11, 1.5, c1, c2, float(max_val))
+        ms = pyr.combine(_lib.MSSSIM_METRIC, 1, 0.0, list(weights))
+    return ps, ms

@@ -47,6 +47,21 @@ unsigned long long hpc_launch_count(void);
 /* 1 when the current device is compute capability 10.x (tcgen05/TMEM/TMA kernels usable) */
 int hpc_device_is_sm100(void);
 
+/* Kernel-class timing for bench.py's roofline (no reference counterpart: the reference has no
+ * profiler below cProfile, main.py:76-86).  While enabled, every launch of a kernel of one of the
+ * classes below is bracketed by a cudaEvent pair on ITS OWN stream and tagged with its algorithmic
+ * work (flops for the GEMM classes, bytes for the streaming classes).  hpc_prof_read synchronises on
+ * the recorded events and returns the summed device time, launch count and work of one class. */
+#define HPC_PROF_IGEMM_FWD 0   /* igemm_fwd_umma_kernel: conv / deconv / dgrad / GDN contraction  (flops) */
+#define HPC_PROF_IGEMM_WGRAD 1 /* igemm_wgrad_umma_kernel + its split-K reduce                    (flops) */
+#define HPC_PROF_CONDITIONAL 2 /* conditional likelihood fwd + bwd (K5)                           (bytes) */
+#define HPC_PROF_FACTORIZED 3  /* factorised prior fwd + bwd (K4)                                 (bytes) */
+#define HPC_PROF_THIN 4        /* conv_c3 / deconv_c3 / wgrad_c3 (3-channel head and tail)        (bytes) */
+#define HPC_PROF_DISTORTION 5  /* clamp+SSE fwd/bwd, SSIM levels (K6/K7)                          (bytes) */
+#define HPC_PROF_NCLASSES 6
+int hpc_prof_enable(int on); /* on!=0: clear the records and start; 0: stop recording (records kept) */
+int hpc_prof_read(int cls, double* ms_total, unsigned long long* launches, double* work_total);
+
 /* ------------------------------------------------------------------------------------------
  * Bounds and the GDN non-negative reparameterisation
  * ---------------------------------------------------------------------------------------- */
