@@ -309,7 +309,7 @@ def _std_cdf(t, kind):
     """entropy_model.py:362 (Normal.cdf: torch/distributions/normal.py:104-109) and
     :375 (Laplace.cdf: torch/distributions/laplace.py:92-97), loc=0, scale=1."""
     if kind == "GaussianConditionalModel":
-        return 0.5 * (1 + torch.erf(t * (1.0 / math.sqrt(2))))
+        return 0.5 * (1 + torch.erf(t / math.sqrt(2)))
     if kind == "LaplacianConditionalModel":
         return 0.5 - 0.5 * t.sign() * torch.expm1(-t.abs())
     raise KeyError(kind)
