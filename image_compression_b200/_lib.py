@@ -16,7 +16,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(_HERE, "libhpcodec_sm100a.so")
 SOURCES = ["hpc_api.cu", "entropy_kernels.cu", "loss_kernels.cu", "igemm_simt.cu", "thin_kernels.cu",
-           "igemm_umma.cu", "misc_kernels.cu"]
+           "igemm_umma.cu", "thin_umma.cu", "misc_kernels.cu"]
 # no --use_fast_math: IEEE division / sqrt / expf are part of the parity contract
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC"]
@@ -181,6 +181,13 @@ _SIGNATURES = {
     "hpc_wgrad_c3": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int64,
                              c_int64, c_void_p, c_size_t, c_void_p]),
     "hpc_wgrad_c3_scratch_bytes": (c_size_t, [c_int, c_int, c_int, c_int, c_int]),
+    "hpc_pack_c3_weight": (c_int, [c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p, c_void_p]),
+    "hpc_conv_c3_fwd_umma": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
+                                     c_void_p]),
+    "hpc_deconv_c3_fwd_umma": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "hpc_wgrad_c3_umma": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int64, c_int64, c_void_p,
+                                  c_size_t, c_void_p]),
+    "hpc_wgrad_c3_umma_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "hpc_nchw_channel_sum": (c_int, [c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p]),
     "hpc_rd_combine": (c_int, [c_void_p, c_void_p, POINTER(DistTerms), c_float, c_float, c_void_p, c_void_p]),
 }

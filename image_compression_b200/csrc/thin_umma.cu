@@ -1,0 +1,747 @@
+// tcgen05 versions of the thin-channel layers (sm_100a): the Cin=3 head of g_a (analysis.py:55), the
+// Cout=3 tail of g_s (synthesis.py:55-57) and their weight gradients.  All three are HBM-bound
+// (SURVEY 8d): the 192-channel tensor is streamed exactly once; the 75-long (cs,kh,kw) axis is padded to
+// 80 and becomes the K (conv), N (transposed conv) or M (wgrad) dimension of a dense UMMA.
+//
+//   conv    D[128 px x Cw]   = im2col(x)[128 x 80] . W[Cw x 80]^T        im2col rows built in smem by 4 warps
+//   deconv  P[128 px x 80]   = X[128 x Cw] . W'[80 x Cw]^T  then col2im gather of the 2x2 output phases in smem
+//   wgrad   G[80 x Cw]      += im2col(thin)[px x 80]^T . wide[px x Cw]   split-K over pixel blocks, 2-pass reduce
+//
+// k = cs*25 + kh*5 + kw everywhere (the reference's own weight memory order for both (Cw,Cs,5,5) layouts).
+#include <cuda.h>
+
+#include "tmap.cuh"
+#include "umma_ptx.cuh"
+
+using namespace umma;
+
+namespace {
+
+constexpr int KPAD = 80;            // 75 taps*channels padded to a multiple of 16
+constexpr int TCS = 3;              // thin channels (RGB)
+constexpr int ATOM_BYTES = 8192;    // 64 rows x 128 B
+
+__device__ __forceinline__ void named_bar(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+__device__ __forceinline__ uint32_t pack2_bf16(float a, float b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+// One 16-byte unit (8 consecutive k) of the im2col row of pixel (il, jl) of a stride-2, 5x5, pad-2 conv:
+// value(k) = patch[cs][2*il + kh][2*jl + kw], k = cs*25 + kh*5 + kw; k >= 75 -> 0.  PW = patch row pitch.
+template <int PH, int PW>
+__device__ __forceinline__ uint4 im2col_unit(const float* patch, int il, int jl, int unit) {
+  float v[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const int k = unit * 8 + e;
+    if (k < 75) {
+      const int cs = k / 25, kh = (k % 25) / 5, kw = k % 5;
+      v[e] = patch[(cs * PH + 2 * il + kh) * PW + 2 * jl + kw];
+    } else {
+      v[e] = 0.f;
+    }
+  }
+  return make_uint4(pack2_bf16(v[0], v[1]), pack2_bf16(v[2], v[3]), pack2_bf16(v[4], v[5]), pack2_bf16(v[6], v[7]));
+}
+
+// thin patch (TCS x PH x PW floats, zero outside the image) for the tile whose first output pixel is (i0, j0)
+template <int PH, int PWV, int PW>
+__device__ __forceinline__ void load_patch(float* patch, const float* __restrict__ x, int n, int H, int W, int i0, int j0,
+                                           int tid, int nthreads) {
+  for (int e = tid; e < TCS * PH * PWV; e += nthreads) {
+    const int c = e % PWV, r = (e / PWV) % PH, cs = e / (PWV * PH);
+    const int gy = 2 * i0 - 2 + r, gx = 2 * j0 - 2 + c;
+    patch[(cs * PH + r) * PW + c] =
+        (gy >= 0 && gy < H && gx >= 0 && gx < W) ? __ldg(&x[(((int64_t)n * TCS + cs) * H + gy) * W + gx]) : 0.f;
+  }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------
+// weight packing: w[cw*w_sr + cs*w_sc + t] (t = kh*5+kw) ->
+//   kmaj [Cw][128] bf16 (k contiguous, zero padded)   : B operand of the conv
+//   nmaj [80][Cw]  bf16 (cw contiguous, rows >= 75 zero): B operand of the transposed conv
+// ---------------------------------------------------------------------------------------
+__global__ void pack_c3_weight_kernel(const float* __restrict__ w, int64_t w_sr, int64_t w_sc, int Cw,
+                                      __nv_bfloat16* __restrict__ kmaj, __nv_bfloat16* __restrict__ nmaj) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (kmaj && i < Cw * 128) {
+    const int cw = i / 128, k = i % 128;
+    kmaj[i] = __float2bfloat16_rn(k < 75 ? w[cw * w_sr + (k / 25) * w_sc + (k % 25)] : 0.f);
+  }
+  if (nmaj && i < KPAD * Cw) {
+    const int k = i / Cw, cw = i % Cw;
+    nmaj[i] = __float2bfloat16_rn(k < 75 ? w[cw * w_sr + (k / 25) * w_sc + (k % 25)] : 0.f);
+  }
+}
+
+int hpc_pack_c3_weight(const float* w, int64_t w_sr, int64_t w_sc, int Cw, void* kmaj_bf16, void* nmaj_bf16,
+                       hpc_stream_t stream) {
+  HPC_REQUIRE(w && Cw > 0 && (kmaj_bf16 || nmaj_bf16), HPC_ERR_BAD_SHAPE, "hpc_pack_c3_weight: bad arguments");
+  const int n = Cw * 128;
+  pack_c3_weight_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(w, w_sr, w_sc, Cw, (__nv_bfloat16*)kmaj_bf16,
+                                                                         (__nv_bfloat16*)nmaj_bf16);
+  HPC_LAUNCH_CHECK();
+  return HPC_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// T1: Conv2d(3 -> Cw, 5, s2, p2) : x NCHW fp32 -> out NHWC bf16 (+ squares)
+//   warp 0: weights via TMA, MMA issue, TMEM owner | warps 1-4: im2col builders | warps 5-8: epilogue
+// ---------------------------------------------------------------------------------------
+namespace {
+constexpr int T1_TH = 8, T1_TW = 16;                      // 128 output pixels per tile
+constexpr int T1_PH = 2 * T1_TH + 3, T1_PWV = 2 * T1_TW + 3, T1_PW = T1_PWV + 1;   // 19 x 35 (+1 pad)
+constexpr int T1_THREADS = 288;
+constexpr int T1_A_BYTES = 2 * 16384;                     // two 64-wide K chunks of [128 x 128 B]
+constexpr int T1_ST_ROW = 144;                            // staging row pitch: 64 bf16 + 16 B pad
+constexpr int T1_ST_BYTES = 128 * T1_ST_ROW;              // one tensor, one 64-channel chunk
+
+struct T1Params {
+  const float* x; const float* bias;
+  __nv_bfloat16* out_lp; __nv_bfloat16* out_sq;
+  int N, H, W, OH, OW, Cw;
+  int tiles_w, tiles_h, total_tiles;
+};
+
+template <int CW>
+struct T1Cfg {
+  static constexpr int B_BYTES = 2 * CW * 128;
+  static constexpr int ACC_STRIDE = CW <= 64 ? 64 : (CW <= 128 ? 128 : 256);
+  static constexpr int TMEM_COLS = 2 * ACC_STRIDE;
+  static constexpr int PATCH_BYTES = ((TCS * T1_PH * T1_PW * 4 + 127) / 128) * 128;
+  static constexpr int SMEM = 1024 + 2 * T1_A_BYTES + B_BYTES + PATCH_BYTES + 4 * T1_ST_BYTES + 1024 /*bias*/ + 256;
+};
+
+template <int CW>
+__global__ void __launch_bounds__(T1_THREADS, 1)
+conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constant__ T1Params p) {
+  using Cfg = T1Cfg<CW>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;                                   // 2 x 32 KB
+  uint8_t* smem_b = smem_a + 2 * T1_A_BYTES;                // 2 chunks x [CW x 128 B]
+  float* patch = reinterpret_cast<float*>(smem_b + Cfg::B_BYTES);
+  uint8_t* stage = reinterpret_cast<uint8_t*>(patch) + Cfg::PATCH_BYTES;     // [2 parity][2 tensors][128 x 144]
+  float* bias_s = reinterpret_cast<float*>(stage + 4 * T1_ST_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(bias_s + 256);
+  uint64_t* full_a = bars;          // [2] builders -> MMA   (128 arrivals)
+  uint64_t* empty_a = bars + 2;     // [2] MMA -> builders   (tcgen05.commit)
+  uint64_t* tfull = bars + 4;       // [2] MMA -> epilogue
+  uint64_t* tempty = bars + 6;      // [2] epilogue -> MMA   (4 arrivals)
+  uint64_t* b_full = bars + 8;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // zero the A buffers once: the padded K columns (k >= 80) are never written again
+  for (int i = threadIdx.x; i < 2 * T1_A_BYTES / 16; i += T1_THREADS) reinterpret_cast<uint4*>(smem_a)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = threadIdx.x; i < 256; i += T1_THREADS) bias_s[i] = (p.bias && i < CW) ? p.bias[i] : 0.f;
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmB);
+    for (int s = 0; s < 2; ++s) { mbar_init(&full_a[s], 128); mbar_init(&empty_a[s], 1); mbar_init(&tfull[s], 1); mbar_init(&tempty[s], 4); }
+    mbar_init(b_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int tiles_per_img = p.tiles_w * p.tiles_h;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_arrive_expect_tx(b_full, Cfg::B_BYTES);
+      tma_load_2d(smem_b, &tmB, b_full, 0, 0);
+      tma_load_2d(smem_b + CW * 128, &tmB, b_full, 64, 0);
+      mbar_wait(b_full, 0);
+      constexpr uint32_t idesc = make_idesc_bf16(128, CW, 0, 0);
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+        const int buf = it & 1;
+        const uint32_t ph = (it >> 1) & 1;
+        mbar_wait(&tempty[buf], ph ^ 1);
+        mbar_wait(&full_a[buf], ph);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem_a + buf * T1_A_BYTES), b_addr = smem_u32(smem_b);
+        const uint32_t d = tmem_base + buf * Cfg::ACC_STRIDE;
+#pragma unroll
+        for (int k = 0; k < KPAD / 16; ++k) {
+          const uint32_t ao = (k >> 2) * 16384 + (k & 3) * 32, bo = (k >> 2) * (CW * 128) + (k & 3) * 32;
+          mma_bf16_ss(d, make_smem_desc_sw128(a_addr + ao, 16, 1024), make_smem_desc_sw128(b_addr + bo, 16, 1024), idesc,
+                      k != 0);
+        }
+        mma_commit(&empty_a[buf]);
+        mma_commit(&tfull[buf]);
+      }
+    }
+  } else if (warp <= 4) {
+    // ============================ im2col builders (128 threads) ============================
+    const int t = threadIdx.x - 32;
+    const int il = t >> 4, jl = t & 15;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+      const int buf = it & 1;
+      const uint32_t ph = (it >> 1) & 1;
+      const int n = tile / tiles_per_img, r = tile % tiles_per_img;
+      const int i0 = (r / p.tiles_w) * T1_TH, j0 = (r % p.tiles_w) * T1_TW;
+      named_bar(1, 128);                                   // previous gather finished with `patch`
+      load_patch<T1_PH, T1_PWV, T1_PW>(patch, p.x, n, p.H, p.W, i0, j0, t, 128);
+      named_bar(1, 128);
+      mbar_wait(&empty_a[buf], ph ^ 1);
+      uint8_t* arow = smem_a + buf * T1_A_BYTES + t * 128;
+#pragma unroll
+      for (int u = 0; u < KPAD / 8; ++u) {
+        const uint4 v = im2col_unit<T1_PH, T1_PW>(patch, il, jl, u);
+        *reinterpret_cast<uint4*>(arow + (u >> 3) * 16384 + (((u & 7) ^ (t & 7)) << 4)) = v;
+      }
+      fence_proxy_async();
+      mbar_arrive(&full_a[buf]);
+    }
+  } else {
+    // ============================ epilogue (128 threads) ===================================
+    const int t = threadIdx.x - 160;
+    const int q = warp & 3;
+    const int row = q * 32 + lane;                          // TMEM lane == tile pixel
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+      const int buf = it & 1;
+      const uint32_t ph = (it >> 1) & 1;
+      const int n = tile / tiles_per_img, r = tile % tiles_per_img;
+      const int i0 = (r / p.tiles_w) * T1_TH, j0 = (r % p.tiles_w) * T1_TW;
+      mbar_wait(&tfull[buf], ph);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + buf * Cfg::ACC_STRIDE + ((uint32_t)(q * 32) << 16);
+#pragma unroll 1
+      for (int cc = 0; cc < CW / 64; ++cc) {
+        // staging buffers alternate on the RUNNING chunk count (3 chunks per tile: a per-tile parity would
+        // reuse buffer 0 back to back across tiles), so one barrier per chunk orders writers after readers
+        uint8_t* st_lp = stage + ((it * (CW / 64) + cc) & 1) * 2 * T1_ST_BYTES;
+        uint8_t* st_sq = st_lp + T1_ST_BYTES;
+#pragma unroll
+        for (int c16 = 0; c16 < 4; ++c16) {
+          float v[16];
+          tmem_ld16(taddr + cc * 64 + c16 * 16, v);
+          tmem_ld_wait();
+          uint32_t lo[8], sq[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const float a = v[2 * e] + bias_s[cc * 64 + c16 * 16 + 2 * e];
+            const float b = v[2 * e + 1] + bias_s[cc * 64 + c16 * 16 + 2 * e + 1];
+            lo[e] = pack2_bf16(a, b);
+            sq[e] = pack2_bf16(a * a, b * b);
+          }
+          uint4* d0 = reinterpret_cast<uint4*>(st_lp + row * T1_ST_ROW + c16 * 32);
+          d0[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+          d0[1] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+          if (p.out_sq) {
+            uint4* d1 = reinterpret_cast<uint4*>(st_sq + row * T1_ST_ROW + c16 * 32);
+            d1[0] = make_uint4(sq[0], sq[1], sq[2], sq[3]);
+            d1[1] = make_uint4(sq[4], sq[5], sq[6], sq[7]);
+          }
+        }
+        if (cc == CW / 64 - 1) {                           // accumulator fully read: hand it back early
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tempty[buf]);
+        }
+        named_bar(2, 128);
+        // coalesced copy-out: 8 lanes cover one pixel's 128-byte channel chunk
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int idx = t + 128 * i, rr = idx >> 3, u = idx & 7;
+          const int oh = i0 + (rr >> 4), ow = j0 + (rr & 15);
+          if (oh < p.OH && ow < p.OW) {
+            const int64_t o = (((int64_t)n * p.OH + oh) * p.OW + ow) * CW + cc * 64 + u * 8;
+            *reinterpret_cast<uint4*>(p.out_lp + o) = *reinterpret_cast<const uint4*>(st_lp + rr * T1_ST_ROW + u * 16);
+            if (p.out_sq)
+              *reinterpret_cast<uint4*>(p.out_sq + o) = *reinterpret_cast<const uint4*>(st_sq + rr * T1_ST_ROW + u * 16);
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+}
+
+template <int CW>
+int launch_t1(const CUtensorMap& tmB, const T1Params& kp, cudaStream_t st) {
+  using Cfg = T1Cfg<CW>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    HPC_CUDA(cudaFuncSetAttribute(conv_c3_umma_kernel<CW>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
+    attr_set = true;
+  }
+  const int grid = kp.total_tiles < hpc_num_sms() ? kp.total_tiles : hpc_num_sms();
+  conv_c3_umma_kernel<CW><<<grid, T1_THREADS, Cfg::SMEM, st>>>(tmB, kp);
+  HPC_LAUNCH_CHECK();
+  return HPC_OK;
+}
+}  // namespace
+
+int hpc_conv_c3_fwd_umma(const float* x_nchw, const void* w_kmaj_bf16, const float* bias, int N, int H, int W, int Cw,
+                         void* out_lp_bf16, void* out_sq_bf16, hpc_stream_t stream) {
+  HPC_REQUIRE(N > 0 && H > 0 && W > 0, HPC_ERR_BAD_SHAPE, "hpc_conv_c3_fwd_umma: empty tensor");
+  HPC_REQUIRE(H % 2 == 0 && W % 2 == 0, HPC_ERR_BAD_SHAPE, "hpc_conv_c3_fwd_umma: H, W must be even (got %dx%d)", H, W);
+  HPC_REQUIRE(Cw == 64 || Cw == 128 || Cw == 192 || Cw == 256, HPC_ERR_UNSUPPORTED,
+              "hpc_conv_c3_fwd_umma: Cw=%d not in {64,128,192,256}", Cw);
+  HPC_REQUIRE(x_nchw && w_kmaj_bf16 && out_lp_bf16, HPC_ERR_BAD_SHAPE, "hpc_conv_c3_fwd_umma: NULL pointer");
+  HPC_REQUIRE(hpc_aligned16(w_kmaj_bf16) && hpc_aligned16(out_lp_bf16) && hpc_aligned16(out_sq_bf16), HPC_ERR_BAD_ALIGNMENT,
+              "hpc_conv_c3_fwd_umma: pointers must be 16B aligned");
+  T1Params kp;
+  kp.x = x_nchw; kp.bias = bias; kp.out_lp = (__nv_bfloat16*)out_lp_bf16; kp.out_sq = (__nv_bfloat16*)out_sq_bf16;
+  kp.N = N; kp.H = H; kp.W = W; kp.OH = H / 2; kp.OW = W / 2; kp.Cw = Cw;
+  kp.tiles_w = (kp.OW + T1_TW - 1) / T1_TW; kp.tiles_h = (kp.OH + T1_TH - 1) / T1_TH;
+  kp.total_tiles = N * kp.tiles_w * kp.tiles_h;
+  CUtensorMap tmB;
+  uint64_t dims[2] = {128, (uint64_t)Cw};
+  uint64_t strides[1] = {256};
+  uint32_t box[2] = {64, (uint32_t)Cw};
+  uint32_t estr[2] = {1, 1};
+  int rc = make_tmap(&tmB, w_kmaj_bf16, 2, dims, strides, box, estr);
+  if (rc) return rc;
+  const double opix = (double)N * kp.OH * kp.OW * Cw;
+  HpcProfScope prof(HPC_PROF_THIN, (double)N * TCS * H * W * 4 + opix * (2 + (out_sq_bf16 ? 2 : 0)), stream);
+  auto st = (cudaStream_t)stream;
+  switch (Cw) {
+    case 64: return launch_t1<64>(tmB, kp, st);
+    case 128: return launch_t1<128>(tmB, kp, st);
+    case 192: return launch_t1<192>(tmB, kp, st);
+    default: return launch_t1<256>(tmB, kp, st);
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// T2: ConvTranspose2d(Cw -> 3, 5, s2, p2, op1): x NHWC bf16 -> out NCHW fp32
+//   P[pixel][k] = sum_cw x[pixel][cw] * w[cw][k]   (one UMMA chain per 8x16 input patch, halo included)
+//   out[n][cs][2i+a][2j+b] = bias[cs] + sum_{kh = a (2), kw = b (2)} P[i + (a+2-kh)/2][j + (b+2-kw)/2][cs,kh,kw]
+//   The patch carries a 1-pixel halo, so every output of its 6x14 interior is complete inside the CTA:
+//   no atomics, deterministic.  warp 0: TMA | warp 1: MMA, TMEM | warps 2-5: epilogue (TMEM -> smem -> gather)
+// ---------------------------------------------------------------------------------------
+namespace {
+constexpr int T2_TH = 8, T2_TW = 16, T2_IH = T2_TH - 2, T2_IW = T2_TW - 2;
+constexpr int T2_THREADS = 192;
+constexpr int T2_STAGES = 3;
+constexpr int T2_PROW = 77;                                // floats per pixel row of P in smem (75 + pad, odd)
+
+struct T2Params {
+  const float* bias; float* out;
+  int N, H, W, Cw;                                         // input grid
+  int tiles_w, tiles_h, total_tiles;
+};
+
+template <int CW>
+struct T2Cfg {
+  static constexpr int A_BYTES = (CW / 64) * 16384;       // whole K of one patch
+  static constexpr int B_BYTES = (CW / 64) * KPAD * 128;
+  static constexpr int P_BYTES = 128 * T2_PROW * 4;
+  static constexpr int SMEM = 1024 + T2_STAGES * A_BYTES + ((B_BYTES + 1023) / 1024) * 1024 + P_BYTES + 256;
+};
+
+template <int CW>
+__global__ void __launch_bounds__(T2_THREADS, 1)
+deconv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                      const __grid_constant__ T2Params p) {
+  using Cfg = T2Cfg<CW>;
+  constexpr int KC = CW / 64;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem_a + T2_STAGES * Cfg::A_BYTES;
+  float* Ps = reinterpret_cast<float*>(smem_b + ((Cfg::B_BYTES + 1023) / 1024) * 1024);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(Ps) + Cfg::P_BYTES);
+  uint64_t* full_bar = bars;                    // [STAGES]
+  uint64_t* empty_bar = bars + T2_STAGES;       // [STAGES]
+  uint64_t* tfull = bars + 2 * T2_STAGES;       // [2]
+  uint64_t* tempty = tfull + 2;                 // [2]
+  uint64_t* b_full = tempty + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(b_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    for (int s = 0; s < T2_STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], 4); }
+    mbar_init(b_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 256);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int tiles_per_img = p.tiles_w * p.tiles_h;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_arrive_expect_tx(b_full, Cfg::B_BYTES);
+      for (int c = 0; c < KC; ++c) tma_load_2d(smem_b + c * KPAD * 128, &tmB, b_full, c * 64, 0);
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+        const int n = tile / tiles_per_img, r = tile % tiles_per_img;
+        const int i0 = (r / p.tiles_w) * T2_IH - 1, j0 = (r % p.tiles_w) * T2_IW - 1;   // patch origin (halo)
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        mbar_arrive_expect_tx(&full_bar[stage], Cfg::A_BYTES);
+        for (int c = 0; c < KC; ++c)
+          tma_load_4d(smem_a + stage * Cfg::A_BYTES + c * 16384, &tmA, &full_bar[stage], c * 64, j0, i0, n);
+        if (++stage == T2_STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, KPAD, 0, 0);
+      mbar_wait(b_full, 0);
+      int stage = 0; uint32_t phase = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+        const int acc = it & 1;
+        const uint32_t aph = (it >> 1) & 1;
+        mbar_wait(&tempty[acc], aph ^ 1);
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem_a + stage * Cfg::A_BYTES), b_addr = smem_u32(smem_b);
+        const uint32_t d = tmem_base + acc * 128;
+#pragma unroll
+        for (int k = 0; k < CW / 16; ++k) {
+          const uint32_t ao = (k >> 2) * 16384 + (k & 3) * 32, bo = (k >> 2) * (KPAD * 128) + (k & 3) * 32;
+          mma_bf16_ss(d, make_smem_desc_sw128(a_addr + ao, 16, 1024), make_smem_desc_sw128(b_addr + bo, 16, 1024), idesc,
+                      k != 0);
+        }
+        mma_commit(&empty_bar[stage]);
+        mma_commit(&tfull[acc]);
+        if (++stage == T2_STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else {
+    const int t = threadIdx.x - 64;
+    const int q = warp & 3;
+    const int row = q * 32 + lane;                          // patch pixel index = il*16 + jl
+    const int OH = 2 * p.H, OW = 2 * p.W;
+    float bs[TCS];
+#pragma unroll
+    for (int cs = 0; cs < TCS; ++cs) bs[cs] = p.bias ? p.bias[cs] : 0.f;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+      const int acc = it & 1;
+      const uint32_t aph = (it >> 1) & 1;
+      const int n = tile / tiles_per_img, r = tile % tiles_per_img;
+      const int ii0 = (r / p.tiles_w) * T2_IH, jj0 = (r % p.tiles_w) * T2_IW;            // interior origin
+      mbar_wait(&tfull[acc], aph);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + acc * 128 + ((uint32_t)(q * 32) << 16);
+      named_bar(3, 128);                                    // previous tile's gather is done with Ps
+#pragma unroll
+      for (int c16 = 0; c16 < KPAD / 16; ++c16) {
+        float v[16];
+        tmem_ld16(taddr + c16 * 16, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int e = 0; e < 16; ++e)
+          if (c16 * 16 + e < 75) Ps[row * T2_PROW + c16 * 16 + e] = v[e];
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[acc]);
+      named_bar(3, 128);
+      // gather the 2x2 output phases of the 6x14 interior: (cs, ro, co) with co fastest
+      for (int idx = t; idx < TCS * 2 * T2_IH * 2 * T2_IW; idx += 128) {
+        const int co = idx % (2 * T2_IW), ro = (idx / (2 * T2_IW)) % (2 * T2_IH), cs = idx / (4 * T2_IH * T2_IW);
+        const int a = ro & 1, b = co & 1;
+        const int gi = ii0 + (ro >> 1), gj = jj0 + (co >> 1);
+        if (gi >= p.H || gj >= p.W) continue;
+        const int il = (ro >> 1) + 1, jl = (co >> 1) + 1;
+        float s = bs[cs];
+        for (int kh = a; kh < 5; kh += 2) {
+          const int pr = il + (a + 2 - kh) / 2;
+          for (int kw = b; kw < 5; kw += 2) {
+            const int pc = jl + (b + 2 - kw) / 2;
+            s += Ps[(pr * T2_TW + pc) * T2_PROW + cs * 25 + kh * 5 + kw];
+          }
+        }
+        p.out[(((int64_t)n * TCS + cs) * OH + 2 * gi + a) * OW + 2 * gj + b] = s;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 256);
+}
+
+template <int CW>
+int launch_t2(const CUtensorMap& tmA, const CUtensorMap& tmB, const T2Params& kp, cudaStream_t st) {
+  using Cfg = T2Cfg<CW>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    HPC_CUDA(cudaFuncSetAttribute(deconv_c3_umma_kernel<CW>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
+    attr_set = true;
+  }
+  const int grid = kp.total_tiles < hpc_num_sms() ? kp.total_tiles : hpc_num_sms();
+  deconv_c3_umma_kernel<CW><<<grid, T2_THREADS, Cfg::SMEM, st>>>(tmA, tmB, kp);
+  HPC_LAUNCH_CHECK();
+  return HPC_OK;
+}
+}  // namespace
+
+int hpc_deconv_c3_fwd_umma(const void* x_nhwc_bf16, const void* w_nmaj_bf16, const float* bias, int N, int Cw, int H,
+                           int W, float* out_nchw, hpc_stream_t stream) {
+  HPC_REQUIRE(N > 0 && H > 0 && W > 0, HPC_ERR_BAD_SHAPE, "hpc_deconv_c3_fwd_umma: empty tensor");
+  HPC_REQUIRE(Cw == 64 || Cw == 128 || Cw == 192, HPC_ERR_UNSUPPORTED, "hpc_deconv_c3_fwd_umma: Cw=%d not in {64,128,192}", Cw);
+  HPC_REQUIRE(x_nhwc_bf16 && w_nmaj_bf16 && out_nchw, HPC_ERR_BAD_SHAPE, "hpc_deconv_c3_fwd_umma: NULL pointer");
+  HPC_REQUIRE(hpc_aligned16(x_nhwc_bf16) && hpc_aligned16(w_nmaj_bf16), HPC_ERR_BAD_ALIGNMENT,
+              "hpc_deconv_c3_fwd_umma: pointers must be 16B aligned");
+  T2Params kp;
+  kp.bias = bias; kp.out = out_nchw; kp.N = N; kp.H = H; kp.W = W; kp.Cw = Cw;
+  kp.tiles_w = (W + T2_IW - 1) / T2_IW; kp.tiles_h = (H + T2_IH - 1) / T2_IH;
+  kp.total_tiles = N * kp.tiles_w * kp.tiles_h;
+  CUtensorMap tmA, tmB;
+  {
+    uint64_t dims[4] = {(uint64_t)Cw, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+    uint64_t strides[3] = {(uint64_t)Cw * 2, (uint64_t)W * Cw * 2, (uint64_t)H * W * Cw * 2};
+    uint32_t box[4] = {64, T2_TW, T2_TH, 1};
+    uint32_t estr[4] = {1, 1, 1, 1};
+    int rc = make_tmap(&tmA, x_nhwc_bf16, 4, dims, strides, box, estr);
+    if (rc) return rc;
+  }
+  {
+    uint64_t dims[2] = {(uint64_t)Cw, KPAD};
+    uint64_t strides[1] = {(uint64_t)Cw * 2};
+    uint32_t box[2] = {64, KPAD};
+    uint32_t estr[2] = {1, 1};
+    int rc = make_tmap(&tmB, w_nmaj_bf16, 2, dims, strides, box, estr);
+    if (rc) return rc;
+  }
+  const double npix = (double)N * H * W;
+  HpcProfScope prof(HPC_PROF_THIN, npix * Cw * 2 + npix * 4 * TCS * 4, stream);
+  auto st = (cudaStream_t)stream;
+  switch (Cw) {
+    case 64: return launch_t2<64>(tmA, tmB, kp, st);
+    case 128: return launch_t2<128>(tmA, tmB, kp, st);
+    default: return launch_t2<192>(tmA, tmB, kp, st);
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// T3: weight gradient of both thin layers:
+//   gw[cw][cs][kh][kw] = sum_{n,i,j} wide[n,i,j,cw] * thin[n,cs,2i-2+kh,2j-2+kw]
+//   D[M = 128 (k, 80 live)][N = Cw] += A^T B over K = pixels.  Both operands are MN-major SWIZZLE_128B atoms
+//   ([64 pixels] x [64 values]): `wide` straight from NHWC by TMA, the im2col of `thin` written by 4 warps.
+//   Split-K over 64-pixel blocks across the grid; partials go to the workspace, a second kernel reduces them
+//   in a fixed order (deterministic) into the reference weight layout.
+//   warp 0: TMA | warp 1: MMA, TMEM | warps 2-5: im2col builders, then the TMEM -> workspace epilogue
+// ---------------------------------------------------------------------------------------
+namespace {
+constexpr int T3_TH = 4, T3_TW = 16;                      // 64 pixels per K block
+constexpr int T3_PH = 2 * T3_TH + 3, T3_PWV = 2 * T3_TW + 3, T3_PW = T3_PWV + 1;   // 11 x 35 (+1)
+constexpr int T3_THREADS = 192;
+constexpr int T3_STAGES = 4;
+
+struct T3Params {
+  const float* thin; float* ws;
+  int N, H, W, Cw;                                         // wide grid (thin is 2H x 2W)
+  int tiles_w, tiles_h, kblocks, nsplits;
+};
+
+template <int CW>
+struct T3Cfg {
+  static constexpr int STAGE_BYTES = (2 + CW / 64) * ATOM_BYTES;
+  static constexpr int PATCH_BYTES = ((TCS * T3_PH * T3_PW * 4 + 127) / 128) * 128;
+  static constexpr int SMEM = 1024 + T3_STAGES * STAGE_BYTES + PATCH_BYTES + 256;
+};
+
+template <int CW>
+__global__ void __launch_bounds__(T3_THREADS, 1)
+wgrad_c3_umma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ T3Params p) {
+  using Cfg = T3Cfg<CW>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  float* patch = reinterpret_cast<float*>(smem + T3_STAGES * Cfg::STAGE_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(patch) + Cfg::PATCH_BYTES);
+  uint64_t* full_bar = bars;                    // [STAGES] 1 TMA arrival (+tx) + 128 builder arrivals
+  uint64_t* empty_bar = bars + T3_STAGES;       // [STAGES] tcgen05.commit
+  uint64_t* done_bar = bars + 2 * T3_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done_bar + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int split = blockIdx.x;
+  const int kb0 = (int)(((int64_t)split * p.kblocks) / p.nsplits);
+  const int kb1 = (int)(((int64_t)(split + 1) * p.kblocks) / p.nsplits);
+  const int tiles_per_img = p.tiles_w * p.tiles_h;
+
+  // zero all im2col atoms once: rows k >= 80 of the second atom are never written again
+  for (int s = 0; s < T3_STAGES; ++s)
+    for (int i = threadIdx.x; i < 2 * ATOM_BYTES / 16; i += T3_THREADS)
+      reinterpret_cast<uint4*>(smem + s * Cfg::STAGE_BYTES)[i] = make_uint4(0, 0, 0, 0);
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmW);
+    for (int s = 0; s < T3_STAGES; ++s) { mbar_init(&full_bar[s], 129); mbar_init(&empty_bar[s], 1); }
+    mbar_init(done_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 256);
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        const int n = kb / tiles_per_img, r = kb % tiles_per_img;
+        const int i0 = (r / p.tiles_w) * T3_TH, j0 = (r % p.tiles_w) * T3_TW;
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        mbar_arrive_expect_tx(&full_bar[stage], (CW / 64) * ATOM_BYTES);
+        uint8_t* sb = smem + stage * Cfg::STAGE_BYTES + 2 * ATOM_BYTES;
+        for (int c = 0; c < CW / 64; ++c) tma_load_4d(sb + c * ATOM_BYTES, &tmW, &full_bar[stage], c * 64, j0, i0, n);
+        if (++stage == T3_STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, CW, 1, 1);
+      int stage = 0; uint32_t phase = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem + stage * Cfg::STAGE_BYTES);
+        const uint32_t b_addr = a_addr + 2 * ATOM_BYTES;
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks)
+          mma_bf16_ss(tmem_base, make_smem_desc_sw128(a_addr + ks * 2048, ATOM_BYTES, 1024),
+                      make_smem_desc_sw128(b_addr + ks * 2048, ATOM_BYTES, 1024), idesc, (kb != kb0) || ks != 0);
+        mma_commit(&empty_bar[stage]);
+        if (++stage == T3_STAGES) { stage = 0; phase ^= 1; }
+      }
+      mma_commit(done_bar);
+    }
+  } else {
+    const int t = threadIdx.x - 64;
+    const int px = t & 63, half = t >> 6;                  // pixel of the K block, which half of its 10 units
+    const int il = px >> 4, jl = px & 15;
+    int stage = 0; uint32_t phase = 0;
+    for (int kb = kb0; kb < kb1; ++kb) {
+      const int n = kb / tiles_per_img, r = kb % tiles_per_img;
+      const int i0 = (r / p.tiles_w) * T3_TH, j0 = (r % p.tiles_w) * T3_TW;
+      named_bar(1, 128);
+      load_patch<T3_PH, T3_PWV, T3_PW>(patch, p.thin, n, 2 * p.H, 2 * p.W, i0, j0, t, 128);
+      named_bar(1, 128);
+      mbar_wait(&empty_bar[stage], phase ^ 1);
+      uint8_t* arow = smem + stage * Cfg::STAGE_BYTES + px * 128;
+#pragma unroll
+      for (int uu = 0; uu < 5; ++uu) {
+        const int u = half * 5 + uu;                       // units 0..4 | 5..9 of the 80-long row
+        const uint4 v = im2col_unit<T3_PH, T3_PW>(patch, il, jl, u);
+        *reinterpret_cast<uint4*>(arow + (u >> 3) * ATOM_BYTES + (((u & 7) ^ (px & 7)) << 4)) = v;
+      }
+      fence_proxy_async();
+      mbar_arrive(&full_bar[stage]);
+      if (++stage == T3_STAGES) { stage = 0; phase ^= 1; }
+    }
+    // epilogue: row = k (TMEM lane); rows >= 80 are padding
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    mbar_wait(done_bar, 0);
+    tc_fence_after();
+    if (q * 32 < KPAD) {
+      float* dst = p.ws + ((int64_t)split * KPAD + row) * CW;
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+      for (int c0 = 0; c0 < CW; c0 += 16) {
+        float v[16];
+        if (kb1 > kb0) {
+          tmem_ld16(taddr + c0, v);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int e = 0; e < 16; ++e) v[e] = 0.f;
+        }
+        if (row < KPAD) {
+#pragma unroll
+          for (int e = 0; e < 16; e += 4) *reinterpret_cast<float4*>(dst + c0 + e) = make_float4(v[e], v[e + 1], v[e + 2], v[e + 3]);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 256);
+}
+
+// gw[cw*w_sr + cs*w_sc + t] = sum_s ws[s][cs*25+t][cw]
+__global__ void wgrad_c3_umma_reduce(const float* __restrict__ ws, int nsplits, int Cw, float* __restrict__ gw, int64_t w_sr,
+                                     int64_t w_sc) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 75 * Cw) return;
+  const int k = i / Cw, cw = i % Cw;
+  float a = 0.f;
+  for (int s = 0; s < nsplits; ++s) a += ws[((int64_t)s * KPAD + k) * Cw + cw];
+  gw[cw * w_sr + (k / 25) * w_sc + (k % 25)] = a;
+}
+
+int t3_splits(int kblocks) {
+  int ns = hpc_num_sms();
+  return ns < kblocks ? ns : kblocks;
+}
+}  // namespace
+
+size_t hpc_wgrad_c3_umma_workspace_bytes(int N, int Cw, int H, int W) {
+  const int kblocks = N * ((H + T3_TH - 1) / T3_TH) * ((W + T3_TW - 1) / T3_TW);
+  return (size_t)t3_splits(kblocks) * KPAD * Cw * sizeof(float);
+}
+
+int hpc_wgrad_c3_umma(const void* wide_nhwc_bf16, const float* thin_nchw, int N, int Cw, int H, int W, float* gw,
+                      int64_t w_sr, int64_t w_sc, void* workspace, size_t workspace_bytes, hpc_stream_t stream) {
+  HPC_REQUIRE(N > 0 && H > 0 && W > 0, HPC_ERR_BAD_SHAPE, "hpc_wgrad_c3_umma: empty tensor");
+  HPC_REQUIRE(Cw == 64 || Cw == 128 || Cw == 192 || Cw == 256, HPC_ERR_UNSUPPORTED,
+              "hpc_wgrad_c3_umma: Cw=%d not in {64,128,192,256}", Cw);
+  HPC_REQUIRE(wide_nhwc_bf16 && thin_nchw && gw, HPC_ERR_BAD_SHAPE, "hpc_wgrad_c3_umma: NULL pointer");
+  HPC_REQUIRE(hpc_aligned16(wide_nhwc_bf16) && hpc_aligned16(workspace), HPC_ERR_BAD_ALIGNMENT,
+              "hpc_wgrad_c3_umma: pointers must be 16B aligned");
+  T3Params kp;
+  kp.thin = thin_nchw; kp.ws = (float*)workspace; kp.N = N; kp.H = H; kp.W = W; kp.Cw = Cw;
+  kp.tiles_w = (W + T3_TW - 1) / T3_TW; kp.tiles_h = (H + T3_TH - 1) / T3_TH;
+  kp.kblocks = N * kp.tiles_w * kp.tiles_h;
+  kp.nsplits = t3_splits(kp.kblocks);
+  const size_t need = (size_t)kp.nsplits * KPAD * Cw * sizeof(float);
+  HPC_REQUIRE(workspace && workspace_bytes >= need, HPC_ERR_BAD_SHAPE, "hpc_wgrad_c3_umma: workspace too small (%zu < %zu)",
+              workspace_bytes, need);
+  CUtensorMap tmW;
+  uint64_t dims[4] = {(uint64_t)Cw, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+  uint64_t strides[3] = {(uint64_t)Cw * 2, (uint64_t)W * Cw * 2, (uint64_t)H * W * Cw * 2};
+  uint32_t box[4] = {64, T3_TW, T3_TH, 1};
+  uint32_t estr[4] = {1, 1, 1, 1};
+  int rc = make_tmap(&tmW, wide_nhwc_bf16, 4, dims, strides, box, estr);
+  if (rc) return rc;
+  HpcProfScope prof(HPC_PROF_THIN, (double)N * H * W * Cw * 2 + (double)N * TCS * 4 * H * W * 4, stream);
+  auto st = (cudaStream_t)stream;
+#define LAUNCH_T3(CW_)                                                                                               \
+  do {                                                                                                               \
+    static bool attr_set = false;                                                                                    \
+    if (!attr_set) {                                                                                                 \
+      HPC_CUDA(cudaFuncSetAttribute(wgrad_c3_umma_kernel<CW_>, cudaFuncAttributeMaxDynamicSharedMemorySize,          \
+                                    T3Cfg<CW_>::SMEM));                                                              \
+      attr_set = true;                                                                                               \
+    }                                                                                                                \
+    wgrad_c3_umma_kernel<CW_><<<kp.nsplits, T3_THREADS, T3Cfg<CW_>::SMEM, st>>>(tmW, kp);                            \
+  } while (0)
+  switch (Cw) {
+    case 64: LAUNCH_T3(64); break;
+    case 128: LAUNCH_T3(128); break;
+    case 192: LAUNCH_T3(192); break;
+    default: LAUNCH_T3(256); break;
+  }
+#undef LAUNCH_T3
+  HPC_LAUNCH_CHECK();
+  wgrad_c3_umma_reduce<<<(75 * Cw + 255) / 256, 256, 0, st>>>(kp.ws, kp.nsplits, Cw, gw, w_sr, w_sc);
+  HPC_LAUNCH_CHECK();
+  return HPC_OK;
+}

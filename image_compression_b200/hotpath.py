@@ -387,6 +387,27 @@ def gdn_backward(g, x, xsq, nrm, gamma_eff, inverse=False, need_dx=True):
 # ----------------------------------------------------------------------------------------
 # thin-channel layers
 # ----------------------------------------------------------------------------------------
+def _thin_umma_ok(Cw, Cs, dt):
+    return engine() == ENGINE_UMMA and dt == torch.bfloat16 and Cs == 3 and Cw in (64, 128, 192, 256)
+
+
+def pack_c3_weight(weight, kind):
+    """bf16 operand of the tcgen05 thin kernels from a (Cw,3,5,5)-laid-out weight (Conv2d(3->Cw) weight or
+    ConvTranspose2d(Cw->3) weight): kind "k" -> [Cw][128] (k contiguous), "n" -> [80][Cw].  Cached like pack_weight."""
+    key = (id(weight), "c3", kind)
+    hit = _pack_cache.get(key)
+    if hit is not None and hit[0]() is weight and hit[1] == weight._version and hit[2] == weight.data_ptr():
+        return hit[3]
+    Cw, Cs = weight.shape[0], weight.shape[1]
+    out = torch.empty((Cw, 128) if kind == "k" else (80, Cw), dtype=torch.bfloat16, device=weight.device)
+    check(lib().hpc_pack_c3_weight(ptr(weight), Cs * 25, 25, Cw, ptr(out) if kind == "k" else None,
+                                   ptr(out) if kind == "n" else None, stream()))
+    if len(_pack_cache) > 256:
+        _pack_cache.clear()
+    _pack_cache[key] = (weakref.ref(weight), weight._version, weight.data_ptr(), out)
+    return out
+
+
 def conv_c3_forward(x_nchw, weight, bias, want_sq=True, want_f32=False):
     """Conv2d(3->C,5,2,2) on an NCHW fp32 image -> NHWC lp (+ squares)."""
     N, Cs, H, W = x_nchw.shape
@@ -395,6 +416,10 @@ def conv_c3_forward(x_nchw, weight, bias, want_sq=True, want_f32=False):
     shape = (N, H // 2, W // 2, Cw)
     out = torch.empty(shape, dtype=dt, device=x_nchw.device)
     sq = torch.empty(shape, dtype=dt, device=x_nchw.device) if want_sq else None
+    if _thin_umma_ok(Cw, Cs, dt) and not want_f32:
+        check(lib().hpc_conv_c3_fwd_umma(ptr(x_nchw), ptr(pack_c3_weight(weight, "k")), ptr(bias), N, H, W, Cw, ptr(out),
+                                         ptr(sq), stream()))
+        return out, sq, None
     of = torch.empty(shape, dtype=torch.float32, device=x_nchw.device) if want_f32 else None
     check(lib().hpc_conv_c3_fwd(ptr(x_nchw), ptr(weight), Cs * 25, 25, ptr(bias), N, Cs, H, W, Cw, ptr(of), ptr(out),
                                 ptr(sq), _lib.dtype_code(dt), stream()))
@@ -405,6 +430,12 @@ def wgrad_c3(wide_nhwc, thin_nchw, Cw, Cs):
     """gw (Cw,Cs,5,5) = sum wide[n,i,j,cw]*thin[n,cs,2i-2+kh,2j-2+kw]."""
     N, H, W, _ = wide_nhwc.shape
     gw = torch.empty((Cw, Cs, 5, 5), dtype=torch.float32, device=wide_nhwc.device)
+    if _thin_umma_ok(Cw, Cs, wide_nhwc.dtype):
+        nb = lib().hpc_wgrad_c3_umma_workspace_bytes(N, Cw, H, W)
+        sc = torch.empty(nb, dtype=torch.uint8, device=wide_nhwc.device)
+        check(lib().hpc_wgrad_c3_umma(ptr(wide_nhwc), ptr(thin_nchw), N, Cw, H, W, ptr(gw), Cs * 25, 25, ptr(sc), nb,
+                                      stream()))
+        return gw
     nb = lib().hpc_wgrad_c3_scratch_bytes(N, Cw, Cs, H, W)
     sc = torch.empty(nb, dtype=torch.uint8, device=wide_nhwc.device)
     check(lib().hpc_wgrad_c3(ptr(wide_nhwc), _lib.dtype_code(wide_nhwc), ptr(thin_nchw), N, Cw, Cs, H, W, ptr(gw),
@@ -417,6 +448,10 @@ def deconv_c3_forward(x_nhwc, weight, bias):
     N, H, W, Cw = x_nhwc.shape
     Cs = weight.shape[1]
     out = torch.empty((N, Cs, 2 * H, 2 * W), dtype=torch.float32, device=x_nhwc.device)
+    if _thin_umma_ok(Cw, Cs, x_nhwc.dtype) and Cw <= 192:
+        check(lib().hpc_deconv_c3_fwd_umma(ptr(x_nhwc), ptr(pack_c3_weight(weight, "n")), ptr(bias), N, Cw, H, W,
+                                           ptr(out), stream()))
+        return out
     check(lib().hpc_deconv_c3_fwd(ptr(x_nhwc), _lib.dtype_code(x_nhwc), ptr(weight), Cs * 25, 25, ptr(bias), N, Cw, H,
                                   W, Cs, ptr(out), stream()))
     return out
@@ -430,8 +465,12 @@ def deconv_c3_backward(g_nchw, x_nhwc, weight, need_dx=True):
     dx = None
     if need_dx:
         dx = torch.empty((N, H2 // 2, W2 // 2, Cw), dtype=dt, device=g_nchw.device)
-        check(lib().hpc_conv_c3_fwd(ptr(g_nchw), ptr(weight), Cs * 25, 25, None, N, Cs, H2, W2, Cw, None, ptr(dx), None,
-                                    _lib.dtype_code(dt), stream()))
+        if _thin_umma_ok(Cw, Cs, dt):
+            check(lib().hpc_conv_c3_fwd_umma(ptr(g_nchw), ptr(pack_c3_weight(weight, "k")), None, N, H2, W2, Cw, ptr(dx),
+                                             None, stream()))
+        else:
+            check(lib().hpc_conv_c3_fwd(ptr(g_nchw), ptr(weight), Cs * 25, 25, None, N, Cs, H2, W2, Cw, None, ptr(dx),
+                                        None, _lib.dtype_code(dt), stream()))
     gw = wgrad_c3(x_nhwc, g_nchw, Cw, Cs)
     gb = torch.empty((Cs,), dtype=torch.float32, device=g_nchw.device)
     check(lib().hpc_nchw_channel_sum(ptr(g_nchw), N, Cs, H2 * W2, ptr(gb), stream()))

@@ -365,6 +365,22 @@ int hpc_wgrad_c3(const void* wide_nhwc, int lp_dtype, const float* thin_nchw, in
                  float* gw, int64_t w_sr, int64_t w_sc, void* scratch, size_t scratch_bytes,
                  hpc_stream_t stream);
 size_t hpc_wgrad_c3_scratch_bytes(int N, int Cw, int Cs, int H, int W);
+/* tcgen05 (sm_100a, bf16 operands, fp32 accumulate) versions of the three thin-channel kernels above; same
+ * arithmetic, same reference call sites (analysis.py:55, synthesis.py:55-57 and their autograd).
+ *   pack_c3_weight:  w[cw*w_sr + cs*w_sc + kh*5+kw] -> kmaj [Cw][128] bf16 (k = cs*25+kh*5+kw contiguous, zero padded;
+ *                    operand of conv_c3_fwd_umma) and/or nmaj [80][Cw] bf16 (operand of deconv_c3_fwd_umma)
+ *   conv_c3_fwd_umma:   x NCHW float (N,3,H,W) -> out NHWC bf16 (N,H/2,W/2,Cw) (+ squares, may be NULL)
+ *   deconv_c3_fwd_umma: x NHWC bf16 (N,H,W,Cw) -> out NCHW float (N,3,2H,2W)
+ *   wgrad_c3_umma:      as wgrad_c3 with wide bf16; workspace from hpc_wgrad_c3_umma_workspace_bytes */
+int hpc_pack_c3_weight(const float* w, int64_t w_sr, int64_t w_sc, int Cw, void* kmaj_bf16, void* nmaj_bf16,
+                       hpc_stream_t stream);
+int hpc_conv_c3_fwd_umma(const float* x_nchw, const void* w_kmaj_bf16, const float* bias, int N, int H, int W, int Cw,
+                         void* out_lp_bf16, void* out_sq_bf16, hpc_stream_t stream);
+int hpc_deconv_c3_fwd_umma(const void* x_nhwc_bf16, const void* w_nmaj_bf16, const float* bias, int N, int Cw, int H,
+                           int W, float* out_nchw, hpc_stream_t stream);
+int hpc_wgrad_c3_umma(const void* wide_nhwc_bf16, const float* thin_nchw, int N, int Cw, int H, int W, float* gw,
+                      int64_t w_sr, int64_t w_sc, void* workspace, size_t workspace_bytes, hpc_stream_t stream);
+size_t hpc_wgrad_c3_umma_workspace_bytes(int N, int Cw, int H, int W);
 /* per-channel sum of an NCHW float tensor (bias grad of the tail deconv) */
 int hpc_nchw_channel_sum(const float* x, int N, int C, int64_t HW, float* out, hpc_stream_t stream);
 

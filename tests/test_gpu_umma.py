@@ -109,3 +109,69 @@ def test_wgrad(transposed, k, s, N, H, W, C):
     w = torch.empty(C, C, k, k, device=DEV)
     out, ref = _both(lambda: {"f32": spec.wgrad(x, g, w)})
     _cmp(out, ref, tol=1e-3)
+
+
+# ---------------------------------------------------------------------------------------------
+# thin-channel layers on tensor cores (thin_umma.cu) against the CUDA-core kernels (thin_kernels.cu)
+# ---------------------------------------------------------------------------------------------
+THIN_SHAPES = [(2, 32, 64, 192), (1, 16, 16, 192), (3, 12, 20, 192), (1, 2, 2, 192), (2, 14, 30, 64), (1, 18, 34, 128),
+               (2, 6, 14, 192), (1, 7, 15, 192)]
+
+
+@pytest.mark.parametrize("N,H,W,C", THIN_SHAPES)
+def test_conv_c3_forward_umma(N, H, W, C):
+    """H, W: output grid; image is (N,3,2H,2W)."""
+    torch.manual_seed(4)
+    x = torch.rand(N, 3, 2 * H, 2 * W, device=DEV)
+    w = torch.randn(C, 3, 5, 5, device=DEV) / 75 ** 0.5
+    b = torch.randn(C, device=DEV)
+
+    def run():
+        out, sq, _ = hp.conv_c3_forward(x, w, b, want_sq=True)
+        return {"lp": out, "sq": sq}
+    out, ref = _both(run)
+    for k in ref:       # the CUDA-core kernel keeps fp32 operands, the tensor-core one rounds them to bf16
+        err = float((out[k].float() - ref[k].float()).abs().max()) / float(ref[k].float().abs().max())
+        assert err < 2e-2, (k, err)
+    # operands are rounded to bf16 inside the tensor-core kernel: compare with an fp32 conv at bf16 accuracy
+    y = torch.nn.functional.conv2d(x, w, b, stride=2, padding=2).permute(0, 2, 3, 1)
+    err = float((out["lp"].float() - y).abs().max()) / float(y.abs().max())
+    assert err < 2e-2, err
+
+
+@pytest.mark.parametrize("N,H,W,C", THIN_SHAPES)
+def test_deconv_c3_forward_backward_umma(N, H, W, C):
+    torch.manual_seed(5)
+    x = torch.randn(N, H, W, C, device=DEV).to(torch.bfloat16)
+    w = torch.randn(C, 3, 5, 5, device=DEV) / (C * 6.25) ** 0.5
+    b = torch.randn(3, device=DEV)
+    g = torch.randn(N, 3, 2 * H, 2 * W, device=DEV)
+
+    def run():
+        out = hp.deconv_c3_forward(x, w, b)
+        dx, gw, gb = hp.deconv_c3_backward(g, x, w)
+        return {"out": out, "dx": dx, "gw": gw, "gb": gb}
+    out, ref = _both(run)
+    y = torch.nn.functional.conv_transpose2d(x.float().permute(0, 3, 1, 2), w, b, stride=2, padding=2, output_padding=1)
+    assert float((out["out"] - y).abs().max()) / float(y.abs().max()) < 2e-2        # weights rounded to bf16
+    # SIMT kernel keeps fp32 weights, the tensor-core kernel rounds them to bf16: 2^-9 relative per product
+    for k, tol in (("out", 1e-2), ("dx", 2e-2), ("gw", 1e-2), ("gb", 1e-5)):
+        a, r = out[k].float(), ref[k].float()
+        err = float((a - r).abs().max()) / (float(r.abs().max()) + 1e-20)
+        assert err < tol, (k, err)
+
+
+@pytest.mark.parametrize("N,H,W,C", THIN_SHAPES)
+def test_wgrad_c3_umma(N, H, W, C):
+    torch.manual_seed(6)
+    wide = torch.randn(N, H, W, C, device=DEV).to(torch.bfloat16)
+    thin = torch.rand(N, 3, 2 * H, 2 * W, device=DEV)
+    out, ref = _both(lambda: {"gw": hp.wgrad_c3(wide, thin, C, 3)})
+    a, r = out["gw"], ref["gw"]
+    err = float((a - r).abs().max()) / float(r.abs().max())
+    assert err < 1e-2, err        # thin operand rounded to bf16 on the tensor-core path
+    xw = thin.clone().requires_grad_(True)
+    wt = torch.zeros(C, 3, 5, 5, device=DEV, requires_grad=True)
+    torch.nn.functional.conv2d(xw, wt, None, stride=2, padding=2).backward(wide.float().permute(0, 3, 1, 2))
+    err = float((a - wt.grad).abs().max()) / float(wt.grad.abs().max())
+    assert err < 1e-2, err
