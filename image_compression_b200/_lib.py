@@ -16,7 +16,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(_HERE, "libhpcodec_sm100a.so")
 SOURCES = ["hpc_api.cu", "entropy_kernels.cu", "loss_kernels.cu", "igemm_simt.cu", "thin_kernels.cu",
-           "igemm_umma.cu", "thin_umma.cu", "misc_kernels.cu"]
+           "igemm_umma.cu", "thin_umma.cu", "gdn_umma.cu", "misc_kernels.cu"]
 # no --use_fast_math: IEEE division / sqrt / expf are part of the parity contract
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC"]
@@ -28,8 +28,8 @@ MAX_TAPS, MAX_PHASES = 25, 4
 (EPI_LINEAR, EPI_RELU, EPI_EXP_CLAMP, EPI_GDN, EPI_IGDN, EPI_GDN_BWD, EPI_IGDN_BWD, EPI_RELU_MASK,
  EPI_SIGN_ADD) = range(9)
 DIST_LAPLACE, DIST_GAUSS = 0, 1
-(PROF_IGEMM_FWD, PROF_IGEMM_WGRAD, PROF_CONDITIONAL, PROF_FACTORIZED, PROF_THIN, PROF_DISTORTION) = range(6)
-PROF_NAMES = ("igemm_fwd_umma", "igemm_wgrad_umma", "conditional", "factorized", "thin_c3", "distortion")
+(PROF_IGEMM_FWD, PROF_IGEMM_WGRAD, PROF_CONDITIONAL, PROF_FACTORIZED, PROF_THIN, PROF_DISTORTION, PROF_GDN) = range(7)
+PROF_NAMES = ("igemm_fwd_umma", "igemm_wgrad_umma", "conditional", "factorized", "thin_c3", "distortion", "gdn_fused")
 MSSSIM_LOSS_LOG, MSSSIM_LOSS_PLAIN, MSSSIM_METRIC, SSIM_LOSS, SSIM_METRIC = range(5)
 
 
@@ -181,6 +181,10 @@ _SIGNATURES = {
     "hpc_wgrad_c3": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int64,
                              c_int64, c_void_p, c_size_t, c_void_p]),
     "hpc_wgrad_c3_scratch_bytes": (c_size_t, [c_int, c_int, c_int, c_int, c_int]),
+    "hpc_gdn_fwd_umma": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "hpc_gdn_bwd_umma_parts": (c_int, [c_int64]),
+    "hpc_gdn_bwd_umma": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p,
+                                 c_void_p, c_void_p, c_void_p]),
     "hpc_pack_c3_weight": (c_int, [c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p, c_void_p]),
     "hpc_conv_c3_fwd_umma": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
                                      c_void_p]),

@@ -47,7 +47,8 @@ def ga_forward(x_nchw, convs, gdns, k=5, strides=(2, 2, 2, 2), want_abs=False, s
         raise NotImplementedError("g_a head: only Conv2d(<=4 channels, k=5, s=2) is built (analysis.py:55 with the "
                                   "reference's cfg defaults)")
     last = (n == 1)
-    cur, cur_sq, cur_f32 = hp.conv_c3_forward(x_nchw, w0, b0, want_sq=not last, want_f32=last)
+    need_sq = not hp.gdn_fused_ok(hp.lp_dtype(), w0.shape[0])     # the fused GDN kernel squares in shared memory
+    cur, cur_sq, cur_f32 = hp.conv_c3_forward(x_nchw, w0, b0, want_sq=(not last) and need_sq, want_f32=last)
     y_f32, y_abs = cur_f32, None
     for i in range(n):
         if i > 0:
@@ -55,7 +56,7 @@ def ga_forward(x_nchw, convs, gdns, k=5, strides=(2, 2, 2, 2), want_abs=False, s
             spec = hp.ConvSpec(False, w.shape[1], w.shape[0], k, strides[i])
             last = (i == n - 1)
             inp = cur
-            o = spec.forward(inp, w, b, EPI_LINEAR, want_lp=not last, want_sq=not last, want_f32=last,
+            o = spec.forward(inp, w, b, EPI_LINEAR, want_lp=not last, want_sq=(not last) and need_sq, want_f32=last,
                              want_abs=last and want_abs)
             cur, cur_sq = o.get("lp"), o.get("sq")
             if last:
@@ -126,12 +127,12 @@ def gs_forward(yt_lp, convs, gdns, k=5, strides=(2, 2, 2, 2), save=True):
             S.layers.append(("tail", None, cur))
         else:
             spec = hp.ConvSpec(True, w.shape[0], w.shape[1], k, strides[i])
-            o = spec.forward(cur, w, b, EPI_LINEAR, want_sq=True)
+            o = spec.forward(cur, w, b, EPI_LINEAR, want_sq=not hp.gdn_fused_ok(cur.dtype, w.shape[1]))
             S.layers.append(("deconv", spec, cur))
             gp, bp = gdns[i]
             gamma, beta = _gdn_params(gp, bp)
-            yv, nrm = hp.gdn_forward(o["lp"], o["sq"], gamma, beta)
-            S.layers.append(("gdn", (o["lp"], o["sq"], nrm, gamma), None))
+            yv, nrm = hp.gdn_forward(o["lp"], o.get("sq"), gamma, beta)
+            S.layers.append(("gdn", (o["lp"], o.get("sq"), nrm, gamma), None))
             cur = yv
     S.convs, S.gdns = convs, gdns
     return raw, (S if save else None)

@@ -1,0 +1,463 @@
+// Fused GDN / IGDN kernels on tcgen05 (sm_100a) -- modelling/layers/gdn.py:79-88 and its autograd.
+//
+// GDN is a 1x1 "convolution": the activation is a [P pixels][C] bf16 matrix, so a tile is 128 consecutive
+// rows (C/64 TMA boxes of [128 x 64] in the canonical K-major SWIZZLE_128B layout).  gamma (C x C bf16,
+// 72 KB for C = 192) stays resident in shared memory for the whole persistent CTA.
+//
+//   forward : x tile --TMA--> smem;  8 warps square it into the A operand;  UMMA n = x^2 . gamma^T;  epilogue
+//             r = rsqrt(beta + n), y = x r  written IN PLACE over x and x^2;  TMA stores of y and r.
+//             HBM traffic: read x, write y, write r (3 passes; no x^2 tensor exists in global memory).
+//   backward: g, x, r tiles --TMA--> smem;  t = g x r^3 (in place over r), u = g r (in place over g);
+//             UMMA a = t . gamma;  dx = u - x a (over u), x^2 (over x);  TMA stores of dx, t, x^2;  column sums
+//             of t (d beta) accumulated per CTA.  6 passes instead of 10 for the unfused sequence.
+//
+// warp 0: TMA loads | warp 1: MMA issue + TMEM owner | warp 2: TMA stores | warps 3-10: 256 workers, two
+// threads per tile row (each owns half of the channels; warps w and w+4 share a TMEM lane quarter).
+#include <cuda.h>
+
+#include <initializer_list>
+
+#include "tmap.cuh"
+#include "umma_ptx.cuh"
+
+using namespace umma;
+
+namespace {
+
+constexpr int G_THREADS = 352;
+constexpr int G_WORKERS = 256;
+constexpr int G_CHUNK = 16384;                 // [128 rows x 128 B]
+
+__device__ __forceinline__ void named_bar(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(m)),
+               "r"(smem_u32(src)), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+__device__ __forceinline__ void unpack8(const uint4& u, float* f) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = __bfloat1622float2(h[i]);
+    f[2 * i] = t.x; f[2 * i + 1] = t.y;
+  }
+}
+__device__ __forceinline__ uint4 pack8(const float* f) {
+  uint4 u;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+  return u;
+}
+// byte offset of 16-byte unit U (8 channels) of tile row r in the [chunk][128 rows][128 B] swizzled tile
+__device__ __forceinline__ uint32_t unit_off(int r, int U) {
+  return (uint32_t)((U >> 3) * G_CHUNK + r * 128 + (((U & 7) ^ (r & 7)) << 4));
+}
+
+struct GdnParams {
+  const float* beta;       // forward only
+  float* colsum_part;      // backward only: [gridDim.x][C]
+  int64_t P;
+  int tiles;
+  int inverse;
+};
+
+template <int C>
+struct GCfg {
+  static constexpr int KC = C / 64;
+  static constexpr int TILE = KC * G_CHUNK;
+  static constexpr int GAMMA = C * C * 2;
+  static constexpr int TMEM_COLS = C <= 64 ? 64 : (C <= 128 ? 128 : 256);
+  static constexpr int SMEM = 1024 + GAMMA + 3 * TILE + 1024 /*beta*/ + 256;
+};
+
+// ---------------------------------------------------------------------------------------
+// forward
+// ---------------------------------------------------------------------------------------
+template <int C>
+__global__ void __launch_bounds__(G_THREADS, 1)
+gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmY,
+                    const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmG,
+                    const __grid_constant__ GdnParams p) {
+  using Cfg = GCfg<C>;
+  constexpr int KC = Cfg::KC;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* gam = smem;                           // KC chunks of [C rows x 128 B]
+  uint8_t* xs = gam + Cfg::GAMMA;                // [2][TILE]   x, later y
+  uint8_t* a2 = xs + 2 * Cfg::TILE;              // [TILE]      x^2, later r
+  float* beta_s = reinterpret_cast<float*>(a2 + Cfg::TILE);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(beta_s + 256);
+  uint64_t* g_full = bars;
+  uint64_t* xs_full = bars + 1;     // [2]
+  uint64_t* xs_empty = bars + 3;    // [2]  store warp, after the y store has finished READING smem
+  uint64_t* a2_full = bars + 5;     // 256 worker arrivals
+  uint64_t* a2_empty = bars + 6;    // store warp
+  uint64_t* tfull = bars + 7;       // tcgen05.commit
+  uint64_t* out_full = bars + 8;    // 256 worker arrivals
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x; i < 256; i += G_THREADS) beta_s[i] = i < C ? p.beta[i] : 1.f;
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmX); prefetch_tmap(&tmY); prefetch_tmap(&tmR); prefetch_tmap(&tmG);
+    mbar_init(g_full, 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(&xs_full[s], 1); mbar_init(&xs_empty[s], 1); }
+    mbar_init(a2_full, G_WORKERS); mbar_init(a2_empty, 1); mbar_init(tfull, 1); mbar_init(out_full, G_WORKERS);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_arrive_expect_tx(g_full, Cfg::GAMMA);
+      for (int c = 0; c < KC; ++c) tma_load_2d(gam + c * (C * 128), &tmG, g_full, c * 64, 0);
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
+        const int b = it & 1;
+        mbar_wait(&xs_empty[b], ((it >> 1) & 1) ^ 1);
+        mbar_arrive_expect_tx(&xs_full[b], Cfg::TILE);
+        for (int c = 0; c < KC; ++c) tma_load_2d(xs + b * Cfg::TILE + c * G_CHUNK, &tmX, &xs_full[b], c * 64, tile * 128);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, C, 0, 0);
+      mbar_wait(g_full, 0);
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
+        mbar_wait(a2_full, it & 1);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(a2), b_addr = smem_u32(gam);
+#pragma unroll
+        for (int k = 0; k < C / 16; ++k)
+          mma_bf16_ss(tmem_base, make_smem_desc_sw128(a_addr + (k >> 2) * G_CHUNK + (k & 3) * 32, 16, 1024),
+                      make_smem_desc_sw128(b_addr + (k >> 2) * (C * 128) + (k & 3) * 32, 16, 1024), idesc, k != 0);
+        mma_commit(tfull);
+      }
+    }
+  } else if (warp == 2) {
+    if (lane == 0) {
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
+        const int b = it & 1;
+        mbar_wait(out_full, it & 1);
+        for (int c = 0; c < KC; ++c) tma_store_2d(&tmY, xs + b * Cfg::TILE + c * G_CHUNK, c * 64, tile * 128);
+        for (int c = 0; c < KC; ++c) tma_store_2d(&tmR, a2 + c * G_CHUNK, c * 64, tile * 128);
+        bulk_commit();
+        bulk_wait_read0();
+        mbar_arrive(&xs_empty[b]);
+        mbar_arrive(a2_empty);
+      }
+      bulk_wait0();
+    }
+  } else {
+    const int w = warp - 3;                       // 0..7
+    const int q = warp & 3, half = w >> 2;
+    const int row = q * 32 + lane;
+    constexpr int UH = C / 16;                    // 16-byte units per half row
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
+      const int b = it & 1;
+      uint8_t* xt = xs + b * Cfg::TILE;
+      mbar_wait(&xs_full[b], (it >> 1) & 1);
+      mbar_wait(a2_empty, (it & 1) ^ 1);
+#pragma unroll
+      for (int uu = 0; uu < UH; ++uu) {
+        const uint32_t o = unit_off(row, half * UH + uu);
+        float f[8];
+        unpack8(*reinterpret_cast<const uint4*>(xt + o), f);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] *= f[e];
+        *reinterpret_cast<uint4*>(a2 + o) = pack8(f);
+      }
+      fence_proxy_async();
+      mbar_arrive(a2_full);
+      mbar_wait(tfull, it & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + half * (C / 2);
+#pragma unroll 2
+      for (int g16 = 0; g16 < C / 32; ++g16) {
+        float v[16];
+        tmem_ld16(taddr + g16 * 16, v);
+        tmem_ld_wait();
+        const int c0 = half * (C / 2) + g16 * 16;
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          const uint32_t o = unit_off(row, (c0 >> 3) + hh);
+          float x[8], y[8], r[8];
+          unpack8(*reinterpret_cast<const uint4*>(xt + o), x);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const float n = v[hh * 8 + e] + beta_s[c0 + hh * 8 + e];
+            r[e] = rsqrtf(n);
+            y[e] = p.inverse ? x[e] * (n * r[e]) : x[e] * r[e];
+          }
+          *reinterpret_cast<uint4*>(xt + o) = pack8(y);
+          *reinterpret_cast<uint4*>(a2 + o) = pack8(r);
+        }
+      }
+      tc_fence_before();
+      fence_proxy_async();
+      mbar_arrive(out_full);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+}
+
+// ---------------------------------------------------------------------------------------
+// backward:  t = g x r^3 | g x r (inverse);  a = t . gamma;  dx = g r - x a | g / r + x a
+// ---------------------------------------------------------------------------------------
+template <int C>
+__global__ void __launch_bounds__(G_THREADS, 1)
+gdn_bwd_umma_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_constant__ CUtensorMap tmX,
+                    const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmDx,
+                    const __grid_constant__ CUtensorMap tmT, const __grid_constant__ CUtensorMap tmSq,
+                    const __grid_constant__ CUtensorMap tmG, const __grid_constant__ GdnParams p) {
+  using Cfg = GCfg<C>;
+  constexpr int KC = Cfg::KC;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* gam = smem;                           // gamma^T as the K-major B operand
+  uint8_t* bg = gam + Cfg::GAMMA;                // g   -> u = g r -> dx
+  uint8_t* bx = bg + Cfg::TILE;                  // x   -> x^2
+  uint8_t* bn = bx + Cfg::TILE;                  // r   -> t
+  uint64_t* bars = reinterpret_cast<uint64_t*>(bn + Cfg::TILE + 1024);
+  uint64_t* g_full = bars;
+  uint64_t* in_full = bars + 1;     // TMA: g, x, r tiles landed
+  uint64_t* in_empty = bars + 2;    // store warp: all three buffers have been read by the TMA stores
+  uint64_t* a_full = bars + 3;      // 256 workers: t (and u) written
+  uint64_t* tfull = bars + 4;
+  uint64_t* out_full = bars + 5;    // 256 workers: dx, x^2 written
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 6);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmGr); prefetch_tmap(&tmX); prefetch_tmap(&tmR); prefetch_tmap(&tmDx); prefetch_tmap(&tmT);
+    prefetch_tmap(&tmSq); prefetch_tmap(&tmG);
+    mbar_init(g_full, 1); mbar_init(in_full, 1); mbar_init(in_empty, 1);
+    mbar_init(a_full, G_WORKERS); mbar_init(tfull, 1); mbar_init(out_full, G_WORKERS);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_arrive_expect_tx(g_full, Cfg::GAMMA);
+      for (int c = 0; c < KC; ++c) tma_load_2d(gam + c * (C * 128), &tmG, g_full, c * 64, 0);
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
+        mbar_wait(in_empty, (it & 1) ^ 1);
+        mbar_arrive_expect_tx(in_full, 3 * Cfg::TILE);
+        for (int c = 0; c < KC; ++c) {
+          tma_load_2d(bg + c * G_CHUNK, &tmGr, in_full, c * 64, tile * 128);
+          tma_load_2d(bx + c * G_CHUNK, &tmX, in_full, c * 64, tile * 128);
+          tma_load_2d(bn + c * G_CHUNK, &tmR, in_full, c * 64, tile * 128);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, C, 0, 0);
+      mbar_wait(g_full, 0);
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
+        mbar_wait(a_full, it & 1);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(bn), b_addr = smem_u32(gam);
+#pragma unroll
+        for (int k = 0; k < C / 16; ++k)
+          mma_bf16_ss(tmem_base, make_smem_desc_sw128(a_addr + (k >> 2) * G_CHUNK + (k & 3) * 32, 16, 1024),
+                      make_smem_desc_sw128(b_addr + (k >> 2) * (C * 128) + (k & 3) * 32, 16, 1024), idesc, k != 0);
+        mma_commit(tfull);
+      }
+    }
+  } else if (warp == 2) {
+    if (lane == 0) {
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
+        mbar_wait(out_full, it & 1);
+        for (int c = 0; c < KC; ++c) {
+          tma_store_2d(&tmDx, bg + c * G_CHUNK, c * 64, tile * 128);
+          tma_store_2d(&tmT, bn + c * G_CHUNK, c * 64, tile * 128);
+          tma_store_2d(&tmSq, bx + c * G_CHUNK, c * 64, tile * 128);
+        }
+        bulk_commit();
+        bulk_wait_read0();
+        mbar_arrive(in_empty);
+      }
+      bulk_wait0();
+    }
+  } else {
+    const int w = warp - 3;
+    const int q = warp & 3, half = w >> 2;
+    const int row = q * 32 + lane;
+    const int wt = threadIdx.x - 96;              // 0..255: column owner for the d(beta) sums
+    constexpr int UH = C / 16;
+    float bsum = 0.f;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
+      mbar_wait(in_full, it & 1);
+#pragma unroll
+      for (int uu = 0; uu < UH; ++uu) {
+        const uint32_t o = unit_off(row, half * UH + uu);
+        float g[8], x[8], r[8], t[8], u[8];
+        unpack8(*reinterpret_cast<const uint4*>(bg + o), g);
+        unpack8(*reinterpret_cast<const uint4*>(bx + o), x);
+        unpack8(*reinterpret_cast<const uint4*>(bn + o), r);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          t[e] = g[e] * x[e] * (p.inverse ? r[e] : r[e] * r[e] * r[e]);
+          u[e] = p.inverse ? g[e] / r[e] : g[e] * r[e];
+        }
+        *reinterpret_cast<uint4*>(bn + o) = pack8(t);
+        *reinterpret_cast<uint4*>(bg + o) = pack8(u);
+      }
+      fence_proxy_async();
+      mbar_arrive(a_full);
+      // d(beta): column sums of the bf16 t tile, while the MMA runs (rows past P are zero: TMA zero fill)
+      named_bar(4, G_WORKERS);
+      if (wt < C) {
+        const int U = wt >> 3, e = wt & 7;
+        float s = 0.f;
+#pragma unroll 8
+        for (int r2 = 0; r2 < 128; ++r2)
+          s += __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(bn + unit_off(r2, U) + e * 2));
+        bsum += s;
+      }
+      mbar_wait(tfull, it & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + half * (C / 2);
+#pragma unroll 2
+      for (int g16 = 0; g16 < C / 32; ++g16) {
+        float v[16];
+        tmem_ld16(taddr + g16 * 16, v);
+        tmem_ld_wait();
+        const int c0 = half * (C / 2) + g16 * 16;
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          const uint32_t o = unit_off(row, (c0 >> 3) + hh);
+          float u[8], x[8], d[8];
+          unpack8(*reinterpret_cast<const uint4*>(bg + o), u);
+          unpack8(*reinterpret_cast<const uint4*>(bx + o), x);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            d[e] = p.inverse ? u[e] + x[e] * v[hh * 8 + e] : u[e] - x[e] * v[hh * 8 + e];
+            x[e] *= x[e];
+          }
+          *reinterpret_cast<uint4*>(bg + o) = pack8(d);
+          *reinterpret_cast<uint4*>(bx + o) = pack8(x);
+        }
+      }
+      tc_fence_before();
+      fence_proxy_async();
+      mbar_arrive(out_full);
+    }
+    if (wt < C) p.colsum_part[(int64_t)blockIdx.x * C + wt] = bsum;
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+}
+
+int make_rows_tmap(CUtensorMap* m, const void* base, int64_t P, int C, int box_rows) {
+  uint64_t dims[2] = {(uint64_t)C, (uint64_t)P};
+  uint64_t strides[1] = {(uint64_t)C * 2};
+  uint32_t box[2] = {64, (uint32_t)box_rows};
+  uint32_t estr[2] = {1, 1};
+  return make_tmap(m, base, 2, dims, strides, box, estr);
+}
+
+int gdn_grid(int tiles) { return tiles < hpc_num_sms() ? tiles : hpc_num_sms(); }
+
+}  // namespace
+
+#define GDN_DISPATCH(C_, ...)      \
+  switch (C_) {                     \
+    case 64: { constexpr int CC = 64; __VA_ARGS__; } break;    \
+    case 128: { constexpr int CC = 128; __VA_ARGS__; } break;  \
+    default: { constexpr int CC = 192; __VA_ARGS__; } break;   \
+  }
+
+static int gdn_check(const char* who, int64_t P, int C, std::initializer_list<const void*> ptrs) {
+  HPC_REQUIRE(P > 0, HPC_ERR_BAD_SHAPE, "%s: empty input", who);
+  HPC_REQUIRE(C == 64 || C == 128 || C == 192, HPC_ERR_UNSUPPORTED, "%s: C=%d not in {64,128,192}", who, C);
+  for (const void* q : ptrs) {
+    HPC_REQUIRE(q, HPC_ERR_BAD_SHAPE, "%s: NULL pointer", who);
+    HPC_REQUIRE(hpc_aligned16(q), HPC_ERR_BAD_ALIGNMENT, "%s: pointers must be 16B aligned", who);
+  }
+  return HPC_OK;
+}
+
+int hpc_gdn_fwd_umma(const void* x_bf16, const void* gamma_bf16, const float* beta, int64_t P, int C, int inverse,
+                     void* y_bf16, void* rnorm_bf16, hpc_stream_t stream) {
+  int rc = gdn_check("hpc_gdn_fwd_umma", P, C, {x_bf16, gamma_bf16, beta, y_bf16, rnorm_bf16});
+  if (rc) return rc;
+  GdnParams kp;
+  kp.beta = beta; kp.colsum_part = nullptr; kp.P = P; kp.tiles = (int)((P + 127) / 128); kp.inverse = inverse;
+  CUtensorMap tmX, tmY, tmR, tmG;
+  if ((rc = make_rows_tmap(&tmX, x_bf16, P, C, 128))) return rc;
+  if ((rc = make_rows_tmap(&tmY, y_bf16, P, C, 128))) return rc;
+  if ((rc = make_rows_tmap(&tmR, rnorm_bf16, P, C, 128))) return rc;
+  if ((rc = make_rows_tmap(&tmG, gamma_bf16, C, C, C))) return rc;
+  HpcProfScope prof(HPC_PROF_GDN, (double)P * C * 2 * 3, stream);
+  auto st = (cudaStream_t)stream;
+  GDN_DISPATCH(C, {
+    static bool attr_set = false;
+    if (!attr_set) {
+      HPC_CUDA(cudaFuncSetAttribute(gdn_fwd_umma_kernel<CC>, cudaFuncAttributeMaxDynamicSharedMemorySize, GCfg<CC>::SMEM));
+      attr_set = true;
+    }
+    gdn_fwd_umma_kernel<CC><<<gdn_grid(kp.tiles), G_THREADS, GCfg<CC>::SMEM, st>>>(tmX, tmY, tmR, tmG, kp);
+  });
+  HPC_LAUNCH_CHECK();
+  return HPC_OK;
+}
+
+int hpc_gdn_bwd_umma_parts(int64_t P) { return gdn_grid((int)((P + 127) / 128)); }
+
+int hpc_gdn_bwd_umma(const void* g_bf16, const void* x_bf16, const void* rnorm_bf16, const void* gammaT_bf16, int64_t P,
+                     int C, int inverse, void* dx_bf16, void* t_bf16, void* xsq_bf16, float* colsum_part,
+                     hpc_stream_t stream) {
+  int rc = gdn_check("hpc_gdn_bwd_umma", P, C, {g_bf16, x_bf16, rnorm_bf16, gammaT_bf16, dx_bf16, t_bf16, xsq_bf16, colsum_part});
+  if (rc) return rc;
+  GdnParams kp;
+  kp.beta = nullptr; kp.colsum_part = colsum_part; kp.P = P; kp.tiles = (int)((P + 127) / 128); kp.inverse = inverse;
+  CUtensorMap tmGr, tmX, tmR, tmDx, tmT, tmSq, tmG;
+  if ((rc = make_rows_tmap(&tmGr, g_bf16, P, C, 128))) return rc;
+  if ((rc = make_rows_tmap(&tmX, x_bf16, P, C, 128))) return rc;
+  if ((rc = make_rows_tmap(&tmR, rnorm_bf16, P, C, 128))) return rc;
+  if ((rc = make_rows_tmap(&tmDx, dx_bf16, P, C, 128))) return rc;
+  if ((rc = make_rows_tmap(&tmT, t_bf16, P, C, 128))) return rc;
+  if ((rc = make_rows_tmap(&tmSq, xsq_bf16, P, C, 128))) return rc;
+  if ((rc = make_rows_tmap(&tmG, gammaT_bf16, C, C, C))) return rc;
+  HpcProfScope prof(HPC_PROF_GDN, (double)P * C * 2 * 6, stream);
+  auto st = (cudaStream_t)stream;
+  GDN_DISPATCH(C, {
+    static bool attr_set = false;
+    if (!attr_set) {
+      HPC_CUDA(cudaFuncSetAttribute(gdn_bwd_umma_kernel<CC>, cudaFuncAttributeMaxDynamicSharedMemorySize, GCfg<CC>::SMEM));
+      attr_set = true;
+    }
+    gdn_bwd_umma_kernel<CC><<<gdn_grid(kp.tiles), G_THREADS, GCfg<CC>::SMEM, st>>>(tmGr, tmX, tmR, tmDx, tmT, tmSq, tmG, kp);
+  });
+  HPC_LAUNCH_CHECK();
+  return HPC_OK;
+}

@@ -358,9 +358,24 @@ def square(x, relu=False):
     return out, ro
 
 
+def gdn_fused_ok(dtype, C):
+    """True when the fused tcgen05 GDN kernels (gdn_umma.cu) serve this layer: they square the activation in
+    shared memory, so the producing conv need not write a squared copy."""
+    return engine() == ENGINE_UMMA and dtype == torch.bfloat16 and C in (64, 128, 192)
+
+
 def gdn_forward(x, xsq, gamma_eff, beta_eff, inverse=False):
-    """x, xsq: NHWC lp; gamma_eff (C,C,1,1) fp32, beta_eff (C,) fp32 -> (y, nrm) NHWC lp."""
+    """x (, xsq): NHWC lp; gamma_eff (C,C,1,1) fp32, beta_eff (C,) fp32 -> (y, nrm) NHWC lp.
+    xsq may be None (computed here, or never materialised on the fused path)."""
     N, H, W, C = x.shape
+    if gdn_fused_ok(x.dtype, C):
+        wp = pack_weight(gamma_eff, _ONE_TAP[0], C, C, C, 1, x.dtype, cache=False)
+        y, nrm = torch.empty_like(x), torch.empty_like(x)
+        check(lib().hpc_gdn_fwd_umma(ptr(x), ptr(wp), ptr(beta_eff), N * H * W, C, int(inverse), ptr(y), ptr(nrm),
+                                     stream()))
+        return y, nrm
+    if xsq is None:
+        xsq, _ = square(x)
     wp = pack_weight(gamma_eff, _ONE_TAP[0], C, C, C, 1, x.dtype, cache=False)
     o = igemm_fwd(xsq, wp, _ONE_TAP[0], _ONE_TAP[1], (H, W), 1, 1, (H, W), C, EPI_IGDN if inverse else EPI_GDN,
                   beta_eff, aux0=x, want_nrm=True)
@@ -370,6 +385,18 @@ def gdn_forward(x, xsq, gamma_eff, beta_eff, inverse=False):
 def gdn_backward(g, x, xsq, nrm, gamma_eff, inverse=False, need_dx=True):
     """SURVEY A.4.  Returns (dx lp, dgamma_eff (C,C,1,1) fp32, dbeta_eff (C,) fp32)."""
     N, H, W, C = x.shape
+    sgn = 0.5 if inverse else -0.5
+    if gdn_fused_ok(x.dtype, C) and need_dx:
+        P = N * H * W
+        wp = pack_weight(gamma_eff, _ONE_TAP[0], C, C, 1, C, x.dtype, cache=False)   # rows=k, cols=i: gamma[i][k]
+        dx, t, sq = torch.empty_like(x), torch.empty_like(x), torch.empty_like(x)
+        parts = torch.empty((lib().hpc_gdn_bwd_umma_parts(P), C), dtype=torch.float32, device=x.device)
+        check(lib().hpc_gdn_bwd_umma(ptr(g), ptr(x), ptr(nrm), ptr(wp), P, C, int(inverse), ptr(dx), ptr(t), ptr(sq),
+                                     ptr(parts), stream()))
+        dgamma = igemm_wgrad(t, sq, _ONE_TAP[0], _ONE_TAP[1], 1, sgn).view(C, C, 1, 1)
+        return dx, dgamma, colsum(parts, sgn)
+    if xsq is None:
+        xsq, _ = square(x)
     t = torch.empty_like(x)
     check(lib().hpc_gdn_bwd_t(ptr(g), ptr(x), ptr(nrm), ptr(t), _lib.dtype_code(x), x.numel(), int(inverse),
                               stream()))
@@ -378,7 +405,6 @@ def gdn_backward(g, x, xsq, nrm, gamma_eff, inverse=False, need_dx=True):
         wp = pack_weight(gamma_eff, _ONE_TAP[0], C, C, 1, C, x.dtype, cache=False)  # rows=k, cols=i: gamma[i][k]
         dx = igemm_fwd(t, wp, _ONE_TAP[0], _ONE_TAP[1], (H, W), 1, 1, (H, W), C,
                        EPI_IGDN_BWD if inverse else EPI_GDN_BWD, None, aux0=g, aux1=x, aux2=nrm)["lp"]
-    sgn = 0.5 if inverse else -0.5
     dgamma = igemm_wgrad(t, xsq, _ONE_TAP[0], _ONE_TAP[1], 1, sgn).view(C, C, 1, 1)
     dbeta = colsum(t, sgn)
     return dx, dgamma, dbeta

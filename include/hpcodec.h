@@ -58,7 +58,8 @@ int hpc_device_is_sm100(void);
 #define HPC_PROF_FACTORIZED 3  /* factorised prior fwd + bwd (K4)                                 (bytes) */
 #define HPC_PROF_THIN 4        /* conv_c3 / deconv_c3 / wgrad_c3 (3-channel head and tail)        (bytes) */
 #define HPC_PROF_DISTORTION 5  /* clamp+SSE fwd/bwd, SSIM levels (K6/K7)                          (bytes) */
-#define HPC_PROF_NCLASSES 6
+#define HPC_PROF_GDN 6        /* fused GDN forward / backward (gdn_umma.cu)                      (bytes) */
+#define HPC_PROF_NCLASSES 7
 int hpc_prof_enable(int on); /* on!=0: clear the records and start; 0: stop recording (records kept) */
 int hpc_prof_read(int cls, double* ms_total, unsigned long long* launches, double* work_total);
 
@@ -365,6 +366,21 @@ int hpc_wgrad_c3(const void* wide_nhwc, int lp_dtype, const float* thin_nchw, in
                  float* gw, int64_t w_sr, int64_t w_sc, void* scratch, size_t scratch_bytes,
                  hpc_stream_t stream);
 size_t hpc_wgrad_c3_scratch_bytes(int N, int Cw, int Cs, int H, int W);
+/* Fused GDN / IGDN on tcgen05 (sm_100a, bf16 activations, fp32 accumulate) -- modelling/layers/gdn.py:79-88.
+ * The activation is a [P pixels][C] row-major bf16 matrix (NHWC flattened), C in {64,128,192}.
+ *  gdn_fwd_umma: n = beta + x^2 . gamma^T ; rnorm = rsqrt(n) ; y = x*rnorm (inverse: x*n*rnorm).
+ *                gamma_bf16 = effective gamma (gdn.py:59-62 applied) as [C][C] bf16, row i = output channel.
+ *  gdn_bwd_umma: SURVEY A.4.  t = g x rnorm^3 (inverse: g x rnorm); dx = g rnorm - x (t . gamma) (inverse:
+ *                g / rnorm + x (t . gamma)); also writes t and x^2 (operands of the d(gamma) contraction through
+ *                hpc_igemm_wgrad) and per-CTA column sums of t: colsum_part[parts][C], parts =
+ *                hpc_gdn_bwd_umma_parts(P); d(beta) = -+1/2 * sum over parts.  gammaT_bf16[k][i] = gamma[i][k]. */
+int hpc_gdn_fwd_umma(const void* x_bf16, const void* gamma_bf16, const float* beta, int64_t P, int C, int inverse,
+                     void* y_bf16, void* rnorm_bf16, hpc_stream_t stream);
+int hpc_gdn_bwd_umma_parts(int64_t P);
+int hpc_gdn_bwd_umma(const void* g_bf16, const void* x_bf16, const void* rnorm_bf16, const void* gammaT_bf16, int64_t P,
+                     int C, int inverse, void* dx_bf16, void* t_bf16, void* xsq_bf16, float* colsum_part,
+                     hpc_stream_t stream);
+
 /* tcgen05 (sm_100a, bf16 operands, fp32 accumulate) versions of the three thin-channel kernels above; same
  * arithmetic, same reference call sites (analysis.py:55, synthesis.py:55-57 and their autograd).
  *   pack_c3_weight:  w[cw*w_sr + cs*w_sc + kh*5+kw] -> kmaj [Cw][128] bf16 (k = cs*25+kh*5+kw contiguous, zero padded;

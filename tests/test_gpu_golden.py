@@ -158,7 +158,7 @@ def test_whole_model_against_reference_outputs(name, mode):
             ref = g["grad." + k]
             d = digest(p.grad.float().cpu())
             nrm, nrm0 = float(d[0]), float(ref[0])
-            assert abs(nrm - nrm0) <= (2e-3 if tight else 0.12) * max(nrm0, 1e-12), (k, nrm, nrm0)
+            assert abs(nrm - nrm0) <= (2e-3 if tight else 0.15) * max(nrm0, 1e-12), (k, nrm, nrm0)
             if tight:
                 close(d[2:], ref[2:], 5e-3, k)
     else:
