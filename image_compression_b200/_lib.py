@@ -192,7 +192,7 @@ _SIGNATURES = {
     "hpc_wgrad_c3_umma": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int64, c_int64, c_void_p,
                                   c_size_t, c_void_p]),
     "hpc_wgrad_c3_umma_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
-    "hpc_nchw_channel_sum": (c_int, [c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p]),
+    "hpc_nchw_channel_sum": (c_int, [c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p, c_void_p]),
     "hpc_rd_combine": (c_int, [c_void_p, c_void_p, POINTER(DistTerms), c_float, c_float, c_void_p, c_void_p]),
 }
 

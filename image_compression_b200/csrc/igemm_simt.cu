@@ -268,8 +268,9 @@ int hpc_unpack_wgrad(const float* src, float* dst, int ntaps, int rows, int cols
 // ---------------------------------------------------------------------------------------
 // column sums: out[c] = scale * sum_p x[p][c]   (deterministic two-stage)
 // ---------------------------------------------------------------------------------------
-static constexpr int kColsumRows = 64;  // row-blocks in stage 1
+static constexpr int kColsumParts = 148 * 4;  // row blocks in stage 1
 
+// generic (any C): one thread per column, rows split over blockIdx.y
 template <typename T>
 __global__ void colsum_stage1(const T* __restrict__ x, int64_t P, int C, float* __restrict__ part) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -288,33 +289,73 @@ __global__ void colsum_stage1(const T* __restrict__ x, int64_t P, int C, float* 
   for (; r < r1; ++r) a0 += ld_as_float<T>(x, r * C + c);
   part[(int64_t)blockIdx.y * C + c] = (a0 + a1) + (a2 + a3);
 }
+// vectorised bf16 (C % 8 == 0, C <= 2048): a thread owns one 16-byte unit column and every RL-th row of the
+// block's row range; 256 threads = (C/8 units) x RL row lanes; lanes are combined through shared memory
+__global__ void __launch_bounds__(256)
+colsum_stage1_bf16x8(const __nv_bfloat16* __restrict__ x, int64_t P, int C, float* __restrict__ part) {
+  extern __shared__ float csm[];                // [RL][C]
+  const int units = C >> 3;
+  const int RL = 256 / units;
+  const int u = threadIdx.x % units, rl = threadIdx.x / units;
+  const int64_t rows_per = (P + gridDim.x - 1) / gridDim.x;
+  int64_t r0 = blockIdx.x * rows_per, r1 = r0 + rows_per;
+  if (r1 > P) r1 = P;
+  float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (rl < RL) {
+    for (int64_t r = r0 + rl; r < r1; r += RL) {
+      const uint4 v = *reinterpret_cast<const uint4*>(x + r * C + u * 8);
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float2 t = __bfloat1622float2(h[i]);
+        a[2 * i] += t.x; a[2 * i + 1] += t.y;
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) csm[rl * C + u * 8 + i] = a[i];
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += 256) {
+    float s = 0.f;
+    for (int l = 0; l < RL; ++l) s += csm[l * C + c];
+    part[(int64_t)blockIdx.x * C + c] = s;
+  }
+}
+// 32 lanes per column: fixed-order fp64 partial sums + shuffle tree (deterministic)
 __global__ void colsum_stage2(const float* __restrict__ part, int nparts, int C, float scale, float* __restrict__ out) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  const int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (c >= C) return;
   double s = 0.0;
-  for (int i = 0; i < nparts; ++i) s += (double)part[(int64_t)i * C + c];
-  out[c] = (float)(s * (double)scale);
+  for (int i = lane; i < nparts; i += 32) s += (double)part[(int64_t)i * C + c];
+  s = warp_sum_d(s);
+  if (lane == 0) out[c] = (float)(s * (double)scale);
 }
 size_t hpc_colsum_scratch_bytes(int64_t P, int C) {
   (void)P;
-  return (size_t)kColsumRows * 148 / 16 * (size_t)C * sizeof(float);
+  return (size_t)kColsumParts * (size_t)C * sizeof(float);
 }
 int hpc_colsum(const void* x, int dtype, int64_t P, int C, float scale, float* out, void* scratch,
                size_t scratch_bytes, hpc_stream_t stream) {
   HPC_REQUIRE(P > 0 && C > 0, HPC_ERR_BAD_SHAPE, "hpc_colsum: empty input");
-  int nparts = kColsumRows * 148 / 16;  // 592 row blocks
+  int nparts = kColsumParts;
   if ((int64_t)nparts > P) nparts = (int)P;
   HPC_REQUIRE(scratch && scratch_bytes >= (size_t)nparts * C * sizeof(float), HPC_ERR_BAD_SHAPE,
               "hpc_colsum: scratch too small (%zu < %zu)", scratch_bytes, (size_t)nparts * C * sizeof(float));
-  int threads = C >= 128 ? 128 : ((C + 31) / 32) * 32;
-  dim3 grid((C + threads - 1) / threads, nparts);
   auto st = (cudaStream_t)stream;
-  if (dtype == HPC_BF16)
-    colsum_stage1<__nv_bfloat16><<<grid, threads, 0, st>>>((const __nv_bfloat16*)x, P, C, (float*)scratch);
-  else
-    colsum_stage1<float><<<grid, threads, 0, st>>>((const float*)x, P, C, (float*)scratch);
+  if (dtype == HPC_BF16 && (C & 7) == 0 && C <= 2048 && hpc_aligned16(x)) {
+    const int RL = 256 / (C >> 3);
+    colsum_stage1_bf16x8<<<nparts, 256, (size_t)RL * C * sizeof(float), st>>>((const __nv_bfloat16*)x, P, C, (float*)scratch);
+  } else {
+    int threads = C >= 128 ? 128 : ((C + 31) / 32) * 32;
+    dim3 grid((C + threads - 1) / threads, nparts);
+    if (dtype == HPC_BF16)
+      colsum_stage1<__nv_bfloat16><<<grid, threads, 0, st>>>((const __nv_bfloat16*)x, P, C, (float*)scratch);
+    else
+      colsum_stage1<float><<<grid, threads, 0, st>>>((const float*)x, P, C, (float*)scratch);
+  }
   HPC_LAUNCH_CHECK();
-  colsum_stage2<<<(C + threads - 1) / threads, threads, 0, st>>>((const float*)scratch, nparts, C, scale, out);
+  colsum_stage2<<<(C + 7) / 8, 256, 0, st>>>((const float*)scratch, nparts, C, scale, out);
   HPC_LAUNCH_CHECK();
   return HPC_OK;
 }
@@ -472,22 +513,36 @@ int hpc_cast(const void* src, int src_dtype, void* dst, int dst_dtype, int64_t n
   return HPC_OK;
 }
 
-__global__ void nchw_channel_sum_kernel(const float* __restrict__ x, int N, int C, int64_t HW, float* __restrict__ out) {
+// per-channel sum of an NCHW tensor: one block per (n, c) plane, then a fixed-order fp64 sum over n
+__global__ void nchw_plane_sum_kernel(const float* __restrict__ x, int64_t HW, float* __restrict__ part) {
   __shared__ float sm[32];
-  const int c = blockIdx.x;
-  double tot = 0.0;
-  for (int n = 0; n < N; ++n) {
-    const float* p = x + ((int64_t)n * C + c) * HW;
-    float a = 0.f;
+  const float* p = x + (int64_t)blockIdx.x * HW;
+  float a = 0.f;
+  if ((HW & 3) == 0 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) {
+    const float4* p4 = reinterpret_cast<const float4*>(p);
+    for (int64_t i = threadIdx.x; i < (HW >> 2); i += blockDim.x) {
+      const float4 v = p4[i];
+      a += (v.x + v.y) + (v.z + v.w);
+    }
+  } else {
     for (int64_t i = threadIdx.x; i < HW; i += blockDim.x) a += p[i];
-    float s = block_sum(a, sm);
-    if (threadIdx.x == 0) tot += (double)s;
   }
-  if (threadIdx.x == 0) out[c] = (float)tot;
+  const float s = block_sum(a, sm);
+  if (threadIdx.x == 0) part[blockIdx.x] = s;
 }
-int hpc_nchw_channel_sum(const float* x, int N, int C, int64_t HW, float* out, hpc_stream_t stream) {
+__global__ void nchw_plane_sum_final(const float* __restrict__ part, int N, int C, float* __restrict__ out) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double tot = 0.0;
+  for (int n = 0; n < N; ++n) tot += (double)part[(int64_t)n * C + c];
+  out[c] = (float)tot;
+}
+int hpc_nchw_channel_sum(const float* x, int N, int C, int64_t HW, float* out, float* scratch, hpc_stream_t stream) {
   HPC_REQUIRE(N > 0 && C > 0 && HW > 0, HPC_ERR_BAD_SHAPE, "hpc_nchw_channel_sum: empty tensor");
-  nchw_channel_sum_kernel<<<C, 1024, 0, (cudaStream_t)stream>>>(x, N, C, HW, out);
+  HPC_REQUIRE(scratch, HPC_ERR_BAD_SHAPE, "hpc_nchw_channel_sum: scratch (N*C floats) is NULL");
+  nchw_plane_sum_kernel<<<N * C, 256, 0, (cudaStream_t)stream>>>(x, HW, scratch);
+  HPC_LAUNCH_CHECK();
+  nchw_plane_sum_final<<<(C + 63) / 64, 64, 0, (cudaStream_t)stream>>>(scratch, N, C, out);
   HPC_LAUNCH_CHECK();
   return HPC_OK;
 }

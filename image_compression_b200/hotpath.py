@@ -499,7 +499,8 @@ def deconv_c3_backward(g_nchw, x_nhwc, weight, need_dx=True):
                                         None, _lib.dtype_code(dt), stream()))
     gw = wgrad_c3(x_nhwc, g_nchw, Cw, Cs)
     gb = torch.empty((Cs,), dtype=torch.float32, device=g_nchw.device)
-    check(lib().hpc_nchw_channel_sum(ptr(g_nchw), N, Cs, H2 * W2, ptr(gb), stream()))
+    sc = torch.empty((N * Cs,), dtype=torch.float32, device=g_nchw.device)
+    check(lib().hpc_nchw_channel_sum(ptr(g_nchw), N, Cs, H2 * W2, ptr(gb), ptr(sc), stream()))
     return dx, gw, gb
 
 

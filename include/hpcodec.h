@@ -397,8 +397,8 @@ int hpc_deconv_c3_fwd_umma(const void* x_nhwc_bf16, const void* w_nmaj_bf16, con
 int hpc_wgrad_c3_umma(const void* wide_nhwc_bf16, const float* thin_nchw, int N, int Cw, int H, int W, float* gw,
                       int64_t w_sr, int64_t w_sc, void* workspace, size_t workspace_bytes, hpc_stream_t stream);
 size_t hpc_wgrad_c3_umma_workspace_bytes(int N, int Cw, int H, int W);
-/* per-channel sum of an NCHW float tensor (bias grad of the tail deconv) */
-int hpc_nchw_channel_sum(const float* x, int N, int C, int64_t HW, float* out, hpc_stream_t stream);
+/* per-channel sum of an NCHW float tensor (bias grad of the tail deconv); scratch: N*C floats */
+int hpc_nchw_channel_sum(const float* x, int N, int C, int64_t HW, float* out, float* scratch, hpc_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------
  * Rate-distortion combine (bmshl2018.py:84-96): device scalars in, device scalars out, no sync
