@@ -1,0 +1,79 @@
+"""World-size-2 CPU (gloo) tests of the N>1 host logic: flat gradient aliasing + mean all-reduce equals the
+gradient of the concatenated batch with per-replica normalisation (engine/trainer.py:180), per-image
+evaluation sharding and gather."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from image_compression_b200 import sharding
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, results):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.manual_seed(0)
+        net = torch.nn.Sequential(torch.nn.Linear(5, 7), torch.nn.Tanh(), torch.nn.Linear(7, 3))
+        sharding.broadcast_parameters(net)
+        fg = sharding.FlatGradients(net.parameters())
+        assert all(p.grad.data_ptr() >= fg.flat.data_ptr() for p in net.parameters())
+        x = torch.randn(4 * world, 5, generator=torch.Generator().manual_seed(1))
+        xs = x[rank * 4:(rank + 1) * 4]
+        for _ in range(2):                       # second pass checks fg.zero() really resets the aliased grads
+            fg.zero()
+            net(xs).pow(2).mean().backward()     # local normalisation, like a DataParallel replica
+            fg.all_reduce_mean()
+        # reference: mean over replicas of the per-replica losses on one process
+        ref = torch.nn.Sequential(torch.nn.Linear(5, 7), torch.nn.Tanh(), torch.nn.Linear(7, 3))
+        ref.load_state_dict(net.state_dict())
+        sum(ref(x[r * 4:(r + 1) * 4]).pow(2).mean() for r in range(world)).div(world).backward()
+        err = max(float((p.grad - q.grad).abs().max()) for p, q in zip(net.parameters(), ref.parameters()))
+        # evaluation sharding: 7 images over 2 ranks, 3 metrics each
+        idx = sharding.shard_indices(7, rank, world)
+        vals = torch.tensor([[i, 10.0 * i, -i] for i in idx], dtype=torch.float32).reshape(len(idx), 3)
+        table = sharding.gather_per_image(vals, 7, rank, world)
+        ok = torch.equal(table, torch.tensor([[i, 10.0 * i, -i] for i in range(7)], dtype=torch.float32))
+        results[rank] = (err, ok, fg.numel, fg.flat.numel())
+    finally:
+        dist.destroy_process_group()
+
+
+def test_flat_gradients_and_eval_sharding_world2():
+    world = 2
+    mgr = mp.Manager()
+    results = mgr.dict()
+    mp.spawn(_worker, args=(world, _free_port(), results), nprocs=world, join=True)
+    assert len(results) == world
+    for rank in range(world):
+        err, ok, numel, flat = results[rank]
+        assert err < 1e-6, err
+        assert ok
+        assert numel == 5 * 7 + 7 + 7 * 3 + 3 and flat >= numel and flat % 4 == 0
+
+
+def test_shard_indices_cover_everything_once():
+    for n, w in ((24, 8), (7, 2), (3, 4), (1, 1)):
+        seen = sorted(i for r in range(w) for i in sharding.shard_indices(n, r, w))
+        assert seen == list(range(n))
+    with pytest.raises(ValueError):
+        sharding.shard_indices(4, 2, 2)
+
+
+def test_flat_gradients_single_process_noop():
+    net = torch.nn.Linear(3, 2)
+    fg = sharding.FlatGradients(net.parameters())
+    net(torch.ones(1, 3)).sum().backward()
+    assert fg.all_reduce_mean() is None
+    assert float(fg.flat.abs().sum()) > 0
+    fg.zero()
+    assert float(net.weight.grad.abs().sum()) == 0.0
