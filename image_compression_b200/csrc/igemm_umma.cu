@@ -42,7 +42,7 @@ struct FwdCfg {
   static constexpr int STAGES = (200 * 1024 / STAGE_BYTES) > 8 ? 8 : (200 * 1024 / STAGE_BYTES);
   static constexpr int ACC_STRIDE = BLOCK_N <= 32 ? 32 : (BLOCK_N <= 64 ? 64 : (BLOCK_N <= 128 ? 128 : 256));
   static constexpr int TMEM_COLS = 2 * ACC_STRIDE;          // 64..512, power of two
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + 1024 /*bias*/;
 };
 
 __device__ __forceinline__ void tile_coords(const FwdKParams& p, int tile, int& ph, int& n0, int& i0, int& j0) {
@@ -170,8 +170,11 @@ igemm_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   uint64_t* tfull_bar = bars + 2 * Cfg::STAGES; // [2]       MMA -> epilogue
   uint64_t* tempty_bar = tfull_bar + 2;         // [2]       epilogue -> MMA
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  float* bias_s = reinterpret_cast<float*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256);   // bias staged once per CTA
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (p.epi.bias)
+    for (int i = threadIdx.x; i < BLOCK_N; i += FW_THREADS) bias_s[i] = p.epi.bias[i];
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
@@ -241,6 +244,8 @@ igemm_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     // ================================ epilogue (4 warps) ==========================
     const int q = warp & 3;                 // TMEM lane quarter this warp may access
     const int row = q * 32 + lane;          // tile row == TMEM lane
+    EpiArgs epi = p.epi;
+    if (epi.bias) epi.bias = bias_s;        // broadcast shared-memory reads instead of 48 global loads per tile
     int acc = 0; uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
       int ph, n0, i0, j0;
@@ -260,8 +265,8 @@ igemm_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         tmem_ld16(taddr + c0, v);
         tmem_ld_wait();
         if (valid) {
-          epilogue8(p.epi, v, obase + c0, c0);
-          epilogue8(p.epi, v + 8, obase + c0 + 8, c0 + 8);
+          epilogue8(epi, v, obase + c0, c0);
+          epilogue8(epi, v + 8, obase + c0 + 8, c0 + 8);
         }
       }
       tc_fence_before();
