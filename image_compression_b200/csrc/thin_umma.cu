@@ -60,6 +60,32 @@ __device__ __forceinline__ void load_patch(float* patch, const float* __restrict
   }
 }
 
+
+// Register-prefetched variant: `patch_fetch` issues all global loads of the NEXT tile's patch (independent, so
+// their latencies overlap each other and the current tile's gather), `patch_commit` writes them to smem later.
+template <int PH, int PWV, int NPF>
+__device__ __forceinline__ void patch_fetch(float (&pf)[NPF], const float* __restrict__ x, int n, int H, int W, int i0,
+                                            int j0, int tid) {
+#pragma unroll
+  for (int k = 0; k < NPF; ++k) {
+    const int e = tid + k * 128;
+    const int c = e % PWV, r = (e / PWV) % PH, cs = e / (PWV * PH);
+    const int gy = 2 * i0 - 2 + r, gx = 2 * j0 - 2 + c;
+    pf[k] = (cs < TCS && gy >= 0 && gy < H && gx >= 0 && gx < W) ? __ldg(&x[(((int64_t)n * TCS + cs) * H + gy) * W + gx]) : 0.f;
+  }
+}
+template <int PH, int PWV, int PW, int NPF>
+__device__ __forceinline__ void patch_commit(float* patch, const float (&pf)[NPF], int tid) {
+#pragma unroll
+  for (int k = 0; k < NPF; ++k) {
+    const int e = tid + k * 128;
+    if (e < TCS * PH * PWV) {
+      const int c = e % PWV, r = (e / PWV) % PH, cs = e / (PWV * PH);
+      patch[(cs * PH + r) * PW + c] = pf[k];
+    }
+  }
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------------------------------
@@ -185,15 +211,24 @@ conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_consta
     // ============================ im2col builders (128 threads) ============================
     const int t = threadIdx.x - 32;
     const int il = t >> 4, jl = t & 15;
+    constexpr int NPF = (TCS * T1_PH * T1_PWV + 127) / 128;
+    float pf[NPF];
+    if ((int)blockIdx.x < p.total_tiles) {
+      const int n = blockIdx.x / tiles_per_img, r = blockIdx.x % tiles_per_img;
+      patch_fetch<T1_PH, T1_PWV, NPF>(pf, p.x, n, p.H, p.W, (r / p.tiles_w) * T1_TH, (r % p.tiles_w) * T1_TW, t);
+    }
     int it = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
       const int buf = it & 1;
       const uint32_t ph = (it >> 1) & 1;
-      const int n = tile / tiles_per_img, r = tile % tiles_per_img;
-      const int i0 = (r / p.tiles_w) * T1_TH, j0 = (r % p.tiles_w) * T1_TW;
       named_bar(1, 128);                                   // previous gather finished with `patch`
-      load_patch<T1_PH, T1_PWV, T1_PW>(patch, p.x, n, p.H, p.W, i0, j0, t, 128);
+      patch_commit<T1_PH, T1_PWV, T1_PW, NPF>(patch, pf, t);
       named_bar(1, 128);
+      const int nxt = tile + gridDim.x;
+      if (nxt < p.total_tiles) {
+        const int n = nxt / tiles_per_img, r = nxt % tiles_per_img;
+        patch_fetch<T1_PH, T1_PWV, NPF>(pf, p.x, n, p.H, p.W, (r / p.tiles_w) * T1_TH, (r % p.tiles_w) * T1_TW, t);
+      }
       mbar_wait(&empty_a[buf], ph ^ 1);
       uint8_t* arow = smem_a + buf * T1_A_BYTES + t * 128;
 #pragma unroll
@@ -224,11 +259,13 @@ conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_consta
         // reuse buffer 0 back to back across tiles), so one barrier per chunk orders writers after readers
         uint8_t* st_lp = stage + ((it * (CW / 64) + cc) & 1) * 2 * T1_ST_BYTES;
         uint8_t* st_sq = st_lp + T1_ST_BYTES;
+        float v4[4][16];
+#pragma unroll
+        for (int c16 = 0; c16 < 4; ++c16) tmem_ld16(taddr + cc * 64 + c16 * 16, v4[c16]);
+        tmem_ld_wait();
 #pragma unroll
         for (int c16 = 0; c16 < 4; ++c16) {
-          float v[16];
-          tmem_ld16(taddr + cc * 64 + c16 * 16, v);
-          tmem_ld_wait();
+          const float* v = v4[c16];
           uint32_t lo[8], sq[8];
 #pragma unroll
           for (int e = 0; e < 8; ++e) {
@@ -328,7 +365,7 @@ int hpc_conv_c3_fwd_umma(const float* x_nchw, const void* w_kmaj_bf16, const flo
 // ---------------------------------------------------------------------------------------
 namespace {
 constexpr int T2_TH = 8, T2_TW = 16, T2_IH = T2_TH - 2, T2_IW = T2_TW - 2;
-constexpr int T2_THREADS = 192;
+constexpr int T2_THREADS = 320;                          // TMA, MMA, 8 epilogue warps
 constexpr int T2_STAGES = 3;
 constexpr int T2_PROW = 77;                                // floats per pixel row of P in smem (75 + pad, odd)
 
@@ -370,7 +407,7 @@ deconv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
     for (int s = 0; s < T2_STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], 4); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], 8); }
     mbar_init(b_full, 1);
     fence_barrier_init();
   }
@@ -422,13 +459,15 @@ deconv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       }
     }
   } else {
-    const int t = threadIdx.x - 64;
-    const int q = warp & 3;
+    const int t = threadIdx.x - 64;                         // 0..255
+    const int q = warp & 3, half = (warp - 2) >> 2;         // warps w and w+4 share a TMEM lane quarter
     const int row = q * 32 + lane;                          // patch pixel index = il*16 + jl
     const int OH = 2 * p.H, OW = 2 * p.W;
-    float bs[TCS];
-#pragma unroll
-    for (int cs = 0; cs < TCS; ++cs) bs[cs] = p.bias ? p.bias[cs] : 0.f;
+    // gather work item: one interior input pixel x one output channel -> its 2x2 outputs (252 of 256 threads)
+    const int g_cs = t / (T2_IH * T2_IW), g_px = t % (T2_IH * T2_IW);
+    const int g_i = g_px / T2_IW, g_j = g_px % T2_IW;
+    const bool g_on = t < TCS * T2_IH * T2_IW;
+    const float bs = (g_on && p.bias) ? p.bias[g_cs] : 0.f;
     int it = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
       const int acc = it & 1;
@@ -438,36 +477,50 @@ deconv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       mbar_wait(&tfull[acc], aph);
       tc_fence_after();
       const uint32_t taddr = tmem_base + acc * 128 + ((uint32_t)(q * 32) << 16);
-      named_bar(3, 128);                                    // previous tile's gather is done with Ps
+      named_bar(3, 256);                                    // previous tile's gather is done with Ps
+      if (half == 0) {
+        float v[3][16];
 #pragma unroll
-      for (int c16 = 0; c16 < KPAD / 16; ++c16) {
-        float v[16];
-        tmem_ld16(taddr + c16 * 16, v);
+        for (int c = 0; c < 3; ++c) tmem_ld16(taddr + c * 16, v[c]);
         tmem_ld_wait();
 #pragma unroll
-        for (int e = 0; e < 16; ++e)
-          if (c16 * 16 + e < 75) Ps[row * T2_PROW + c16 * 16 + e] = v[e];
+        for (int c = 0; c < 3; ++c)
+#pragma unroll
+          for (int e = 0; e < 16; ++e) Ps[row * T2_PROW + c * 16 + e] = v[c][e];
+      } else {
+        float v[2][16];
+#pragma unroll
+        for (int c = 0; c < 2; ++c) tmem_ld16(taddr + 48 + c * 16, v[c]);
+        tmem_ld_wait();
+#pragma unroll
+        for (int c = 0; c < 2; ++c)
+#pragma unroll
+          for (int e = 0; e < 16; ++e)
+            if (48 + c * 16 + e < 75) Ps[row * T2_PROW + 48 + c * 16 + e] = v[c][e];
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[acc]);
-      named_bar(3, 128);
-      // gather the 2x2 output phases of the 6x14 interior: (cs, ro, co) with co fastest
-      for (int idx = t; idx < TCS * 2 * T2_IH * 2 * T2_IW; idx += 128) {
-        const int co = idx % (2 * T2_IW), ro = (idx / (2 * T2_IW)) % (2 * T2_IH), cs = idx / (4 * T2_IH * T2_IW);
-        const int a = ro & 1, b = co & 1;
-        const int gi = ii0 + (ro >> 1), gj = jj0 + (co >> 1);
-        if (gi >= p.H || gj >= p.W) continue;
-        const int il = (ro >> 1) + 1, jl = (co >> 1) + 1;
-        float s = bs[cs];
-        for (int kh = a; kh < 5; kh += 2) {
-          const int pr = il + (a + 2 - kh) / 2;
-          for (int kw = b; kw < 5; kw += 2) {
-            const int pc = jl + (b + 2 - kw) / 2;
-            s += Ps[(pr * T2_TW + pc) * T2_PROW + cs * 25 + kh * 5 + kw];
+      named_bar(3, 256);
+      const int gi = ii0 + g_i, gj = jj0 + g_j;
+      if (g_on && gi < p.H && gj < p.W) {
+        const float* P0 = Ps + ((g_i + 1) * T2_TW + (g_j + 1)) * T2_PROW + g_cs * 25;
+        float* o = p.out + (((int64_t)n * TCS + g_cs) * OH + 2 * gi) * OW + 2 * gj;
+#pragma unroll
+        for (int a = 0; a < 2; ++a) {
+          float s0 = bs, s1 = bs;
+#pragma unroll
+          for (int kh = a; kh < 5; kh += 2) {
+            const int dh = (a + 2 - kh) / 2;
+#pragma unroll
+            for (int kw = 0; kw < 5; ++kw) {
+              const int b = kw & 1, dw = (b + 2 - kw) / 2;
+              const float pv = P0[(dh * T2_TW + dw) * T2_PROW + kh * 5 + kw];
+              if (b == 0) s0 += pv; else s1 += pv;
+            }
           }
+          *reinterpret_cast<float2*>(o + (int64_t)a * OW) = make_float2(s0, s1);
         }
-        p.out[(((int64_t)n * TCS + cs) * OH + 2 * gi + a) * OW + 2 * gj + b] = s;
       }
     }
   }
@@ -629,19 +682,31 @@ wgrad_c3_umma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
     const int px = t & 63, half = t >> 6;                  // pixel of the K block, which half of its 10 units
     const int il = px >> 4, jl = px & 15;
     int stage = 0; uint32_t phase = 0;
+    constexpr int NPF = (TCS * T3_PH * T3_PWV + 127) / 128;
+    float pf[NPF];
+    if (kb0 < kb1) {
+      const int n = kb0 / tiles_per_img, r = kb0 % tiles_per_img;
+      patch_fetch<T3_PH, T3_PWV, NPF>(pf, p.thin, n, 2 * p.H, 2 * p.W, (r / p.tiles_w) * T3_TH, (r % p.tiles_w) * T3_TW, t);
+    }
     for (int kb = kb0; kb < kb1; ++kb) {
-      const int n = kb / tiles_per_img, r = kb % tiles_per_img;
-      const int i0 = (r / p.tiles_w) * T3_TH, j0 = (r % p.tiles_w) * T3_TW;
       named_bar(1, 128);
-      load_patch<T3_PH, T3_PWV, T3_PW>(patch, p.thin, n, 2 * p.H, 2 * p.W, i0, j0, t, 128);
+      patch_commit<T3_PH, T3_PWV, T3_PW, NPF>(patch, pf, t);
       named_bar(1, 128);
+      if (kb + 1 < kb1) {
+        const int n = (kb + 1) / tiles_per_img, r = (kb + 1) % tiles_per_img;
+        patch_fetch<T3_PH, T3_PWV, NPF>(pf, p.thin, n, 2 * p.H, 2 * p.W, (r / p.tiles_w) * T3_TH, (r % p.tiles_w) * T3_TW, t);
+      }
       mbar_wait(&empty_bar[stage], phase ^ 1);
       uint8_t* arow = smem + stage * Cfg::STAGE_BYTES + px * 128;
+      if (half == 0) {                                    // units 0..4 | 5..9 of the 80-long row (compile-time k)
 #pragma unroll
-      for (int uu = 0; uu < 5; ++uu) {
-        const int u = half * 5 + uu;                       // units 0..4 | 5..9 of the 80-long row
-        const uint4 v = im2col_unit<T3_PH, T3_PW>(patch, il, jl, u);
-        *reinterpret_cast<uint4*>(arow + (u >> 3) * ATOM_BYTES + (((u & 7) ^ (px & 7)) << 4)) = v;
+        for (int u = 0; u < 5; ++u)
+          *reinterpret_cast<uint4*>(arow + (((u & 7) ^ (px & 7)) << 4)) = im2col_unit<T3_PH, T3_PW>(patch, il, jl, u);
+      } else {
+#pragma unroll
+        for (int u = 5; u < 10; ++u)
+          *reinterpret_cast<uint4*>(arow + (u >> 3) * ATOM_BYTES + (((u & 7) ^ (px & 7)) << 4)) =
+              im2col_unit<T3_PH, T3_PW>(patch, il, jl, u);
       }
       fence_proxy_async();
       mbar_arrive(&full_bar[stage]);
