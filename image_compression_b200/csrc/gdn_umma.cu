@@ -173,39 +173,54 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
       uint8_t* xt = xs + b * Cfg::TILE;
       mbar_wait(&xs_full[b], (it >> 1) & 1);
       mbar_wait(a2_empty, (it & 1) ^ 1);
+      {   // all loads first (xt and a2 may alias for the compiler: a load/store chain would serialise on LDS latency)
+        uint4 raw[UH];
 #pragma unroll
-      for (int uu = 0; uu < UH; ++uu) {
-        const uint32_t o = unit_off(row, half * UH + uu);
-        float f[8];
-        unpack8(*reinterpret_cast<const uint4*>(xt + o), f);
+        for (int uu = 0; uu < UH; ++uu) raw[uu] = *reinterpret_cast<const uint4*>(xt + unit_off(row, half * UH + uu));
 #pragma unroll
-        for (int e = 0; e < 8; ++e) f[e] *= f[e];
-        *reinterpret_cast<uint4*>(a2 + o) = pack8(f);
+        for (int uu = 0; uu < UH; ++uu) {
+          float f[8];
+          unpack8(raw[uu], f);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) f[e] *= f[e];
+          *reinterpret_cast<uint4*>(a2 + unit_off(row, half * UH + uu)) = pack8(f);
+        }
       }
       fence_proxy_async();
       mbar_arrive(a2_full);
       mbar_wait(tfull, it & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + half * (C / 2);
-#pragma unroll 2
-      for (int g16 = 0; g16 < C / 32; ++g16) {
-        float v[16];
-        tmem_ld16(taddr + g16 * 16, v);
+      constexpr int GB = (C / 32) % 3 == 0 ? 3 : ((C / 32) % 2 == 0 ? 2 : 1);      // ld16 groups per batch
+#pragma unroll 1
+      for (int gb = 0; gb < C / 32; gb += GB) {
+        float v[GB][16];
+        uint4 xr[GB][2];
+#pragma unroll
+        for (int j = 0; j < GB; ++j) tmem_ld16(taddr + (gb + j) * 16, v[j]);
+#pragma unroll
+        for (int j = 0; j < GB; ++j)
+#pragma unroll
+          for (int hh = 0; hh < 2; ++hh)
+            xr[j][hh] = *reinterpret_cast<const uint4*>(xt + unit_off(row, ((half * (C / 2) + (gb + j) * 16) >> 3) + hh));
         tmem_ld_wait();
-        const int c0 = half * (C / 2) + g16 * 16;
 #pragma unroll
-        for (int hh = 0; hh < 2; ++hh) {
-          const uint32_t o = unit_off(row, (c0 >> 3) + hh);
-          float x[8], y[8], r[8];
-          unpack8(*reinterpret_cast<const uint4*>(xt + o), x);
+        for (int j = 0; j < GB; ++j) {
+          const int c0 = half * (C / 2) + (gb + j) * 16;
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const float n = v[hh * 8 + e] + beta_s[c0 + hh * 8 + e];
-            r[e] = rsqrtf(n);
-            y[e] = p.inverse ? x[e] * (n * r[e]) : x[e] * r[e];
+          for (int hh = 0; hh < 2; ++hh) {
+            const uint32_t o = unit_off(row, (c0 >> 3) + hh);
+            float x[8], y[8], r[8];
+            unpack8(xr[j][hh], x);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const float n = v[j][hh * 8 + e] + beta_s[c0 + hh * 8 + e];
+              r[e] = rsqrtf(n);
+              y[e] = p.inverse ? x[e] * (n * r[e]) : x[e] * r[e];
+            }
+            *reinterpret_cast<uint4*>(xt + o) = pack8(y);
+            *reinterpret_cast<uint4*>(a2 + o) = pack8(r);
           }
-          *reinterpret_cast<uint4*>(xt + o) = pack8(y);
-          *reinterpret_cast<uint4*>(a2 + o) = pack8(r);
         }
       }
       tc_fence_before();
@@ -315,20 +330,32 @@ gdn_bwd_umma_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
     int it = 0;
     for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
       mbar_wait(in_full, it & 1);
+      constexpr int UB = UH % 4 == 0 ? 4 : (UH % 3 == 0 ? 3 : (UH % 2 == 0 ? 2 : 1));
+#pragma unroll 1
+      for (int ub = 0; ub < UH; ub += UB) {
+        uint4 rg[UB], rx[UB], rr[UB];
 #pragma unroll
-      for (int uu = 0; uu < UH; ++uu) {
-        const uint32_t o = unit_off(row, half * UH + uu);
-        float g[8], x[8], r[8], t[8], u[8];
-        unpack8(*reinterpret_cast<const uint4*>(bg + o), g);
-        unpack8(*reinterpret_cast<const uint4*>(bx + o), x);
-        unpack8(*reinterpret_cast<const uint4*>(bn + o), r);
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          t[e] = g[e] * x[e] * (p.inverse ? r[e] : r[e] * r[e] * r[e]);
-          u[e] = p.inverse ? g[e] / r[e] : g[e] * r[e];
+        for (int j = 0; j < UB; ++j) {
+          const uint32_t o = unit_off(row, half * UH + ub + j);
+          rg[j] = *reinterpret_cast<const uint4*>(bg + o);
+          rx[j] = *reinterpret_cast<const uint4*>(bx + o);
+          rr[j] = *reinterpret_cast<const uint4*>(bn + o);
         }
-        *reinterpret_cast<uint4*>(bn + o) = pack8(t);
-        *reinterpret_cast<uint4*>(bg + o) = pack8(u);
+#pragma unroll
+        for (int j = 0; j < UB; ++j) {
+          const uint32_t o = unit_off(row, half * UH + ub + j);
+          float g[8], x[8], r[8], t[8], u[8];
+          unpack8(rg[j], g);
+          unpack8(rx[j], x);
+          unpack8(rr[j], r);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            t[e] = g[e] * x[e] * (p.inverse ? r[e] : r[e] * r[e] * r[e]);
+            u[e] = p.inverse ? g[e] / r[e] : g[e] * r[e];
+          }
+          *reinterpret_cast<uint4*>(bn + o) = pack8(t);
+          *reinterpret_cast<uint4*>(bg + o) = pack8(u);
+        }
       }
       fence_proxy_async();
       mbar_arrive(a_full);
@@ -345,25 +372,39 @@ gdn_bwd_umma_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
       mbar_wait(tfull, it & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + half * (C / 2);
-#pragma unroll 2
-      for (int g16 = 0; g16 < C / 32; ++g16) {
-        float v[16];
-        tmem_ld16(taddr + g16 * 16, v);
-        tmem_ld_wait();
-        const int c0 = half * (C / 2) + g16 * 16;
+      constexpr int GB = (C / 32) % 3 == 0 ? 3 : ((C / 32) % 2 == 0 ? 2 : 1);
+#pragma unroll 1
+      for (int gb = 0; gb < C / 32; gb += GB) {
+        float v[GB][16];
+        uint4 ur[GB][2], xr[GB][2];
 #pragma unroll
-        for (int hh = 0; hh < 2; ++hh) {
-          const uint32_t o = unit_off(row, (c0 >> 3) + hh);
-          float u[8], x[8], d[8];
-          unpack8(*reinterpret_cast<const uint4*>(bg + o), u);
-          unpack8(*reinterpret_cast<const uint4*>(bx + o), x);
+        for (int j = 0; j < GB; ++j) tmem_ld16(taddr + (gb + j) * 16, v[j]);
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            d[e] = p.inverse ? u[e] + x[e] * v[hh * 8 + e] : u[e] - x[e] * v[hh * 8 + e];
-            x[e] *= x[e];
+        for (int j = 0; j < GB; ++j)
+#pragma unroll
+          for (int hh = 0; hh < 2; ++hh) {
+            const uint32_t o = unit_off(row, ((half * (C / 2) + (gb + j) * 16) >> 3) + hh);
+            ur[j][hh] = *reinterpret_cast<const uint4*>(bg + o);
+            xr[j][hh] = *reinterpret_cast<const uint4*>(bx + o);
           }
-          *reinterpret_cast<uint4*>(bg + o) = pack8(d);
-          *reinterpret_cast<uint4*>(bx + o) = pack8(x);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < GB; ++j) {
+          const int c0 = half * (C / 2) + (gb + j) * 16;
+#pragma unroll
+          for (int hh = 0; hh < 2; ++hh) {
+            const uint32_t o = unit_off(row, (c0 >> 3) + hh);
+            float u[8], x[8], d[8];
+            unpack8(ur[j][hh], u);
+            unpack8(xr[j][hh], x);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              d[e] = p.inverse ? u[e] + x[e] * v[j][hh * 8 + e] : u[e] - x[e] * v[j][hh * 8 + e];
+              x[e] *= x[e];
+            }
+            *reinterpret_cast<uint4*>(bg + o) = pack8(d);
+            *reinterpret_cast<uint4*>(bx + o) = pack8(x);
+          }
         }
       }
       tc_fence_before();
