@@ -11,8 +11,8 @@
 //             UMMA a = t . gamma;  dx = u - x a (over u), x^2 (over x);  TMA stores of dx, t, x^2;  column sums
 //             of t (d beta) accumulated per CTA.  6 passes instead of 10 for the unfused sequence.
 //
-// warp 0: TMA loads | warp 1: MMA issue + TMEM owner | warp 2: TMA stores | warps 3-10: 256 workers, two
-// threads per tile row (each owns half of the channels; warps w and w+4 share a TMEM lane quarter).
+// warp 0: TMA loads | warp 1: MMA issue + TMEM owner | warp 2: TMA stores | warps 3-18: 512 workers, four
+// threads per tile row (each owns a quarter of the channels; warps w, w+4, w+8, w+12 share a TMEM lane quarter).
 #include <cuda.h>
 
 #include <initializer_list>
@@ -24,8 +24,8 @@ using namespace umma;
 
 namespace {
 
-constexpr int G_THREADS = 352;
-constexpr int G_WORKERS = 256;
+constexpr int G_WORKERS = 512;                 // 16 worker warps: the elementwise phases are latency bound, warps hide it
+constexpr int G_THREADS = 96 + G_WORKERS;
 constexpr int G_CHUNK = 16384;                 // [128 rows x 128 B]
 
 __device__ __forceinline__ void named_bar(int id, int nthreads) {
@@ -163,10 +163,10 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
       bulk_wait0();
     }
   } else {
-    const int w = warp - 3;                       // 0..7
-    const int q = warp & 3, half = w >> 2;
+    const int w = warp - 3;                       // 0..15
+    const int q = warp & 3, half = w >> 2;        // `half` = which quarter of the channels (0..3)
     const int row = q * 32 + lane;
-    constexpr int UH = C / 16;                    // 16-byte units per half row
+    constexpr int UH = C / 32;                    // 16-byte units per quarter row
     int it = 0;
     for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
       const int b = it & 1;
@@ -190,10 +190,10 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
       mbar_arrive(a2_full);
       mbar_wait(tfull, it & 1);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + half * (C / 2);
-      constexpr int GB = (C / 32) % 3 == 0 ? 3 : ((C / 32) % 2 == 0 ? 2 : 1);      // ld16 groups per batch
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + half * (C / 4);
+      constexpr int GB = (C / 64) % 3 == 0 ? 3 : ((C / 64) % 2 == 0 ? 2 : 1);      // ld16 groups per batch
 #pragma unroll 1
-      for (int gb = 0; gb < C / 32; gb += GB) {
+      for (int gb = 0; gb < C / 64; gb += GB) {
         float v[GB][16];
         uint4 xr[GB][2];
 #pragma unroll
@@ -202,11 +202,11 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
         for (int j = 0; j < GB; ++j)
 #pragma unroll
           for (int hh = 0; hh < 2; ++hh)
-            xr[j][hh] = *reinterpret_cast<const uint4*>(xt + unit_off(row, ((half * (C / 2) + (gb + j) * 16) >> 3) + hh));
+            xr[j][hh] = *reinterpret_cast<const uint4*>(xt + unit_off(row, ((half * (C / 4) + (gb + j) * 16) >> 3) + hh));
         tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < GB; ++j) {
-          const int c0 = half * (C / 2) + (gb + j) * 16;
+          const int c0 = half * (C / 4) + (gb + j) * 16;
 #pragma unroll
           for (int hh = 0; hh < 2; ++hh) {
             const uint32_t o = unit_off(row, (c0 >> 3) + hh);
@@ -324,8 +324,8 @@ gdn_bwd_umma_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
     const int w = warp - 3;
     const int q = warp & 3, half = w >> 2;
     const int row = q * 32 + lane;
-    const int wt = threadIdx.x - 96;              // 0..255: column owner for the d(beta) sums
-    constexpr int UH = C / 16;
+    const int wt = threadIdx.x - 96;              // 0..511: column owner for the d(beta) sums
+    constexpr int UH = C / 32;
     float bsum = 0.f;
     int it = 0;
     for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
@@ -371,10 +371,10 @@ gdn_bwd_umma_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
       }
       mbar_wait(tfull, it & 1);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + half * (C / 2);
-      constexpr int GB = (C / 32) % 3 == 0 ? 3 : ((C / 32) % 2 == 0 ? 2 : 1);
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + half * (C / 4);
+      constexpr int GB = 1;   // 96-register budget at 608 threads: the 16 warps hide latency instead
 #pragma unroll 1
-      for (int gb = 0; gb < C / 32; gb += GB) {
+      for (int gb = 0; gb < C / 64; gb += GB) {
         float v[GB][16];
         uint4 ur[GB][2], xr[GB][2];
 #pragma unroll
@@ -383,14 +383,14 @@ gdn_bwd_umma_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
         for (int j = 0; j < GB; ++j)
 #pragma unroll
           for (int hh = 0; hh < 2; ++hh) {
-            const uint32_t o = unit_off(row, ((half * (C / 2) + (gb + j) * 16) >> 3) + hh);
+            const uint32_t o = unit_off(row, ((half * (C / 4) + (gb + j) * 16) >> 3) + hh);
             ur[j][hh] = *reinterpret_cast<const uint4*>(bg + o);
             xr[j][hh] = *reinterpret_cast<const uint4*>(bx + o);
           }
         tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < GB; ++j) {
-          const int c0 = half * (C / 2) + (gb + j) * 16;
+          const int c0 = half * (C / 4) + (gb + j) * 16;
 #pragma unroll
           for (int hh = 0; hh < 2; ++hh) {
             const uint32_t o = unit_off(row, (c0 >> 3) + hh);
