@@ -119,6 +119,7 @@ _SIGNATURES = {
     "hpc_device_is_sm100": (c_int, []),
     "hpc_launch_count": (ctypes.c_ulonglong, []),
     "hpc_prof_enable": (c_int, [c_int]),
+    "hpc_prof_pause": (c_int, [c_int]),
     "hpc_prof_read": (c_int, [c_int, POINTER(c_double), POINTER(ctypes.c_ulonglong), POINTER(c_double)]),
     "hpc_bound_fwd": (c_int, [c_void_p, c_void_p, c_int64, c_float, c_int, c_void_p]),
     "hpc_bound_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_float, c_int, c_void_p]),
@@ -228,8 +229,23 @@ def check(rc):
         raise HpcError(f"hpcodec error {rc}: {msg.decode() if msg else '?'}")
 
 
+_prof_state = {"on": False}
+
+
 def prof_enable(on):
+    """Start (clearing earlier records) or stop the kernel-class event timing."""
     check(lib().hpc_prof_enable(int(on)))
+    _prof_state["on"] = bool(on)
+
+
+def prof_is_on():
+    return _prof_state["on"]
+
+
+def prof_pause(paused):
+    """Suspend / resume recording without clearing the records (used around CUDA-graph capture)."""
+    check(lib().hpc_prof_pause(int(paused)))
+    _prof_state["on"] = not paused
 
 
 def prof_read(cls):

@@ -73,6 +73,12 @@ int hpc_prof_enable(int on) {
   return HPC_OK;
 }
 
+int hpc_prof_pause(int paused) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  g_hpc_prof_on = paused ? 0 : 1;
+  return HPC_OK;
+}
+
 int hpc_prof_read(int cls, double* ms_total, unsigned long long* launches, double* work_total) {
   HPC_REQUIRE(cls >= 0 && cls < HPC_PROF_NCLASSES, HPC_ERR_BAD_SHAPE, "hpc_prof_read: class %d", cls);
   std::lock_guard<std::mutex> lk(g_prof_mu);

@@ -166,12 +166,21 @@ def _fill_taps(P, taps, phases):
 
 
 _pack_cache = {}
+_capturing = False
+
+
+def set_capturing(flag):
+    """While a CUDA graph is being captured the packed-weight cache is bypassed, so that the pack kernels are
+    nodes of the graph and replays always see the current weights."""
+    global _capturing
+    _capturing = bool(flag)
 
 
 def pack_weight(w, taps, rows, cols, stride_r, stride_c, dtype, cache=True):
     """Packed (ntaps, rows, cols) copy of a reference-layout weight in `dtype` (hpc_pack_weight).
     Cached on (storage, version) so evaluation loops do not repack unchanged weights."""
     key = (id(w), rows, cols, stride_r, stride_c, dtype, tuple(t[2] for t in taps))
+    cache = cache and not _capturing
     if cache:
         hit = _pack_cache.get(key)
         # valid only for the very same live tensor object at the same version and storage: ids and
@@ -421,16 +430,17 @@ def pack_c3_weight(weight, kind):
     """bf16 operand of the tcgen05 thin kernels from a (Cw,3,5,5)-laid-out weight (Conv2d(3->Cw) weight or
     ConvTranspose2d(Cw->3) weight): kind "k" -> [Cw][128] (k contiguous), "n" -> [80][Cw].  Cached like pack_weight."""
     key = (id(weight), "c3", kind)
-    hit = _pack_cache.get(key)
+    hit = None if _capturing else _pack_cache.get(key)
     if hit is not None and hit[0]() is weight and hit[1] == weight._version and hit[2] == weight.data_ptr():
         return hit[3]
     Cw, Cs = weight.shape[0], weight.shape[1]
     out = torch.empty((Cw, 128) if kind == "k" else (80, Cw), dtype=torch.bfloat16, device=weight.device)
     check(lib().hpc_pack_c3_weight(ptr(weight), Cs * 25, 25, Cw, ptr(out) if kind == "k" else None,
                                    ptr(out) if kind == "n" else None, stream()))
-    if len(_pack_cache) > 256:
-        _pack_cache.clear()
-    _pack_cache[key] = (weakref.ref(weight), weight._version, weight.data_ptr(), out)
+    if not _capturing:
+        if len(_pack_cache) > 256:
+            _pack_cache.clear()
+        _pack_cache[key] = (weakref.ref(weight), weight._version, weight.data_ptr(), out)
     return out
 
 

@@ -9,6 +9,7 @@ Two execution paths, both on the hand-written kernels only:
   * composed: the reference's forward line by line over the block modules -- used for loss
     configurations the fused node does not cover, and by the parity tests as a cross-check.
 """
+import torch
 import torch.nn as nn
 
 from ...autograd_ops import Compressor2018Fn, ModelMeta
@@ -39,6 +40,8 @@ class Compressor2018(nn.Module):
                                list(self.distortion_loss_fns.keys()), getattr(m.LOSS, "REDUCTION", "mean"),
                                m.LOSS.SSIM)
         self.fused = True
+        self.cuda_graphs = False      # opt-in: replay evaluation forwards (no_grad, eval mode) as one CUDA graph
+        self._graphs = {}
 
     # ------------------------------------------------------------------------------
     def _flat_params(self):
@@ -50,8 +53,23 @@ class Compressor2018(nn.Module):
         """noise_z / noise_y: optional U[0,1) tensors shaped like z / y (NCHW) replacing the in-kernel
         Philox noise of training mode (parity tests inject the reference's draws here)."""
         if self.fused and self._meta.fusable():
+            if self.cuda_graphs and not self.training and not torch.is_grad_enabled() and noise_z is None:
+                return self._forward_graphed(x)
             return self._forward_fused(x, noise_z, noise_y)
         return self._forward_composed(x, noise_z, noise_y)
+
+    def _forward_graphed(self, x):
+        """Static-shape evaluation forward replayed as a CUDA graph (outputs are static tensors: consume them
+        before the next call).  One graph per (shape, compute mode)."""
+        from ...hotpath import get_compute_mode
+        from ...utils.graphs import GraphedCallable
+        key = (tuple(x.shape), x.dtype, x.device, get_compute_mode())
+        g = self._graphs.get(key)
+        if g is None:
+            if len(self._graphs) >= 8:
+                self._graphs.clear()
+            g = self._graphs[key] = GraphedCallable(lambda t: self._forward_fused(t, None, None), x.contiguous())
+        return g(x.contiguous())
 
     def _forward_fused(self, x, noise_z, noise_y):
         self._meta.lmbda = float(self.distortion_loss_weight)

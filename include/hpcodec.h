@@ -61,6 +61,7 @@ int hpc_device_is_sm100(void);
 #define HPC_PROF_GDN 6        /* fused GDN forward / backward (gdn_umma.cu)                      (bytes) */
 #define HPC_PROF_NCLASSES 7
 int hpc_prof_enable(int on); /* on!=0: clear the records and start; 0: stop recording (records kept) */
+int hpc_prof_pause(int paused); /* suspend / resume recording, records kept (needed around CUDA-graph capture) */
 int hpc_prof_read(int cls, double* ms_total, unsigned long long* launches, double* work_total);
 
 /* ------------------------------------------------------------------------------------------
