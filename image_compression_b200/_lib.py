@@ -106,6 +106,8 @@ class IgemmWgradParams(Structure):
         ("HH", c_int), ("HW", c_int), ("Cc", c_int), ("hs", c_int), ("nphases", c_int),
         ("phase", IgemmPhase * MAX_PHASES), ("dh", c_int * MAX_TAPS), ("dw", c_int * MAX_TAPS),
         ("scale", c_float), ("gw_f32", c_void_p), ("workspace", c_void_p), ("workspace_bytes", c_size_t),
+        ("out_mode", c_int), ("out_accumulate", c_int), ("out_stride_r", c_int64), ("out_stride_c", c_int64),
+        ("out_tap_src", c_int * MAX_TAPS),
     ]
 
 
@@ -183,6 +185,9 @@ _SIGNATURES = {
                              c_int64, c_void_p, c_size_t, c_void_p]),
     "hpc_wgrad_c3_scratch_bytes": (c_size_t, [c_int, c_int, c_int, c_int, c_int]),
     "hpc_gdn_fwd_umma": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "hpc_gdn_bwd_fused_umma_workspace_bytes": (c_size_t, [c_int64, c_int]),
+    "hpc_gdn_bwd_fused_umma": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p,
+                                       c_void_p, c_float, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "hpc_gdn_bwd_umma_parts": (c_int, [c_int64]),
     "hpc_gdn_bwd_umma": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p,
                                  c_void_p, c_void_p, c_void_p]),

@@ -80,13 +80,14 @@ def ga_backward(S, gy_lp):
     """gy_lp: NHWC lp gradient wrt y.  Returns (conv grads [(gw,gb)], gdn grads [(ggamma,gbeta)])."""
     conv_grads = [None] * len(S.convs)
     gdn_grads = [None] * len(S.gdns)
-    g = gy_lp
+    g, gsum = gy_lp, None      # gsum: column sums of g when the GDN backward kernel already produced them
     ci, gi = len(S.convs) - 1, len(S.gdns) - 1
     for kind, a, inp in reversed(S.layers):
         if kind == "conv":
             spec = a
             w, b = S.convs[ci]
-            gb = hp.colsum(g) if b is not None else None
+            gb = (gsum if gsum is not None else hp.colsum(g)) if b is not None else None
+            gsum = None
             gw = spec.wgrad(inp, g, w)
             conv_grads[ci] = (gw, gb)
             g = spec.dgrad(g, w, inp.shape[1:3])["lp"]
@@ -94,14 +95,14 @@ def ga_backward(S, gy_lp):
         elif kind == "gdn":
             x, xsq, nrm, gamma = a
             gp, bp = S.gdns[gi]
-            dx, dgamma, dbeta = hp.gdn_backward(g, x, xsq, nrm, gamma)
+            dx, dgamma, dbeta, gsum = hp.gdn_backward(g, x, xsq, nrm, gamma, want_dxsum=True)
             gdn_grads[gi] = _gdn_param_grads(gp, bp, dgamma, dbeta)
             g = dx
             gi -= 1
         else:  # head conv: weight + bias grads only (the image needs no gradient)
             w, b = S.convs[0]
             gw = hp.wgrad_c3(g, S.x, w.shape[0], w.shape[1])
-            gb = hp.colsum(g) if b is not None else None
+            gb = (gsum if gsum is not None else hp.colsum(g)) if b is not None else None
             conv_grads[0] = (gw, gb)
     return conv_grads, gdn_grads
 
@@ -143,7 +144,7 @@ def gs_backward(S, g_raw_nchw, need_input_grad=True):
     conv_grads = [None] * len(S.convs)
     gdn_grads = [None] * len(S.gdns)
     ci, gi = len(S.convs) - 1, len(S.gdns) - 1
-    g = None
+    g, gsum = None, None
     for idx in range(len(S.layers) - 1, -1, -1):
         kind, a, inp = S.layers[idx]
         first = (idx == 0)
@@ -155,14 +156,15 @@ def gs_backward(S, g_raw_nchw, need_input_grad=True):
         elif kind == "gdn":
             x, xsq, nrm, gamma = a
             gp, bp = S.gdns[gi]
-            dx, dgamma, dbeta = hp.gdn_backward(g, x, xsq, nrm, gamma)
+            dx, dgamma, dbeta, gsum = hp.gdn_backward(g, x, xsq, nrm, gamma, want_dxsum=True)
             gdn_grads[gi] = _gdn_param_grads(gp, bp, dgamma, dbeta)
             g = dx
             gi -= 1
         else:
             spec = a
             w, b = S.convs[ci]
-            gb = hp.colsum(g) if b is not None else None
+            gb = (gsum if gsum is not None else hp.colsum(g)) if b is not None else None
+            gsum = None
             gw = spec.wgrad(inp, g, w)
             conv_grads[ci] = (gw, gb)
             g = spec.dgrad(g, w, inp.shape[1:3])["lp"] if (not first or need_input_grad) else None

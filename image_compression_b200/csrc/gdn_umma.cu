@@ -15,6 +15,7 @@
 // threads per tile row (each owns a quarter of the channels; warps w, w+4, w+8, w+12 share a TMEM lane quarter).
 #include <cuda.h>
 
+#include <cstdlib>
 #include <initializer_list>
 
 #include "tmap.cuh"
@@ -418,6 +419,289 @@ gdn_bwd_umma_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
   if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
 }
 
+// ---------------------------------------------------------------------------------------
+// backward with d(gamma) and the bias gradient of the preceding layer folded in (C = 128, 192):
+//   d(gamma)[i][j] = sum_p t[p][i] x^2[p][j] is a second UMMA on the SAME shared-memory tiles -- a K-major
+//   [128 rows][64 ch] SWIZZLE_128B tile read as an MN-major operand has M/N = channel and K = row -- so t and
+//   x^2 never go to HBM (4 passes instead of 6, and no separate one-tap wgrad over them).  The C x C fp32
+//   accumulator stays in TMEM for the whole persistent CTA: rows i < 128 as one M=128 x N=C accumulator; for
+//   C = 192 the remaining 64 rows are held transposed (x^2^T . t[:,128:192], two M=128 x N=64 accumulators over
+//   j = 0..127 and j = 64..191), 192 + 192 + 64 + 64 = 512 columns with the `a` accumulator.  Each CTA writes its
+//   partial to dgamma_part[blockIdx]; a second kernel reduces the partials in a fixed order (deterministic).
+//   Column sums of dx (= d bias of the conv / deconv that feeds this GDN) are accumulated like those of t.
+// ---------------------------------------------------------------------------------------
+struct GdnFusedParams {
+  float* colsum_part;      // [gridDim.x][C]      column sums of t  (d beta)
+  float* dxsum_part;       // [gridDim.x][C]      column sums of dx (d bias of the producer layer)
+  float* dgamma_part;      // [gridDim.x][C][C]   sum_p t[p][i] x^2[p][j]
+  int64_t P;
+  int tiles;
+  int inverse;
+  int dbg;
+};
+
+template <int C>
+__global__ void __launch_bounds__(G_THREADS, 1)
+gdn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_constant__ CUtensorMap tmX,
+                     const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmDx,
+                     const __grid_constant__ CUtensorMap tmG, const __grid_constant__ GdnFusedParams p) {
+  static_assert(C == 128 || C == 192, "fused d(gamma): C in {128, 192}");
+  using Cfg = GCfg<C>;
+  constexpr int KC = Cfg::KC;
+  constexpr int REM = C - 128;                    // 0 or 64 rows of d(gamma) held transposed
+  constexpr int COL_DGA = C, COL_DGB = 2 * C;     // TMEM columns: a | dgamma[0:128][:] | transposed remainder x2
+  constexpr int TCOLS = C == 128 ? 256 : 512;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* gam = smem;                           // gamma^T as the K-major B operand
+  uint8_t* bg = gam + Cfg::GAMMA;                // g   -> u = g r -> dx
+  uint8_t* bx = bg + Cfg::TILE;                  // x   -> x^2
+  uint8_t* bn = bx + Cfg::TILE;                  // r   -> t
+  uint64_t* bars = reinterpret_cast<uint64_t*>(bn + Cfg::TILE + 1024);
+  uint64_t* g_full = bars;
+  uint64_t* in_full = bars + 1;     // TMA: g, x, r tiles landed
+  uint64_t* in_empty = bars + 2;    // store warp (dx read out) + d(gamma) MMA commit (t, x^2 read) + 16 worker warps (sums)
+  uint64_t* a_full = bars + 3;      // workers: t (and u) written
+  uint64_t* tfull = bars + 4;
+  uint64_t* out_full = bars + 5;    // workers: dx, x^2 written
+  uint64_t* dg_done = bars + 6;     // last d(gamma) MMA retired
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 7);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmGr); prefetch_tmap(&tmX); prefetch_tmap(&tmR); prefetch_tmap(&tmDx); prefetch_tmap(&tmG);
+    mbar_init(g_full, 1); mbar_init(in_full, 1); mbar_init(in_empty, 2 + G_WORKERS / 32);
+    mbar_init(a_full, G_WORKERS); mbar_init(tfull, 1); mbar_init(out_full, G_WORKERS); mbar_init(dg_done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, TCOLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_arrive_expect_tx(g_full, Cfg::GAMMA);
+      for (int c = 0; c < KC; ++c) tma_load_2d(gam + c * (C * 128), &tmG, g_full, c * 64, 0);
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
+        mbar_wait(in_empty, (it & 1) ^ 1);
+        mbar_arrive_expect_tx(in_full, 3 * Cfg::TILE);
+        for (int c = 0; c < KC; ++c) {
+          tma_load_2d(bg + c * G_CHUNK, &tmGr, in_full, c * 64, tile * 128);
+          tma_load_2d(bx + c * G_CHUNK, &tmX, in_full, c * 64, tile * 128);
+          tma_load_2d(bn + c * G_CHUNK, &tmR, in_full, c * 64, tile * 128);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, C, 0, 0);
+      constexpr uint32_t idesc_dga = make_idesc_bf16(128, C, 1, 1);     // both operands MN-major
+      constexpr uint32_t idesc_dgb = make_idesc_bf16(128, 64, 1, 1);
+      mbar_wait(g_full, 0);
+      const uint32_t t_addr = smem_u32(bn), sq_addr = smem_u32(bx), b_addr = smem_u32(gam);
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
+        mbar_wait(a_full, it & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < C / 16; ++k)
+          mma_bf16_ss(tmem_base, make_smem_desc_sw128(t_addr + (k >> 2) * G_CHUNK + (k & 3) * 32, 16, 1024),
+                      make_smem_desc_sw128(b_addr + (k >> 2) * (C * 128) + (k & 3) * 32, 16, 1024), idesc, k != 0);
+        mma_commit(tfull);
+        mbar_wait(out_full, it & 1);
+        tc_fence_after();
+        if (!(p.dbg & 2))
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {            // K = 128 tile rows, 16 per MMA (16 rows x 128 B = 2 KB)
+          const uint32_t acc = (it | ks) != 0;
+          const uint64_t td = make_smem_desc_sw128(t_addr + ks * 2048, G_CHUNK, 1024);
+          const uint64_t sd = make_smem_desc_sw128(sq_addr + ks * 2048, G_CHUNK, 1024);
+          mma_bf16_ss(tmem_base + COL_DGA, td, sd, idesc_dga, acc);
+          if (REM) {
+            const uint64_t tr = make_smem_desc_sw128(t_addr + 2 * G_CHUNK + ks * 2048, G_CHUNK, 1024);
+            const uint64_t s1 = make_smem_desc_sw128(sq_addr + G_CHUNK + ks * 2048, G_CHUNK, 1024);
+            mma_bf16_ss(tmem_base + COL_DGB, sd, tr, idesc_dgb, acc);         // j = 0..127   x  i = 128..191
+            mma_bf16_ss(tmem_base + COL_DGB + 64, s1, tr, idesc_dgb, acc);    // j = 64..191  x  i = 128..191
+          }
+        }
+        mma_commit(in_empty);                       // arrives once the MMAs above have read t and x^2
+      }
+      mma_commit(dg_done);
+    }
+  } else if (warp == 2) {
+    if (lane == 0) {
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
+        mbar_wait(out_full, it & 1);
+        for (int c = 0; c < KC; ++c) tma_store_2d(&tmDx, bg + c * G_CHUNK, c * 64, tile * 128);
+        bulk_commit();
+        bulk_wait_read0();
+        mbar_arrive(in_empty);
+      }
+      bulk_wait0();
+    }
+  } else {
+    const int w = warp - 3;
+    const int q = warp & 3, half = w >> 2;
+    const int row = q * 32 + lane;
+    const int wt = threadIdx.x - 96;              // 0..511: column owner for the column sums
+    constexpr int UH = C / 32;
+    float bsum = 0.f, dsum = 0.f;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
+      mbar_wait(in_full, it & 1);
+      constexpr int UB = UH % 4 == 0 ? 4 : (UH % 3 == 0 ? 3 : (UH % 2 == 0 ? 2 : 1));
+#pragma unroll 1
+      for (int ub = 0; ub < UH; ub += UB) {
+        uint4 rg[UB], rx[UB], rr[UB];
+#pragma unroll
+        for (int j = 0; j < UB; ++j) {
+          const uint32_t o = unit_off(row, half * UH + ub + j);
+          rg[j] = *reinterpret_cast<const uint4*>(bg + o);
+          rx[j] = *reinterpret_cast<const uint4*>(bx + o);
+          rr[j] = *reinterpret_cast<const uint4*>(bn + o);
+        }
+#pragma unroll
+        for (int j = 0; j < UB; ++j) {
+          const uint32_t o = unit_off(row, half * UH + ub + j);
+          float g[8], x[8], r[8], t[8], u[8];
+          unpack8(rg[j], g);
+          unpack8(rx[j], x);
+          unpack8(rr[j], r);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            t[e] = g[e] * x[e] * (p.inverse ? r[e] : r[e] * r[e] * r[e]);
+            u[e] = p.inverse ? g[e] / r[e] : g[e] * r[e];
+          }
+          *reinterpret_cast<uint4*>(bn + o) = pack8(t);
+          *reinterpret_cast<uint4*>(bg + o) = pack8(u);
+        }
+      }
+      fence_proxy_async();
+      mbar_arrive(a_full);
+      // d(beta): column sums of the bf16 t tile, while the MMA runs (rows past P are zero: TMA zero fill)
+      named_bar(4, G_WORKERS);
+      if (wt < C && !(p.dbg & 4)) {
+        const int U = wt >> 3, e = wt & 7;
+        float s = 0.f;
+#pragma unroll 8
+        for (int r2 = 0; r2 < 128; ++r2)
+          s += __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(bn + unit_off(r2, U) + e * 2));
+        bsum += s;
+      }
+      mbar_wait(tfull, it & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + half * (C / 4);
+#pragma unroll 1
+      for (int gb = 0; gb < C / 64; ++gb) {
+        float v[16];
+        uint4 ur[2], xr[2];
+        tmem_ld16(taddr + gb * 16, v);
+        const int c0 = half * (C / 4) + gb * 16;
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          const uint32_t o = unit_off(row, (c0 >> 3) + hh);
+          ur[hh] = *reinterpret_cast<const uint4*>(bg + o);
+          xr[hh] = *reinterpret_cast<const uint4*>(bx + o);
+        }
+        tmem_ld_wait();
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          const uint32_t o = unit_off(row, (c0 >> 3) + hh);
+          float u[8], x[8], d[8];
+          unpack8(ur[hh], u);
+          unpack8(xr[hh], x);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            d[e] = p.inverse ? u[e] + x[e] * v[hh * 8 + e] : u[e] - x[e] * v[hh * 8 + e];
+            x[e] *= x[e];
+          }
+          *reinterpret_cast<uint4*>(bg + o) = pack8(d);
+          *reinterpret_cast<uint4*>(bx + o) = pack8(x);
+        }
+      }
+      tc_fence_before();
+      fence_proxy_async();
+      mbar_arrive(out_full);
+      // d(bias) of the producer layer: column sums of the bf16 dx tile, while it is being stored.  Rows past P
+      // are skipped: the inverse form divides the zero-filled g by the zero-filled r there.
+      named_bar(4, G_WORKERS);
+      if (wt < C && !(p.dbg & 1)) {
+        const int U = wt >> 3, e = wt & 7;
+        const int64_t left = p.P - (int64_t)tile * 128;
+        const int nrows = left < 128 ? (int)left : 128;
+        float s = 0.f;
+#pragma unroll 8
+        for (int r2 = 0; r2 < nrows; ++r2)
+          s += __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(bg + unit_off(r2, U) + e * 2));
+        dsum += s;
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(in_empty);
+    }
+    if (wt < C) {
+      p.colsum_part[(int64_t)blockIdx.x * C + wt] = bsum;
+      p.dxsum_part[(int64_t)blockIdx.x * C + wt] = dsum;
+    }
+    // ---- d(gamma) partial of this CTA: TMEM -> dgamma_part[blockIdx] ----
+    mbar_wait(dg_done, 0);
+    tc_fence_after();
+    float* dst = p.dgamma_part + (int64_t)blockIdx.x * C * C;
+    const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+#pragma unroll 1
+    for (int c0 = 0; c0 < C / 4; c0 += 16) {       // rows i = row (0..127), this thread's quarter of the columns
+      float v[16];
+      tmem_ld16(tmem_base + lane_off + COL_DGA + half * (C / 4) + c0, v);
+      tmem_ld_wait();
+      float4* d4 = reinterpret_cast<float4*>(dst + (int64_t)row * C + half * (C / 4) + c0);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) d4[k] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+    }
+    if (REM) {                                     // rows i = 128 + i', held as [j][i']: lanes run along j (coalesced)
+      float v[16];
+      tmem_ld16(tmem_base + lane_off + COL_DGB + half * 16, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int k = 0; k < 16; ++k) dst[(int64_t)(128 + half * 16 + k) * C + row] = v[k];
+      if (q >= 2) {                                // second accumulator: j = 64 + row, only j >= 128 is new
+        tmem_ld16(tmem_base + lane_off + COL_DGB + 64 + half * 16, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int k = 0; k < 16; ++k) dst[(int64_t)(128 + half * 16 + k) * C + 64 + row] = v[k];
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, TCOLS);
+}
+
+// fixed-order reduction of the per-CTA d(gamma) partials: out[i] = scale * sum_s part[s][i]
+__global__ void __launch_bounds__(256)
+gdn_dgamma_reduce_kernel(const float* __restrict__ part, int nparts, int n, float scale, float* __restrict__ out) {
+  __shared__ float4 sm[8][32];
+  const int qd = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const int i = (blockIdx.x * 32 + qd) * 4;
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (i < n)
+    for (int s2 = g; s2 < nparts; s2 += 8) {
+      const float4 v = __ldcs(reinterpret_cast<const float4*>(part + (int64_t)s2 * n + i));
+      a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+    }
+  sm[g][qd] = a;
+  __syncthreads();
+  if (g != 0 || i >= n) return;
+#pragma unroll
+  for (int k = 1; k < 8; ++k) {
+    const float4 v = sm[k][qd];
+    a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+  }
+  *reinterpret_cast<float4*>(out + i) = make_float4(a.x * scale, a.y * scale, a.z * scale, a.w * scale);
+}
+
 int make_rows_tmap(CUtensorMap* m, const void* base, int64_t P, int C, int box_rows) {
   uint64_t dims[2] = {(uint64_t)C, (uint64_t)P};
   uint64_t strides[1] = {(uint64_t)C * 2};
@@ -502,3 +786,54 @@ int hpc_gdn_bwd_umma(const void* g_bf16, const void* x_bf16, const void* rnorm_b
   HPC_LAUNCH_CHECK();
   return HPC_OK;
 }
+
+size_t hpc_gdn_bwd_fused_umma_workspace_bytes(int64_t P, int C) {
+  if (C != 128 && C != 192) return 0;
+  return (size_t)hpc_gdn_bwd_umma_parts(P) * C * C * sizeof(float);
+}
+
+int hpc_gdn_bwd_fused_umma(const void* g_bf16, const void* x_bf16, const void* rnorm_bf16, const void* gammaT_bf16,
+                           int64_t P, int C, int inverse, void* dx_bf16, float* dgamma, float dgamma_scale,
+                           float* colsum_part, float* dxsum_part, void* workspace, size_t workspace_bytes,
+                           hpc_stream_t stream) {
+  int rc = gdn_check("hpc_gdn_bwd_fused_umma", P, C,
+                     {g_bf16, x_bf16, rnorm_bf16, gammaT_bf16, dx_bf16, dgamma, colsum_part, dxsum_part, workspace});
+  if (rc) return rc;
+  HPC_REQUIRE(C == 128 || C == 192, HPC_ERR_UNSUPPORTED, "hpc_gdn_bwd_fused_umma: C=%d not in {128,192}", C);
+  HPC_REQUIRE(workspace_bytes >= hpc_gdn_bwd_fused_umma_workspace_bytes(P, C), HPC_ERR_BAD_SHAPE,
+              "hpc_gdn_bwd_fused_umma: workspace too small (%zu)", workspace_bytes);
+  GdnFusedParams kp;
+  kp.colsum_part = colsum_part; kp.dxsum_part = dxsum_part; kp.dgamma_part = (float*)workspace;
+  kp.tiles = (int)((P + 127) / 128); kp.inverse = inverse; kp.P = P;
+  { const char* e = getenv("HPC_GDN_DBG"); kp.dbg = e ? atoi(e) : 0; }
+  CUtensorMap tmGr, tmX, tmR, tmDx, tmG;
+  if ((rc = make_rows_tmap(&tmGr, g_bf16, P, C, 128))) return rc;
+  if ((rc = make_rows_tmap(&tmX, x_bf16, P, C, 128))) return rc;
+  if ((rc = make_rows_tmap(&tmR, rnorm_bf16, P, C, 128))) return rc;
+  if ((rc = make_rows_tmap(&tmDx, dx_bf16, P, C, 128))) return rc;
+  if ((rc = make_rows_tmap(&tmG, gammaT_bf16, C, C, C))) return rc;
+  HpcProfScope prof(HPC_PROF_GDN, (double)P * C * 2 * 4, stream);
+  auto st = (cudaStream_t)stream;
+  const int grid = gdn_grid(kp.tiles);
+  if (C == 128) {
+    static bool attr_set = false;
+    if (!attr_set) {
+      HPC_CUDA(cudaFuncSetAttribute(gdn_bwd_fused_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, GCfg<128>::SMEM));
+      attr_set = true;
+    }
+    gdn_bwd_fused_kernel<128><<<grid, G_THREADS, GCfg<128>::SMEM, st>>>(tmGr, tmX, tmR, tmDx, tmG, kp);
+  } else {
+    static bool attr_set = false;
+    if (!attr_set) {
+      HPC_CUDA(cudaFuncSetAttribute(gdn_bwd_fused_kernel<192>, cudaFuncAttributeMaxDynamicSharedMemorySize, GCfg<192>::SMEM));
+      attr_set = true;
+    }
+    gdn_bwd_fused_kernel<192><<<grid, G_THREADS, GCfg<192>::SMEM, st>>>(tmGr, tmX, tmR, tmDx, tmG, kp);
+  }
+  HPC_LAUNCH_CHECK();
+  const int n = C * C;
+  gdn_dgamma_reduce_kernel<<<(n + 127) / 128, 256, 0, st>>>(kp.dgamma_part, grid, n, dgamma_scale, dgamma);
+  HPC_LAUNCH_CHECK();
+  return HPC_OK;
+}
+

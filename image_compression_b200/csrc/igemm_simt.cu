@@ -178,6 +178,8 @@ int hpc_igemm_wgrad(const hpc_igemm_wgrad_params* p, hpc_stream_t stream) {
   if (rc) return rc;
   if (p->engine == HPC_ENGINE_UMMA) return hpc_igemm_wgrad_umma(p, stream);
   HPC_REQUIRE(p->engine == HPC_ENGINE_SIMT, HPC_ERR_UNSUPPORTED, "hpc_igemm_wgrad: unknown engine %d", p->engine);
+  HPC_REQUIRE(p->out_mode == 0 && p->out_accumulate == 0, HPC_ERR_UNSUPPORTED,
+              "hpc_igemm_wgrad: the SIMT engine writes the packed layout only (use hpc_unpack_wgrad)");
   WgradGeom g;
   g.N = p->N; g.GH = p->GH; g.GW = p->GW; g.R = p->R; g.HH = p->HH; g.HW = p->HW; g.Cc = p->Cc; g.hs = p->hs;
   g.nphases = p->nphases;

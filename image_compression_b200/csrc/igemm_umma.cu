@@ -513,15 +513,45 @@ igemm_wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmLo, const __grid_c
   if (warp == 1) tmem_dealloc(tmem_base, 512);
 }
 
-__global__ void wgrad_reduce_kernel(const float* __restrict__ ws, int nsplits, int64_t n, float scale,
-                                    float* __restrict__ gw) {
-  for (int64_t i = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) * 4; i < n; i += (int64_t)gridDim.x * blockDim.x * 4) {
-    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int s = 0; s < nsplits; ++s) {
-      const float4 v = *reinterpret_cast<const float4*>(ws + (int64_t)s * n + i);
+// Split-K reduction + output layout in one pass.  A block owns 128 consecutive floats of the packed
+// [tap][r][c] result: 32 float4 columns x 8 split lanes; lane g sums splits g, g+8, ... in order and the
+// 8 partials are combined in a fixed order (deterministic).  The result goes either to the packed layout
+// or straight into the reference weight layout dst[r*sr + c*sc + tap_src[t]] (optionally accumulating).
+struct WgOut { int mode, accumulate, R, Cc; int64_t sr, sc; int tap_src[HPC_MAX_TAPS]; };
+
+__global__ void __launch_bounds__(256)
+wgrad_reduce_kernel(const float* __restrict__ ws, int nsplits, int64_t n, float scale, float* __restrict__ gw,
+                    const __grid_constant__ WgOut o) {
+  __shared__ float4 part[8][32];
+  const int q = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const int64_t i = ((int64_t)blockIdx.x * 32 + q) * 4;
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (i < n)
+    for (int s = g; s < nsplits; s += 8) {
+      const float4 v = __ldcs(reinterpret_cast<const float4*>(ws + (int64_t)s * n + i));
       a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
     }
-    *reinterpret_cast<float4*>(gw + i) = make_float4(a.x * scale, a.y * scale, a.z * scale, a.w * scale);
+  part[g][q] = a;
+  __syncthreads();
+  if (g != 0 || i >= n) return;
+#pragma unroll
+  for (int k = 1; k < 8; ++k) {
+    const float4 v = part[k][q];
+    a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+  }
+  a.x *= scale; a.y *= scale; a.z *= scale; a.w *= scale;
+  if (o.mode == 0) {
+    float4* d = reinterpret_cast<float4*>(gw + i);
+    if (o.accumulate) { const float4 c = *d; a.x += c.x; a.y += c.y; a.z += c.z; a.w += c.w; }
+    *d = a;
+  } else {
+    const int c = (int)(i % o.Cc);
+    const int64_t tr = i / o.Cc;
+    const int r = (int)(tr % o.R), t = (int)(tr / o.R);
+    float* d = gw + r * o.sr + c * o.sc + o.tap_src[t];
+    const float v[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) d[k * o.sc] = o.accumulate ? d[k * o.sc] + v[k] : v[k];
   }
 }
 
@@ -564,8 +594,9 @@ static int wgrad_check(const hpc_igemm_wgrad_params* p) {
   HPC_REQUIRE(p->Cc % 64 == 0 && p->Cc >= 64 && p->Cc <= 256, HPC_ERR_UNSUPPORTED,
               "umma wgrad: Cc=%d must be a multiple of 64 in [64,256]", p->Cc);
   HPC_REQUIRE(p->hs >= 1 && p->hs <= 8, HPC_ERR_UNSUPPORTED, "umma wgrad: hs=%d not in [1,8]", p->hs);
-  HPC_REQUIRE(hpc_aligned16(p->lo) && hpc_aligned16(p->hi) && hpc_aligned16(p->gw_f32), HPC_ERR_BAD_ALIGNMENT,
-              "umma wgrad: pointers must be 16B aligned");
+  HPC_REQUIRE(hpc_aligned16(p->lo) && hpc_aligned16(p->hi) && (p->out_mode == 1 || hpc_aligned16(p->gw_f32)),
+              HPC_ERR_BAD_ALIGNMENT, "umma wgrad: pointers must be 16B aligned");
+  HPC_REQUIRE(p->out_mode == 0 || p->out_mode == 1, HPC_ERR_BAD_SHAPE, "umma wgrad: out_mode %d", p->out_mode);
   return HPC_OK;
 }
 
@@ -615,9 +646,12 @@ int hpc_igemm_wgrad_umma(const hpc_igemm_wgrad_params* p, hpc_stream_t stream) {
   igemm_wgrad_umma_kernel<<<local.nunits * local.nsplits, WG_THREADS, smem_bytes, st>>>(tmLo, tmHi, local);
   HPC_LAUNCH_CHECK();
   const int64_t n = (int64_t)local.ntaps * p->R * p->Cc;
-  int grid = (int)((n / 4 + 255) / 256);
-  if (grid > 148 * 8) grid = 148 * 8;
-  wgrad_reduce_kernel<<<grid, 256, 0, st>>>(local.ws, local.nsplits, n, p->scale, p->gw_f32);
+  WgOut o;
+  memset(&o, 0, sizeof(o));
+  o.mode = p->out_mode; o.accumulate = p->out_accumulate; o.R = p->R; o.Cc = p->Cc;
+  o.sr = p->out_stride_r; o.sc = p->out_stride_c;
+  for (int t = 0; t < local.ntaps && t < HPC_MAX_TAPS; ++t) o.tap_src[t] = p->out_tap_src[t];
+  wgrad_reduce_kernel<<<(int)((n + 127) / 128), 256, 0, st>>>(local.ws, local.nsplits, n, p->scale, p->gw_f32, o);
   HPC_LAUNCH_CHECK();
   return HPC_OK;
 }

@@ -183,7 +183,7 @@ template <int MODE>
 __global__ void __launch_bounds__(256)
 ssim_level_kernel(const float* __restrict__ img1, const float* __restrict__ img2, int C, int H, int W,
                   const float* __restrict__ filt, int fs, float in_scale, float c1, float c2,
-                  float* __restrict__ ssim_sum, float* __restrict__ cs_sum, const float* __restrict__ g_ssim,
+                  unsigned long long* __restrict__ fx_sums, const float* __restrict__ g_ssim,
                   const float* __restrict__ g_cs, float* __restrict__ maps) {
   __shared__ float p1[SS_PH][SS_PW + 1], p2[SS_PH][SS_PW + 1];
   __shared__ float hbuf[5][SS_PH][SS_TW + 1];
@@ -251,11 +251,21 @@ ssim_level_kernel(const float* __restrict__ img1, const float* __restrict__ img2
   if (MODE == 0) {
     float s = block_sum(acc_s, red);
     float c = block_sum(acc_c, red);
+    // block partials are accumulated in 32.32 fixed point: integer addition is associative, so the per-image
+    // sums do not depend on the order in which the blocks retire (|partial| <= 512, <= 2^22 blocks per image)
     if (tid == 0) {
-      atomicAdd(&ssim_sum[n], s);
-      atomicAdd(&cs_sum[n], c);
+      atomicAdd(&fx_sums[2 * n], (unsigned long long)__double2ll_rn((double)s * 4294967296.0));
+      atomicAdd(&fx_sums[2 * n + 1], (unsigned long long)__double2ll_rn((double)c * 4294967296.0));
     }
   }
+}
+
+__global__ void ssim_sums_finish_kernel(const unsigned long long* __restrict__ fx, int N, float* __restrict__ ssim_sum,
+                                        float* __restrict__ cs_sum) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  ssim_sum[n] = (float)((double)(long long)fx[2 * n] * (1.0 / 4294967296.0));
+  cs_sum[n] = (float)((double)(long long)fx[2 * n + 1] * (1.0 / 4294967296.0));
 }
 
 // backward filter: g_img2(p) = in_scale * ( FA + 2*x2*FB + x1*FC ),  F* = full correlation with g (x) g
@@ -328,16 +338,19 @@ static int ssim_check(int N, int C, int H, int W, int fs) {
 int hpc_ssim_level_fwd(const float* img1, const float* img2, int N, int C, int H, int W, const float* filt1d,
                        int fs, float in_scale, float c1, float c2, float* ssim_sum, float* cs_sum,
                        void* scratch, hpc_stream_t stream) {
-  (void)scratch;
   int rc = ssim_check(N, C, H, W, fs);
   if (rc) return rc;
+  HPC_REQUIRE(scratch && ((uintptr_t)scratch & 7) == 0, HPC_ERR_BAD_ALIGNMENT,
+              "hpc_ssim_level_fwd: scratch (16*N bytes, 8B aligned) is required");
   auto st = (cudaStream_t)stream;
-  HPC_CUDA(cudaMemsetAsync(ssim_sum, 0, N * sizeof(float), st));
-  HPC_CUDA(cudaMemsetAsync(cs_sum, 0, N * sizeof(float), st));
+  auto* fx = (unsigned long long*)scratch;
+  HPC_CUDA(cudaMemsetAsync(fx, 0, (size_t)N * 16, st));
   const int OH = H - fs + 1, OW = W - fs + 1;
   dim3 grid((OW + SS_TW - 1) / SS_TW, (OH + SS_TH - 1) / SS_TH, N * C);
-  ssim_level_kernel<0><<<grid, dim3(32, 8), 0, st>>>(img1, img2, C, H, W, filt1d, fs, in_scale, c1, c2, ssim_sum,
-                                                    cs_sum, nullptr, nullptr, nullptr);
+  ssim_level_kernel<0><<<grid, dim3(32, 8), 0, st>>>(img1, img2, C, H, W, filt1d, fs, in_scale, c1, c2, fx, nullptr,
+                                                    nullptr, nullptr);
+  HPC_LAUNCH_CHECK();
+  ssim_sums_finish_kernel<<<(N + 127) / 128, 128, 0, st>>>(fx, N, ssim_sum, cs_sum);
   HPC_LAUNCH_CHECK();
   return HPC_OK;
 }
@@ -351,7 +364,7 @@ int hpc_ssim_level_bwd(const float* img1, const float* img2, int N, int C, int H
   const int OH = H - fs + 1, OW = W - fs + 1;
   dim3 grid((OW + SS_TW - 1) / SS_TW, (OH + SS_TH - 1) / SS_TH, N * C);
   ssim_level_kernel<1><<<grid, dim3(32, 8), 0, st>>>(img1, img2, C, H, W, filt1d, fs, in_scale, c1, c2, nullptr,
-                                                    nullptr, g_ssim, g_cs, maps);
+                                                    g_ssim, g_cs, maps);
   HPC_LAUNCH_CHECK();
   dim3 grid2((W + SS_TW - 1) / SS_TW, (H + SS_TH - 1) / SS_TH, N * C);
   ssim_bwd_filter_kernel<<<grid2, dim3(32, 8), 0, st>>>(img1, img2, H, W, filt1d, fs, in_scale, maps,

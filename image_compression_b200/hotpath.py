@@ -240,8 +240,9 @@ def igemm_fwd(x, w_packed, taps, phases, grid_hw, is_, os_, out_hw, Co, epi=EPI_
     return outs
 
 
-def igemm_wgrad(lo, hi, taps, phases, hs, scale=1.0):
-    """Returns packed gw (ntaps, R, Cc) fp32."""
+def igemm_wgrad(lo, hi, taps, phases, hs, scale=1.0, out=None, out_strides=None):
+    """Returns packed gw (ntaps, R, Cc) fp32; with `out` (a weight-shaped fp32 tensor) and
+    out_strides=(stride_r, stride_c) the tcgen05 engine's reduction writes the reference layout directly."""
     N, GH, GW, R = lo.shape
     _, HH, HW, Cc = hi.shape
     P = _lib.IgemmWgradParams()
@@ -251,7 +252,14 @@ def igemm_wgrad(lo, hi, taps, phases, hs, scale=1.0):
     P.HH, P.HW, P.Cc, P.hs = HH, HW, Cc, hs
     _fill_taps(P, taps, phases)
     P.scale = scale
-    gw = torch.empty((len(taps), R, Cc), dtype=torch.float32, device=lo.device)
+    if out is not None:
+        assert P.engine == _lib.ENGINE_UMMA and out.is_contiguous() and out.dtype == torch.float32
+        gw = out
+        P.out_mode, (P.out_stride_r, P.out_stride_c) = 1, out_strides
+        for i, t in enumerate(taps):
+            P.out_tap_src[i] = t[2]
+    else:
+        gw = torch.empty((len(taps), R, Cc), dtype=torch.float32, device=lo.device)
     P.gw_f32 = ptr(gw)
     wsb = lib().hpc_igemm_wgrad_workspace_bytes(byref(P))
     ws = torch.empty(max(wsb, 1), dtype=torch.uint8, device=lo.device) if wsb else None
@@ -325,12 +333,12 @@ class ConvSpec:
         K, Ci, Co = self.K, self.cin, self.cout
         taps, phases = self.deconv_taps
         gw_ref = torch.empty(weight_shape_like.shape, dtype=torch.float32, device=x.device)
-        if self.transposed:   # lo = x (rows=Ci), hi = g (cols=Co); W[ci][co][k]
-            gw = igemm_wgrad(x, g, taps, phases, self.s)
-            unpack_wgrad(gw, gw_ref, taps, Ci, Co, Co * K, K)
-        else:                 # lo = g (rows=Co), hi = x (cols=Ci); W[co][ci][k]
-            gw = igemm_wgrad(g, x, taps, phases, self.s)
-            unpack_wgrad(gw, gw_ref, taps, Co, Ci, Ci * K, K)
+        lo, hi, rows, cols, sr, sc = (x, g, Ci, Co, Co * K, K) if self.transposed else (g, x, Co, Ci, Ci * K, K)
+        # transposed: lo = x (rows=Ci), hi = g (cols=Co), W[ci][co][k]; else lo = g (rows=Co), hi = x, W[co][ci][k]
+        if engine() == _lib.ENGINE_UMMA:
+            igemm_wgrad(lo, hi, taps, phases, self.s, out=gw_ref, out_strides=(sr, sc))
+        else:
+            unpack_wgrad(igemm_wgrad(lo, hi, taps, phases, self.s), gw_ref, taps, rows, cols, sr, sc)
         return gw_ref
 
 
@@ -391,19 +399,36 @@ def gdn_forward(x, xsq, gamma_eff, beta_eff, inverse=False):
     return o["lp"], o["nrm"]
 
 
-def gdn_backward(g, x, xsq, nrm, gamma_eff, inverse=False, need_dx=True):
-    """SURVEY A.4.  Returns (dx lp, dgamma_eff (C,C,1,1) fp32, dbeta_eff (C,) fp32)."""
+def gdn_backward(g, x, xsq, nrm, gamma_eff, inverse=False, need_dx=True, want_dxsum=False):
+    """SURVEY A.4.  Returns (dx lp, dgamma_eff (C,C,1,1) fp32, dbeta_eff (C,) fp32) and, with want_dxsum, a
+    fourth value: the column sums of dx (the bias gradient of the layer that feeds this GDN) when the fused
+    kernel produced them, else None."""
+    out = _gdn_backward(g, x, xsq, nrm, gamma_eff, inverse, need_dx)
+    return out if want_dxsum else out[:3]
+
+
+def _gdn_backward(g, x, xsq, nrm, gamma_eff, inverse, need_dx):
     N, H, W, C = x.shape
     sgn = 0.5 if inverse else -0.5
     if gdn_fused_ok(x.dtype, C) and need_dx:
         P = N * H * W
         wp = pack_weight(gamma_eff, _ONE_TAP[0], C, C, 1, C, x.dtype, cache=False)   # rows=k, cols=i: gamma[i][k]
+        if C in (128, 192):      # d(gamma) and the dx column sums inside the kernel: t and x^2 never reach HBM
+            dx = torch.empty_like(x)
+            nparts = lib().hpc_gdn_bwd_umma_parts(P)
+            parts = torch.empty((2, nparts, C), dtype=torch.float32, device=x.device)
+            dgamma = torch.empty((C, C, 1, 1), dtype=torch.float32, device=x.device)
+            wsb = lib().hpc_gdn_bwd_fused_umma_workspace_bytes(P, C)
+            ws = torch.empty(wsb, dtype=torch.uint8, device=x.device)
+            check(lib().hpc_gdn_bwd_fused_umma(ptr(g), ptr(x), ptr(nrm), ptr(wp), P, C, int(inverse), ptr(dx),
+                                               ptr(dgamma), sgn, ptr(parts[0]), ptr(parts[1]), ptr(ws), wsb, stream()))
+            return dx, dgamma, colsum(parts[0], sgn), colsum(parts[1])
         dx, t, sq = torch.empty_like(x), torch.empty_like(x), torch.empty_like(x)
         parts = torch.empty((lib().hpc_gdn_bwd_umma_parts(P), C), dtype=torch.float32, device=x.device)
         check(lib().hpc_gdn_bwd_umma(ptr(g), ptr(x), ptr(nrm), ptr(wp), P, C, int(inverse), ptr(dx), ptr(t), ptr(sq),
                                      ptr(parts), stream()))
         dgamma = igemm_wgrad(t, sq, _ONE_TAP[0], _ONE_TAP[1], 1, sgn).view(C, C, 1, 1)
-        return dx, dgamma, colsum(parts, sgn)
+        return dx, dgamma, colsum(parts, sgn), None
     if xsq is None:
         xsq, _ = square(x)
     t = torch.empty_like(x)
@@ -416,7 +441,7 @@ def gdn_backward(g, x, xsq, nrm, gamma_eff, inverse=False, need_dx=True):
                        EPI_IGDN_BWD if inverse else EPI_GDN_BWD, None, aux0=g, aux1=x, aux2=nrm)["lp"]
     dgamma = igemm_wgrad(t, xsq, _ONE_TAP[0], _ONE_TAP[1], 1, sgn).view(C, C, 1, 1)
     dbeta = colsum(t, sgn)
-    return dx, dgamma, dbeta
+    return dx, dgamma, dbeta, None
 
 
 # ----------------------------------------------------------------------------------------
@@ -650,13 +675,14 @@ class SsimPyramid:
         self.imgs = [(img1, img2, H, W, in_scale)]
         self.sums = torch.empty((levels, 2, N), dtype=torch.float32, device=img1.device)
         self.counts = []
+        fx = torch.empty((levels, 2 * N), dtype=torch.int64, device=img1.device)   # fixed-point accumulators
         a, b, h, w, sc = img1, img2, H, W, in_scale
         for l in range(levels):
             if h < fs or w < fs:
                 raise ValueError(f"(MS-)SSIM level {l}: image {h}x{w} smaller than the {fs}-tap window "
                                  "(the reference's F.conv2d raises here too)")
             check(lib().hpc_ssim_level_fwd(ptr(a), ptr(b), N, C, h, w, ptr(self.filt), fs, sc, c1, c2,
-                                           ptr(self.sums[l, 0]), ptr(self.sums[l, 1]), None, stream()))
+                                           ptr(self.sums[l, 0]), ptr(self.sums[l, 1]), ptr(fx[l]), stream()))
             self.counts.append(float(C * (h - fs + 1) * (w - fs + 1)))
             if l < levels - 1:
                 oh, ow = (h + 1) // 2, (w + 1) // 2

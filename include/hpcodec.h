@@ -190,7 +190,9 @@ int hpc_psnr_from_sse(const float* sse_per_image, int N, int64_t per_image, floa
  * Replaces modelling/loss.py:75-91,103-121 and utils/metric.py:56-72,79-97.
  *   img1,img2 (N,C,H,W); in_scale multiplies both on load (the x255 of loss.py:67-68)
  *   filt1d    fs floats on the device (the 2-D softmax window is exactly g (x) g)
- *   ssim_sum, cs_sum (N) out: sums over (C,H',W'), H'=H-fs+1 (caller divides)       */
+ *   ssim_sum, cs_sum (N) out: sums over (C,H',W'), H'=H-fs+1 (caller divides)
+ *   scratch   16*N bytes, 8-byte aligned: 32.32 fixed-point accumulators, so the sums are bit-reproducible
+ *             from run to run (no floating-point atomics) */
 int hpc_ssim_level_fwd(const float* img1, const float* img2, int N, int C, int H, int W, const float* filt1d,
                        int fs, float in_scale, float c1, float c2, float* ssim_sum, float* cs_sum,
                        void* scratch, hpc_stream_t stream);
@@ -308,6 +310,14 @@ typedef struct {
   float* gw_f32;
   void* workspace;        /* UMMA engine split-K partials; >= hpc_igemm_wgrad_workspace_bytes() */
   size_t workspace_bytes;
+  /* Output layout.  out_mode 0: gw_f32 is the packed [tap][R][Cc] array.  out_mode 1 (UMMA engine only):
+   * gw_f32 is the reference's weight-gradient tensor and element (t, r, c) goes to
+   * gw_f32[r*out_stride_r + c*out_stride_c + out_tap_src[t]] -- nn.Conv2d's (Co,Ci,kh,kw) or
+   * nn.ConvTranspose2d's (Ci,Co,kh,kw) -- so no separate hpc_unpack_wgrad pass is needed.
+   * out_accumulate != 0 adds to what gw_f32 holds (.grad accumulation) instead of overwriting. */
+  int out_mode, out_accumulate;
+  int64_t out_stride_r, out_stride_c;
+  int out_tap_src[HPC_MAX_TAPS];
 } hpc_igemm_wgrad_params;
 
 int hpc_igemm_wgrad(const hpc_igemm_wgrad_params* p, hpc_stream_t stream);
@@ -378,6 +388,17 @@ size_t hpc_wgrad_c3_scratch_bytes(int N, int Cw, int Cs, int H, int W);
 int hpc_gdn_fwd_umma(const void* x_bf16, const void* gamma_bf16, const float* beta, int64_t P, int C, int inverse,
                      void* y_bf16, void* rnorm_bf16, hpc_stream_t stream);
 int hpc_gdn_bwd_umma_parts(int64_t P);
+/*  gdn_bwd_fused_umma (C in {128,192}): as gdn_bwd_umma, but the d(gamma) contraction
+ *                dgamma[i][j] = dgamma_scale * sum_p t[p][i] x[p][j]^2 runs inside the kernel on the same shared-
+ *                memory tiles (t and x^2 are never written to HBM), accumulated per CTA in TMEM and reduced over the
+ *                CTAs in a fixed order through `workspace` (>= hpc_gdn_bwd_fused_umma_workspace_bytes()).  Also
+ *                returns per-CTA column sums of dx: dxsum_part[parts][C] -- summed over parts this is the bias
+ *                gradient of the conv / transposed conv whose output feeds the GDN (analysis.py:55-58). */
+size_t hpc_gdn_bwd_fused_umma_workspace_bytes(int64_t P, int C);
+int hpc_gdn_bwd_fused_umma(const void* g_bf16, const void* x_bf16, const void* rnorm_bf16, const void* gammaT_bf16,
+                           int64_t P, int C, int inverse, void* dx_bf16, float* dgamma, float dgamma_scale,
+                           float* colsum_part, float* dxsum_part, void* workspace, size_t workspace_bytes,
+                           hpc_stream_t stream);
 int hpc_gdn_bwd_umma(const void* g_bf16, const void* x_bf16, const void* rnorm_bf16, const void* gammaT_bf16, int64_t P,
                      int C, int inverse, void* dx_bf16, void* t_bf16, void* xsq_bf16, float* colsum_part,
                      hpc_stream_t stream);

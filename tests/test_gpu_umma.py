@@ -69,9 +69,8 @@ def test_epilogues(epi):
 
 
 @pytest.mark.parametrize("inverse", [False, True])
-def test_gdn_forward_backward_engines(inverse):
+def test_gdn_forward_backward_engines(inverse, C=192, N=2, H=16, W=24):
     torch.manual_seed(2)
-    C, N, H, W = 192, 2, 16, 24
     x = torch.randn(N, H, W, C, device=DEV).to(torch.bfloat16)
     g = torch.randn(N, H, W, C, device=DEV).to(torch.bfloat16)
     gamma = (0.1 * torch.eye(C, device=DEV) + 0.01 * torch.rand(C, C, device=DEV)).view(C, C, 1, 1)
@@ -80,13 +79,40 @@ def test_gdn_forward_backward_engines(inverse):
     def run():
         xsq, _ = hp.square(x)
         y, nrm = hp.gdn_forward(x, xsq, gamma, beta, inverse)
-        dx, dg, db = hp.gdn_backward(g, x, xsq, nrm, gamma, inverse)
-        return {"y": y, "nrm": nrm, "dx": dx, "dg": dg, "db": db}
+        dx, dg, db, dxsum = hp.gdn_backward(g, x, xsq, nrm, gamma, inverse, want_dxsum=True)
+        if dxsum is None:
+            dxsum = hp.colsum(dx)
+        return {"y": y, "nrm": nrm, "dx": dx, "dg": dg, "db": db, "dxsum": dxsum}
     out, ref = _both(run)
     for k in ref:
         a, b = out[k].float(), ref[k].float()
         err = float((a - b).abs().max()) / (float(b.abs().max()) + 1e-20)
         assert err < 2e-2, (k, err)
+    # the in-kernel column sums are those of the bf16 dx the kernel stored
+    assert torch.allclose(out["dxsum"], out["dx"].float().sum((0, 1, 2)), rtol=1e-4, atol=1e-2)
+
+
+@pytest.mark.parametrize("inverse", [False, True])
+@pytest.mark.parametrize("C,N,H,W", [(192, 1, 9, 13), (192, 3, 96, 96), (128, 2, 16, 24), (128, 1, 150, 131),
+                                     (64, 2, 16, 24)])
+def test_gdn_fused_backward_shapes(inverse, C, N, H, W):
+    """Ragged last tile (P % 128 != 0), more tiles than CTAs (TMEM accumulation of d(gamma) over tiles), the
+    C = 128 column plan, and C = 64 (unfused d(gamma) path)."""
+    test_gdn_forward_backward_engines(inverse, C, N, H, W)
+
+
+def test_gdn_fused_backward_is_deterministic():
+    torch.manual_seed(5)
+    C = 192
+    x = torch.randn(2, 64, 64, C, device=DEV).to(torch.bfloat16)
+    g = torch.randn(2, 64, 64, C, device=DEV).to(torch.bfloat16)
+    gamma = (0.1 * torch.eye(C, device=DEV) + 0.01 * torch.rand(C, C, device=DEV)).view(C, C, 1, 1)
+    with pkg.compute_mode("bf16"):
+        y, nrm = hp.gdn_forward(x, None, gamma, 1 + torch.rand(C, device=DEV), False)
+        a = hp.gdn_backward(g, x, None, nrm, gamma, False, want_dxsum=True)
+        b = hp.gdn_backward(g, x, None, nrm, gamma, False, want_dxsum=True)
+    for u, v in zip(a, b):
+        assert torch.equal(u, v)
 
 
 def test_rejects_unsupported_shapes_loudly():
