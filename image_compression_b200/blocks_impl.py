@@ -86,7 +86,7 @@ def ga_backward(S, gy_lp):
         if kind == "conv":
             spec = a
             w, b = S.convs[ci]
-            gb = (gsum if gsum is not None else hp.colsum(g)) if b is not None else None
+            gb = (gsum if gsum is not None else hp.colsum(g, out=hp.grad_buffer(b))) if b is not None else None
             gsum = None
             gw = spec.wgrad(inp, g, w)
             conv_grads[ci] = (gw, gb)
@@ -95,14 +95,16 @@ def ga_backward(S, gy_lp):
         elif kind == "gdn":
             x, xsq, nrm, gamma = a
             gp, bp = S.gdns[gi]
-            dx, dgamma, dbeta, gsum = hp.gdn_backward(g, x, xsq, nrm, gamma, want_dxsum=True)
+            b_prod = S.convs[ci][1]       # bias of the layer that feeds this GDN: its gradient is colsum(dx)
+            dx, dgamma, dbeta, gsum = hp.gdn_backward(g, x, xsq, nrm, gamma, want_dxsum=True,
+                                                      dxsum_out=hp.grad_buffer(b_prod) if b_prod is not None and hp.gdn_bwd_has_dxsum(x) else None)
             gdn_grads[gi] = _gdn_param_grads(gp, bp, dgamma, dbeta)
             g = dx
             gi -= 1
         else:  # head conv: weight + bias grads only (the image needs no gradient)
             w, b = S.convs[0]
-            gw = hp.wgrad_c3(g, S.x, w.shape[0], w.shape[1])
-            gb = (gsum if gsum is not None else hp.colsum(g)) if b is not None else None
+            gw = hp.wgrad_c3(g, S.x, w.shape[0], w.shape[1], w)
+            gb = (gsum if gsum is not None else hp.colsum(g, out=hp.grad_buffer(b))) if b is not None else None
             conv_grads[0] = (gw, gb)
     return conv_grads, gdn_grads
 
@@ -150,20 +152,22 @@ def gs_backward(S, g_raw_nchw, need_input_grad=True):
         first = (idx == 0)
         if kind == "tail":
             w, b = S.convs[ci]
-            g, gw, gb = hp.deconv_c3_backward(g_raw_nchw, inp, w, need_dx=(not first) or need_input_grad)
+            g, gw, gb = hp.deconv_c3_backward(g_raw_nchw, inp, w, need_dx=(not first) or need_input_grad, bias=b)
             conv_grads[ci] = (gw, gb if b is not None else None)
             ci -= 1
         elif kind == "gdn":
             x, xsq, nrm, gamma = a
             gp, bp = S.gdns[gi]
-            dx, dgamma, dbeta, gsum = hp.gdn_backward(g, x, xsq, nrm, gamma, want_dxsum=True)
+            b_prod = S.convs[ci][1]       # bias of the layer that feeds this GDN: its gradient is colsum(dx)
+            dx, dgamma, dbeta, gsum = hp.gdn_backward(g, x, xsq, nrm, gamma, want_dxsum=True,
+                                                      dxsum_out=hp.grad_buffer(b_prod) if b_prod is not None and hp.gdn_bwd_has_dxsum(x) else None)
             gdn_grads[gi] = _gdn_param_grads(gp, bp, dgamma, dbeta)
             g = dx
             gi -= 1
         else:
             spec = a
             w, b = S.convs[ci]
-            gb = (gsum if gsum is not None else hp.colsum(g)) if b is not None else None
+            gb = (gsum if gsum is not None else hp.colsum(g, out=hp.grad_buffer(b))) if b is not None else None
             gsum = None
             gw = spec.wgrad(inp, g, w)
             conv_grads[ci] = (gw, gb)
@@ -204,7 +208,7 @@ def ha_backward(S, gz_lp, sign_add=None, need_input_grad=True):
     for i in range(len(S.convs) - 1, -1, -1):
         spec, inp = S.layers[i]
         w, b = S.convs[i]
-        gb = hp.colsum(g) if b is not None else None
+        gb = hp.colsum(g, out=hp.grad_buffer(b)) if b is not None else None
         gw = spec.wgrad(inp, g, w)
         conv_grads[i] = (gw, gb)
         if i > 0:
@@ -254,7 +258,7 @@ def hs_backward(S, gpre_lp, need_input_grad=True, want_f32=False):
     for i in range(len(S.convs) - 1, -1, -1):
         spec, inp = S.layers[i]
         w, b = S.convs[i]
-        gb = hp.colsum(g) if b is not None else None
+        gb = hp.colsum(g, out=hp.grad_buffer(b)) if b is not None else None
         gw = spec.wgrad(inp, g, w)
         conv_grads[i] = (gw, gb)
         if i > 0:

@@ -167,6 +167,27 @@ def _fill_taps(P, taps, phases):
 
 _pack_cache = {}
 _capturing = False
+_grad_sink = None
+
+
+def set_grad_sink(sink):
+    """sink: {param.data_ptr(): zero-filled fp32 view shaped like the parameter} or None.  While armed, the
+    backward functions below take the OUTPUT buffer of a parameter's gradient from the sink (each entry once), so
+    the kernels write into the caller's flat gradient buffer (sharding.FlatGradients) instead of fresh tensors."""
+    global _grad_sink
+    _grad_sink = sink if sink else None
+
+
+def grad_buffer(param, zero=False):
+    """Output buffer for the gradient of `param` (fp32, param's shape)."""
+    s = _grad_sink
+    if s is not None and param is not None:
+        v = s.pop(param.data_ptr(), None)
+        if v is not None and v.shape == param.shape and v.device == param.device:
+            return v                      # zero-filled by FlatGradients.zero()
+    if zero:
+        return torch.zeros(param.shape, dtype=torch.float32, device=param.device)
+    return torch.empty(param.shape, dtype=torch.float32, device=param.device)
 
 
 def set_capturing(flag):
@@ -268,11 +289,13 @@ def igemm_wgrad(lo, hi, taps, phases, hs, scale=1.0, out=None, out_strides=None)
     return gw
 
 
-def colsum(x2d_like, scale=1.0):
+def colsum(x2d_like, scale=1.0, out=None):
     """sum over all leading dims -> (C,) fp32."""
     C = x2d_like.shape[-1]
     P = x2d_like.numel() // C
-    out = torch.empty((C,), dtype=torch.float32, device=x2d_like.device)
+    if out is None:
+        out = torch.empty((C,), dtype=torch.float32, device=x2d_like.device)
+    assert out.numel() == C and out.dtype == torch.float32 and out.is_contiguous()
     nb = lib().hpc_colsum_scratch_bytes(P, C)
     sc = torch.empty(nb, dtype=torch.uint8, device=x2d_like.device)
     check(lib().hpc_colsum(ptr(x2d_like), _lib.dtype_code(x2d_like), P, C, scale, ptr(out), ptr(sc), nb, stream()))
@@ -332,7 +355,7 @@ class ConvSpec:
         reference weight layout (fp32)."""
         K, Ci, Co = self.K, self.cin, self.cout
         taps, phases = self.deconv_taps
-        gw_ref = torch.empty(weight_shape_like.shape, dtype=torch.float32, device=x.device)
+        gw_ref = grad_buffer(weight_shape_like)
         lo, hi, rows, cols, sr, sc = (x, g, Ci, Co, Co * K, K) if self.transposed else (g, x, Co, Ci, Ci * K, K)
         # transposed: lo = x (rows=Ci), hi = g (cols=Co), W[ci][co][k]; else lo = g (rows=Co), hi = x, W[co][ci][k]
         if engine() == _lib.ENGINE_UMMA:
@@ -363,7 +386,7 @@ def nonneg_fwd(param, bound, pedestal=PEDESTAL):
 
 
 def nonneg_bwd(param, gout, bound, scale=1.0):
-    g = torch.empty_like(param)
+    g = grad_buffer(param)
     check(lib().hpc_nonneg_bwd(ptr(param), ptr(gout), ptr(g), param.numel(), bound, scale, stream()))
     return g
 
@@ -399,15 +422,20 @@ def gdn_forward(x, xsq, gamma_eff, beta_eff, inverse=False):
     return o["lp"], o["nrm"]
 
 
-def gdn_backward(g, x, xsq, nrm, gamma_eff, inverse=False, need_dx=True, want_dxsum=False):
+def gdn_bwd_has_dxsum(x):
+    """True when gdn_backward(x, ..., want_dxsum=True) will return the column sums of dx."""
+    return gdn_fused_ok(x.dtype, x.shape[-1]) and x.shape[-1] in (128, 192)
+
+
+def gdn_backward(g, x, xsq, nrm, gamma_eff, inverse=False, need_dx=True, want_dxsum=False, dxsum_out=None):
     """SURVEY A.4.  Returns (dx lp, dgamma_eff (C,C,1,1) fp32, dbeta_eff (C,) fp32) and, with want_dxsum, a
     fourth value: the column sums of dx (the bias gradient of the layer that feeds this GDN) when the fused
     kernel produced them, else None."""
-    out = _gdn_backward(g, x, xsq, nrm, gamma_eff, inverse, need_dx)
+    out = _gdn_backward(g, x, xsq, nrm, gamma_eff, inverse, need_dx, dxsum_out if want_dxsum else None)
     return out if want_dxsum else out[:3]
 
 
-def _gdn_backward(g, x, xsq, nrm, gamma_eff, inverse, need_dx):
+def _gdn_backward(g, x, xsq, nrm, gamma_eff, inverse, need_dx, dxsum_out=None):
     N, H, W, C = x.shape
     sgn = 0.5 if inverse else -0.5
     if gdn_fused_ok(x.dtype, C) and need_dx:
@@ -422,7 +450,7 @@ def _gdn_backward(g, x, xsq, nrm, gamma_eff, inverse, need_dx):
             ws = torch.empty(wsb, dtype=torch.uint8, device=x.device)
             check(lib().hpc_gdn_bwd_fused_umma(ptr(g), ptr(x), ptr(nrm), ptr(wp), P, C, int(inverse), ptr(dx),
                                                ptr(dgamma), sgn, ptr(parts[0]), ptr(parts[1]), ptr(ws), wsb, stream()))
-            return dx, dgamma, colsum(parts[0], sgn), colsum(parts[1])
+            return dx, dgamma, colsum(parts[0], sgn), colsum(parts[1], out=dxsum_out)
         dx, t, sq = torch.empty_like(x), torch.empty_like(x), torch.empty_like(x)
         parts = torch.empty((lib().hpc_gdn_bwd_umma_parts(P), C), dtype=torch.float32, device=x.device)
         check(lib().hpc_gdn_bwd_umma(ptr(g), ptr(x), ptr(nrm), ptr(wp), P, C, int(inverse), ptr(dx), ptr(t), ptr(sq),
@@ -487,10 +515,14 @@ def conv_c3_forward(x_nchw, weight, bias, want_sq=True, want_f32=False):
     return out, sq, of
 
 
-def wgrad_c3(wide_nhwc, thin_nchw, Cw, Cs):
-    """gw (Cw,Cs,5,5) = sum wide[n,i,j,cw]*thin[n,cs,2i-2+kh,2j-2+kw]."""
+def wgrad_c3(wide_nhwc, thin_nchw, Cw, Cs, weight=None):
+    """gw (Cw,Cs,5,5) = sum wide[n,i,j,cw]*thin[n,cs,2i-2+kh,2j-2+kw].  `weight`: the parameter this is the
+    gradient of (selects the output buffer, see grad_buffer)."""
     N, H, W, _ = wide_nhwc.shape
-    gw = torch.empty((Cw, Cs, 5, 5), dtype=torch.float32, device=wide_nhwc.device)
+    if weight is not None and tuple(weight.shape) == (Cw, Cs, 5, 5):
+        gw = grad_buffer(weight)
+    else:
+        gw = torch.empty((Cw, Cs, 5, 5), dtype=torch.float32, device=wide_nhwc.device)
     if _thin_umma_ok(Cw, Cs, wide_nhwc.dtype):
         nb = lib().hpc_wgrad_c3_umma_workspace_bytes(N, Cw, H, W)
         sc = torch.empty(nb, dtype=torch.uint8, device=wide_nhwc.device)
@@ -518,7 +550,7 @@ def deconv_c3_forward(x_nhwc, weight, bias):
     return out
 
 
-def deconv_c3_backward(g_nchw, x_nhwc, weight, need_dx=True):
+def deconv_c3_backward(g_nchw, x_nhwc, weight, need_dx=True, bias=None):
     """g: (N,3,2H,2W) fp32.  dgrad = Conv2d(3->C) with the same weight layout; wgrad; bias grad."""
     N, Cs, H2, W2 = g_nchw.shape
     Cw = weight.shape[0]
@@ -532,8 +564,8 @@ def deconv_c3_backward(g_nchw, x_nhwc, weight, need_dx=True):
         else:
             check(lib().hpc_conv_c3_fwd(ptr(g_nchw), ptr(weight), Cs * 25, 25, None, N, Cs, H2, W2, Cw, None, ptr(dx),
                                         None, _lib.dtype_code(dt), stream()))
-    gw = wgrad_c3(x_nhwc, g_nchw, Cw, Cs)
-    gb = torch.empty((Cs,), dtype=torch.float32, device=g_nchw.device)
+    gw = wgrad_c3(x_nhwc, g_nchw, Cw, Cs, weight)
+    gb = grad_buffer(bias) if bias is not None else torch.empty((Cs,), dtype=torch.float32, device=g_nchw.device)
     sc = torch.empty((N * Cs,), dtype=torch.float32, device=g_nchw.device)
     check(lib().hpc_nchw_channel_sum(ptr(g_nchw), N, Cs, H2 * W2, ptr(gb), ptr(sc), stream()))
     return dx, gw, gb
@@ -590,7 +622,7 @@ def factorized_backward(zt, cdf, training, g_bits, g_scale, g_probs=None, g_zt=N
     C = zt.shape[-1]
     P = zt.numel() // C
     gz = torch.empty_like(zt)
-    grads = {k: torch.zeros_like(v) for k, v in cdf.items()}
+    grads = {k: grad_buffer(v, zero=True) for k, v in cdf.items()}
     s, gs = _cdf_struct(cdf), _cdf_struct(grads)
     check(lib().hpc_factorized_bwd(ptr(zt), byref(s), P, C, int(training), bin_, ptr(g_bits), g_scale, ptr(g_probs),
                                    ptr(g_zt), ptr(gz), byref(gs), stream()))

@@ -35,14 +35,54 @@ class FlatGradients:
             n += (p.numel() + 3) // 4 * 4
         self.flat = torch.zeros(n, dtype=torch.float32, device=device)
         self.numel = sum(p.numel() for p in self.params)
-        for p, o in zip(self.params, offs):
-            p.grad = self.flat[o:o + p.numel()].view(p.shape)
+        self.offsets = offs
+        self.direct = self.flat.is_cuda       # the CUDA backward writes into the slots itself (see zero())
+        self.copies = 0                       # slots that had to be filled by a copy in collect() (0 when direct)
+        for p in self.params:
+            p.grad = self._view(p)
+
+    def _view(self, p):
+        o = self.offsets[self._index(p)]
+        return self.flat[o:o + p.numel()].view(p.shape)
+
+    def _index(self, p):
+        if not hasattr(self, "_idx"):
+            self._idx = {id(q): i for i, q in enumerate(self.params)}
+        return self._idx[id(p)]
 
     def zero(self):
+        """One fill of the flat buffer.  On CUDA the slots are then handed to the backward kernels as their
+        OUTPUT buffers (hotpath.set_grad_sink): `.grad` is dropped, the package's backward writes every gradient
+        straight into its slot and autograd adopts the returned view as the new `.grad` -- no per-parameter
+        AccumulateGrad add.  A second backward before the next zero() accumulates the ordinary way."""
         self.flat.zero_()
+        if self.direct:
+            from . import hotpath as hp
+            sink = {}
+            for p in self.params:
+                p.grad = None
+                sink[p.data_ptr()] = self._view(p)       # a fresh view object: autograd must be its only owner
+            hp.set_grad_sink(sink)
+
+    def collect(self):
+        """Re-establish `.grad is a view of the flat buffer` after backward (a no-op check when the backward wrote
+        the slots directly; otherwise one copy per stray gradient)."""
+        if self.direct:
+            from . import hotpath as hp
+            hp.set_grad_sink(None)
+        for p, o in zip(self.params, self.offsets):
+            g = p.grad
+            if g is not None and g.data_ptr() == self.flat.data_ptr() + 4 * o:
+                continue
+            v = self.flat[o:o + p.numel()].view(p.shape)
+            if g is not None:
+                v.copy_(g)
+                self.copies += 1
+            p.grad = v
 
     def all_reduce_mean(self, group=None, async_op=False):
         """Mean over ranks of the whole gradient (no-op without an initialised process group)."""
+        self.collect()
         if not (dist.is_available() and dist.is_initialized()):
             return None
         world = dist.get_world_size(group)
