@@ -121,15 +121,19 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
-      mbar_arrive_expect_tx(g_full, Cfg::GAMMA);
-      for (int c = 0; c < KC; ++c) tma_load_2d(gam + c * (C * 128), &tmG, g_full, c * 64, 0);
+    // lane c issues chunk c: the TMA instructions of a tile go out in parallel (each costs its thread ~100+ cycles)
+    if (lane < KC) {
+      constexpr uint32_t lanes = (1u << KC) - 1;
+      if (lane == 0) mbar_arrive_expect_tx(g_full, Cfg::GAMMA);
+      __syncwarp(lanes);
+      tma_load_2d(gam + lane * (C * 128), &tmG, g_full, lane * 64, 0);
       int it = 0;
       for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
         const int b = it & 1;
         mbar_wait(&xs_empty[b], ((it >> 1) & 1) ^ 1);
-        mbar_arrive_expect_tx(&xs_full[b], Cfg::TILE);
-        for (int c = 0; c < KC; ++c) tma_load_2d(xs + b * Cfg::TILE + c * G_CHUNK, &tmX, &xs_full[b], c * 64, tile * 128);
+        if (lane == 0) mbar_arrive_expect_tx(&xs_full[b], Cfg::TILE);
+        __syncwarp(lanes);
+        tma_load_2d(xs + b * Cfg::TILE + lane * G_CHUNK, &tmX, &xs_full[b], lane * 64, tile * 128);
       }
     }
   } else if (warp == 1) {
@@ -149,17 +153,23 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
       }
     }
   } else if (warp == 2) {
-    if (lane == 0) {
+    // lanes 0..KC-1 store the y chunks, lanes KC..2KC-1 the r chunks (bulk groups are per thread)
+    if (lane < 2 * KC) {
+      constexpr uint32_t lanes = (1u << (2 * KC)) - 1;
+      const int c = lane % KC;
       int it = 0;
       for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
         const int b = it & 1;
         mbar_wait(out_full, it & 1);
-        for (int c = 0; c < KC; ++c) tma_store_2d(&tmY, xs + b * Cfg::TILE + c * G_CHUNK, c * 64, tile * 128);
-        for (int c = 0; c < KC; ++c) tma_store_2d(&tmR, a2 + c * G_CHUNK, c * 64, tile * 128);
+        if (lane < KC) tma_store_2d(&tmY, xs + b * Cfg::TILE + c * G_CHUNK, c * 64, tile * 128);
+        else tma_store_2d(&tmR, a2 + c * G_CHUNK, c * 64, tile * 128);
         bulk_commit();
         bulk_wait_read0();
-        mbar_arrive(&xs_empty[b]);
-        mbar_arrive(a2_empty);
+        __syncwarp(lanes);
+        if (lane == 0) {
+          mbar_arrive(&xs_empty[b]);
+          mbar_arrive(a2_empty);
+        }
       }
       bulk_wait0();
     }
@@ -275,18 +285,21 @@ gdn_bwd_umma_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
-      mbar_arrive_expect_tx(g_full, Cfg::GAMMA);
-      for (int c = 0; c < KC; ++c) tma_load_2d(gam + c * (C * 128), &tmG, g_full, c * 64, 0);
+    // lane l issues chunk l % KC of tensor l / KC (g, x, r): 3 KC TMA instructions per tile, issued in parallel
+    if (lane < 3 * KC) {
+      constexpr uint32_t lanes = (1u << (3 * KC)) - 1;
+      const int c = lane % KC, which = lane / KC;
+      if (lane == 0) mbar_arrive_expect_tx(g_full, Cfg::GAMMA);
+      __syncwarp(lanes);
+      if (lane < KC) tma_load_2d(gam + lane * (C * 128), &tmG, g_full, lane * 64, 0);
+      uint8_t* dst = (which == 0 ? bg : (which == 1 ? bx : bn)) + c * G_CHUNK;
+      const CUtensorMap* tm = which == 0 ? &tmGr : (which == 1 ? &tmX : &tmR);
       int it = 0;
       for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
         mbar_wait(in_empty, (it & 1) ^ 1);
-        mbar_arrive_expect_tx(in_full, 3 * Cfg::TILE);
-        for (int c = 0; c < KC; ++c) {
-          tma_load_2d(bg + c * G_CHUNK, &tmGr, in_full, c * 64, tile * 128);
-          tma_load_2d(bx + c * G_CHUNK, &tmX, in_full, c * 64, tile * 128);
-          tma_load_2d(bn + c * G_CHUNK, &tmR, in_full, c * 64, tile * 128);
-        }
+        if (lane == 0) mbar_arrive_expect_tx(in_full, 3 * Cfg::TILE);
+        __syncwarp(lanes);
+        tma_load_2d(dst, tm, in_full, c * 64, tile * 128);
       }
     }
   } else if (warp == 1) {
@@ -306,18 +319,19 @@ gdn_bwd_umma_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
       }
     }
   } else if (warp == 2) {
-    if (lane == 0) {
+    if (lane < 3 * KC) {
+      constexpr uint32_t lanes = (1u << (3 * KC)) - 1;
+      const int c = lane % KC, which = lane / KC;
+      const uint8_t* src = (which == 0 ? bg : (which == 1 ? bn : bx)) + c * G_CHUNK;
+      const CUtensorMap* tm = which == 0 ? &tmDx : (which == 1 ? &tmT : &tmSq);
       int it = 0;
       for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
         mbar_wait(out_full, it & 1);
-        for (int c = 0; c < KC; ++c) {
-          tma_store_2d(&tmDx, bg + c * G_CHUNK, c * 64, tile * 128);
-          tma_store_2d(&tmT, bn + c * G_CHUNK, c * 64, tile * 128);
-          tma_store_2d(&tmSq, bx + c * G_CHUNK, c * 64, tile * 128);
-        }
+        tma_store_2d(tm, src, c * 64, tile * 128);
         bulk_commit();
         bulk_wait_read0();
-        mbar_arrive(in_empty);
+        __syncwarp(lanes);
+        if (lane == 0) mbar_arrive(in_empty);
       }
       bulk_wait0();
     }
@@ -481,18 +495,21 @@ gdn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_cons
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
-      mbar_arrive_expect_tx(g_full, Cfg::GAMMA);
-      for (int c = 0; c < KC; ++c) tma_load_2d(gam + c * (C * 128), &tmG, g_full, c * 64, 0);
+    // lane l issues chunk l % KC of tensor l / KC (g, x, r): 3 KC TMA instructions per tile, issued in parallel
+    if (lane < 3 * KC) {
+      constexpr uint32_t lanes = (1u << (3 * KC)) - 1;
+      const int c = lane % KC, which = lane / KC;
+      if (lane == 0) mbar_arrive_expect_tx(g_full, Cfg::GAMMA);
+      __syncwarp(lanes);
+      if (lane < KC) tma_load_2d(gam + lane * (C * 128), &tmG, g_full, lane * 64, 0);
+      uint8_t* dst = (which == 0 ? bg : (which == 1 ? bx : bn)) + c * G_CHUNK;
+      const CUtensorMap* tm = which == 0 ? &tmGr : (which == 1 ? &tmX : &tmR);
       int it = 0;
       for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
         mbar_wait(in_empty, (it & 1) ^ 1);
-        mbar_arrive_expect_tx(in_full, 3 * Cfg::TILE);
-        for (int c = 0; c < KC; ++c) {
-          tma_load_2d(bg + c * G_CHUNK, &tmGr, in_full, c * 64, tile * 128);
-          tma_load_2d(bx + c * G_CHUNK, &tmX, in_full, c * 64, tile * 128);
-          tma_load_2d(bn + c * G_CHUNK, &tmR, in_full, c * 64, tile * 128);
-        }
+        if (lane == 0) mbar_arrive_expect_tx(in_full, 3 * Cfg::TILE);
+        __syncwarp(lanes);
+        tma_load_2d(dst, tm, in_full, c * 64, tile * 128);
       }
     }
   } else if (warp == 1) {
@@ -532,14 +549,16 @@ gdn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_cons
       mma_commit(dg_done);
     }
   } else if (warp == 2) {
-    if (lane == 0) {
+    if (lane < KC) {
+      constexpr uint32_t lanes = (1u << KC) - 1;
       int it = 0;
       for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
         mbar_wait(out_full, it & 1);
-        for (int c = 0; c < KC; ++c) tma_store_2d(&tmDx, bg + c * G_CHUNK, c * 64, tile * 128);
+        tma_store_2d(&tmDx, bg + lane * G_CHUNK, lane * 64, tile * 128);
         bulk_commit();
         bulk_wait_read0();
-        mbar_arrive(in_empty);
+        __syncwarp(lanes);
+        if (lane == 0) mbar_arrive(in_empty);
       }
       bulk_wait0();
     }

@@ -10,6 +10,8 @@
 //   tile i overlaps the MMAs of tile i+1.
 #include <cuda.h>
 
+#include <cstdlib>
+
 #include "igemm_epilogue.cuh"
 #include "tmap.cuh"
 #include "umma_ptx.cuh"
@@ -34,10 +36,10 @@ struct FwdKParams {
   EpiArgs epi;
 };
 
-template <int BLOCK_N>
+template <int BLOCK_N, int NCTA>
 struct FwdCfg {
   static constexpr int A_BYTES = FW_BM * FW_BK * 2;        // 16 KB
-  static constexpr int B_BYTES = BLOCK_N * FW_BK * 2;
+  static constexpr int B_BYTES = (BLOCK_N / NCTA) * FW_BK * 2;   // a CTA of a pair holds half of the weight tile
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGES = (200 * 1024 / STAGE_BYTES) > 8 ? 8 : (200 * 1024 / STAGE_BYTES);
   static constexpr int ACC_STRIDE = BLOCK_N <= 32 ? 32 : (BLOCK_N <= 64 ? 64 : (BLOCK_N <= 128 ? 128 : 256));
@@ -45,9 +47,14 @@ struct FwdCfg {
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + 1024 /*bias*/;
 };
 
-__device__ __forceinline__ void tile_coords(const FwdKParams& p, int tile, int& ph, int& n0, int& i0, int& j0) {
-  ph = tile / p.tiles_per_phase;
-  int r = tile - ph * p.tiles_per_phase;
+// Work item `w` of the persistent loop -> (phase, tile origin).  NCTA == 1: w is a tile.  NCTA == 2: w is a PAIR of
+// consecutive tiles of one phase (so both CTAs run the same tap sequence) and `rank` picks the tile; a phase with an
+// odd tile count ends in a phantom tile whose batch origin n0 >= N (TMA zero fill, no rows stored).
+template <int NCTA>
+__device__ __forceinline__ void tile_coords(const FwdKParams& p, int w, int rank, int& ph, int& n0, int& i0, int& j0) {
+  const int per = NCTA == 1 ? p.tiles_per_phase : (p.tiles_per_phase + 1) / 2;
+  ph = w / per;
+  int r = (w - ph * per) * NCTA + rank;
   const int tj = r % p.tiles_w; r /= p.tiles_w;
   const int ti = r % p.tiles_h; r /= p.tiles_h;
   n0 = r * p.nb; i0 = ti * p.th; j0 = tj * p.tw;
@@ -155,24 +162,26 @@ __device__ __forceinline__ void epilogue8(const EpiArgs& e, const float* acc, in
   if (e.out_nrm_lp && (e.epi == HPC_EPI_GDN || e.epi == HPC_EPI_IGDN)) store8_bf16(e.out_nrm_lp, o, nrm);
 }
 
-template <int BLOCK_N>
-__global__ void __launch_bounds__(FW_THREADS, 1)
-igemm_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                      const __grid_constant__ FwdKParams p) {
-  using Cfg = FwdCfg<BLOCK_N>;
+template <int BLOCK_N, int NCTA>
+__device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const FwdKParams& p) {
+  using Cfg = FwdCfg<BLOCK_N, NCTA>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;                                  // STAGES x 16 KB
   uint8_t* smem_b = smem + Cfg::STAGES * Cfg::A_BYTES;     // STAGES x B_BYTES (multiples of 1 KB)
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
-  uint64_t* full_bar = bars;                    // [STAGES]  TMA -> MMA
-  uint64_t* empty_bar = bars + Cfg::STAGES;     // [STAGES]  MMA -> TMA
-  uint64_t* tfull_bar = bars + 2 * Cfg::STAGES; // [2]       MMA -> epilogue
-  uint64_t* tempty_bar = tfull_bar + 2;         // [2]       epilogue -> MMA
+  uint64_t* full_bar = bars;                    // [STAGES]  TMA -> MMA     (pair: the leader's collects both CTAs)
+  uint64_t* empty_bar = bars + Cfg::STAGES;     // [STAGES]  MMA -> TMA     (pair: commit multicast to both CTAs)
+  uint64_t* tfull_bar = bars + 2 * Cfg::STAGES; // [2]       MMA -> epilogue (pair: multicast)
+  uint64_t* tempty_bar = tfull_bar + 2;         // [2]       epilogue -> MMA (pair: both CTAs arrive at the leader's)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
   float* bias_s = reinterpret_cast<float*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256);   // bias staged once per CTA
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int rank = NCTA == 2 ? (int)cluster_ctarank() : 0;
+  const int worker = blockIdx.x / NCTA, nworkers = gridDim.x / NCTA;       // CTA (or CTA pair) index
+  const int per_phase = NCTA == 1 ? p.tiles_per_phase : (p.tiles_per_phase + 1) / 2;
+  const int total_work = per_phase * p.nphases;
   if (p.epi.bias)
     for (int i = threadIdx.x; i < BLOCK_N; i += FW_THREADS) bias_s[i] = p.epi.bias[i];
 
@@ -180,46 +189,60 @@ igemm_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
     for (int s = 0; s < Cfg::STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&tfull_bar[s], 1); mbar_init(&tempty_bar[s], 4); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&tfull_bar[s], 1); mbar_init(&tempty_bar[s], 4 * NCTA); }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+  if (warp == 1) {
+    if (NCTA == 2) tmem_alloc_pair(tmem_slot, Cfg::TMEM_COLS); else tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+  }
   tc_fence_before();
-  __syncthreads();
+  if (NCTA == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
     // ================================ TMA producer ================================
-    if (lane == 0) {
+    // The whole warp runs the loop; lane 0 issues the activation box and lane 1 the weight box of a stage (a TMA
+    // instruction costs its issuing thread ~100+ cycles, so the boxes of one stage are issued from different lanes).
+    if (lane < 2) {
       int stage = 0; uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+      for (int w = worker; w < total_work; w += nworkers) {
         int ph, n0, i0, j0;
-        tile_coords(p, tile, ph, n0, i0, j0);
+        tile_coords<NCTA>(p, w, rank, ph, n0, i0, j0);
         const hpc_igemm_phase P = p.phase[ph];
         for (int t = P.tap_begin; t < P.tap_begin + P.ntaps; ++t) {
           const int cw = j0 * p.is + p.dw[t], chh = i0 * p.is + p.dh[t];
           for (int c = 0; c < p.kchunks; ++c) {
             mbar_wait(&empty_bar[stage], phase ^ 1);
-            mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
-            tma_load_4d(smem_a + stage * Cfg::A_BYTES, &tmA, &full_bar[stage], c * FW_BK, cw, chh, n0);
-            tma_load_2d(smem_b + stage * Cfg::B_BYTES, &tmB, &full_bar[stage], c * FW_BK, t * p.Co);
+            if (NCTA == 1) {
+              if (lane == 0) mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+              __syncwarp(3u);
+              if (lane == 0) tma_load_4d(smem_a + stage * Cfg::A_BYTES, &tmA, &full_bar[stage], c * FW_BK, cw, chh, n0);
+              else tma_load_2d(smem_b + stage * Cfg::B_BYTES, &tmB, &full_bar[stage], c * FW_BK, t * p.Co);
+            } else {
+              // each CTA loads its own pixels and its half of the output channels; all bytes complete on the leader
+              if (rank == 0 && lane == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::STAGE_BYTES);
+              __syncwarp(3u);
+              const uint32_t lead = mapa_u32(smem_u32(&full_bar[stage]), 0);
+              if (lane == 0) tma_load_4d_pair(smem_a + stage * Cfg::A_BYTES, &tmA, lead, c * FW_BK, cw, chh, n0);
+              else tma_load_2d_pair(smem_b + stage * Cfg::B_BYTES, &tmB, lead, c * FW_BK, t * p.Co + rank * (BLOCK_N / 2));
+            }
             if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
           }
         }
       }
     }
   } else if (warp == 1) {
-    // ================================ MMA issuer ==================================
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(FW_BM, BLOCK_N, 0, 0);
+    // ================================ MMA issuer (pair: leader only) ==============
+    if (lane == 0 && rank == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(FW_BM * NCTA, BLOCK_N, 0, 0);
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+      for (int w = worker; w < total_work; w += nworkers) {
         int ph, n0, i0, j0;
-        tile_coords(p, tile, ph, n0, i0, j0);
+        tile_coords<NCTA>(p, w, 0, ph, n0, i0, j0);
         const int ksteps = p.phase[ph].ntaps * p.kchunks;
-        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);     // epilogue has drained this accumulator
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);     // epilogue(s) have drained this accumulator
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * Cfg::ACC_STRIDE;
         for (int ks = 0; ks < ksteps; ++ks) {
@@ -231,12 +254,14 @@ igemm_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           for (int k = 0; k < FW_BK / 16; ++k) {
             const uint64_t ad = make_smem_desc_sw128(a_addr + k * 32, 16, 1024);
             const uint64_t bd = make_smem_desc_sw128(b_addr + k * 32, 16, 1024);
-            mma_bf16_ss(d_tmem, ad, bd, idesc, (ks | k) != 0);
+            if (NCTA == 1) mma_bf16_ss(d_tmem, ad, bd, idesc, (ks | k) != 0);
+            else mma_bf16_ss_pair(d_tmem, ad, bd, idesc, (ks | k) != 0);
           }
-          mma_commit(&empty_bar[stage]);                // frees the smem stage when these MMAs retire
+          // frees the smem stage (in both CTAs) when these MMAs retire
+          if (NCTA == 1) mma_commit(&empty_bar[stage]); else mma_commit_pair(&empty_bar[stage]);
           if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
         }
-        mma_commit(&tfull_bar[acc]);                    // accumulator complete -> epilogue
+        if (NCTA == 1) mma_commit(&tfull_bar[acc]); else mma_commit_pair(&tfull_bar[acc]);   // accumulator complete
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
@@ -247,9 +272,9 @@ igemm_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     EpiArgs epi = p.epi;
     if (epi.bias) epi.bias = bias_s;        // broadcast shared-memory reads instead of 48 global loads per tile
     int acc = 0; uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+    for (int w = worker; w < total_work; w += nworkers) {
       int ph, n0, i0, j0;
-      tile_coords(p, tile, ph, n0, i0, j0);
+      tile_coords<NCTA>(p, w, rank, ph, n0, i0, j0);
       const hpc_igemm_phase P = p.phase[ph];
       const int jl = row % p.tw, il = (row / p.tw) % p.th, nl = row / (p.tw * p.th);
       const int n = n0 + nl, i = i0 + il, j = j0 + jl;
@@ -271,13 +296,35 @@ igemm_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      if (lane == 0) {
+        if (NCTA == 1) mbar_arrive(&tempty_bar[acc]);
+        else mbar_arrive_cluster(mapa_u32(smem_u32(&tempty_bar[acc]), 0));
+      }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   }
   tc_fence_before();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  if (NCTA == 2) cluster_sync_all(); else __syncthreads();
+  if (warp == 1) {
+    if (NCTA == 2) tmem_dealloc_pair(tmem_base, Cfg::TMEM_COLS); else tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(FW_THREADS, 1)
+igemm_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                      const __grid_constant__ FwdKParams p) {
+  igemm_fwd_body<BLOCK_N, 1>(tmA, tmB, p);
+}
+
+// CTA-pair version: cluster of two CTAs = the two SMs of a TPC, one tcgen05.mma.cta_group::2 of M = 256 per k-step.
+// Each CTA stages only half of the weight tile, so a pipeline stage is 28 KB instead of 40 KB (C = 192): 7 stages in
+// flight and 30% fewer operand bytes per MMA -- the single-CTA kernel is bound by bytes-in-flight x L2 latency.
+template <int BLOCK_N>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FW_THREADS, 1)
+igemm_fwd_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                           const __grid_constant__ FwdKParams p) {
+  igemm_fwd_body<BLOCK_N, 2>(tmA, tmB, p);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -286,18 +333,39 @@ igemm_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
 static int pow2_floor(int v) { int r = 1; while (r * 2 <= v) r *= 2; return r; }
 
 template <int BLOCK_N>
-static int launch_fwd(const CUtensorMap& tmA, const CUtensorMap& tmB, const FwdKParams& kp, cudaStream_t st) {
-  using Cfg = FwdCfg<BLOCK_N>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    HPC_CUDA(cudaFuncSetAttribute(igemm_fwd_umma_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  Cfg::SMEM_BYTES));
-    attr_set = true;
+static int launch_fwd(const CUtensorMap& tmA, const CUtensorMap& tmB, const FwdKParams& kp, bool pair, cudaStream_t st) {
+  if (pair) {
+    using Cfg = FwdCfg<BLOCK_N, 2>;
+    static bool attr_set = false;
+    if (!attr_set) {
+      HPC_CUDA(cudaFuncSetAttribute(igemm_fwd_umma_pair_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    Cfg::SMEM_BYTES));
+      attr_set = true;
+    }
+    const int pairs = (kp.tiles_per_phase + 1) / 2 * kp.nphases, tpcs = hpc_num_sms() / 2;
+    const int grid = 2 * (pairs < tpcs ? pairs : tpcs);
+    igemm_fwd_umma_pair_kernel<BLOCK_N><<<grid, FW_THREADS, Cfg::SMEM_BYTES, st>>>(tmA, tmB, kp);
+  } else {
+    using Cfg = FwdCfg<BLOCK_N, 1>;
+    static bool attr_set = false;
+    if (!attr_set) {
+      HPC_CUDA(cudaFuncSetAttribute(igemm_fwd_umma_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    Cfg::SMEM_BYTES));
+      attr_set = true;
+    }
+    const int grid = kp.total_tiles < hpc_num_sms() ? kp.total_tiles : hpc_num_sms();
+    igemm_fwd_umma_kernel<BLOCK_N><<<grid, FW_THREADS, Cfg::SMEM_BYTES, st>>>(tmA, tmB, kp);
   }
-  int grid = kp.total_tiles < hpc_num_sms() ? kp.total_tiles : hpc_num_sms();
-  igemm_fwd_umma_kernel<BLOCK_N><<<grid, FW_THREADS, Cfg::SMEM_BYTES, st>>>(tmA, tmB, kp);
   HPC_LAUNCH_CHECK();
   return HPC_OK;
+}
+
+// CTA pairs pay off once every TPC has a pair of tiles; below that the single-CTA kernel keeps more SMs busy.
+static bool fwd_use_pair(const FwdKParams& kp) {
+  static int mode = -1;                       // HPC_FWD_PAIR=0 / 1 forces the choice (A/B measurements)
+  if (mode < 0) { const char* e = getenv("HPC_FWD_PAIR"); mode = e ? (atoi(e) ? 1 : 0) : 2; }
+  if (mode != 2) return mode == 1;
+  return kp.total_tiles >= hpc_num_sms();
 }
 
 static int ntaps_total_all(const hpc_igemm_fwd_params* p) {
@@ -341,6 +409,7 @@ int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
     if (e > ntaps_total) ntaps_total = e;
   }
 
+  const bool pair = fwd_use_pair(kp);
   CUtensorMap tmA, tmB;
   {
     uint64_t dims[4] = {(uint64_t)p->Ci, (uint64_t)p->W, (uint64_t)p->H, (uint64_t)p->N};
@@ -353,7 +422,7 @@ int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
   {
     uint64_t dims[2] = {(uint64_t)p->Ci, (uint64_t)ntaps_total * p->Co};
     uint64_t strides[1] = {(uint64_t)p->Ci * 2};
-    uint32_t box[2] = {(uint32_t)FW_BK, (uint32_t)p->Co};
+    uint32_t box[2] = {(uint32_t)FW_BK, (uint32_t)(pair ? p->Co / 2 : p->Co)};
     uint32_t estr[2] = {1, 1};
     int rc = make_tmap(&tmB, p->w, 2, dims, strides, box, estr);
     if (rc) return rc;
@@ -364,10 +433,10 @@ int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
   HpcProfScope prof(HPC_PROF_IGEMM_FWD,
                     2.0 * p->N * p->GH * p->GW * (double)ntaps_total_all(p) * p->Ci * p->Co, stream);
   switch (p->Co) {
-    case 64: return launch_fwd<64>(tmA, tmB, kp, st);
-    case 128: return launch_fwd<128>(tmA, tmB, kp, st);
-    case 192: return launch_fwd<192>(tmA, tmB, kp, st);
-    default: return launch_fwd<256>(tmA, tmB, kp, st);
+    case 64: return launch_fwd<64>(tmA, tmB, kp, pair, st);
+    case 128: return launch_fwd<128>(tmA, tmB, kp, pair, st);
+    case 192: return launch_fwd<192>(tmA, tmB, kp, pair, st);
+    default: return launch_fwd<256>(tmA, tmB, kp, pair, st);
   }
 }
 
@@ -384,7 +453,7 @@ int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
 constexpr int WG_THREADS = 192;
 constexpr int WG_P = 64;                       // pixels per stage (K block)
 constexpr int WG_ATOM_BYTES = WG_P * 128;      // 8 KB: 64 pixels x 64 bf16
-constexpr int WG_STAGES = 3;
+constexpr int WG_MAX_STAGES = 4;               // 4 x 56 KB for C = 192 (the kernel is bound by bytes in flight x latency)
 constexpr int WG_MAX_UNITS = 32;
 
 struct WgUnit { int phase, atom_begin, natoms; };   // atoms index the phase's (tap, r-chunk) list
@@ -393,6 +462,7 @@ struct WgKParams {
   int N, GH, GW, R, HH, HW, Cc, hs;
   int tw, th, nb, tiles_w, tiles_h, tiles_n, kblocks;
   int nunits, nsplits, rchunks, cchunks, ntaps;
+  int stages;
   hpc_igemm_phase phase[HPC_MAX_PHASES];
   int dh[HPC_MAX_TAPS], dw[HPC_MAX_TAPS];
   WgUnit unit[WG_MAX_UNITS];
@@ -405,10 +475,11 @@ igemm_wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmLo, const __grid_c
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int stage_bytes = (4 + p.cchunks) * WG_ATOM_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + WG_STAGES * stage_bytes);
+  const int nstages = p.stages;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + nstages * stage_bytes);
   uint64_t* full_bar = bars;
-  uint64_t* empty_bar = bars + WG_STAGES;
-  uint64_t* done_bar = bars + 2 * WG_STAGES;
+  uint64_t* empty_bar = bars + WG_MAX_STAGES;
+  uint64_t* done_bar = bars + 2 * WG_MAX_STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done_bar + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -422,7 +493,7 @@ igemm_wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmLo, const __grid_c
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmLo);
     prefetch_tmap(&tmHi);
-    for (int s = 0; s < WG_STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < nstages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     mbar_init(done_bar, 1);
     fence_barrier_init();
   }
@@ -433,28 +504,32 @@ igemm_wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmLo, const __grid_c
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
-      int stage = 0; uint32_t phase = 0;
-      const uint32_t tx = (uint32_t)(U.natoms + p.cchunks) * WG_ATOM_BYTES;
-      for (int kb = kb0; kb < kb1; ++kb) {
-        int r = kb;
-        const int tj = r % p.tiles_w; r /= p.tiles_w;
-        const int ti = r % p.tiles_h; r /= p.tiles_h;
-        const int n0 = r * p.nb, i0 = ti * p.th, j0 = tj * p.tw;
-        mbar_wait(&empty_bar[stage], phase ^ 1);
-        mbar_arrive_expect_tx(&full_bar[stage], tx);
-        uint8_t* sa = smem + stage * stage_bytes;
-        uint8_t* sb = sa + 4 * WG_ATOM_BYTES;
-        for (int a = 0; a < U.natoms; ++a) {
-          const int atom = U.atom_begin + a;
-          const int t = P.tap_begin + atom / p.rchunks, rc = atom % p.rchunks;
-          tma_load_4d(sa + a * WG_ATOM_BYTES, &tmLo, &full_bar[stage], rc * 64, j0 + p.dw[t], i0 + p.dh[t], n0);
-        }
-        for (int c = 0; c < p.cchunks; ++c)
-          tma_load_4d(sb + c * WG_ATOM_BYTES, &tmHi, &full_bar[stage], c * 64, j0 * p.hs + P.ow_off,
-                      i0 * p.hs + P.oh_off, n0);
-        if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
-      }
+    // Producer: the whole warp runs the loop and lane l issues box l of the stage (up to 4 `lo` atoms + Cc/64 `hi`
+    // atoms), so the TMA instructions of a stage are issued in parallel instead of one after another by one thread.
+    int stage = 0; uint32_t phase = 0;
+    const uint32_t tx = (uint32_t)(U.natoms + p.cchunks) * WG_ATOM_BYTES;
+    const bool is_lo = lane < U.natoms, is_hi = lane >= 4 && lane < 4 + p.cchunks;
+    int t = 0, rc = 0;
+    if (is_lo) {
+      const int atom = U.atom_begin + lane;
+      t = P.tap_begin + atom / p.rchunks; rc = atom % p.rchunks;
+    }
+    const int dwt = p.dw[t], dht = p.dh[t];
+    for (int kb = kb0; kb < kb1; ++kb) {
+      int r = kb;
+      const int tj = r % p.tiles_w; r /= p.tiles_w;
+      const int ti = r % p.tiles_h; r /= p.tiles_h;
+      const int n0 = r * p.nb, i0 = ti * p.th, j0 = tj * p.tw;
+      mbar_wait(&empty_bar[stage], phase ^ 1);
+      if (lane == 0) mbar_arrive_expect_tx(&full_bar[stage], tx);
+      __syncwarp();
+      uint8_t* sa = smem + stage * stage_bytes;
+      if (is_lo)
+        tma_load_4d(sa + lane * WG_ATOM_BYTES, &tmLo, &full_bar[stage], rc * 64, j0 + dwt, i0 + dht, n0);
+      else if (is_hi)
+        tma_load_4d(sa + lane * WG_ATOM_BYTES, &tmHi, &full_bar[stage], (lane - 4) * 64, j0 * p.hs + P.ow_off,
+                    i0 * p.hs + P.oh_off, n0);
+      if (++stage == nstages) { stage = 0; phase ^= 1; }
     }
   } else if (warp == 1) {
     if (lane == 0) {
@@ -475,7 +550,7 @@ igemm_wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmLo, const __grid_c
           }
         }
         mma_commit(&empty_bar[stage]);
-        if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
+        if (++stage == nstages) { stage = 0; phase ^= 1; }
       }
       mma_commit(done_bar);
     }
@@ -634,11 +709,13 @@ int hpc_igemm_wgrad_umma(const hpc_igemm_wgrad_params* p, hpc_stream_t stream) {
     rc = make_tmap(&tmHi, p->hi, 4, dims, strides, box, estr);
     if (rc) return rc;
   }
-  const int smem_bytes = WG_STAGES * (4 + local.cchunks) * WG_ATOM_BYTES + 1024 + 256;
+  local.stages = local.cchunks <= 3 ? WG_MAX_STAGES : 3;       // 224 KB for C = 192, 192 KB for C = 256
+  { const char* e = getenv("HPC_WG_STAGES"); if (e && atoi(e) >= 2 && atoi(e) <= local.stages) local.stages = atoi(e); }
+  const int smem_bytes = local.stages * (4 + local.cchunks) * WG_ATOM_BYTES + 1024 + 256;
   static bool attr_set = false;
   if (!attr_set) {
     HPC_CUDA(cudaFuncSetAttribute(igemm_wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  WG_STAGES * 8 * WG_ATOM_BYTES + 1024 + 256));
+                                  WG_MAX_STAGES * 7 * WG_ATOM_BYTES + 1024 + 256));
     attr_set = true;
   }
   auto st = (cudaStream_t)stream;

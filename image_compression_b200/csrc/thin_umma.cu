@@ -419,17 +419,19 @@ deconv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   const int tiles_per_img = p.tiles_w * p.tiles_h;
 
   if (warp == 0) {
-    if (lane == 0) {
-      mbar_arrive_expect_tx(b_full, Cfg::B_BYTES);
-      for (int c = 0; c < KC; ++c) tma_load_2d(smem_b + c * KPAD * 128, &tmB, b_full, c * 64, 0);
+    if (lane < KC) {                    // lane c issues channel chunk c (TMA instructions of a stage in parallel)
+      constexpr uint32_t lanes = (1u << KC) - 1;
+      if (lane == 0) mbar_arrive_expect_tx(b_full, Cfg::B_BYTES);
+      __syncwarp(lanes);
+      tma_load_2d(smem_b + lane * KPAD * 128, &tmB, b_full, lane * 64, 0);
       int stage = 0; uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
         const int n = tile / tiles_per_img, r = tile % tiles_per_img;
         const int i0 = (r / p.tiles_w) * T2_IH - 1, j0 = (r % p.tiles_w) * T2_IW - 1;   // patch origin (halo)
         mbar_wait(&empty_bar[stage], phase ^ 1);
-        mbar_arrive_expect_tx(&full_bar[stage], Cfg::A_BYTES);
-        for (int c = 0; c < KC; ++c)
-          tma_load_4d(smem_a + stage * Cfg::A_BYTES + c * 16384, &tmA, &full_bar[stage], c * 64, j0, i0, n);
+        if (lane == 0) mbar_arrive_expect_tx(&full_bar[stage], Cfg::A_BYTES);
+        __syncwarp(lanes);
+        tma_load_4d(smem_a + stage * Cfg::A_BYTES + lane * 16384, &tmA, &full_bar[stage], lane * 64, j0, i0, n);
         if (++stage == T2_STAGES) { stage = 0; phase ^= 1; }
       }
     }
@@ -647,15 +649,17 @@ wgrad_c3_umma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (lane < CW / 64) {               // lane c issues channel chunk c
+      constexpr uint32_t lanes = (1u << (CW / 64)) - 1;
       int stage = 0; uint32_t phase = 0;
       for (int kb = kb0; kb < kb1; ++kb) {
         const int n = kb / tiles_per_img, r = kb % tiles_per_img;
         const int i0 = (r / p.tiles_w) * T3_TH, j0 = (r % p.tiles_w) * T3_TW;
         mbar_wait(&empty_bar[stage], phase ^ 1);
-        mbar_arrive_expect_tx(&full_bar[stage], (CW / 64) * ATOM_BYTES);
+        if (lane == 0) mbar_arrive_expect_tx(&full_bar[stage], (CW / 64) * ATOM_BYTES);
+        __syncwarp(lanes);
         uint8_t* sb = smem + stage * Cfg::STAGE_BYTES + 2 * ATOM_BYTES;
-        for (int c = 0; c < CW / 64; ++c) tma_load_4d(sb + c * ATOM_BYTES, &tmW, &full_bar[stage], c * 64, j0, i0, n);
+        tma_load_4d(sb + lane * ATOM_BYTES, &tmW, &full_bar[stage], lane * 64, j0, i0, n);
         if (++stage == T3_STAGES) { stage = 0; phase ^= 1; }
       }
     }

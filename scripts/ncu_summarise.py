@@ -39,6 +39,26 @@ def launch_list(path):
     return agg, total
 
 
+def traffic_list(path, skip_frac=0.0):
+    """Per-kernel DRAM bytes per launch (read + write, averaged over the launches of the capture) from
+    `ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --csv`."""
+    with open(path) as f:
+        lines = f.readlines()
+    start = [i for i, l in enumerate(lines) if l.startswith('"ID"')][0]
+    per = collections.OrderedDict()
+    for row in csv.DictReader(lines[start:]):
+        m = row["Metric Name"]
+        if not m.startswith("dram__bytes"):
+            continue
+        v = float(row["Metric Value"].replace(",", ""))
+        v *= {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[row["Metric Unit"]]
+        name = re.sub(r"[<(].*", "", row["Kernel Name"].replace("<unnamed>::", "")).replace("void ", "").split("::")[-1]
+        d = per.setdefault(name, {})
+        d[row["ID"]] = d.get(row["ID"], 0.0) + v
+    return {k: {"launches": len(d), "avg_bytes_per_launch": sum(d.values()) / len(d), "max": max(d.values())}
+            for k, d in per.items()}
+
+
 def full_capture(rep):
     out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(out.splitlines()))
@@ -63,13 +83,25 @@ def main(src, dst):
         for k, (n, v) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
             md.append(f"| `{k[:90]}` | {n} | {v:.0f} | {100 * v / total:.1f}% |")
         md.append(f"| **total** | | {total:.0f} | |\n")
+    tl = os.path.join(src, "traffic.csv")
+    if os.path.exists(tl):
+        t = traffic_list(tl)
+        md.append("## DRAM traffic per launch (`ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum`, same command)\n")
+        md.append("| kernel | launches | avg MB / launch | max MB |\n|---|---:|---:|---:|")
+        for k, d in sorted(t.items(), key=lambda kv: -kv[1]["avg_bytes_per_launch"] * kv[1]["launches"]):
+            md.append(f"| `{k[:70]}` | {d['launches']} | {d['avg_bytes_per_launch'] / 1e6:.1f} | {d['max'] / 1e6:.1f} |")
+        md.append("")
+        flat = {k: d["avg_bytes_per_launch"] for k, d in t.items()}
+        for path in (dst + "_traffic_avg.json", os.path.join(os.path.dirname(dst) or ".", "traffic.json")):
+            with open(path, "w") as f:
+                json.dump(flat, f, indent=1)
     traffic = {}
     for f in sorted(os.listdir(src)):
         if f.endswith(".ncu-rep"):
             md.append(f"## `{f}` (`ncu --set full --clock-control none --import-source on`)\n")
             for i, d in enumerate(full_capture(os.path.join(src, f))):
                 md.append(f"launch {i}: " + "; ".join(f"{k} = {v}" for k, v in d.items()) + "\n")
-                name = re.sub(r"[<(].*", "", d.get("Kernel Name", "")).replace("void ", "")
+                name = re.sub(r"[<(].*", "", d.get("Kernel Name", "").replace("<unnamed>::", "")).replace("void ", "")
                 try:
                     rd = [float(v) for k, v in d.items() if k.startswith("dram__bytes_read.sum")][0]
                     wr = [float(v) for k, v in d.items() if k.startswith("dram__bytes_write.sum")][0]
