@@ -4,9 +4,11 @@
 // rows (C/64 TMA boxes of [128 x 64] in the canonical K-major SWIZZLE_128B layout).  gamma (C x C bf16,
 // 72 KB for C = 192) stays resident in shared memory for the whole persistent CTA.
 //
-//   forward : x tile --TMA--> smem;  8 warps square it into the A operand;  UMMA n = x^2 . gamma^T;  epilogue
-//             r = rsqrt(beta + n), y = x r  written IN PLACE over x and x^2;  TMA stores of y and r.
-//             HBM traffic: read x, write y, write r (3 passes; no x^2 tensor exists in global memory).
+//   forward : x tile --TMA--> smem;  the workers square it straight into TMEM (tcgen05.st), where it is the A operand
+//             of the UMMA n = x^2 . gamma^T (A-from-TMEM form) -- x^2 exists neither in global nor in shared memory,
+//             and the squares of tile i+1 overlap the MMA of tile i (two A buffers);  epilogue r = rsqrt(beta + n),
+//             y = x r written in place over x, r into a staging tile;  TMA stores of y and r.
+//             HBM traffic: read x, write y, write r (3 passes).
 //   backward: g, x, r tiles --TMA--> smem;  t = g x r^3 (in place over r), u = g r (in place over g);
 //             UMMA a = t . gamma;  dx = u - x a (over u), x^2 (over x);  TMA stores of dx, t, x^2;  column sums
 //             of t (d beta) accumulated per CTA.  6 passes instead of 10 for the unfused sequence.
@@ -76,6 +78,9 @@ struct GCfg {
   static constexpr int TILE = KC * G_CHUNK;
   static constexpr int GAMMA = C * C * 2;
   static constexpr int TMEM_COLS = C <= 64 ? 64 : (C <= 128 ? 128 : 256);
+  // forward: accumulator (C columns) + two x^2 A-operand buffers of C/2 columns each
+  static constexpr int FWD_A_COL = C;
+  static constexpr int FWD_TMEM_COLS = C <= 64 ? 128 : (C <= 128 ? 256 : 512);
   static constexpr int SMEM = 1024 + GAMMA + 3 * TILE + 1024 /*beta*/ + 256;
 };
 
@@ -89,20 +94,21 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
                     const __grid_constant__ GdnParams p) {
   using Cfg = GCfg<C>;
   constexpr int KC = Cfg::KC;
+  constexpr int A_COL = Cfg::FWD_A_COL, A_COLS = C / 2;     // x^2 as the TMEM-resident A operand, double buffered
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* gam = smem;                           // KC chunks of [C rows x 128 B]
   uint8_t* xs = gam + Cfg::GAMMA;                // [2][TILE]   x, later y
-  uint8_t* a2 = xs + 2 * Cfg::TILE;              // [TILE]      x^2, later r
-  float* beta_s = reinterpret_cast<float*>(a2 + Cfg::TILE);
+  uint8_t* rs = xs + 2 * Cfg::TILE;              // [TILE]      r staging for the TMA store
+  float* beta_s = reinterpret_cast<float*>(rs + Cfg::TILE);
   uint64_t* bars = reinterpret_cast<uint64_t*>(beta_s + 256);
   uint64_t* g_full = bars;
   uint64_t* xs_full = bars + 1;     // [2]
   uint64_t* xs_empty = bars + 3;    // [2]  store warp, after the y store has finished READING smem
-  uint64_t* a2_full = bars + 5;     // 256 worker arrivals
-  uint64_t* a2_empty = bars + 6;    // store warp
+  uint64_t* a_full = bars + 5;      // workers: x^2 of the tile is in TMEM (and the accumulator has been drained)
+  uint64_t* rs_empty = bars + 6;    // store warp, after the r store has finished reading smem
   uint64_t* tfull = bars + 7;       // tcgen05.commit
-  uint64_t* out_full = bars + 8;    // 256 worker arrivals
+  uint64_t* out_full = bars + 8;    // workers: y and r written
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -111,10 +117,10 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
     prefetch_tmap(&tmX); prefetch_tmap(&tmY); prefetch_tmap(&tmR); prefetch_tmap(&tmG);
     mbar_init(g_full, 1);
     for (int s = 0; s < 2; ++s) { mbar_init(&xs_full[s], 1); mbar_init(&xs_empty[s], 1); }
-    mbar_init(a2_full, G_WORKERS); mbar_init(a2_empty, 1); mbar_init(tfull, 1); mbar_init(out_full, G_WORKERS);
+    mbar_init(a_full, G_WORKERS); mbar_init(rs_empty, 1); mbar_init(tfull, 1); mbar_init(out_full, G_WORKERS);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+  if (warp == 1) tmem_alloc(tmem_slot, Cfg::FWD_TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -140,35 +146,38 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc_bf16(128, C, 0, 0);
       mbar_wait(g_full, 0);
+      const uint32_t b_addr = smem_u32(gam);
       int it = 0;
       for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
-        mbar_wait(a2_full, it & 1);
+        mbar_wait(a_full, it & 1);
         tc_fence_after();
-        const uint32_t a_addr = smem_u32(a2), b_addr = smem_u32(gam);
+        const uint32_t a_tmem = tmem_base + A_COL + (it & 1) * A_COLS;
 #pragma unroll
         for (int k = 0; k < C / 16; ++k)
-          mma_bf16_ss(tmem_base, make_smem_desc_sw128(a_addr + (k >> 2) * G_CHUNK + (k & 3) * 32, 16, 1024),
+          mma_bf16_ts(tmem_base, a_tmem + k * 8,
                       make_smem_desc_sw128(b_addr + (k >> 2) * (C * 128) + (k & 3) * 32, 16, 1024), idesc, k != 0);
         mma_commit(tfull);
       }
     }
   } else if (warp == 2) {
-    // lanes 0..KC-1 store the y chunks, lanes KC..2KC-1 the r chunks (bulk groups are per thread)
+    // lanes 0..KC-1 store the r chunks, lanes KC..2KC-1 the y chunks (bulk groups are per thread); each group frees
+    // its own buffer as soon as ITS stores have been read out of shared memory
     if (lane < 2 * KC) {
-      constexpr uint32_t lanes = (1u << (2 * KC)) - 1;
       const int c = lane % KC;
       int it = 0;
       for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
         const int b = it & 1;
         mbar_wait(out_full, it & 1);
-        if (lane < KC) tma_store_2d(&tmY, xs + b * Cfg::TILE + c * G_CHUNK, c * 64, tile * 128);
-        else tma_store_2d(&tmR, a2 + c * G_CHUNK, c * 64, tile * 128);
+        if (lane < KC) tma_store_2d(&tmR, rs + c * G_CHUNK, c * 64, tile * 128);
+        else tma_store_2d(&tmY, xs + b * Cfg::TILE + c * G_CHUNK, c * 64, tile * 128);
         bulk_commit();
         bulk_wait_read0();
-        __syncwarp(lanes);
-        if (lane == 0) {
-          mbar_arrive(&xs_empty[b]);
-          mbar_arrive(a2_empty);
+        if (lane < KC) {
+          __syncwarp((1u << KC) - 1);
+          if (lane == 0) mbar_arrive(rs_empty);
+        } else {
+          __syncwarp(((1u << KC) - 1) << KC);
+          if (lane == KC) mbar_arrive(&xs_empty[b]);
         }
       }
       bulk_wait0();
@@ -177,31 +186,58 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
     const int w = warp - 3;                       // 0..15
     const int q = warp & 3, half = w >> 2;        // `half` = which quarter of the channels (0..3)
     const int row = q * 32 + lane;
-    constexpr int UH = C / 32;                    // 16-byte units per quarter row
-    int it = 0;
-    for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
+    constexpr int UH = C / 32;                    // 16-byte units (8 channels) per quarter row
+    static_assert(UH % 2 == 0, "two units per tcgen05.st");
+    const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+
+    // x^2 of tile `it2` -> TMEM A buffer it2 & 1 (bf16 pairs, K order): 4 columns per 8-channel unit
+    auto square_to_tmem = [&](int it2) {
+      const uint8_t* xt = xs + (it2 & 1) * Cfg::TILE;
+      mbar_wait(&xs_full[it2 & 1], (it2 >> 1) & 1);
+      const uint32_t abase = tmem_base + lane_off + A_COL + (it2 & 1) * A_COLS + half * (UH * 4);
+#pragma unroll 1
+      for (int uu = 0; uu < UH; uu += 2) {
+        const uint4 raw0 = *reinterpret_cast<const uint4*>(xt + unit_off(row, half * UH + uu));
+        const uint4 raw1 = *reinterpret_cast<const uint4*>(xt + unit_off(row, half * UH + uu + 1));
+        uint32_t v[8];
+        float f[8];
+        unpack8(raw0, f);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] *= f[e];
+        uint4 pk = pack8(f);
+        v[0] = pk.x; v[1] = pk.y; v[2] = pk.z; v[3] = pk.w;
+        unpack8(raw1, f);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] *= f[e];
+        pk = pack8(f);
+        v[4] = pk.x; v[5] = pk.y; v[6] = pk.z; v[7] = pk.w;
+        tmem_st8(abase + uu * 4, v);
+      }
+      tmem_st_wait();
+    };
+
+    // software pipeline with ONE copy of each phase: iteration `it` publishes x^2(it) (computed at the end of the
+    // previous iteration, after x(it) had a whole tile time to land), then runs the epilogue of tile it; the squares
+    // of tile it+1 follow it, so the MMA of tile it+1 never waits for a staging buffer to drain
+    const int ntile = ((int)blockIdx.x < p.tiles) ? (p.tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+    for (int it = -1; it < ntile; ++it) {
+      if (it >= 0) {
+        // x^2(it) is in TMEM and (program order) this thread has finished reading the accumulator of tile it-1
+        tc_fence_before();
+        mbar_arrive(a_full);
+      }
+      if (it < 0) {
+        if (ntile > 0) square_to_tmem(0);
+        continue;
+      }
+      const int tile = blockIdx.x + it * gridDim.x;
+      (void)tile;
       const int b = it & 1;
       uint8_t* xt = xs + b * Cfg::TILE;
-      mbar_wait(&xs_full[b], (it >> 1) & 1);
-      mbar_wait(a2_empty, (it & 1) ^ 1);
-      {   // all loads first (xt and a2 may alias for the compiler: a load/store chain would serialise on LDS latency)
-        uint4 raw[UH];
-#pragma unroll
-        for (int uu = 0; uu < UH; ++uu) raw[uu] = *reinterpret_cast<const uint4*>(xt + unit_off(row, half * UH + uu));
-#pragma unroll
-        for (int uu = 0; uu < UH; ++uu) {
-          float f[8];
-          unpack8(raw[uu], f);
-#pragma unroll
-          for (int e = 0; e < 8; ++e) f[e] *= f[e];
-          *reinterpret_cast<uint4*>(a2 + unit_off(row, half * UH + uu)) = pack8(f);
-        }
-      }
-      fence_proxy_async();
-      mbar_arrive(a2_full);
       mbar_wait(tfull, it & 1);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + half * (C / 4);
+      mbar_wait(rs_empty, (it & 1) ^ 1);          // r of the previous tile has left the staging buffer
+      const uint32_t taddr = tmem_base + lane_off + half * (C / 4);
       constexpr int GB = (C / 64) % 3 == 0 ? 3 : ((C / 64) % 2 == 0 ? 2 : 1);      // ld16 groups per batch
 #pragma unroll 1
       for (int gb = 0; gb < C / 64; gb += GB) {
@@ -230,18 +266,18 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
               y[e] = p.inverse ? x[e] * (n * r[e]) : x[e] * r[e];
             }
             *reinterpret_cast<uint4*>(xt + o) = pack8(y);
-            *reinterpret_cast<uint4*>(a2 + o) = pack8(r);
+            *reinterpret_cast<uint4*>(rs + o) = pack8(r);
           }
         }
       }
-      tc_fence_before();
       fence_proxy_async();
       mbar_arrive(out_full);
+      if (it + 1 < ntile) square_to_tmem(it + 1);   // other A buffer: its last reader (MMA it-1) retired before tfull(it-1)
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  if (warp == 1) tmem_dealloc(tmem_base, Cfg::FWD_TMEM_COLS);
 }
 
 // ---------------------------------------------------------------------------------------

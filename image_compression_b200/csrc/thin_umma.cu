@@ -118,12 +118,14 @@ int hpc_pack_c3_weight(const float* w, int64_t w_sr, int64_t w_sc, int Cw, void*
 
 // ---------------------------------------------------------------------------------------
 // T1: Conv2d(3 -> Cw, 5, s2, p2) : x NCHW fp32 -> out NHWC bf16 (+ squares)
-//   warp 0: weights via TMA, MMA issue, TMEM owner | warps 1-4: im2col builders | warps 5-8: epilogue
+//   warp 0: weights via TMA, MMA issue, TMEM owner | warps 1-4: im2col builders | warps 5-12: epilogue (the kernel is
+//   bound by the epilogue: K = 80 makes the MMA negligible, so two warps share each TMEM lane quarter)
 // ---------------------------------------------------------------------------------------
 namespace {
 constexpr int T1_TH = 8, T1_TW = 16;                      // 128 output pixels per tile
 constexpr int T1_PH = 2 * T1_TH + 3, T1_PWV = 2 * T1_TW + 3, T1_PW = T1_PWV + 1;   // 19 x 35 (+1 pad)
-constexpr int T1_THREADS = 288;
+constexpr int T1_THREADS = 416;
+constexpr int T1_EPI = 256;                               // epilogue threads
 constexpr int T1_A_BYTES = 2 * 16384;                     // two 64-wide K chunks of [128 x 128 B]
 constexpr int T1_ST_ROW = 144;                            // staging row pitch: 64 bf16 + 16 B pad
 constexpr int T1_ST_BYTES = 128 * T1_ST_ROW;              // one tensor, one 64-channel chunk
@@ -169,7 +171,7 @@ conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_consta
   for (int i = threadIdx.x; i < 256; i += T1_THREADS) bias_s[i] = (p.bias && i < CW) ? p.bias[i] : 0.f;
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmB);
-    for (int s = 0; s < 2; ++s) { mbar_init(&full_a[s], 128); mbar_init(&empty_a[s], 1); mbar_init(&tfull[s], 1); mbar_init(&tempty[s], 4); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&full_a[s], 128); mbar_init(&empty_a[s], 1); mbar_init(&tfull[s], 1); mbar_init(&tempty[s], T1_EPI / 32); }
     mbar_init(b_full, 1);
     fence_barrier_init();
   }
@@ -240,9 +242,9 @@ conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_consta
       mbar_arrive(&full_a[buf]);
     }
   } else {
-    // ============================ epilogue (128 threads) ===================================
+    // ============================ epilogue (256 threads) ===================================
     const int t = threadIdx.x - 160;
-    const int q = warp & 3;
+    const int q = warp & 3, half = (warp - 5) >> 2;         // TMEM lane quarter, 32-column half of each 64-channel chunk
     const int row = q * 32 + lane;                          // TMEM lane == tile pixel
     int it = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
@@ -259,26 +261,27 @@ conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_consta
         // reuse buffer 0 back to back across tiles), so one barrier per chunk orders writers after readers
         uint8_t* st_lp = stage + ((it * (CW / 64) + cc) & 1) * 2 * T1_ST_BYTES;
         uint8_t* st_sq = st_lp + T1_ST_BYTES;
-        float v4[4][16];
+        float v2[2][16];
 #pragma unroll
-        for (int c16 = 0; c16 < 4; ++c16) tmem_ld16(taddr + cc * 64 + c16 * 16, v4[c16]);
+        for (int c16 = 0; c16 < 2; ++c16) tmem_ld16(taddr + cc * 64 + half * 32 + c16 * 16, v2[c16]);
         tmem_ld_wait();
 #pragma unroll
-        for (int c16 = 0; c16 < 4; ++c16) {
-          const float* v = v4[c16];
+        for (int c16 = 0; c16 < 2; ++c16) {
+          const float* v = v2[c16];
+          const int cb = half * 32 + c16 * 16;              // first channel of this group within the chunk
           uint32_t lo[8], sq[8];
 #pragma unroll
           for (int e = 0; e < 8; ++e) {
-            const float a = v[2 * e] + bias_s[cc * 64 + c16 * 16 + 2 * e];
-            const float b = v[2 * e + 1] + bias_s[cc * 64 + c16 * 16 + 2 * e + 1];
+            const float a = v[2 * e] + bias_s[cc * 64 + cb + 2 * e];
+            const float b = v[2 * e + 1] + bias_s[cc * 64 + cb + 2 * e + 1];
             lo[e] = pack2_bf16(a, b);
             sq[e] = pack2_bf16(a * a, b * b);
           }
-          uint4* d0 = reinterpret_cast<uint4*>(st_lp + row * T1_ST_ROW + c16 * 32);
+          uint4* d0 = reinterpret_cast<uint4*>(st_lp + row * T1_ST_ROW + cb * 2);
           d0[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
           d0[1] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
           if (p.out_sq) {
-            uint4* d1 = reinterpret_cast<uint4*>(st_sq + row * T1_ST_ROW + c16 * 32);
+            uint4* d1 = reinterpret_cast<uint4*>(st_sq + row * T1_ST_ROW + cb * 2);
             d1[0] = make_uint4(sq[0], sq[1], sq[2], sq[3]);
             d1[1] = make_uint4(sq[4], sq[5], sq[6], sq[7]);
           }
@@ -288,11 +291,11 @@ conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_consta
           __syncwarp();
           if (lane == 0) mbar_arrive(&tempty[buf]);
         }
-        named_bar(2, 128);
+        named_bar(2, T1_EPI);
         // coalesced copy-out: 8 lanes cover one pixel's 128-byte channel chunk
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int idx = t + 128 * i, rr = idx >> 3, u = idx & 7;
+        for (int i = 0; i < 1024 / T1_EPI; ++i) {
+          const int idx = t + T1_EPI * i, rr = idx >> 3, u = idx & 7;
           const int oh = i0 + (rr >> 4), ow = j0 + (rr & 15);
           if (oh < p.OH && ow < p.OW) {
             const int64_t o = (((int64_t)n * p.OH + oh) * p.OW + ow) * CW + cc * 64 + u * 8;
