@@ -13,6 +13,8 @@ import math
 import weakref
 from ctypes import byref, c_double, c_float, c_int
 
+import functools
+
 import torch
 
 from . import _lib
@@ -133,12 +135,14 @@ def contiguous_f32(x):
 # ----------------------------------------------------------------------------------------
 # tap tables
 # ----------------------------------------------------------------------------------------
+@functools.lru_cache(maxsize=None)
 def conv_type_taps(k, s, p):
     """Conv2d(k,s,p) as one dense phase: input pixel = out*s + (kh-p)."""
     taps = [(kh - p, kw - p, kh * k + kw) for kh in range(k) for kw in range(k)]
     return taps, [(len(taps), 0, 0, 0)]
 
 
+@functools.lru_cache(maxsize=None)
 def deconv_type_taps(k, s, p):
     """ConvTranspose2d(k,s,p): one phase per output-pixel parity (a,b); out = i*s+a reads in[i+dh],
     dh = (a+p-kh)/s for the kh with (a+p-kh) % s == 0."""
@@ -157,12 +161,24 @@ def deconv_type_taps(k, s, p):
     return taps, phases
 
 
+_tap_structs = {}
+
+
 def _fill_taps(P, taps, phases):
+    """Tap / phase tables of a parameter struct.  The ctypes arrays are built once per distinct table (a few per
+    model) and block-copied afterwards: filling them element by element costs more host time than the launch."""
+    key = (id(taps), id(phases), len(taps), len(phases))
+    hit = _tap_structs.get(key)
+    if hit is None or hit[0] is not taps or hit[1] is not phases:
+        ph = (_lib.IgemmPhase * _lib.MAX_PHASES)()
+        dh, dw = (_lib.c_int * _lib.MAX_TAPS)(), (_lib.c_int * _lib.MAX_TAPS)()
+        for i, (nt, begin, a, b) in enumerate(phases):
+            ph[i].ntaps, ph[i].tap_begin, ph[i].oh_off, ph[i].ow_off = nt, begin, a, b
+        for i, (d0, d1, _) in enumerate(taps):
+            dh[i], dw[i] = d0, d1
+        hit = _tap_structs[key] = (taps, phases, ph, dh, dw)
     P.nphases = len(phases)
-    for i, (nt, begin, a, b) in enumerate(phases):
-        P.phase[i].ntaps, P.phase[i].tap_begin, P.phase[i].oh_off, P.phase[i].ow_off = nt, begin, a, b
-    for i, (dh, dw, _) in enumerate(taps):
-        P.dh[i], P.dw[i] = dh, dw
+    P.phase, P.dh, P.dw = hit[2], hit[3], hit[4]
 
 
 _pack_cache = {}
