@@ -96,9 +96,10 @@ def ga_backward(S, gy_lp):
             x, xsq, nrm, gamma = a
             gp, bp = S.gdns[gi]
             b_prod = S.convs[ci][1]       # bias of the layer that feeds this GDN: its gradient is colsum(dx)
-            dx, dgamma, dbeta, gsum = hp.gdn_backward(g, x, xsq, nrm, gamma, want_dxsum=True,
-                                                      dxsum_out=hp.grad_buffer(b_prod) if b_prod is not None and hp.gdn_bwd_has_dxsum(x) else None)
-            gdn_grads[gi] = _gdn_param_grads(gp, bp, dgamma, dbeta)
+            dx, ggamma, gbeta, gsum = hp.gdn_backward(
+                g, x, xsq, nrm, gamma, want_dxsum=True, reparam=(gp, bp, 1e-6),
+                dxsum_out=hp.grad_buffer(b_prod) if b_prod is not None and hp.gdn_bwd_has_dxsum(x) else None)
+            gdn_grads[gi] = (ggamma, gbeta)
             g = dx
             gi -= 1
         else:  # head conv: weight + bias grads only (the image needs no gradient)
@@ -159,9 +160,10 @@ def gs_backward(S, g_raw_nchw, need_input_grad=True):
             x, xsq, nrm, gamma = a
             gp, bp = S.gdns[gi]
             b_prod = S.convs[ci][1]       # bias of the layer that feeds this GDN: its gradient is colsum(dx)
-            dx, dgamma, dbeta, gsum = hp.gdn_backward(g, x, xsq, nrm, gamma, want_dxsum=True,
-                                                      dxsum_out=hp.grad_buffer(b_prod) if b_prod is not None and hp.gdn_bwd_has_dxsum(x) else None)
-            gdn_grads[gi] = _gdn_param_grads(gp, bp, dgamma, dbeta)
+            dx, ggamma, gbeta, gsum = hp.gdn_backward(
+                g, x, xsq, nrm, gamma, want_dxsum=True, reparam=(gp, bp, 1e-6),
+                dxsum_out=hp.grad_buffer(b_prod) if b_prod is not None and hp.gdn_bwd_has_dxsum(x) else None)
+            gdn_grads[gi] = (ggamma, gbeta)
             g = dx
             gi -= 1
         else:

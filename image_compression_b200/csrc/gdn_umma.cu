@@ -487,7 +487,6 @@ struct GdnFusedParams {
   int64_t P;
   int tiles;
   int inverse;
-  int dbg;
 };
 
 template <int C>
@@ -566,7 +565,6 @@ gdn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_cons
         mma_commit(tfull);
         mbar_wait(out_full, it & 1);
         tc_fence_after();
-        if (!(p.dbg & 2))
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks) {            // K = 128 tile rows, 16 per MMA (16 rows x 128 B = 2 KB)
           const uint32_t acc = (it | ks) != 0;
@@ -639,7 +637,7 @@ gdn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_cons
       mbar_arrive(a_full);
       // d(beta): column sums of the bf16 t tile, while the MMA runs (rows past P are zero: TMA zero fill)
       named_bar(4, G_WORKERS);
-      if (wt < C && !(p.dbg & 4)) {
+      if (wt < C) {
         const int U = wt >> 3, e = wt & 7;
         float s = 0.f;
 #pragma unroll 8
@@ -684,7 +682,7 @@ gdn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_cons
       // d(bias) of the producer layer: column sums of the bf16 dx tile, while it is being stored.  Rows past P
       // are skipped: the inverse form divides the zero-filled g by the zero-filled r there.
       named_bar(4, G_WORKERS);
-      if (wt < C && !(p.dbg & 1)) {
+      if (wt < C) {
         const int U = wt >> 3, e = wt & 7;
         const int64_t left = p.P - (int64_t)tile * 128;
         const int nrows = left < 128 ? (int)left : 128;
@@ -734,15 +732,40 @@ gdn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_cons
   if (warp == 1) tmem_dealloc(tmem_base, TCOLS);
 }
 
-// fixed-order reduction of the per-CTA d(gamma) partials: out[i] = scale * sum_s part[s][i]
+// One launch finishes the backward of a GDN layer from the per-CTA partials, in a fixed summation order:
+//   blocks [0, ng)        d(gamma)[i]   = R(gamma_param[i], sgn * sum_s dgamma_part[s][i])     (128 elements per block)
+//   blocks [ng, ng+nc)    d(beta)[c]    = R(beta_param[c],  sgn * sum_s colsum_part[s][c])
+//   blocks [ng+nc, ..)    d(bias)[c]    = sum_s dxsum_part[s][c]                                (producer layer)
+// R(p, g) is the backward of the non-negative reparametrisation (gdn.py:42-62: v = max(p, bound), value v^2 - pedestal,
+// LowerBound pass-through rule bound.py:36-46) when the raw parameter is given, the identity otherwise.
+struct GdnFinish {
+  const float* dgamma_part; const float* colsum_part; const float* dxsum_part;
+  const float* gamma_param; const float* beta_param;
+  float* dgamma; float* dbeta; float* dbias;
+  int nparts, C, ng, nc;
+  float sgn, gamma_bound, beta_bound;
+};
+
+__device__ __forceinline__ float reparam_bwd(const float* param, int i, float g, float bound) {
+  if (!param) return g;
+  const float pv = param[i], v = fmaxf(pv, bound);
+  const float gp = 2.f * v * g;
+  return ((pv >= bound) || (gp < 0.f)) ? gp : 0.f;
+}
+
 __global__ void __launch_bounds__(256)
-gdn_dgamma_reduce_kernel(const float* __restrict__ part, int nparts, int n, float scale, float* __restrict__ out) {
+gdn_bwd_finish_kernel(const __grid_constant__ GdnFinish f) {
   __shared__ float4 sm[8][32];
   const int qd = threadIdx.x & 31, g = threadIdx.x >> 5;
-  const int i = (blockIdx.x * 32 + qd) * 4;
+  int blk = blockIdx.x;
+  const float* part; const float* param; float* out; int n; float scale, bound;
+  if (blk < f.ng) { part = f.dgamma_part; param = f.gamma_param; out = f.dgamma; n = f.C * f.C; scale = f.sgn; bound = f.gamma_bound; }
+  else if (blk < f.ng + f.nc) { blk -= f.ng; part = f.colsum_part; param = f.beta_param; out = f.dbeta; n = f.C; scale = f.sgn; bound = f.beta_bound; }
+  else { blk -= f.ng + f.nc; part = f.dxsum_part; param = nullptr; out = f.dbias; n = f.C; scale = 1.f; bound = 0.f; }
+  const int i = (blk * 32 + qd) * 4;
   float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
   if (i < n)
-    for (int s2 = g; s2 < nparts; s2 += 8) {
+    for (int s2 = g; s2 < f.nparts; s2 += 8) {
       const float4 v = __ldcs(reinterpret_cast<const float4*>(part + (int64_t)s2 * n + i));
       a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
     }
@@ -754,7 +777,12 @@ gdn_dgamma_reduce_kernel(const float* __restrict__ part, int nparts, int n, floa
     const float4 v = sm[k][qd];
     a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
   }
-  *reinterpret_cast<float4*>(out + i) = make_float4(a.x * scale, a.y * scale, a.z * scale, a.w * scale);
+  float4 r;
+  r.x = reparam_bwd(param, i, a.x * scale, bound);
+  r.y = reparam_bwd(param, i + 1, a.y * scale, bound);
+  r.z = reparam_bwd(param, i + 2, a.z * scale, bound);
+  r.w = reparam_bwd(param, i + 3, a.w * scale, bound);
+  *reinterpret_cast<float4*>(out + i) = r;
 }
 
 int make_rows_tmap(CUtensorMap* m, const void* base, int64_t P, int C, int box_rows) {
@@ -844,23 +872,26 @@ int hpc_gdn_bwd_umma(const void* g_bf16, const void* x_bf16, const void* rnorm_b
 
 size_t hpc_gdn_bwd_fused_umma_workspace_bytes(int64_t P, int C) {
   if (C != 128 && C != 192) return 0;
-  return (size_t)hpc_gdn_bwd_umma_parts(P) * C * C * sizeof(float);
+  return (size_t)hpc_gdn_bwd_umma_parts(P) * (C * C + 2 * C) * sizeof(float);
 }
 
 int hpc_gdn_bwd_fused_umma(const void* g_bf16, const void* x_bf16, const void* rnorm_bf16, const void* gammaT_bf16,
-                           int64_t P, int C, int inverse, void* dx_bf16, float* dgamma, float dgamma_scale,
-                           float* colsum_part, float* dxsum_part, void* workspace, size_t workspace_bytes,
-                           hpc_stream_t stream) {
+                           int64_t P, int C, int inverse, void* dx_bf16, const float* gamma_param, float gamma_bound,
+                           const float* beta_param, float beta_bound, float* dgamma, float* dbeta, float* dbias,
+                           void* workspace, size_t workspace_bytes, hpc_stream_t stream) {
   int rc = gdn_check("hpc_gdn_bwd_fused_umma", P, C,
-                     {g_bf16, x_bf16, rnorm_bf16, gammaT_bf16, dx_bf16, dgamma, colsum_part, dxsum_part, workspace});
+                     {g_bf16, x_bf16, rnorm_bf16, gammaT_bf16, dx_bf16, dgamma, dbeta, workspace});
   if (rc) return rc;
   HPC_REQUIRE(C == 128 || C == 192, HPC_ERR_UNSUPPORTED, "hpc_gdn_bwd_fused_umma: C=%d not in {128,192}", C);
   HPC_REQUIRE(workspace_bytes >= hpc_gdn_bwd_fused_umma_workspace_bytes(P, C), HPC_ERR_BAD_SHAPE,
               "hpc_gdn_bwd_fused_umma: workspace too small (%zu)", workspace_bytes);
+  HPC_REQUIRE(!dbias || hpc_aligned16(dbias), HPC_ERR_BAD_ALIGNMENT, "hpc_gdn_bwd_fused_umma: dbias must be 16B aligned");
+  const int grid = gdn_grid((int)((P + 127) / 128));
   GdnFusedParams kp;
-  kp.colsum_part = colsum_part; kp.dxsum_part = dxsum_part; kp.dgamma_part = (float*)workspace;
+  kp.dgamma_part = (float*)workspace;
+  kp.colsum_part = kp.dgamma_part + (size_t)grid * C * C;
+  kp.dxsum_part = kp.colsum_part + (size_t)grid * C;
   kp.tiles = (int)((P + 127) / 128); kp.inverse = inverse; kp.P = P;
-  { const char* e = getenv("HPC_GDN_DBG"); kp.dbg = e ? atoi(e) : 0; }
   CUtensorMap tmGr, tmX, tmR, tmDx, tmG;
   if ((rc = make_rows_tmap(&tmGr, g_bf16, P, C, 128))) return rc;
   if ((rc = make_rows_tmap(&tmX, x_bf16, P, C, 128))) return rc;
@@ -869,7 +900,6 @@ int hpc_gdn_bwd_fused_umma(const void* g_bf16, const void* x_bf16, const void* r
   if ((rc = make_rows_tmap(&tmG, gammaT_bf16, C, C, C))) return rc;
   HpcProfScope prof(HPC_PROF_GDN, (double)P * C * 2 * 4, stream);
   auto st = (cudaStream_t)stream;
-  const int grid = gdn_grid(kp.tiles);
   if (C == 128) {
     static bool attr_set = false;
     if (!attr_set) {
@@ -886,9 +916,13 @@ int hpc_gdn_bwd_fused_umma(const void* g_bf16, const void* x_bf16, const void* r
     gdn_bwd_fused_kernel<192><<<grid, G_THREADS, GCfg<192>::SMEM, st>>>(tmGr, tmX, tmR, tmDx, tmG, kp);
   }
   HPC_LAUNCH_CHECK();
-  const int n = C * C;
-  gdn_dgamma_reduce_kernel<<<(n + 127) / 128, 256, 0, st>>>(kp.dgamma_part, grid, n, dgamma_scale, dgamma);
+  GdnFinish f;
+  f.dgamma_part = kp.dgamma_part; f.colsum_part = kp.colsum_part; f.dxsum_part = kp.dxsum_part;
+  f.gamma_param = gamma_param; f.beta_param = beta_param;
+  f.dgamma = dgamma; f.dbeta = dbeta; f.dbias = dbias;
+  f.nparts = grid; f.C = C; f.ng = (C * C + 127) / 128; f.nc = (C + 127) / 128;
+  f.sgn = inverse ? 0.5f : -0.5f; f.gamma_bound = gamma_bound; f.beta_bound = beta_bound;
+  gdn_bwd_finish_kernel<<<f.ng + f.nc + (dbias ? f.nc : 0), 256, 0, st>>>(f);
   HPC_LAUNCH_CHECK();
   return HPC_OK;
 }
-

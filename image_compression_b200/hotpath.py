@@ -443,36 +443,54 @@ def gdn_bwd_has_dxsum(x):
     return gdn_fused_ok(x.dtype, x.shape[-1]) and x.shape[-1] in (128, 192)
 
 
-def gdn_backward(g, x, xsq, nrm, gamma_eff, inverse=False, need_dx=True, want_dxsum=False, dxsum_out=None):
+def gdn_backward(g, x, xsq, nrm, gamma_eff, inverse=False, need_dx=True, want_dxsum=False, dxsum_out=None,
+                 reparam=None):
     """SURVEY A.4.  Returns (dx lp, dgamma_eff (C,C,1,1) fp32, dbeta_eff (C,) fp32) and, with want_dxsum, a
     fourth value: the column sums of dx (the bias gradient of the layer that feeds this GDN) when the fused
-    kernel produced them, else None."""
-    out = _gdn_backward(g, x, xsq, nrm, gamma_eff, inverse, need_dx, dxsum_out if want_dxsum else None)
+    kernel produced them, else None.  reparam = (gamma_param, beta_param, beta_min): return the gradients of the
+    RAW parameters instead (gdn.py:42-62 backward), fused into the finishing kernel where that exists."""
+    out = _gdn_backward(g, x, xsq, nrm, gamma_eff, inverse, need_dx, dxsum_out if want_dxsum else None, reparam)
     return out if want_dxsum else out[:3]
 
 
-def _gdn_backward(g, x, xsq, nrm, gamma_eff, inverse, need_dx, dxsum_out=None):
+def _gdn_backward(g, x, xsq, nrm, gamma_eff, inverse, need_dx, dxsum_out=None, reparam=None):
+    dx, dgamma, dbeta, dxsum, done = _gdn_backward_eff(g, x, xsq, nrm, gamma_eff, inverse, need_dx, dxsum_out, reparam)
+    if reparam is not None and not done:
+        gp, bp, beta_min = reparam
+        dgamma = nonneg_bwd(gp, dgamma, GAMMA_BOUND)
+        dbeta = nonneg_bwd(bp, dbeta, beta_bound(beta_min))
+    return dx, dgamma, dbeta, dxsum
+
+
+def _gdn_backward_eff(g, x, xsq, nrm, gamma_eff, inverse, need_dx, dxsum_out, reparam):
     N, H, W, C = x.shape
     sgn = 0.5 if inverse else -0.5
     if gdn_fused_ok(x.dtype, C) and need_dx:
         P = N * H * W
         wp = pack_weight(gamma_eff, _ONE_TAP[0], C, C, 1, C, x.dtype, cache=False)   # rows=k, cols=i: gamma[i][k]
-        if C in (128, 192):      # d(gamma) and the dx column sums inside the kernel: t and x^2 never reach HBM
+        if C in (128, 192):      # d(gamma), d(beta), the dx column sums and the reparametrisation in two launches
             dx = torch.empty_like(x)
-            nparts = lib().hpc_gdn_bwd_umma_parts(P)
-            parts = torch.empty((2, nparts, C), dtype=torch.float32, device=x.device)
-            dgamma = torch.empty((C, C, 1, 1), dtype=torch.float32, device=x.device)
+            dev = x.device
+            if reparam is not None:
+                gp, bp, beta_min = reparam
+                dgamma, dbeta = grad_buffer(gp), grad_buffer(bp)
+                gpp, gb, bpp, bb = ptr(gp), GAMMA_BOUND, ptr(bp), beta_bound(beta_min)
+            else:
+                dgamma = torch.empty((C, C, 1, 1), dtype=torch.float32, device=dev)
+                dbeta = torch.empty((C,), dtype=torch.float32, device=dev)
+                gpp, gb, bpp, bb = None, 0.0, None, 0.0
+            dxsum = dxsum_out if dxsum_out is not None else torch.empty((C,), dtype=torch.float32, device=dev)
             wsb = lib().hpc_gdn_bwd_fused_umma_workspace_bytes(P, C)
-            ws = torch.empty(wsb, dtype=torch.uint8, device=x.device)
-            check(lib().hpc_gdn_bwd_fused_umma(ptr(g), ptr(x), ptr(nrm), ptr(wp), P, C, int(inverse), ptr(dx),
-                                               ptr(dgamma), sgn, ptr(parts[0]), ptr(parts[1]), ptr(ws), wsb, stream()))
-            return dx, dgamma, colsum(parts[0], sgn), colsum(parts[1], out=dxsum_out)
+            ws = torch.empty(wsb, dtype=torch.uint8, device=dev)
+            check(lib().hpc_gdn_bwd_fused_umma(ptr(g), ptr(x), ptr(nrm), ptr(wp), P, C, int(inverse), ptr(dx), gpp, gb,
+                                               bpp, bb, ptr(dgamma), ptr(dbeta), ptr(dxsum), ptr(ws), wsb, stream()))
+            return dx, dgamma, dbeta, dxsum, True
         dx, t, sq = torch.empty_like(x), torch.empty_like(x), torch.empty_like(x)
         parts = torch.empty((lib().hpc_gdn_bwd_umma_parts(P), C), dtype=torch.float32, device=x.device)
         check(lib().hpc_gdn_bwd_umma(ptr(g), ptr(x), ptr(nrm), ptr(wp), P, C, int(inverse), ptr(dx), ptr(t), ptr(sq),
                                      ptr(parts), stream()))
         dgamma = igemm_wgrad(t, sq, _ONE_TAP[0], _ONE_TAP[1], 1, sgn).view(C, C, 1, 1)
-        return dx, dgamma, colsum(parts, sgn), None
+        return dx, dgamma, colsum(parts, sgn), None, False
     if xsq is None:
         xsq, _ = square(x)
     t = torch.empty_like(x)
@@ -485,7 +503,7 @@ def _gdn_backward(g, x, xsq, nrm, gamma_eff, inverse, need_dx, dxsum_out=None):
                        EPI_IGDN_BWD if inverse else EPI_GDN_BWD, None, aux0=g, aux1=x, aux2=nrm)["lp"]
     dgamma = igemm_wgrad(t, xsq, _ONE_TAP[0], _ONE_TAP[1], 1, sgn).view(C, C, 1, 1)
     dbeta = colsum(t, sgn)
-    return dx, dgamma, dbeta, None
+    return dx, dgamma, dbeta, None, False
 
 
 # ----------------------------------------------------------------------------------------

@@ -388,17 +388,20 @@ size_t hpc_wgrad_c3_scratch_bytes(int N, int Cw, int Cs, int H, int W);
 int hpc_gdn_fwd_umma(const void* x_bf16, const void* gamma_bf16, const float* beta, int64_t P, int C, int inverse,
                      void* y_bf16, void* rnorm_bf16, hpc_stream_t stream);
 int hpc_gdn_bwd_umma_parts(int64_t P);
-/*  gdn_bwd_fused_umma (C in {128,192}): as gdn_bwd_umma, but the d(gamma) contraction
- *                dgamma[i][j] = dgamma_scale * sum_p t[p][i] x[p][j]^2 runs inside the kernel on the same shared-
- *                memory tiles (t and x^2 are never written to HBM), accumulated per CTA in TMEM and reduced over the
- *                CTAs in a fixed order through `workspace` (>= hpc_gdn_bwd_fused_umma_workspace_bytes()).  Also
- *                returns per-CTA column sums of dx: dxsum_part[parts][C] -- summed over parts this is the bias
- *                gradient of the conv / transposed conv whose output feeds the GDN (analysis.py:55-58). */
+/*  gdn_bwd_fused_umma (C in {128,192}): the whole backward of a GDN layer in two launches.  As gdn_bwd_umma, but the
+ *                d(gamma) contraction sum_p t[p][i] x[p][j]^2 runs inside the kernel on the same shared-memory tiles
+ *                (t and x^2 are never written to HBM), accumulated per CTA in TMEM; a finishing kernel reduces the
+ *                per-CTA partials of d(gamma), of the column sums of t and of the column sums of dx in a fixed order
+ *                (through `workspace`, >= hpc_gdn_bwd_fused_umma_workspace_bytes()) and writes
+ *                  dgamma[C][C] = R(-+1/2 sum_p t x^2),  dbeta[C] = R(-+1/2 sum_p t),  dbias[C] = sum_p dx (nullable)
+ *                where R is the backward of the non-negative reparametrisation (gdn.py:42-62 with bound.py:36-46)
+ *                if the raw parameter (gamma_param / beta_param) is given, the identity if it is NULL.  dbias is
+ *                the bias gradient of the conv / transposed conv whose output feeds the GDN (analysis.py:55-58). */
 size_t hpc_gdn_bwd_fused_umma_workspace_bytes(int64_t P, int C);
 int hpc_gdn_bwd_fused_umma(const void* g_bf16, const void* x_bf16, const void* rnorm_bf16, const void* gammaT_bf16,
-                           int64_t P, int C, int inverse, void* dx_bf16, float* dgamma, float dgamma_scale,
-                           float* colsum_part, float* dxsum_part, void* workspace, size_t workspace_bytes,
-                           hpc_stream_t stream);
+                           int64_t P, int C, int inverse, void* dx_bf16, const float* gamma_param, float gamma_bound,
+                           const float* beta_param, float beta_bound, float* dgamma, float* dbeta, float* dbias,
+                           void* workspace, size_t workspace_bytes, hpc_stream_t stream);
 int hpc_gdn_bwd_umma(const void* g_bf16, const void* x_bf16, const void* rnorm_bf16, const void* gammaT_bf16, int64_t P,
                      int C, int inverse, void* dx_bf16, void* t_bf16, void* xsq_bf16, float* colsum_part,
                      hpc_stream_t stream);
