@@ -17,6 +17,8 @@ class _State:
 
 def _gdn_params(gamma_param, beta_param, beta_min=1e-6):
     """NonNegativeParam.forward for gamma and beta (gdn.py:59-62)."""
+    if hp.gdn_fused_ok(hp.lp_dtype(), beta_param.numel()):
+        return hp.gdn_prepare(gamma_param, beta_param, beta_min), None
     gamma = hp.nonneg_fwd(gamma_param, hp.GAMMA_BOUND)
     beta = hp.nonneg_fwd(beta_param, hp.beta_bound(beta_min))
     return gamma, beta

@@ -926,3 +926,34 @@ int hpc_gdn_bwd_fused_umma(const void* g_bf16, const void* x_bf16, const void* r
   HPC_LAUNCH_CHECK();
   return HPC_OK;
 }
+
+// gdn.py:59-62 for both parameters of a layer + both bf16 operand copies of gamma, one launch:
+//   gamma_eff = max(gamma_param, gamma_bound)^2 - pedestal -> gamma_bf16[i][k] (forward B operand) and gammaT_bf16[k][i]
+//   beta_eff  = max(beta_param, beta_bound)^2 - pedestal   -> beta_eff[C] fp32
+__global__ void gdn_prepare_kernel(const float* __restrict__ gamma_param, const float* __restrict__ beta_param, int C,
+                                   float gamma_bound, float beta_bound, float pedestal, float* __restrict__ beta_eff,
+                                   __nv_bfloat16* __restrict__ g_bf16, __nv_bfloat16* __restrict__ gT_bf16) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx < C * C) {
+    const float v = fmaxf(gamma_param[idx], gamma_bound);
+    const __nv_bfloat16 h = __float2bfloat16_rn(v * v - pedestal);
+    g_bf16[idx] = h;
+    gT_bf16[(idx % C) * C + idx / C] = h;
+  }
+  if (idx < C) {
+    const float v = fmaxf(beta_param[idx], beta_bound);
+    beta_eff[idx] = v * v - pedestal;
+  }
+}
+
+int hpc_gdn_prepare(const float* gamma_param, const float* beta_param, int C, float gamma_bound, float beta_bound,
+                    float pedestal, float* beta_eff, void* gamma_bf16, void* gammaT_bf16, hpc_stream_t stream) {
+  HPC_REQUIRE(gamma_param && beta_param && beta_eff && gamma_bf16 && gammaT_bf16 && C > 0, HPC_ERR_BAD_SHAPE,
+              "hpc_gdn_prepare: bad arguments");
+  gdn_prepare_kernel<<<(C * C + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+      gamma_param, beta_param, C, gamma_bound, beta_bound, pedestal, beta_eff, (__nv_bfloat16*)gamma_bf16,
+      (__nv_bfloat16*)gammaT_bf16);
+  HPC_LAUNCH_CHECK();
+  return HPC_OK;
+}
+

@@ -389,6 +389,7 @@ PEDESTAL = float(2 ** -18) ** 2                      # gdn.py:50
 GAMMA_BOUND = float((0.0 + PEDESTAL ** 2) ** 0.5)    # gdn.py:53 (pedestal squared again: SURVEY 3.5.1)
 
 
+@functools.lru_cache(maxsize=None)
 def beta_bound(beta_min=1e-6):
     # computed like the reference: float32 tensor arithmetic (gdn.py:52-53)
     ped = torch.tensor(PEDESTAL)
@@ -420,12 +421,34 @@ def gdn_fused_ok(dtype, C):
     return engine() == ENGINE_UMMA and dtype == torch.bfloat16 and C in (64, 128, 192)
 
 
+class GdnOperands:
+    """Effective parameters of one GDN layer for the fused tcgen05 kernels: beta_eff (C,) fp32 and the two bf16
+    operand copies of gamma_eff (gamma[i][k] for the forward, gamma^T for the backward)."""
+    __slots__ = ("beta", "g", "gT")
+
+
+def gdn_prepare(gamma_param, beta_param, beta_min=1e-6):
+    """gdn.py:59-62 for both parameters + both operand copies in one launch (fused path only)."""
+    C = beta_param.numel()
+    ops = GdnOperands()
+    ops.beta = torch.empty((C,), dtype=torch.float32, device=beta_param.device)
+    ops.g = torch.empty((2, C, C), dtype=torch.bfloat16, device=beta_param.device)
+    ops.gT = ops.g[1]
+    check(lib().hpc_gdn_prepare(ptr(gamma_param), ptr(beta_param), C, GAMMA_BOUND, beta_bound(beta_min), PEDESTAL,
+                                ptr(ops.beta), ptr(ops.g[0]), ptr(ops.gT), stream()))
+    ops.g = ops.g[0]
+    return ops
+
+
 def gdn_forward(x, xsq, gamma_eff, beta_eff, inverse=False):
     """x (, xsq): NHWC lp; gamma_eff (C,C,1,1) fp32, beta_eff (C,) fp32 -> (y, nrm) NHWC lp.
-    xsq may be None (computed here, or never materialised on the fused path)."""
+    xsq may be None (computed here, or never materialised on the fused path).  gamma_eff may be a GdnOperands."""
     N, H, W, C = x.shape
     if gdn_fused_ok(x.dtype, C):
-        wp = pack_weight(gamma_eff, _ONE_TAP[0], C, C, C, 1, x.dtype, cache=False)
+        if isinstance(gamma_eff, GdnOperands):
+            wp, beta_eff = gamma_eff.g, gamma_eff.beta
+        else:
+            wp = pack_weight(gamma_eff, _ONE_TAP[0], C, C, C, 1, x.dtype, cache=False)
         y, nrm = torch.empty_like(x), torch.empty_like(x)
         check(lib().hpc_gdn_fwd_umma(ptr(x), ptr(wp), ptr(beta_eff), N * H * W, C, int(inverse), ptr(y), ptr(nrm),
                                      stream()))
@@ -467,7 +490,10 @@ def _gdn_backward_eff(g, x, xsq, nrm, gamma_eff, inverse, need_dx, dxsum_out, re
     sgn = 0.5 if inverse else -0.5
     if gdn_fused_ok(x.dtype, C) and need_dx:
         P = N * H * W
-        wp = pack_weight(gamma_eff, _ONE_TAP[0], C, C, 1, C, x.dtype, cache=False)   # rows=k, cols=i: gamma[i][k]
+        if isinstance(gamma_eff, GdnOperands):
+            wp = gamma_eff.gT
+        else:
+            wp = pack_weight(gamma_eff, _ONE_TAP[0], C, C, 1, C, x.dtype, cache=False)   # rows=k, cols=i: gamma[i][k]
         if C in (128, 192):      # d(gamma), d(beta), the dx column sums and the reparametrisation in two launches
             dx = torch.empty_like(x)
             dev = x.device

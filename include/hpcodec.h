@@ -385,6 +385,10 @@ size_t hpc_wgrad_c3_scratch_bytes(int N, int Cw, int Cs, int H, int W);
  *                g / rnorm + x (t . gamma)); also writes t and x^2 (operands of the d(gamma) contraction through
  *                hpc_igemm_wgrad) and per-CTA column sums of t: colsum_part[parts][C], parts =
  *                hpc_gdn_bwd_umma_parts(P); d(beta) = -+1/2 * sum over parts.  gammaT_bf16[k][i] = gamma[i][k]. */
+/*  gdn_prepare: NonNegativeParam.forward (gdn.py:59-62) of gamma and beta and both bf16 operand copies of gamma in
+ *               one launch: beta_eff[C] fp32, gamma_bf16[i][k], gammaT_bf16[k][i]. */
+int hpc_gdn_prepare(const float* gamma_param, const float* beta_param, int C, float gamma_bound, float beta_bound,
+                    float pedestal, float* beta_eff, void* gamma_bf16, void* gammaT_bf16, hpc_stream_t stream);
 int hpc_gdn_fwd_umma(const void* x_bf16, const void* gamma_bf16, const float* beta, int64_t P, int C, int inverse,
                      void* y_bf16, void* rnorm_bf16, hpc_stream_t stream);
 int hpc_gdn_bwd_umma_parts(int64_t P);
