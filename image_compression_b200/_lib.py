@@ -95,7 +95,7 @@ class IgemmFwdParams(Structure):
         ("phase", IgemmPhase * MAX_PHASES), ("dh", c_int * MAX_TAPS), ("dw", c_int * MAX_TAPS),
         ("epi", c_int), ("bias", c_void_p), ("aux0", c_void_p), ("aux1", c_void_p), ("aux2", c_void_p),
         ("out_f32", c_void_p), ("out_lp", c_void_p), ("out_sq_lp", c_void_p), ("out_abs_lp", c_void_p),
-        ("out_nrm_lp", c_void_p),
+        ("out_nrm_lp", c_void_p), ("workspace", c_void_p), ("workspace_bytes", c_size_t),
     ]
 
 
@@ -163,6 +163,7 @@ _SIGNATURES = {
                                        c_int, c_float, c_void_p, c_void_p]),
     "hpc_msssim_combine_bwd": (c_int, [c_void_p, POINTER(c_double), c_int, c_int, POINTER(c_float), c_int,
                                        c_int, c_float, c_void_p, c_float, c_void_p, c_void_p]),
+    "hpc_igemm_fwd_workspace_bytes": (c_size_t, [POINTER(IgemmFwdParams)]),
     "hpc_igemm_fwd": (c_int, [POINTER(IgemmFwdParams), c_void_p]),
     "hpc_igemm_wgrad": (c_int, [POINTER(IgemmWgradParams), c_void_p]),
     "hpc_igemm_wgrad_workspace_bytes": (c_size_t, [POINTER(IgemmWgradParams)]),

@@ -96,7 +96,8 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
   constexpr int KC = Cfg::KC;
   constexpr int A_COL = Cfg::FWD_A_COL, A_COLS = C / 2;     // x^2 as the TMEM-resident A operand, double buffered
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1 KB aligned; pointer arithmetic keeps the
+                                                                                  // shared address space (LDS/STS, not generic LD/ST)
   uint8_t* gam = smem;                           // KC chunks of [C rows x 128 B]
   uint8_t* xs = gam + Cfg::GAMMA;                // [2][TILE]   x, later y
   uint8_t* rs = xs + 2 * Cfg::TILE;              // [TILE]      r staging for the TMA store
@@ -292,7 +293,8 @@ gdn_bwd_umma_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
   using Cfg = GCfg<C>;
   constexpr int KC = Cfg::KC;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1 KB aligned; pointer arithmetic keeps the
+                                                                                  // shared address space (LDS/STS, not generic LD/ST)
   uint8_t* gam = smem;                           // gamma^T as the K-major B operand
   uint8_t* bg = gam + Cfg::GAMMA;                // g   -> u = g r -> dx
   uint8_t* bx = bg + Cfg::TILE;                  // x   -> x^2
@@ -501,7 +503,8 @@ gdn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_cons
   constexpr int COL_DGA = C, COL_DGB = 2 * C;     // TMEM columns: a | dgamma[0:128][:] | transposed remainder x2
   constexpr int TCOLS = C == 128 ? 256 : 512;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1 KB aligned; pointer arithmetic keeps the
+                                                                                  // shared address space (LDS/STS, not generic LD/ST)
   uint8_t* gam = smem;                           // gamma^T as the K-major B operand
   uint8_t* bg = gam + Cfg::GAMMA;                // g   -> u = g r -> dx
   uint8_t* bx = bg + Cfg::TILE;                  // x   -> x^2

@@ -5,6 +5,7 @@
 #include "igemm_epilogue.cuh"
 
 int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream);      // igemm_umma.cu
+size_t hpc_igemm_fwd_umma_workspace_bytes(const hpc_igemm_fwd_params* p);
 int hpc_igemm_wgrad_umma(const hpc_igemm_wgrad_params* p, hpc_stream_t stream);  // igemm_umma.cu
 size_t hpc_igemm_wgrad_umma_workspace_bytes(const hpc_igemm_wgrad_params* p);
 
@@ -166,6 +167,13 @@ static int check_wgrad(const hpc_igemm_wgrad_params* p) {
   }
   HPC_REQUIRE(nt <= HPC_MAX_TAPS, HPC_ERR_BAD_SHAPE, "hpc_igemm_wgrad: %d taps > %d", nt, HPC_MAX_TAPS);
   return HPC_OK;
+}
+
+size_t hpc_igemm_fwd_workspace_bytes(const hpc_igemm_fwd_params* p) {
+  if (p && p->engine == HPC_ENGINE_UMMA && p->dtype == HPC_BF16 && p->Ci % 64 == 0 && p->Ci > 0 && p->N > 0 &&
+      p->GH > 0 && p->GW > 0 && p->nphases >= 1 && p->nphases <= HPC_MAX_PHASES)
+    return hpc_igemm_fwd_umma_workspace_bytes(p);
+  return 0;
 }
 
 size_t hpc_igemm_wgrad_workspace_bytes(const hpc_igemm_wgrad_params* p) {

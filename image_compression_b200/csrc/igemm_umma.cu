@@ -33,6 +33,9 @@ struct FwdKParams {
   hpc_igemm_phase phase[HPC_MAX_PHASES];
   int dh[HPC_MAX_TAPS], dw[HPC_MAX_TAPS];
   int kchunks;               // Ci / 64
+  int ksplit;                // > 1: work item = (tile, K slice); raw fp32 partials go to ws[slice][N,OH,OW,Co]
+  float* ws;
+  int64_t out_elems;
   EpiArgs epi;
 };
 
@@ -166,7 +169,8 @@ template <int BLOCK_N, int NCTA>
 __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const FwdKParams& p) {
   using Cfg = FwdCfg<BLOCK_N, NCTA>;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1 KB aligned; pointer arithmetic keeps the
+                                                                                  // shared address space (LDS/STS, not generic LD/ST)
   uint8_t* smem_a = smem;                                  // STAGES x 16 KB
   uint8_t* smem_b = smem + Cfg::STAGES * Cfg::A_BYTES;     // STAGES x B_BYTES (multiples of 1 KB)
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
@@ -181,7 +185,8 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
   const int rank = NCTA == 2 ? (int)cluster_ctarank() : 0;
   const int worker = blockIdx.x / NCTA, nworkers = gridDim.x / NCTA;       // CTA (or CTA pair) index
   const int per_phase = NCTA == 1 ? p.tiles_per_phase : (p.tiles_per_phase + 1) / 2;
-  const int total_work = per_phase * p.nphases;
+  const int ksplit = NCTA == 1 ? p.ksplit : 1;              // split-K for grids of a few tiles (single-CTA kernel only)
+  const int total_work = per_phase * p.nphases * ksplit;
   if (p.epi.bias)
     for (int i = threadIdx.x; i < BLOCK_N; i += FW_THREADS) bias_s[i] = p.epi.bias[i];
 
@@ -208,11 +213,14 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
       int stage = 0; uint32_t phase = 0;
       for (int w = worker; w < total_work; w += nworkers) {
         int ph, n0, i0, j0;
-        tile_coords<NCTA>(p, w, rank, ph, n0, i0, j0);
+        tile_coords<NCTA>(p, w / ksplit, rank, ph, n0, i0, j0);
         const hpc_igemm_phase P = p.phase[ph];
-        for (int t = P.tap_begin; t < P.tap_begin + P.ntaps; ++t) {
+        const int ksteps = P.ntaps * p.kchunks, sp = w % ksplit;
+        const int ks0 = ksteps * sp / ksplit, ks1 = ksteps * (sp + 1) / ksplit;
+        for (int ks = ks0; ks < ks1; ++ks) {
+          const int t = P.tap_begin + ks / p.kchunks, c = ks % p.kchunks;
           const int cw = j0 * p.is + p.dw[t], chh = i0 * p.is + p.dh[t];
-          for (int c = 0; c < p.kchunks; ++c) {
+          {
             mbar_wait(&empty_bar[stage], phase ^ 1);
             if (NCTA == 1) {
               if (lane == 0) mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
@@ -240,8 +248,9 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
       int acc = 0; uint32_t acc_phase = 0;
       for (int w = worker; w < total_work; w += nworkers) {
         int ph, n0, i0, j0;
-        tile_coords<NCTA>(p, w, 0, ph, n0, i0, j0);
-        const int ksteps = p.phase[ph].ntaps * p.kchunks;
+        tile_coords<NCTA>(p, w / ksplit, 0, ph, n0, i0, j0);
+        const int kall = p.phase[ph].ntaps * p.kchunks, sp = w % ksplit;
+        const int ksteps = kall * (sp + 1) / ksplit - kall * sp / ksplit;
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);     // epilogue(s) have drained this accumulator
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * Cfg::ACC_STRIDE;
@@ -274,7 +283,7 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
     int acc = 0; uint32_t acc_phase = 0;
     for (int w = worker; w < total_work; w += nworkers) {
       int ph, n0, i0, j0;
-      tile_coords<NCTA>(p, w, rank, ph, n0, i0, j0);
+      tile_coords<NCTA>(p, w / ksplit, rank, ph, n0, i0, j0);
       const hpc_igemm_phase P = p.phase[ph];
       const int jl = row % p.tw, il = (row / p.tw) % p.th, nl = row / (p.tw * p.th);
       const int n = n0 + nl, i = i0 + il, j = j0 + jl;
@@ -290,8 +299,14 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
         tmem_ld16(taddr + c0, v);
         tmem_ld_wait();
         if (valid) {
-          epilogue8(epi, v, obase + c0, c0);
-          epilogue8(epi, v + 8, obase + c0 + 8, c0 + 8);
+          if (ksplit > 1) {           // raw partial of this K slice; bias / epilogue run in splitk_epilogue_kernel
+            float* dst = p.ws + (int64_t)(w % ksplit) * p.out_elems;
+            store8_f32(dst, obase + c0, v);
+            store8_f32(dst, obase + c0 + 8, v + 8);
+          } else {
+            epilogue8(epi, v, obase + c0, c0);
+            epilogue8(epi, v + 8, obase + c0 + 8, c0 + 8);
+          }
         }
       }
       tc_fence_before();
@@ -327,10 +342,27 @@ igemm_fwd_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
   igemm_fwd_body<BLOCK_N, 2>(tmA, tmB, p);
 }
 
+// Second pass of a split-K launch: sums the K slices of every output pixel in a fixed order and applies the bias /
+// epilogue exactly like the in-kernel epilogue does (8 channels per thread).
+__global__ void __launch_bounds__(256)
+splitk_epilogue_kernel(const float* __restrict__ ws, int ksplit, int64_t out_elems, int Co, const __grid_constant__ EpiArgs epi) {
+  const int64_t u = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;      // unit of 8 channels
+  const int64_t o = u * 8;
+  if (o >= out_elems) return;
+  float acc[8];
+  load8_f32(ws, o, acc);
+  for (int s = 1; s < ksplit; ++s) {
+    float v[8];
+    load8_f32(ws + (int64_t)s * out_elems, o, v);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] += v[i];
+  }
+  epilogue8(epi, acc, o, (int)(o % Co));
+}
+
 // ---------------------------------------------------------------------------------------
 // host side of the forward kernel
 // ---------------------------------------------------------------------------------------
-static int pow2_floor(int v) { int r = 1; while (r * 2 <= v) r *= 2; return r; }
 
 template <int BLOCK_N>
 static int launch_fwd(const CUtensorMap& tmA, const CUtensorMap& tmB, const FwdKParams& kp, bool pair, cudaStream_t st) {
@@ -353,11 +385,43 @@ static int launch_fwd(const CUtensorMap& tmA, const CUtensorMap& tmB, const FwdK
                                     Cfg::SMEM_BYTES));
       attr_set = true;
     }
-    const int grid = kp.total_tiles < hpc_num_sms() ? kp.total_tiles : hpc_num_sms();
+    const int work = kp.total_tiles * kp.ksplit;
+    const int grid = work < hpc_num_sms() ? work : hpc_num_sms();
     igemm_fwd_umma_kernel<BLOCK_N><<<grid, FW_THREADS, Cfg::SMEM_BYTES, st>>>(tmA, tmB, kp);
   }
   HPC_LAUNCH_CHECK();
   return HPC_OK;
+}
+
+static int pow2_floor(int v) { int r = 1; while (r * 2 <= v) r *= 2; return r; }
+
+// Split-K factor for grids of a few tiles (the h_a / h_s layers: 8-32 tiles of 27-75 k-steps each leave most SMs
+// idle and serialise the K loop): as many slices as fill the SMs, at least 3 k-steps per slice.
+static int fwd_ksplit(const hpc_igemm_fwd_params* p, int total_tiles) {
+  static int mode = -1;                       // HPC_FWD_KSPLIT=0 disables (A/B measurements)
+  if (mode < 0) { const char* e = getenv("HPC_FWD_KSPLIT"); mode = e ? atoi(e) : 1; }
+  if (!mode || total_tiles * 2 > hpc_num_sms()) return 1;
+  int min_ksteps = 1 << 30;
+  for (int i = 0; i < p->nphases; ++i) {
+    const int k = p->phase[i].ntaps * (p->Ci / FW_BK);
+    if (k < min_ksteps) min_ksteps = k;
+  }
+  int ks = hpc_num_sms() / total_tiles;
+  if (ks > min_ksteps / 3) ks = min_ksteps / 3;
+  if (ks > 16) ks = 16;
+  return ks < 2 ? 1 : ks;
+}
+
+static int fwd_total_tiles(const hpc_igemm_fwd_params* p) {
+  int tw = pow2_floor(p->GW < 16 ? p->GW : 16);
+  int th = pow2_floor(p->GH < FW_BM / tw ? p->GH : FW_BM / tw);
+  int nb = FW_BM / (tw * th);
+  return ((p->GW + tw - 1) / tw) * ((p->GH + th - 1) / th) * ((p->N + nb - 1) / nb) * p->nphases;
+}
+
+size_t hpc_igemm_fwd_umma_workspace_bytes(const hpc_igemm_fwd_params* p) {
+  const int ks = fwd_ksplit(p, fwd_total_tiles(p));
+  return ks > 1 ? (size_t)ks * p->N * p->OH * p->OW * p->Co * sizeof(float) : 0;
 }
 
 // CTA pairs pay off once every TPC has a pair of tiles; below that the single-CTA kernel keeps more SMs busy.
@@ -410,6 +474,14 @@ int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
   }
 
   const bool pair = fwd_use_pair(kp);
+  kp.ksplit = 1;
+  if (!pair) {
+    const int ks = fwd_ksplit(p, kp.total_tiles);
+    const size_t need = (size_t)ks * p->N * p->OH * p->OW * p->Co * sizeof(float);
+    if (ks > 1 && p->workspace && p->workspace_bytes >= need && hpc_aligned16(p->workspace)) {
+      kp.ksplit = ks; kp.ws = (float*)p->workspace; kp.out_elems = (int64_t)p->N * p->OH * p->OW * p->Co;
+    }
+  }
   CUtensorMap tmA, tmB;
   {
     uint64_t dims[4] = {(uint64_t)p->Ci, (uint64_t)p->W, (uint64_t)p->H, (uint64_t)p->N};
@@ -432,12 +504,18 @@ int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
   // stride-2 transposed conv are never counted because the phases only hold the live taps)
   HpcProfScope prof(HPC_PROF_IGEMM_FWD,
                     2.0 * p->N * p->GH * p->GW * (double)ntaps_total_all(p) * p->Ci * p->Co, stream);
+  int rc;
   switch (p->Co) {
-    case 64: return launch_fwd<64>(tmA, tmB, kp, pair, st);
-    case 128: return launch_fwd<128>(tmA, tmB, kp, pair, st);
-    case 192: return launch_fwd<192>(tmA, tmB, kp, pair, st);
-    default: return launch_fwd<256>(tmA, tmB, kp, pair, st);
+    case 64: rc = launch_fwd<64>(tmA, tmB, kp, pair, st); break;
+    case 128: rc = launch_fwd<128>(tmA, tmB, kp, pair, st); break;
+    case 192: rc = launch_fwd<192>(tmA, tmB, kp, pair, st); break;
+    default: rc = launch_fwd<256>(tmA, tmB, kp, pair, st); break;
   }
+  if (rc || kp.ksplit == 1) return rc;
+  const int64_t units = kp.out_elems / 8;
+  splitk_epilogue_kernel<<<(int)((units + 255) / 256), 256, 0, st>>>(kp.ws, kp.ksplit, kp.out_elems, p->Co, kp.epi);
+  HPC_LAUNCH_CHECK();
+  return HPC_OK;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -473,7 +551,8 @@ __global__ void __launch_bounds__(WG_THREADS, 1)
 igemm_wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmLo, const __grid_constant__ CUtensorMap tmHi,
                         const __grid_constant__ WgKParams p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1 KB aligned; pointer arithmetic keeps the
+                                                                                  // shared address space (LDS/STS, not generic LD/ST)
   const int stage_bytes = (4 + p.cchunks) * WG_ATOM_BYTES;
   const int nstages = p.stages;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + nstages * stage_bytes);

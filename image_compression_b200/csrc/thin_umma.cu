@@ -151,7 +151,8 @@ __global__ void __launch_bounds__(T1_THREADS, 1)
 conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constant__ T1Params p) {
   using Cfg = T1Cfg<CW>;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1 KB aligned; pointer arithmetic keeps the
+                                                                                  // shared address space (LDS/STS, not generic LD/ST)
   uint8_t* smem_a = smem;                                   // 2 x 32 KB
   uint8_t* smem_b = smem_a + 2 * T1_A_BYTES;                // 2 chunks x [CW x 128 B]
   float* patch = reinterpret_cast<float*>(smem_b + Cfg::B_BYTES);
@@ -393,7 +394,8 @@ deconv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   using Cfg = T2Cfg<CW>;
   constexpr int KC = CW / 64;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1 KB aligned; pointer arithmetic keeps the
+                                                                                  // shared address space (LDS/STS, not generic LD/ST)
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem_a + T2_STAGES * Cfg::A_BYTES;
   float* Ps = reinterpret_cast<float*>(smem_b + ((Cfg::B_BYTES + 1023) / 1024) * 1024);
@@ -620,7 +622,8 @@ __global__ void __launch_bounds__(T3_THREADS, 1)
 wgrad_c3_umma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ T3Params p) {
   using Cfg = T3Cfg<CW>;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1 KB aligned; pointer arithmetic keeps the
+                                                                                  // shared address space (LDS/STS, not generic LD/ST)
   float* patch = reinterpret_cast<float*>(smem + T3_STAGES * Cfg::STAGE_BYTES);
   uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(patch) + Cfg::PATCH_BYTES);
   uint64_t* full_bar = bars;                    // [STAGES] 1 TMA arrival (+tx) + 128 builder arrivals

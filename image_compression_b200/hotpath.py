@@ -273,6 +273,10 @@ def igemm_fwd(x, w_packed, taps, phases, grid_hw, is_, os_, out_hw, Co, epi=EPI_
         outs["nrm"] = torch.empty(shape, dtype=x.dtype, device=x.device)
     P.out_f32, P.out_lp = ptr(outs.get("f32")), ptr(outs.get("lp"))
     P.out_sq_lp, P.out_abs_lp, P.out_nrm_lp = ptr(outs.get("sq")), ptr(outs.get("abs")), ptr(outs.get("nrm"))
+    wsb = lib().hpc_igemm_fwd_workspace_bytes(byref(P))     # > 0: few-tile layer, the engine splits K over CTAs
+    if wsb:
+        ws = torch.empty(wsb, dtype=torch.uint8, device=x.device)
+        P.workspace, P.workspace_bytes = ptr(ws), wsb
     check(lib().hpc_igemm_fwd(byref(P), stream()))
     return outs
 

@@ -284,9 +284,15 @@ typedef struct {
   void* out_sq_lp;    /* optional out^2 (the A operand of the following GDN) */
   void* out_abs_lp;   /* optional |out| (input of h_a, bmshl2018.py:72) */
   void* out_nrm_lp;   /* GDN/IGDN: rsqrt(n), saved for backward */
+  /* Optional scratch for the tcgen05 engine's split-K path (layers with so few 128-pixel tiles that most SMs would
+   * idle: the K loop is split over CTAs, fp32 partials go here and a second kernel sums them in a fixed order and
+   * applies the epilogue).  >= hpc_igemm_fwd_workspace_bytes(p) (0 = the launch does not split); NULL = never split. */
+  void* workspace;
+  size_t workspace_bytes;
 } hpc_igemm_fwd_params;
 
 int hpc_igemm_fwd(const hpc_igemm_fwd_params* p, hpc_stream_t stream);
+size_t hpc_igemm_fwd_workspace_bytes(const hpc_igemm_fwd_params* p);
 
 /* Weight gradient as implicit GEMM over pixels:
  * gw[t][r][c] = scale * sum_{n,i,j} lo[n, i+dh[t], j+dw[t], r] * hi[n, i*hs+oh_off, j*hs+ow_off, c]
