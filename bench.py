@@ -141,15 +141,23 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1590.0, "source": "fallback"}
 
 
-def ncu_traffic(kernel_key):
-    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture
-    (profiles/traffic.json, written by scripts/ncu_summarise.py), or None."""
+def ncu_traffic(*kernel_keys):
+    """DRAM bytes per launch (read + write) of a kernel class from the committed ncu capture of this same command
+    (profiles/traffic.json, written by scripts/ncu_summarise.py from `ncu --metrics dram__bytes_*`): the launch-
+    weighted average over the kernels of the class, or None."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
     if not os.path.exists(p):
         return None
     try:
         with open(p) as f:
-            return json.load(f).get(kernel_key)
+            t = json.load(f)
+        tot = n = 0.0
+        for k in kernel_keys:
+            d = t.get(k)
+            if d:
+                tot += d["avg_bytes_per_launch"] * d["launches"]
+                n += d["launches"]
+        return tot / n if n else None
     except Exception:
         return None
 
@@ -409,8 +417,10 @@ def main():
     if n:
         ach = flops / (ms * 1e-3) / 1e12
         peak = peaks["bf16_tflops_sustained"]   # kernel timed inside a long step -> sustained figure
-        roofline = {"bound": "tensor", "kernel": "igemm_fwd_umma_kernel", "achieved": ach, "peak": peak,
-                    "unit": "TFLOP/s", "frac": ach / peak, "traffic": ncu_traffic("igemm_fwd_umma_kernel"),
+        roofline = {"bound": "tensor", "kernel": "igemm_fwd_umma_pair_kernel + igemm_fwd_umma_kernel (one class: the "
+                    "CTA-pair and single-CTA builds of the implicit-GEMM forward engine)", "achieved": ach, "peak": peak,
+                    "unit": "TFLOP/s", "frac": ach / peak,
+                    "traffic": ncu_traffic("igemm_fwd_umma_pair_kernel", "igemm_fwd_umma_kernel"),
                     "peak_source": f"{peaks['source']} (bf16 sustained)", "launches": n,
                     "avg_launch_ms": ms / n, "share_of_step": ms / r["ms_total"],
                     "algorithmic_flops_per_launch": flops / n}

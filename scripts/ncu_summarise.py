@@ -91,7 +91,7 @@ def main(src, dst):
         for k, d in sorted(t.items(), key=lambda kv: -kv[1]["avg_bytes_per_launch"] * kv[1]["launches"]):
             md.append(f"| `{k[:70]}` | {d['launches']} | {d['avg_bytes_per_launch'] / 1e6:.1f} | {d['max'] / 1e6:.1f} |")
         md.append("")
-        flat = {k: d["avg_bytes_per_launch"] for k, d in t.items()}
+        flat = {k: {"avg_bytes_per_launch": d["avg_bytes_per_launch"], "launches": d["launches"]} for k, d in t.items()}
         for path in (dst + "_traffic_avg.json", os.path.join(os.path.dirname(dst) or ".", "traffic.json")):
             with open(path, "w") as f:
                 json.dump(flat, f, indent=1)
