@@ -242,8 +242,12 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
     }
   } else if (warp == 1) {
     // ================================ MMA issuer (pair: leader only) ==============
-    if (lane == 0 && rank == 0) {
+    // The whole warp runs the loop (convergent code keeps the descriptors in uniform registers); one elected lane
+    // issues.  Descriptors advance by adding to their address field: 32 bytes (one K = 16 step) = 2 units of 16 B.
+    if (rank == 0) {
       constexpr uint32_t idesc = make_idesc_bf16(FW_BM * NCTA, BLOCK_N, 0, 0);
+      const uint64_t adesc0 = make_smem_desc_sw128(smem_u32(smem_a), 16, 1024);
+      const uint64_t bdesc0 = make_smem_desc_sw128(smem_u32(smem_b), 16, 1024);
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0;
       for (int w = worker; w < total_work; w += nworkers) {
@@ -257,20 +261,24 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
         for (int ks = 0; ks < ksteps; ++ks) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          const uint32_t a_addr = smem_u32(smem_a + stage * Cfg::A_BYTES);
-          const uint32_t b_addr = smem_u32(smem_b + stage * Cfg::B_BYTES);
+          const uint64_t ad = adesc0 + (uint64_t)(stage * (Cfg::A_BYTES >> 4));
+          const uint64_t bd = bdesc0 + (uint64_t)(stage * (Cfg::B_BYTES >> 4));
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < FW_BK / 16; ++k) {
-            const uint64_t ad = make_smem_desc_sw128(a_addr + k * 32, 16, 1024);
-            const uint64_t bd = make_smem_desc_sw128(b_addr + k * 32, 16, 1024);
-            if (NCTA == 1) mma_bf16_ss(d_tmem, ad, bd, idesc, (ks | k) != 0);
-            else mma_bf16_ss_pair(d_tmem, ad, bd, idesc, (ks | k) != 0);
+            for (int k = 0; k < FW_BK / 16; ++k) {
+              if (NCTA == 1) mma_bf16_ss(d_tmem, ad + 2 * k, bd + 2 * k, idesc, (ks | k) != 0);
+              else mma_bf16_ss_pair(d_tmem, ad + 2 * k, bd + 2 * k, idesc, (ks | k) != 0);
+            }
+            // frees the smem stage (in both CTAs) when these MMAs retire
+            if (NCTA == 1) mma_commit(&empty_bar[stage]); else mma_commit_pair(&empty_bar[stage]);
           }
-          // frees the smem stage (in both CTAs) when these MMAs retire
-          if (NCTA == 1) mma_commit(&empty_bar[stage]); else mma_commit_pair(&empty_bar[stage]);
+          __syncwarp();
           if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
         }
-        if (NCTA == 1) mma_commit(&tfull_bar[acc]); else mma_commit_pair(&tfull_bar[acc]);   // accumulator complete
+        if (elect_one()) {
+          if (NCTA == 1) mma_commit(&tfull_bar[acc]); else mma_commit_pair(&tfull_bar[acc]);   // accumulator complete
+        }
+        __syncwarp();
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
