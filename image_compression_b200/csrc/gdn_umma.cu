@@ -605,7 +605,11 @@ gdn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_cons
     const int row = q * 32 + lane;
     const int wt = threadIdx.x - 96;              // 0..511: column owner for the column sums
     constexpr int UH = C / 32;
-    float bsum = 0.f, dsum = 0.f;
+    // column sums: warp w owns tile rows 8w..8w+7, lane l < C/8 the 8 channels of unit l (16-byte loads); the
+    // per-thread partials live in registers for the whole kernel and are combined across warps once at the end
+    float tsum[8], dsum[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) tsum[e] = dsum[e] = 0.f;
     int it = 0;
     for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
       mbar_wait(in_full, it & 1);
@@ -640,13 +644,14 @@ gdn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_cons
       mbar_arrive(a_full);
       // d(beta): column sums of the bf16 t tile, while the MMA runs (rows past P are zero: TMA zero fill)
       named_bar(4, G_WORKERS);
-      if (wt < C) {
-        const int U = wt >> 3, e = wt & 7;
-        float s = 0.f;
-#pragma unroll 8
-        for (int r2 = 0; r2 < 128; ++r2)
-          s += __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(bn + unit_off(r2, U) + e * 2));
-        bsum += s;
+      if (lane < C / 8) {
+#pragma unroll
+        for (int rr = 0; rr < 8; ++rr) {
+          float f[8];
+          unpack8(*reinterpret_cast<const uint4*>(bn + unit_off(w * 8 + rr, lane)), f);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) tsum[e] += f[e];
+        }
       }
       mbar_wait(tfull, it & 1);
       tc_fence_after();
@@ -685,26 +690,44 @@ gdn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_cons
       // d(bias) of the producer layer: column sums of the bf16 dx tile, while it is being stored.  Rows past P
       // are skipped: the inverse form divides the zero-filled g by the zero-filled r there.
       named_bar(4, G_WORKERS);
-      if (wt < C) {
-        const int U = wt >> 3, e = wt & 7;
+      if (lane < C / 8) {
         const int64_t left = p.P - (int64_t)tile * 128;
         const int nrows = left < 128 ? (int)left : 128;
-        float s = 0.f;
-#pragma unroll 8
-        for (int r2 = 0; r2 < nrows; ++r2)
-          s += __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(bg + unit_off(r2, U) + e * 2));
-        dsum += s;
+#pragma unroll
+        for (int rr = 0; rr < 8; ++rr) {
+          if (w * 8 + rr < nrows) {
+            float f[8];
+            unpack8(*reinterpret_cast<const uint4*>(bg + unit_off(w * 8 + rr, lane)), f);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) dsum[e] += f[e];
+          }
+        }
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(in_empty);
     }
-    if (wt < C) {
-      p.colsum_part[(int64_t)blockIdx.x * C + wt] = bsum;
-      p.dxsum_part[(int64_t)blockIdx.x * C + wt] = dsum;
-    }
     // ---- d(gamma) partial of this CTA: TMEM -> dgamma_part[blockIdx] ----
     mbar_wait(dg_done, 0);
     tc_fence_after();
+    {   // cross-warp combination of the column sums through the (now idle) t buffer, in a fixed order
+      float* sc_t = reinterpret_cast<float*>(bn);
+      float* sc_d = sc_t + (G_WORKERS / 32) * C;
+      if (lane < C / 8) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          sc_t[w * C + lane * 8 + e] = tsum[e];
+          sc_d[w * C + lane * 8 + e] = dsum[e];
+        }
+      }
+      named_bar(4, G_WORKERS);
+      if (wt < C) {
+        float a = 0.f, b = 0.f;
+#pragma unroll
+        for (int k = 0; k < G_WORKERS / 32; ++k) { a += sc_t[k * C + wt]; b += sc_d[k * C + wt]; }
+        p.colsum_part[(int64_t)blockIdx.x * C + wt] = a;
+        p.dxsum_part[(int64_t)blockIdx.x * C + wt] = b;
+      }
+    }
     float* dst = p.dgamma_part + (int64_t)blockIdx.x * C * C;
     const uint32_t lane_off = (uint32_t)(q * 32) << 16;
 #pragma unroll 1
