@@ -46,6 +46,32 @@ def test_forward_and_dgrad(transposed, k, s, N, H, W, C):
     _cmp(out, ref)
 
 
+@pytest.mark.parametrize("transposed,N,H,W", [(False, 5, 128, 96), (True, 3, 56, 72), (False, 3, 130, 66)])
+def test_forward_large_grids_use_cta_pairs(transposed, N, H, W):
+    """>= 148 tiles: the cta_group::2 kernel (CTA pairs, half of the weight tile per CTA).  The odd tile counts
+    exercise the phantom tile at the end of a phase / of the grid; the SIMT engine is the checker."""
+    torch.manual_seed(4)
+    C = 192
+    spec = hp.ConvSpec(transposed, C, C, 5, 2)
+    x = torch.randn(N, H, W, C, device=DEV).to(torch.bfloat16)
+    w = (torch.randn(C, C, 5, 5, device=DEV) / (C * 25) ** 0.5)
+    b = torch.randn(C, device=DEV)
+    out, ref = _both(lambda: spec.forward(x, w, b, _lib.EPI_LINEAR, want_f32=True))
+    _cmp(out, ref)
+
+
+def test_forced_engine_variants_in_a_subprocess():
+    """HPC_FWD_PAIR=1 forces the CTA-pair kernel for every grid (also 1-2 tiles), HPC_FWD_KSPLIT=0 disables split-K:
+    both variants must agree with the SIMT checker on the whole forward/dgrad/epilogue test set."""
+    import os, subprocess, sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    for env in ({"HPC_FWD_PAIR": "1"}, {"HPC_FWD_PAIR": "0", "HPC_FWD_KSPLIT": "0"}):
+        r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(here, "test_gpu_umma.py"), "-x", "-q", "-k",
+                            "forward_and_dgrad or epilogues or large_grids"], env=dict(os.environ, **env),
+                           capture_output=True, text=True, timeout=900)
+        assert r.returncode == 0, (env, r.stdout[-2000:], r.stderr[-1000:])
+
+
 @pytest.mark.parametrize("epi", ["relu", "exp_clamp", "relu_mask", "sign_add"])
 def test_epilogues(epi):
     torch.manual_seed(1)
