@@ -153,6 +153,36 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
 // U[0,1) with 24 bits, like torch.rand for fp32 (multiples of 2^-24, never 1.0)
 __device__ __forceinline__ float u01_from_bits(uint32_t b) { return (float)(b >> 8) * (1.0f / 16777216.0f); }
 
+// four uniforms for flat element indices 4*i4 .. 4*i4+3 (the same values philox_uniform returns one by one)
+__device__ __forceinline__ void philox_uniform4(uint64_t seed, uint64_t offset, uint64_t i4, float* u) {
+  uint4 ctr = make_uint4((uint32_t)i4, (uint32_t)(i4 >> 32), (uint32_t)offset, (uint32_t)(offset >> 32));
+  uint2 key = make_uint2((uint32_t)seed, (uint32_t)(seed >> 32));
+  const uint4 r = philox4x32_10(ctr, key);
+  u[0] = u01_from_bits(r.x); u[1] = u01_from_bits(r.y); u[2] = u01_from_bits(r.z); u[3] = u01_from_bits(r.w);
+}
+// vector helpers for the element-wise kernels: 4 consecutive elements (index of the first = 4*i4)
+template <typename T> __device__ __forceinline__ void ld4_as_float(const T* p, size_t i4, float* f);
+template <> __device__ __forceinline__ void ld4_as_float<float>(const float* p, size_t i4, float* f) {
+  const float4 v = reinterpret_cast<const float4*>(p)[i4];
+  f[0] = v.x; f[1] = v.y; f[2] = v.z; f[3] = v.w;
+}
+template <> __device__ __forceinline__ void ld4_as_float<__nv_bfloat16>(const __nv_bfloat16* p, size_t i4, float* f) {
+  const uint2 v = reinterpret_cast<const uint2*>(p)[i4];
+  const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&v.x));
+  const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&v.y));
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y;
+}
+template <typename T> __device__ __forceinline__ void st4_from_float(T* p, size_t i4, const float* f);
+template <> __device__ __forceinline__ void st4_from_float<float>(float* p, size_t i4, const float* f) {
+  reinterpret_cast<float4*>(p)[i4] = make_float4(f[0], f[1], f[2], f[3]);
+}
+template <> __device__ __forceinline__ void st4_from_float<__nv_bfloat16>(__nv_bfloat16* p, size_t i4, const float* f) {
+  uint2 v;
+  *reinterpret_cast<__nv_bfloat162*>(&v.x) = __floats2bfloat162_rn(f[0], f[1]);
+  *reinterpret_cast<__nv_bfloat162*>(&v.y) = __floats2bfloat162_rn(f[2], f[3]);
+  reinterpret_cast<uint2*>(p)[i4] = v;
+}
+
 // one uniform for flat element index i
 __device__ __forceinline__ float philox_uniform(uint64_t seed, uint64_t offset, uint64_t i) {
   uint4 ctr = make_uint4((uint32_t)(i >> 2), (uint32_t)(i >> 34), (uint32_t)offset, (uint32_t)(offset >> 32));

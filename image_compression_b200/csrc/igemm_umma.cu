@@ -717,33 +717,6 @@ wgrad_reduce_kernel(const float* __restrict__ ws, int nsplits, int64_t n, float 
   }
 }
 
-// Reference-layout variant for the usual case "all K taps present, taps innermost" (out_stride_c == ntaps): a block
-// owns one row r and 64 columns, sums the splits with coalesced reads (64 consecutive c per tap), transposes the
-// [tap][c] tile through shared memory and writes the 64*K contiguous floats of dst[r][c0..c0+63][0..K-1] coalesced.
-__global__ void __launch_bounds__(256)
-wgrad_reduce_unpack_kernel(const float* __restrict__ ws, int nsplits, int ntaps, float scale, float* __restrict__ gw,
-                           const __grid_constant__ WgOut o) {
-  __shared__ float tile[HPC_MAX_TAPS][65];
-  __shared__ int inv[HPC_MAX_TAPS];
-  const int r = blockIdx.x, c0 = blockIdx.y * 64;
-  const int64_t n = (int64_t)ntaps * o.R * o.Cc;
-  if (threadIdx.x < ntaps) inv[o.tap_src[threadIdx.x]] = threadIdx.x;
-  for (int idx = threadIdx.x; idx < ntaps * 64; idx += 256) {
-    const int t = idx >> 6, cl = idx & 63;
-    const float* src = ws + ((int64_t)t * o.R + r) * o.Cc + c0 + cl;
-    float a = 0.f;
-    for (int s = 0; s < nsplits; ++s) a += __ldcs(src + (int64_t)s * n);
-    tile[t][cl] = a * scale;
-  }
-  __syncthreads();
-  float* dst = gw + r * o.sr + (int64_t)c0 * ntaps;
-  for (int i = threadIdx.x; i < ntaps * 64; i += 256) {
-    const int cl = i / ntaps, pos = i - cl * ntaps;
-    const float v = tile[inv[pos]][cl];
-    dst[i] = o.accumulate ? dst[i] + v : v;
-  }
-}
-
 static int wgrad_plan(const hpc_igemm_wgrad_params* p, WgKParams* kp) {
   memset(kp, 0, sizeof(*kp));
   kp->N = p->N; kp->GH = p->GH; kp->GW = p->GW; kp->R = p->R; kp->HH = p->HH; kp->HW = p->HW; kp->Cc = p->Cc;
@@ -842,20 +815,6 @@ int hpc_igemm_wgrad_umma(const hpc_igemm_wgrad_params* p, hpc_stream_t stream) {
   o.mode = p->out_mode; o.accumulate = p->out_accumulate; o.R = p->R; o.Cc = p->Cc;
   o.sr = p->out_stride_r; o.sc = p->out_stride_c;
   for (int t = 0; t < local.ntaps && t < HPC_MAX_TAPS; ++t) o.tap_src[t] = p->out_tap_src[t];
-  if (o.mode == 1 && o.sc == local.ntaps && p->Cc % 64 == 0 && local.ntaps <= HPC_MAX_TAPS) {
-    bool perm = true;                         // tap_src must be a permutation of 0..ntaps-1
-    unsigned long long seen = 0;
-    for (int t = 0; t < local.ntaps; ++t) {
-      if (o.tap_src[t] < 0 || o.tap_src[t] >= local.ntaps || (seen >> o.tap_src[t] & 1)) perm = false;
-      else seen |= 1ull << o.tap_src[t];
-    }
-    if (perm) {
-      wgrad_reduce_unpack_kernel<<<dim3(p->R, p->Cc / 64), 256, 0, st>>>(local.ws, local.nsplits, local.ntaps, p->scale,
-                                                                        p->gw_f32, o);
-      HPC_LAUNCH_CHECK();
-      return HPC_OK;
-    }
-  }
   wgrad_reduce_kernel<<<(int)((n + 127) / 128), 256, 0, st>>>(local.ws, local.nsplits, n, p->scale, p->gw_f32, o);
   HPC_LAUNCH_CHECK();
   return HPC_OK;
