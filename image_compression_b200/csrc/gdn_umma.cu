@@ -758,6 +758,315 @@ gdn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_cons
   if (warp == 1) tmem_dealloc(tmem_base, TCOLS);
 }
 
+// ---------------------------------------------------------------------------------------
+// Dual-pipeline form of the fused backward.  With gamma^T resident there is shared memory for ONE set of 128-row
+// tile buffers, so in gdn_bwd_fused_kernel the loads of tile i+1 wait for the tail of tile i (ncu: a third of the
+// worker time is spent on the load barrier).  Here the same three 48 KB buffers are split by ROWS into two
+// independent 64-row pipelines (set 0 = rows 0..63, set 1 = rows 64..127 of every [128 x 64] operand chunk), each with
+// its own barriers, its own half of the worker warps (set s = the warps of TMEM lane quarters 2s, 2s+1) and its own
+// half-tiles.  While one set waits for its loads the other computes.  The a = t . gamma UMMA still has the M = 128
+// footprint over both sets (the rows of the other set are whatever is there) but is issued with the
+// disable-output-lane mask of the other half, so the two sets share one accumulator; the d(gamma) UMMAs contract over
+// the 64 rows of their own set only (K = 64).  TMEM budget unchanged (512 columns for C = 192).
+// ---------------------------------------------------------------------------------------
+template <int C>
+__global__ void __launch_bounds__(G_THREADS, 1)
+gdn_bwd_dual_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_constant__ CUtensorMap tmX,
+                    const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmDx,
+                    const __grid_constant__ CUtensorMap tmG, const __grid_constant__ GdnFusedParams p) {
+  static_assert(C == 128 || C == 192, "fused d(gamma): C in {128, 192}");
+  using Cfg = GCfg<C>;
+  constexpr int KC = Cfg::KC;
+  constexpr int REM = C - 128;
+  constexpr int COL_DGA = C, COL_DGB = 2 * C;
+  constexpr int TCOLS = C == 128 ? 256 : 512;
+  constexpr int HROWS = 64, HBYTES = HROWS * 128;          // rows per half-tile, bytes of a half chunk
+  constexpr int GW = G_WORKERS / 2;                        // worker threads per set
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* gam = smem;                           // gamma^T as the K-major B operand
+  uint8_t* bg = gam + Cfg::GAMMA;                // g   -> u = g r -> dx
+  uint8_t* bx = bg + Cfg::TILE;                  // x   -> x^2
+  uint8_t* bn = bx + Cfg::TILE;                  // r   -> t
+  uint64_t* bars = reinterpret_cast<uint64_t*>(bn + Cfg::TILE + 1024);
+  uint64_t* g_full = bars;
+  uint64_t* in_full = bars + 1;     // [2] TMA: g, x, r half-tiles landed
+  uint64_t* in_empty = bars + 3;    // [2] KC store lanes + d(gamma) MMA commit + 8 worker warps
+  uint64_t* a_full = bars + 5;      // [2] workers of the set: t (and u) written
+  uint64_t* tfull = bars + 7;       // [2]
+  uint64_t* out_full = bars + 9;    // [2] workers of the set: dx, x^2 written
+  uint64_t* dg_done = bars + 11;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nh = (int)((p.P + HROWS - 1) / HROWS);                              // half-tiles in the tensor
+  const int mine = (int)blockIdx.x < nh ? (nh - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;   // ... of this CTA
+  // half-tile k of this CTA (rows (blockIdx.x + k gridDim.x) * 64 ...) belongs to set k & 1
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmGr); prefetch_tmap(&tmX); prefetch_tmap(&tmR); prefetch_tmap(&tmDx); prefetch_tmap(&tmG);
+    mbar_init(g_full, 1); mbar_init(dg_done, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&in_full[s], 1); mbar_init(&in_empty[s], KC + 1 + GW / 32);
+      mbar_init(&a_full[s], GW); mbar_init(&tfull[s], 1); mbar_init(&out_full[s], GW);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, TCOLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // lane l: set l / 3KC, tensor (l % 3KC) / KC, chunk l % KC.  The lanes run independently (a complete_tx may
+    // precede the expect_tx of its phase: the phase cannot complete before the expecting arrival).
+    if (lane == 0) {
+      mbar_arrive_expect_tx(g_full, Cfg::GAMMA);
+      for (int c = 0; c < KC; ++c) tma_load_2d(gam + c * (C * 128), &tmG, g_full, c * 64, 0);
+    }
+    if (lane < 6 * KC) {
+      const int s = lane / (3 * KC), rem = lane % (3 * KC), which = rem / KC, c = rem % KC;
+      uint8_t* dst = (which == 0 ? bg : (which == 1 ? bx : bn)) + c * G_CHUNK + s * HBYTES;
+      const CUtensorMap* tm = which == 0 ? &tmGr : (which == 1 ? &tmX : &tmR);
+      for (int k = s, j = 0; k < mine; k += 2, ++j) {
+        const int h = blockIdx.x + k * gridDim.x;
+        mbar_wait(&in_empty[s], (j & 1) ^ 1);
+        if (rem == 0) mbar_arrive_expect_tx(&in_full[s], 3 * Cfg::TILE / 2);
+        tma_load_2d(dst, tm, &in_full[s], c * 64, h * HROWS);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, C, 0, 0);
+      constexpr uint32_t idesc_dga = make_idesc_bf16(128, C, 1, 1);     // both operands MN-major
+      constexpr uint32_t idesc_dgb = make_idesc_bf16(128, 64, 1, 1);
+      mbar_wait(g_full, 0);
+      const uint32_t t_addr = smem_u32(bn), sq_addr = smem_u32(bx), b_addr = smem_u32(gam);
+      int nset[2] = {(mine + 1) / 2, mine / 2};
+      int jA[2] = {0, 0}, jD[2] = {0, 0};
+      uint32_t dg_started = 0, spins = 0;
+      while (jD[0] < nset[0] || jD[1] < nset[1]) {
+        bool progressed = false;
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          if (jA[s] < nset[s] && jA[s] == jD[s]) {
+            if (mbar_try_wait(&a_full[s], jA[s] & 1)) {
+              tc_fence_after();
+              const uint32_t keep = s ? 0u : 0xFFFFFFFFu;   // disable the OTHER set's lanes
+#pragma unroll
+              for (int k = 0; k < C / 16; ++k)
+                mma_bf16_ss_masked(tmem_base, make_smem_desc_sw128(t_addr + (k >> 2) * G_CHUNK + (k & 3) * 32, 16, 1024),
+                                   make_smem_desc_sw128(b_addr + (k >> 2) * (C * 128) + (k & 3) * 32, 16, 1024), idesc,
+                                   k != 0, ~keep, ~keep, keep, keep);
+              mma_commit(&tfull[s]);
+              ++jA[s];
+              progressed = true;
+            }
+          } else if (jD[s] < jA[s]) {
+            if (mbar_try_wait(&out_full[s], jD[s] & 1)) {
+              tc_fence_after();
+#pragma unroll
+              for (int ks = 0; ks < HROWS / 16; ++ks) {     // K = the 64 rows of this set
+                const uint32_t acc = dg_started | (uint32_t)ks;
+                const uint32_t ro = s * HBYTES + ks * 2048;
+                const uint64_t td = make_smem_desc_sw128(t_addr + ro, G_CHUNK, 1024);
+                const uint64_t sd = make_smem_desc_sw128(sq_addr + ro, G_CHUNK, 1024);
+                mma_bf16_ss(tmem_base + COL_DGA, td, sd, idesc_dga, acc);
+                if (REM) {
+                  const uint64_t tr = make_smem_desc_sw128(t_addr + 2 * G_CHUNK + ro, G_CHUNK, 1024);
+                  const uint64_t s1 = make_smem_desc_sw128(sq_addr + G_CHUNK + ro, G_CHUNK, 1024);
+                  mma_bf16_ss(tmem_base + COL_DGB, sd, tr, idesc_dgb, acc);
+                  mma_bf16_ss(tmem_base + COL_DGB + 64, s1, tr, idesc_dgb, acc);
+                }
+              }
+              dg_started = 1;
+              mma_commit(&in_empty[s]);
+              ++jD[s];
+              progressed = true;
+            }
+          }
+        }
+        if (progressed) spins = 0;
+        else if (++spins > (1u << 26)) { printf("hpcodec: gdn_bwd_dual MMA loop timed out (block %d)\n", blockIdx.x); __trap(); }
+      }
+      mma_commit(dg_done);
+    }
+  } else if (warp == 2) {
+    if (lane < 2 * KC) {            // lane: set lane / KC, chunk lane % KC; every lane arrives for itself
+      const int s = lane / KC, c = lane % KC;
+      for (int k = s, j = 0; k < mine; k += 2, ++j) {
+        const int h = blockIdx.x + k * gridDim.x;
+        mbar_wait(&out_full[s], j & 1);
+        tma_store_2d(&tmDx, bg + c * G_CHUNK + s * HBYTES, c * 64, h * HROWS);
+        bulk_commit();
+        bulk_wait_read0();
+        mbar_arrive(&in_empty[s]);
+      }
+      bulk_wait0();
+    }
+  } else {
+    const int w = warp - 3;
+    const int q = warp & 3, half = w >> 2;        // TMEM lane quarter, channel quarter
+    const int s = q >> 1;                         // set of this warp
+    const int row = q * 32 + lane;                // row of the 128-row operand layout == TMEM lane
+    const int gidx = (q & 1) * 4 + half;          // warp index within the set (0..7): owns rows s*64 + 8 gidx .. +7 of the sums
+    const int wt = threadIdx.x - 96;
+    constexpr int UH = C / 32;
+    float tsum[8], dsum[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) tsum[e] = dsum[e] = 0.f;
+    for (int k = s, j = 0; k < mine; k += 2, ++j) {
+      const int h = blockIdx.x + k * gridDim.x;
+      mbar_wait(&in_full[s], j & 1);
+      constexpr int UB = UH % 4 == 0 ? 4 : (UH % 3 == 0 ? 3 : (UH % 2 == 0 ? 2 : 1));
+#pragma unroll 1
+      for (int ub = 0; ub < UH; ub += UB) {
+        uint4 rg[UB], rx[UB], rr[UB];
+#pragma unroll
+        for (int jj = 0; jj < UB; ++jj) {
+          const uint32_t o = unit_off(row, half * UH + ub + jj);
+          rg[jj] = *reinterpret_cast<const uint4*>(bg + o);
+          rx[jj] = *reinterpret_cast<const uint4*>(bx + o);
+          rr[jj] = *reinterpret_cast<const uint4*>(bn + o);
+        }
+#pragma unroll
+        for (int jj = 0; jj < UB; ++jj) {
+          const uint32_t o = unit_off(row, half * UH + ub + jj);
+          float g[8], x[8], r[8], t[8], u[8];
+          unpack8(rg[jj], g);
+          unpack8(rx[jj], x);
+          unpack8(rr[jj], r);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            t[e] = g[e] * x[e] * (p.inverse ? r[e] : r[e] * r[e] * r[e]);
+            u[e] = p.inverse ? g[e] / r[e] : g[e] * r[e];
+          }
+          *reinterpret_cast<uint4*>(bn + o) = pack8(t);
+          *reinterpret_cast<uint4*>(bg + o) = pack8(u);
+        }
+      }
+      fence_proxy_async();
+      tc_fence_before();            // (the accumulator reads of the previous half-tile precede this arrival)
+      mbar_arrive(&a_full[s]);
+      // d(beta): column sums of the bf16 t half-tile, while the MMA runs (rows past P are zero: TMA zero fill)
+      named_bar(4 + s, GW);
+      if (lane < C / 8) {
+#pragma unroll
+        for (int rr2 = 0; rr2 < 8; ++rr2) {
+          float f[8];
+          unpack8(*reinterpret_cast<const uint4*>(bn + unit_off(s * HROWS + gidx * 8 + rr2, lane)), f);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) tsum[e] += f[e];
+        }
+      }
+      mbar_wait(&tfull[s], j & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + half * (C / 4);
+#pragma unroll 1
+      for (int gb = 0; gb < C / 64; ++gb) {
+        float v[16];
+        uint4 ur[2], xr[2];
+        tmem_ld16(taddr + gb * 16, v);
+        const int c0 = half * (C / 4) + gb * 16;
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          const uint32_t o = unit_off(row, (c0 >> 3) + hh);
+          ur[hh] = *reinterpret_cast<const uint4*>(bg + o);
+          xr[hh] = *reinterpret_cast<const uint4*>(bx + o);
+        }
+        tmem_ld_wait();
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          const uint32_t o = unit_off(row, (c0 >> 3) + hh);
+          float u[8], x[8], d[8];
+          unpack8(ur[hh], u);
+          unpack8(xr[hh], x);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            d[e] = p.inverse ? u[e] + x[e] * v[hh * 8 + e] : u[e] - x[e] * v[hh * 8 + e];
+            x[e] *= x[e];
+          }
+          *reinterpret_cast<uint4*>(bg + o) = pack8(d);
+          *reinterpret_cast<uint4*>(bx + o) = pack8(x);
+        }
+      }
+      tc_fence_before();
+      fence_proxy_async();
+      mbar_arrive(&out_full[s]);
+      // d(bias) of the producer layer: column sums of the bf16 dx half-tile, while it is being stored.  Rows past P
+      // are skipped: the inverse form divides the zero-filled g by the zero-filled r there.
+      named_bar(4 + s, GW);
+      if (lane < C / 8) {
+        const int64_t left = p.P - (int64_t)h * HROWS;
+        const int nrows = left < HROWS ? (int)left : HROWS;
+#pragma unroll
+        for (int rr2 = 0; rr2 < 8; ++rr2) {
+          if (gidx * 8 + rr2 < nrows) {
+            float f[8];
+            unpack8(*reinterpret_cast<const uint4*>(bg + unit_off(s * HROWS + gidx * 8 + rr2, lane)), f);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) dsum[e] += f[e];
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&in_empty[s]);
+    }
+    // ---- d(gamma) partial of this CTA: TMEM -> dgamma_part[blockIdx] ----
+    mbar_wait(dg_done, 0);
+    tc_fence_after();
+    {   // cross-warp combination of the column sums through the (now idle) t buffer, in a fixed order
+      float* sc_t = reinterpret_cast<float*>(bn);
+      float* sc_d = sc_t + (G_WORKERS / 32) * C;
+      const int widx = s * 8 + gidx;
+      if (lane < C / 8) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          sc_t[widx * C + lane * 8 + e] = tsum[e];
+          sc_d[widx * C + lane * 8 + e] = dsum[e];
+        }
+      }
+      named_bar(6, G_WORKERS);
+      if (wt < C) {
+        float a = 0.f, b = 0.f;
+#pragma unroll
+        for (int k = 0; k < G_WORKERS / 32; ++k) { a += sc_t[k * C + wt]; b += sc_d[k * C + wt]; }
+        p.colsum_part[(int64_t)blockIdx.x * C + wt] = a;
+        p.dxsum_part[(int64_t)blockIdx.x * C + wt] = b;
+      }
+    }
+    float* dst = p.dgamma_part + (int64_t)blockIdx.x * C * C;
+    const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+    const bool any = mine > 0;                     // a CTA without work never issued an MMA: its partial is zero
+#pragma unroll 1
+    for (int c0 = 0; c0 < C / 4; c0 += 16) {
+      float v[16];
+      tmem_ld16(tmem_base + lane_off + COL_DGA + half * (C / 4) + c0, v);
+      tmem_ld_wait();
+      float4* d4 = reinterpret_cast<float4*>(dst + (int64_t)row * C + half * (C / 4) + c0);
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk)
+        d4[kk] = any ? make_float4(v[4 * kk], v[4 * kk + 1], v[4 * kk + 2], v[4 * kk + 3]) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    if (REM) {
+      float v[16];
+      tmem_ld16(tmem_base + lane_off + COL_DGB + half * 16, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int kk = 0; kk < 16; ++kk) dst[(int64_t)(128 + half * 16 + kk) * C + row] = any ? v[kk] : 0.f;
+      if (q >= 2) {
+        tmem_ld16(tmem_base + lane_off + COL_DGB + 64 + half * 16, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int kk = 0; kk < 16; ++kk) dst[(int64_t)(128 + half * 16 + kk) * C + 64 + row] = any ? v[kk] : 0.f;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, TCOLS);
+}
+
 // One launch finishes the backward of a GDN layer from the per-CTA partials, in a fixed summation order:
 //   blocks [0, ng)        d(gamma)[i]   = R(gamma_param[i], sgn * sum_s dgamma_part[s][i])     (128 elements per block)
 //   blocks [ng, ng+nc)    d(beta)[c]    = R(beta_param[c],  sgn * sum_s colsum_part[s][c])
@@ -898,7 +1207,7 @@ int hpc_gdn_bwd_umma(const void* g_bf16, const void* x_bf16, const void* rnorm_b
 
 size_t hpc_gdn_bwd_fused_umma_workspace_bytes(int64_t P, int C) {
   if (C != 128 && C != 192) return 0;
-  return (size_t)hpc_gdn_bwd_umma_parts(P) * (C * C + 2 * C) * sizeof(float);
+  return (size_t)gdn_grid((int)((P + 63) / 64)) * (C * C + 2 * C) * sizeof(float);   // >= the single-pipeline grid
 }
 
 int hpc_gdn_bwd_fused_umma(const void* g_bf16, const void* x_bf16, const void* rnorm_bf16, const void* gammaT_bf16,
@@ -912,35 +1221,38 @@ int hpc_gdn_bwd_fused_umma(const void* g_bf16, const void* x_bf16, const void* r
   HPC_REQUIRE(workspace_bytes >= hpc_gdn_bwd_fused_umma_workspace_bytes(P, C), HPC_ERR_BAD_SHAPE,
               "hpc_gdn_bwd_fused_umma: workspace too small (%zu)", workspace_bytes);
   HPC_REQUIRE(!dbias || hpc_aligned16(dbias), HPC_ERR_BAD_ALIGNMENT, "hpc_gdn_bwd_fused_umma: dbias must be 16B aligned");
-  const int grid = gdn_grid((int)((P + 127) / 128));
+  static int dual = -1;                          // HPC_GDN_BWD_DUAL=0 selects the single-pipeline kernel (A/B measurements)
+  if (dual < 0) { const char* e = getenv("HPC_GDN_BWD_DUAL"); dual = e ? (atoi(e) ? 1 : 0) : 1; }
+  const int grid = dual ? gdn_grid((int)((P + 63) / 64)) : gdn_grid((int)((P + 127) / 128));
   GdnFusedParams kp;
   kp.dgamma_part = (float*)workspace;
   kp.colsum_part = kp.dgamma_part + (size_t)grid * C * C;
   kp.dxsum_part = kp.colsum_part + (size_t)grid * C;
   kp.tiles = (int)((P + 127) / 128); kp.inverse = inverse; kp.P = P;
+  const int box_rows = dual ? 64 : 128;
   CUtensorMap tmGr, tmX, tmR, tmDx, tmG;
-  if ((rc = make_rows_tmap(&tmGr, g_bf16, P, C, 128))) return rc;
-  if ((rc = make_rows_tmap(&tmX, x_bf16, P, C, 128))) return rc;
-  if ((rc = make_rows_tmap(&tmR, rnorm_bf16, P, C, 128))) return rc;
-  if ((rc = make_rows_tmap(&tmDx, dx_bf16, P, C, 128))) return rc;
+  if ((rc = make_rows_tmap(&tmGr, g_bf16, P, C, box_rows))) return rc;
+  if ((rc = make_rows_tmap(&tmX, x_bf16, P, C, box_rows))) return rc;
+  if ((rc = make_rows_tmap(&tmR, rnorm_bf16, P, C, box_rows))) return rc;
+  if ((rc = make_rows_tmap(&tmDx, dx_bf16, P, C, box_rows))) return rc;
   if ((rc = make_rows_tmap(&tmG, gammaT_bf16, C, C, C))) return rc;
   HpcProfScope prof(HPC_PROF_GDN, (double)P * C * 2 * 4, stream);
   auto st = (cudaStream_t)stream;
-  if (C == 128) {
-    static bool attr_set = false;
-    if (!attr_set) {
-      HPC_CUDA(cudaFuncSetAttribute(gdn_bwd_fused_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, GCfg<128>::SMEM));
-      attr_set = true;
-    }
-    gdn_bwd_fused_kernel<128><<<grid, G_THREADS, GCfg<128>::SMEM, st>>>(tmGr, tmX, tmR, tmDx, tmG, kp);
+#define GDN_BWD_LAUNCH(KERNEL, CC)                                                                              \
+  do {                                                                                                          \
+    static bool attr_set = false;                                                                               \
+    if (!attr_set) {                                                                                            \
+      HPC_CUDA(cudaFuncSetAttribute(KERNEL<CC>, cudaFuncAttributeMaxDynamicSharedMemorySize, GCfg<CC>::SMEM));  \
+      attr_set = true;                                                                                          \
+    }                                                                                                           \
+    KERNEL<CC><<<grid, G_THREADS, GCfg<CC>::SMEM, st>>>(tmGr, tmX, tmR, tmDx, tmG, kp);                         \
+  } while (0)
+  if (dual) {
+    if (C == 128) GDN_BWD_LAUNCH(gdn_bwd_dual_kernel, 128); else GDN_BWD_LAUNCH(gdn_bwd_dual_kernel, 192);
   } else {
-    static bool attr_set = false;
-    if (!attr_set) {
-      HPC_CUDA(cudaFuncSetAttribute(gdn_bwd_fused_kernel<192>, cudaFuncAttributeMaxDynamicSharedMemorySize, GCfg<192>::SMEM));
-      attr_set = true;
-    }
-    gdn_bwd_fused_kernel<192><<<grid, G_THREADS, GCfg<192>::SMEM, st>>>(tmGr, tmX, tmR, tmDx, tmG, kp);
+    if (C == 128) GDN_BWD_LAUNCH(gdn_bwd_fused_kernel, 128); else GDN_BWD_LAUNCH(gdn_bwd_fused_kernel, 192);
   }
+#undef GDN_BWD_LAUNCH
   HPC_LAUNCH_CHECK();
   GdnFinish f;
   f.dgamma_part = kp.dgamma_part; f.colsum_part = kp.colsum_part; f.dxsum_part = kp.dxsum_part;

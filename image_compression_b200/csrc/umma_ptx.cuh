@@ -106,6 +106,17 @@ __device__ __forceinline__ void mma_bf16_ss(uint32_t tmem_d, uint64_t adesc, uin
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// same with a disable-output-lane mask: TMEM lanes whose bit is set in m[lane / 32] keep their old contents (lets two
+// independent 64-row pipelines share one M = 128 MMA footprint: each updates only its own half of the lanes)
+__device__ __forceinline__ void mma_bf16_ss_masked(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                                   uint32_t accumulate, uint32_t m0, uint32_t m1, uint32_t m2,
+                                                   uint32_t m3) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(m0), "r"(m1), "r"(m2), "r"(m3)
+      : "memory");
+}
 // same with the A operand in TMEM (K-major only): row m of A in lane m, 16-bit elements packed two per 32-bit
 // column in K order, so one K = 16 step spans 8 columns
 __device__ __forceinline__ void mma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
