@@ -29,6 +29,7 @@ struct FwdKParams {
   int N, GH, GW, is, os, OH, OW, Co, Ci;
   int tw, th, nb;            // tile shape, tw*th*nb == 128
   int tiles_w, tiles_h, tiles_n, tiles_per_phase, total_tiles;
+  int interleave;           // see work_item()
   int nphases;
   hpc_igemm_phase phase[HPC_MAX_PHASES];
   int dh[HPC_MAX_TAPS], dw[HPC_MAX_TAPS];
@@ -54,13 +55,31 @@ struct FwdCfg {
 // consecutive tiles of one phase (so both CTAs run the same tap sequence) and `rank` picks the tile; a phase with an
 // odd tile count ends in a phantom tile whose batch origin n0 >= N (TMA zero fill, no rows stored).
 template <int NCTA>
-__device__ __forceinline__ void tile_coords(const FwdKParams& p, int w, int rank, int& ph, int& n0, int& i0, int& j0) {
-  const int per = NCTA == 1 ? p.tiles_per_phase : (p.tiles_per_phase + 1) / 2;
-  ph = w / per;
-  int r = (w - ph * per) * NCTA + rank;
+__device__ __forceinline__ void tile_coords(const FwdKParams& p, int ph, int idx, int rank, int& n0, int& i0, int& j0) {
+  int r = idx * NCTA + rank;
   const int tj = r % p.tiles_w; r /= p.tiles_w;
   const int ti = r % p.tiles_h; r /= p.tiles_h;
   n0 = r * p.nb; i0 = ti * p.th; j0 = tj * p.tw;
+}
+
+// Work item w of a worker (CTA or CTA pair) -> (phase, tile of the phase).  Phase-major by default.  With
+// p.interleave (multi-phase = transposed-conv grids of at least one tile per worker and phase) a worker runs the
+// phases of ONE spatial tile back to back: the 9/6/6/4-tap phases then mix in time on every SM, so the epilogue of a
+// short (4-tap) tile hides under the next long one instead of the whole grid becoming epilogue/store-bound for the
+// last phases, and the input pixels the four phases share are read while they are hot.  Returns false for the
+// padding items of the last round (same answer in every warp role, so the pipelines stay in step).
+__device__ __forceinline__ bool work_item(const FwdKParams& p, int w, int worker, int nworkers, int per_phase,
+                                          int ksplit, int& ph, int& idx) {
+  if (p.interleave) {
+    const int r = w / nworkers;
+    ph = r % p.nphases;
+    idx = worker + (r / p.nphases) * nworkers;
+    return idx < per_phase;
+  }
+  const int t = w / ksplit;
+  ph = t / per_phase;
+  idx = t - ph * per_phase;
+  return true;
 }
 
 // epilogue for 8 consecutive channels of one output pixel (bf16 lp tensors)
@@ -186,7 +205,8 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
   const int worker = blockIdx.x / NCTA, nworkers = gridDim.x / NCTA;       // CTA (or CTA pair) index
   const int per_phase = NCTA == 1 ? p.tiles_per_phase : (p.tiles_per_phase + 1) / 2;
   const int ksplit = NCTA == 1 ? p.ksplit : 1;              // split-K for grids of a few tiles (single-CTA kernel only)
-  const int total_work = per_phase * p.nphases * ksplit;
+  const int total_work = p.interleave ? (per_phase + nworkers - 1) / nworkers * nworkers * p.nphases
+                                      : per_phase * p.nphases * ksplit;
   if (p.epi.bias)
     for (int i = threadIdx.x; i < BLOCK_N; i += FW_THREADS) bias_s[i] = p.epi.bias[i];
 
@@ -212,8 +232,9 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
     if (lane < 2) {
       int stage = 0; uint32_t phase = 0;
       for (int w = worker; w < total_work; w += nworkers) {
-        int ph, n0, i0, j0;
-        tile_coords<NCTA>(p, w / ksplit, rank, ph, n0, i0, j0);
+        int ph, idx, n0, i0, j0;
+        if (!work_item(p, w, worker, nworkers, per_phase, ksplit, ph, idx)) continue;
+        tile_coords<NCTA>(p, ph, idx, rank, n0, i0, j0);
         const hpc_igemm_phase P = p.phase[ph];
         const int ksteps = P.ntaps * p.kchunks, sp = w % ksplit;
         const int ks0 = ksteps * sp / ksplit, ks1 = ksteps * (sp + 1) / ksplit;
@@ -251,8 +272,8 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0;
       for (int w = worker; w < total_work; w += nworkers) {
-        int ph, n0, i0, j0;
-        tile_coords<NCTA>(p, w / ksplit, 0, ph, n0, i0, j0);
+        int ph, idx;
+        if (!work_item(p, w, worker, nworkers, per_phase, ksplit, ph, idx)) continue;
         const int kall = p.phase[ph].ntaps * p.kchunks, sp = w % ksplit;
         const int ksteps = kall * (sp + 1) / ksplit - kall * sp / ksplit;
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);     // epilogue(s) have drained this accumulator
@@ -290,8 +311,9 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
     if (epi.bias) epi.bias = bias_s;        // broadcast shared-memory reads instead of 48 global loads per tile
     int acc = 0; uint32_t acc_phase = 0;
     for (int w = worker; w < total_work; w += nworkers) {
-      int ph, n0, i0, j0;
-      tile_coords<NCTA>(p, w / ksplit, rank, ph, n0, i0, j0);
+      int ph, idx, n0, i0, j0;
+      if (!work_item(p, w, worker, nworkers, per_phase, ksplit, ph, idx)) continue;
+      tile_coords<NCTA>(p, ph, idx, rank, n0, i0, j0);
       const hpc_igemm_phase P = p.phase[ph];
       const int jl = row % p.tw, il = (row / p.tw) % p.th, nl = row / (p.tw * p.th);
       const int n = n0 + nl, i = i0 + il, j = j0 + jl;
@@ -489,6 +511,17 @@ int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
     if (ks > 1 && p->workspace && p->workspace_bytes >= need && hpc_aligned16(p->workspace)) {
       kp.ksplit = ks; kp.ws = (float*)p->workspace; kp.out_elems = (int64_t)p->N * p->OH * p->OW * p->Co;
     }
+  }
+  {
+    static int mode = -1;                        // HPC_FWD_INTERLEAVE=0: phase-major tile order everywhere (A/B measurements)
+    if (mode < 0) { const char* e = getenv("HPC_FWD_INTERLEAVE"); mode = e ? atoi(e) : 1; }
+    const int per = pair ? (kp.tiles_per_phase + 1) / 2 : kp.tiles_per_phase;
+    const int workers = pair ? hpc_num_sms() / 2 : hpc_num_sms();
+    // whole rounds of (tile x all phases) per worker: only where that padding costs < 4 % (measured: 64x64 -> 128x128
+    // transposed conv 463 -> 444 us, but 32x32 -> 64x64 with 3.46 rounds 120 -> 130 us)
+    const int rounds = (per + workers - 1) / workers;
+    kp.interleave = mode && kp.nphases > 1 && kp.ksplit == 1 && per >= workers &&
+                    (int64_t)rounds * workers * 100 <= (int64_t)per * 104;
   }
   CUtensorMap tmA, tmB;
   {

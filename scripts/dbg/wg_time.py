@@ -12,7 +12,7 @@ def t(fn, n=10):
     for _ in range(n): fn()
     e1.record(); torch.cuda.synchronize()
     return e0.elapsed_time(e1) / n * 1e3
-for (N, H, W, k, s, tr) in ((64, 128, 128, 5, 2, False), (64, 64, 64, 5, 2, False), (64, 32, 32, 5, 2, False), (64, 16, 16, 3, 1, False), (64, 16, 16, 5, 2, False), (64, 8, 8, 5, 2, False), (64, 64, 64, 5, 2, True)):
+for (N, H, W, k, s, tr) in ((64, 128, 128, 5, 2, False), (64, 64, 64, 5, 2, False), (64, 32, 32, 5, 2, False), (64, 16, 16, 3, 1, False), (64, 16, 16, 5, 2, False), (64, 8, 8, 5, 2, False), (64, 64, 64, 5, 2, True), (64, 32, 32, 5, 2, True), (64, 16, 16, 5, 2, True)):
     spec = hp.ConvSpec(tr, C, C, k, s)
     OH, OW = spec.out_hw(H, W)
     x = torch.randn(N, H, W, C, device="cuda").to(torch.bfloat16)

@@ -60,12 +60,30 @@ def test_forward_large_grids_use_cta_pairs(transposed, N, H, W):
     _cmp(out, ref)
 
 
+@pytest.mark.parametrize("N,H,W", [(37, 32, 32), (29, 40, 32)])
+def test_transposed_grids_interleave_phases(N, H, W):
+    """Multi-phase grids with whole rounds of (tile x 4 phases) per CTA pair run phase-interleaved (work_item() in
+    igemm_umma.cu): 148 pairs per phase = 2 exact rounds, and 145 pairs = 2 rounds with 3 padding items per phase.
+    Forward of the transposed conv and dgrad of the strided conv (the two multi-phase callers)."""
+    torch.manual_seed(6)
+    C = 192
+    w = (torch.randn(C, C, 5, 5, device=DEV) / (C * 25) ** 0.5)
+    b = torch.randn(C, device=DEV)
+    x = torch.randn(N, H, W, C, device=DEV).to(torch.bfloat16)
+    spec = hp.ConvSpec(True, C, C, 5, 2)
+    out, ref = _both(lambda: spec.forward(x, w, b, _lib.EPI_LINEAR, want_f32=True))
+    _cmp(out, ref)
+    spec = hp.ConvSpec(False, C, C, 5, 2)
+    out, ref = _both(lambda: spec.dgrad(x, w, (2 * H, 2 * W), want_f32=True))
+    _cmp(out, ref)
+
+
 def test_forced_engine_variants_in_a_subprocess():
     """HPC_FWD_PAIR=1 forces the CTA-pair kernel for every grid (also 1-2 tiles), HPC_FWD_KSPLIT=0 disables split-K:
     both variants must agree with the SIMT checker on the whole forward/dgrad/epilogue test set."""
     import os, subprocess, sys
     here = os.path.dirname(os.path.abspath(__file__))
-    for env in ({"HPC_FWD_PAIR": "1"}, {"HPC_FWD_PAIR": "0", "HPC_FWD_KSPLIT": "0"}):
+    for env in ({"HPC_FWD_PAIR": "1"}, {"HPC_FWD_PAIR": "0", "HPC_FWD_KSPLIT": "0", "HPC_FWD_INTERLEAVE": "0"}):
         r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(here, "test_gpu_umma.py"), "-x", "-q", "-k",
                             "forward_and_dgrad or epilogues or large_grids"], env=dict(os.environ, **env),
                            capture_output=True, text=True, timeout=900)
