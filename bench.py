@@ -239,7 +239,7 @@ def run_reference(args):
         "e2e": {"value": r["value"], "unit": UNIT[args.workload], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def config_dict(args, per_gpu, note=None):
@@ -274,9 +274,8 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        # NCCL_DEBUG=VERSION makes NCCL print its version banner on STDOUT, in front of the one JSON line
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"
+        # (NCCL prints its version banner on file descriptor 1; main() has pointed fd 1 at stderr for the whole run
+        # and emit() writes the one JSON line to the saved stdout)
         dist.init_process_group("nccl", device_id=dev)
     _lib.lib()  # fail loudly here if the extension is missing
     pkg.set_compute_mode(args.mode)
@@ -403,7 +402,27 @@ def run_ours(args):
                 grad_bytes=fg.nbytes() if fg else 0, graphed=graphed is not None)
 
 
+_REAL_STDOUT = None
+
+
+def capture_stdout():
+    """Point file descriptor 1 at stderr for the whole run: native libraries (NCCL's version banner, torchrun
+    children) write to fd 1 behind Python's back, and stdout must carry exactly ONE JSON line."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
+    capture_stdout()
     args = parse()
     if args.impl == "reference":
         return run_reference(args)
@@ -473,7 +492,7 @@ def main():
             "sample": f"{steps} step(s) of {n} x {H}x{W} synthetic "
                       f"{'crops, fwd+loss+bwd' if wl != 'eval' else 'image, fwd+metrics'}, fp32 torch-CPU oracle port of "
                       f"the reference modules, {c['cores']} threads, after 2 warm-up steps"}
-    print(json.dumps(line), flush=True)
+    emit(line)
     import torch.distributed as dist
     if dist.is_available() and dist.is_initialized():
         dist.destroy_process_group()
