@@ -113,7 +113,6 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int i = threadIdx.x; i < 256; i += G_THREADS) beta_s[i] = i < C ? p.beta[i] : 1.f;
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmX); prefetch_tmap(&tmY); prefetch_tmap(&tmR); prefetch_tmap(&tmG);
     mbar_init(g_full, 1);
@@ -122,10 +121,13 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, Cfg::FWD_TMEM_COLS);
+  pdl_wait();                      // the prologue above overlaps the previous kernel's tail (beta comes from gdn_prepare)
+  for (int i = threadIdx.x; i < 256; i += G_THREADS) beta_s[i] = i < C ? p.beta[i] : 1.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
 
   if (warp == 0) {
     // lane c issues chunk c: the TMA instructions of a tile go out in parallel (each costs its thread ~100+ cycles)
@@ -321,6 +323,8 @@ gdn_bwd_umma_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                      // the prologue above overlaps the previous kernel's tail
+  pdl_launch_dependents();
 
   if (warp == 0) {
     // lane l issues chunk l % KC of tensor l / KC (g, x, r): 3 KC TMA instructions per tile, issued in parallel
@@ -531,6 +535,8 @@ gdn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                      // the prologue above overlaps the previous kernel's tail
+  pdl_launch_dependents();
 
   if (warp == 0) {
     // lane l issues chunk l % KC of tensor l / KC (g, x, r): 3 KC TMA instructions per tile, issued in parallel
@@ -816,6 +822,8 @@ gdn_bwd_dual_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                      // the prologue above overlaps the previous kernel's tail
+  pdl_launch_dependents();
 
   if (warp == 0) {
     // lane l: set l / 3KC, tensor (l % 3KC) / KC, chunk l % KC.  The lanes run independently (a complete_tx may
@@ -1099,6 +1107,8 @@ gdn_bwd_finish_kernel(const __grid_constant__ GdnFinish f) {
   else { blk -= f.ng + f.nc; part = f.dxsum_part; param = nullptr; out = f.dbias; n = f.C; scale = 1.f; bound = 0.f; }
   const int i = (blk * 32 + qd) * 4;
   float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+  pdl_wait();
+  pdl_launch_dependents();
   if (i < n)
     for (int s2 = g; s2 < f.nparts; s2 += 8) {
       const float4 v = __ldcs(reinterpret_cast<const float4*>(part + (int64_t)s2 * n + i));
@@ -1168,7 +1178,7 @@ int hpc_gdn_fwd_umma(const void* x_bf16, const void* gamma_bf16, const float* be
       HPC_CUDA(cudaFuncSetAttribute(gdn_fwd_umma_kernel<CC>, cudaFuncAttributeMaxDynamicSharedMemorySize, GCfg<CC>::SMEM));
       attr_set = true;
     }
-    gdn_fwd_umma_kernel<CC><<<gdn_grid(kp.tiles), G_THREADS, GCfg<CC>::SMEM, st>>>(tmX, tmY, tmR, tmG, kp);
+    HPC_CUDA(hpc_launch_pdl(gdn_fwd_umma_kernel<CC>, dim3(gdn_grid(kp.tiles)), dim3(G_THREADS), GCfg<CC>::SMEM, st, tmX, tmY, tmR, tmG, kp));
   });
   HPC_LAUNCH_CHECK();
   return HPC_OK;
@@ -1245,7 +1255,7 @@ int hpc_gdn_bwd_fused_umma(const void* g_bf16, const void* x_bf16, const void* r
       HPC_CUDA(cudaFuncSetAttribute(KERNEL<CC>, cudaFuncAttributeMaxDynamicSharedMemorySize, GCfg<CC>::SMEM));  \
       attr_set = true;                                                                                          \
     }                                                                                                           \
-    KERNEL<CC><<<grid, G_THREADS, GCfg<CC>::SMEM, st>>>(tmGr, tmX, tmR, tmDx, tmG, kp);                         \
+    HPC_CUDA(hpc_launch_pdl(KERNEL<CC>, dim3(grid), dim3(G_THREADS), GCfg<CC>::SMEM, st, tmGr, tmX, tmR, tmDx, tmG, kp)); \
   } while (0)
   if (dual) {
     if (C == 128) GDN_BWD_LAUNCH(gdn_bwd_dual_kernel, 128); else GDN_BWD_LAUNCH(gdn_bwd_dual_kernel, 192);
@@ -1260,7 +1270,7 @@ int hpc_gdn_bwd_fused_umma(const void* g_bf16, const void* x_bf16, const void* r
   f.dgamma = dgamma; f.dbeta = dbeta; f.dbias = dbias;
   f.nparts = grid; f.C = C; f.ng = (C * C + 127) / 128; f.nc = (C + 127) / 128;
   f.sgn = inverse ? 0.5f : -0.5f; f.gamma_bound = gamma_bound; f.beta_bound = beta_bound;
-  gdn_bwd_finish_kernel<<<f.ng + f.nc + (dbias ? f.nc : 0), 256, 0, st>>>(f);
+  HPC_CUDA(hpc_launch_pdl(gdn_bwd_finish_kernel, dim3(f.ng + f.nc + (dbias ? f.nc : 0)), dim3(256), 0, st, f));
   HPC_LAUNCH_CHECK();
   return HPC_OK;
 }
@@ -1272,6 +1282,8 @@ __global__ void gdn_prepare_kernel(const float* __restrict__ gamma_param, const 
                                    float gamma_bound, float beta_bound, float pedestal, float* __restrict__ beta_eff,
                                    __nv_bfloat16* __restrict__ g_bf16, __nv_bfloat16* __restrict__ gT_bf16) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  pdl_wait();
+  pdl_launch_dependents();
   if (idx < C * C) {
     const float v = fmaxf(gamma_param[idx], gamma_bound);
     const __nv_bfloat16 h = __float2bfloat16_rn(v * v - pedestal);
@@ -1288,9 +1300,9 @@ int hpc_gdn_prepare(const float* gamma_param, const float* beta_param, int C, fl
                     float pedestal, float* beta_eff, void* gamma_bf16, void* gammaT_bf16, hpc_stream_t stream) {
   HPC_REQUIRE(gamma_param && beta_param && beta_eff && gamma_bf16 && gammaT_bf16 && C > 0, HPC_ERR_BAD_SHAPE,
               "hpc_gdn_prepare: bad arguments");
-  gdn_prepare_kernel<<<(C * C + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
-      gamma_param, beta_param, C, gamma_bound, beta_bound, pedestal, beta_eff, (__nv_bfloat16*)gamma_bf16,
-      (__nv_bfloat16*)gammaT_bf16);
+  HPC_CUDA(hpc_launch_pdl(gdn_prepare_kernel, dim3((C * C + 255) / 256), dim3(256), 0, (cudaStream_t)stream, gamma_param,
+                          beta_param, C, gamma_bound, beta_bound, pedestal, beta_eff, (__nv_bfloat16*)gamma_bf16,
+                          (__nv_bfloat16*)gammaT_bf16));
   HPC_LAUNCH_CHECK();
   return HPC_OK;
 }

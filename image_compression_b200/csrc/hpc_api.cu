@@ -1,6 +1,7 @@
 // Library-level entry points: version, error string, device probe.
 #include "hpc_common.cuh"
 
+#include <stdlib.h>
 #include <mutex>
 #include <vector>
 
@@ -27,6 +28,12 @@ int hpc_num_sms() {
   if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
   cached = n > 0 ? n : 148;
   return cached;
+}
+
+int hpc_pdl_enabled() {
+  static int on = -1;
+  if (on < 0) { const char* e = getenv("HPC_PDL"); on = (e && e[0] == '0') ? 0 : 1; }
+  return on;
 }
 
 // ---------------------------------------------------------------------------------------

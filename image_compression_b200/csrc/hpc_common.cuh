@@ -59,6 +59,32 @@ struct HpcProfScope {
   }
 };
 
+// ---------------------------------------------------------------------------------------
+// Programmatic dependent launch (griddepcontrol): a kernel launched through hpc_launch_pdl may become resident
+// while its predecessor in the stream is still draining -- its prologue (barrier init, TMEM allocation, tensor-map
+// prefetch) then overlaps the predecessor's tail.  Contract for every kernel launched this way:
+//   * pdl_wait() before the first global-memory access that depends on (or may race with) earlier work;
+//   * pdl_launch_dependents() once the CTA no longer minds the next kernel's CTAs becoming resident beside it.
+// Both are no-ops for a kernel launched the ordinary way.  HPC_PDL=0 in the environment disables the attribute.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+int hpc_pdl_enabled();
+
+template <typename... KArgs, typename... Args>
+static inline cudaError_t hpc_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                         Args&&... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = hpc_pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 static inline bool hpc_aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 // number of SMs of the current device (cached per thread)

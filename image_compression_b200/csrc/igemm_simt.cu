@@ -311,6 +311,8 @@ colsum_stage1_bf16x8(const __nv_bfloat16* __restrict__ x, int64_t P, int C, floa
   int64_t r0 = blockIdx.x * rows_per, r1 = r0 + rows_per;
   if (r1 > P) r1 = P;
   float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  pdl_wait();
+  pdl_launch_dependents();
   if (rl < RL) {
     for (int64_t r = r0 + rl; r < r1; r += RL) {
       const uint4 v = *reinterpret_cast<const uint4*>(x + r * C + u * 8);
@@ -335,6 +337,8 @@ colsum_stage1_bf16x8(const __nv_bfloat16* __restrict__ x, int64_t P, int C, floa
 __global__ void colsum_stage2(const float* __restrict__ part, int nparts, int C, float scale, float* __restrict__ out) {
   const int lane = threadIdx.x & 31;
   const int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  pdl_wait();
+  pdl_launch_dependents();
   if (c >= C) return;
   double s = 0.0;
   for (int i = lane; i < nparts; i += 32) s += (double)part[(int64_t)i * C + c];
@@ -355,7 +359,8 @@ int hpc_colsum(const void* x, int dtype, int64_t P, int C, float scale, float* o
   auto st = (cudaStream_t)stream;
   if (dtype == HPC_BF16 && (C & 7) == 0 && C <= 2048 && hpc_aligned16(x)) {
     const int RL = 256 / (C >> 3);
-    colsum_stage1_bf16x8<<<nparts, 256, (size_t)RL * C * sizeof(float), st>>>((const __nv_bfloat16*)x, P, C, (float*)scratch);
+    HPC_CUDA(hpc_launch_pdl(colsum_stage1_bf16x8, dim3(nparts), dim3(256), (size_t)RL * C * sizeof(float), st,
+                            (const __nv_bfloat16*)x, P, C, (float*)scratch));
   } else {
     int threads = C >= 128 ? 128 : ((C + 31) / 32) * 32;
     dim3 grid((C + threads - 1) / threads, nparts);
@@ -365,7 +370,7 @@ int hpc_colsum(const void* x, int dtype, int64_t P, int C, float scale, float* o
       colsum_stage1<float><<<grid, threads, 0, st>>>((const float*)x, P, C, (float*)scratch);
   }
   HPC_LAUNCH_CHECK();
-  colsum_stage2<<<(C + 7) / 8, 256, 0, st>>>((const float*)scratch, nparts, C, scale, out);
+  HPC_CUDA(hpc_launch_pdl(colsum_stage2, dim3((C + 7) / 8), dim3(256), 0, st, (const float*)scratch, nparts, C, scale, out));
   HPC_LAUNCH_CHECK();
   return HPC_OK;
 }

@@ -207,9 +207,6 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
   const int ksplit = NCTA == 1 ? p.ksplit : 1;              // split-K for grids of a few tiles (single-CTA kernel only)
   const int total_work = p.interleave ? (per_phase + nworkers - 1) / nworkers * nworkers * p.nphases
                                       : per_phase * p.nphases * ksplit;
-  if (p.epi.bias)
-    for (int i = threadIdx.x; i < BLOCK_N; i += FW_THREADS) bias_s[i] = p.epi.bias[i];
-
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
@@ -220,9 +217,14 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
   if (warp == 1) {
     if (NCTA == 2) tmem_alloc_pair(tmem_slot, Cfg::TMEM_COLS); else tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
   }
+  // everything above overlaps the tail of the previous kernel in the stream (programmatic dependent launch)
+  pdl_wait();
+  if (p.epi.bias)
+    for (int i = threadIdx.x; i < BLOCK_N; i += FW_THREADS) bias_s[i] = p.epi.bias[i];
   tc_fence_before();
   if (NCTA == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
+  pdl_launch_dependents();
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
@@ -378,6 +380,8 @@ __global__ void __launch_bounds__(256)
 splitk_epilogue_kernel(const float* __restrict__ ws, int ksplit, int64_t out_elems, int Co, const __grid_constant__ EpiArgs epi) {
   const int64_t u = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;      // unit of 8 channels
   const int64_t o = u * 8;
+  pdl_wait();
+  pdl_launch_dependents();
   if (o >= out_elems) return;
   float acc[8];
   load8_f32(ws, o, acc);
@@ -406,7 +410,7 @@ static int launch_fwd(const CUtensorMap& tmA, const CUtensorMap& tmB, const FwdK
     }
     const int pairs = (kp.tiles_per_phase + 1) / 2 * kp.nphases, tpcs = hpc_num_sms() / 2;
     const int grid = 2 * (pairs < tpcs ? pairs : tpcs);
-    igemm_fwd_umma_pair_kernel<BLOCK_N><<<grid, FW_THREADS, Cfg::SMEM_BYTES, st>>>(tmA, tmB, kp);
+    HPC_CUDA(hpc_launch_pdl(igemm_fwd_umma_pair_kernel<BLOCK_N>, dim3(grid), dim3(FW_THREADS), Cfg::SMEM_BYTES, st, tmA, tmB, kp));
   } else {
     using Cfg = FwdCfg<BLOCK_N, 1>;
     static bool attr_set = false;
@@ -417,7 +421,7 @@ static int launch_fwd(const CUtensorMap& tmA, const CUtensorMap& tmB, const FwdK
     }
     const int work = kp.total_tiles * kp.ksplit;
     const int grid = work < hpc_num_sms() ? work : hpc_num_sms();
-    igemm_fwd_umma_kernel<BLOCK_N><<<grid, FW_THREADS, Cfg::SMEM_BYTES, st>>>(tmA, tmB, kp);
+    HPC_CUDA(hpc_launch_pdl(igemm_fwd_umma_kernel<BLOCK_N>, dim3(grid), dim3(FW_THREADS), Cfg::SMEM_BYTES, st, tmA, tmB, kp));
   }
   HPC_LAUNCH_CHECK();
   return HPC_OK;
@@ -554,7 +558,8 @@ int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
   }
   if (rc || kp.ksplit == 1) return rc;
   const int64_t units = kp.out_elems / 8;
-  splitk_epilogue_kernel<<<(int)((units + 255) / 256), 256, 0, st>>>(kp.ws, kp.ksplit, kp.out_elems, p->Co, kp.epi);
+  HPC_CUDA(hpc_launch_pdl(splitk_epilogue_kernel, dim3((unsigned)((units + 255) / 256)), dim3(256), 0, st, (const float*)kp.ws,
+                          kp.ksplit, kp.out_elems, p->Co, kp.epi));
   HPC_LAUNCH_CHECK();
   return HPC_OK;
 }
@@ -622,6 +627,8 @@ igemm_wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmLo, const __grid_c
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                      // the prologue above overlaps the previous kernel's tail
+  pdl_launch_dependents();
 
   if (warp == 0) {
     // Producer: the whole warp runs the loop and lane l issues box l of the stage (up to 4 `lo` atoms + Cc/64 `hi`
@@ -721,6 +728,8 @@ wgrad_reduce_kernel(const float* __restrict__ ws, int nsplits, int64_t n, float 
   const int q = threadIdx.x & 31, g = threadIdx.x >> 5;
   const int64_t i = ((int64_t)blockIdx.x * 32 + q) * 4;
   float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+  pdl_wait();
+  pdl_launch_dependents();
   if (i < n)
     for (int s = g; s < nsplits; s += 8) {
       const float4 v = __ldcs(reinterpret_cast<const float4*>(ws + (int64_t)s * n + i));
@@ -747,6 +756,48 @@ wgrad_reduce_kernel(const float* __restrict__ ws, int nsplits, int64_t n, float 
     const float v[4] = {a.x, a.y, a.z, a.w};
 #pragma unroll
     for (int k = 0; k < 4; ++k) d[k * o.sc] = o.accumulate ? d[k * o.sc] + v[k] : v[k];
+  }
+}
+
+// Split-K reduction straight into the reference weight layout (out_mode 1) when the taps of one (r, c) pair are
+// contiguous there (min(sr, sc) == ntaps: (Co,Ci,kh,kw) / (Ci,Co,kh,kw)).  A block owns an RT x CT tile of (r, c)
+// pairs for ALL taps: it sums the K slices in split order (fixed order: deterministic) with 128/32-byte coalesced
+// reads, transposes through shared memory (pair-major, odd stride) and writes runs of ntaps consecutive floats --
+// the scattered 4-byte stores of wgrad_reduce_kernel cost 8x their bytes in 32-byte sectors.
+constexpr int WGR_PAIRS = 128;
+__global__ void __launch_bounds__(256)
+wgrad_reduce_tiled_kernel(const float* __restrict__ ws, int nsplits, int ntaps, float scale, float* __restrict__ gw,
+                          int RT, int CT, const __grid_constant__ WgOut o) {
+  __shared__ float sm[WGR_PAIRS * (HPC_MAX_TAPS | 1)];
+  __shared__ int inv[HPC_MAX_TAPS];
+  const int stride = ntaps | 1;                      // odd: conflict-free reads in the write phase
+  const int ctiles = o.Cc / CT;
+  const int r0 = (blockIdx.x / ctiles) * RT, c0 = (blockIdx.x % ctiles) * CT;
+  if (threadIdx.x < ntaps) inv[o.tap_src[threadIdx.x]] = threadIdx.x;
+  pdl_wait();
+  pdl_launch_dependents();
+  const int q4 = CT / 4;                             // float4 units per tile row
+  const int64_t n = (int64_t)ntaps * o.R * o.Cc;
+  for (int u = threadIdx.x; u < ntaps * RT * q4; u += 256) {
+    const int cq = u % q4, rl = (u / q4) % RT, t = u / (q4 * RT);
+    const float* src = ws + ((int64_t)t * o.R + r0 + rl) * o.Cc + c0 + cq * 4;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int s2 = 0; s2 < nsplits; ++s2) {
+      const float4 v = __ldcs(reinterpret_cast<const float4*>(src + (int64_t)s2 * n));
+      a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+    }
+    float* d = sm + (rl * CT + cq * 4) * stride + t;
+    d[0] = a.x * scale; d[stride] = a.y * scale; d[2 * stride] = a.z * scale; d[3 * stride] = a.w * scale;
+  }
+  __syncthreads();
+  // pairs ordered so that consecutive pairs are neighbours along the small-stride dimension
+  const bool c_inner = o.sc < o.sr;
+  for (int e = threadIdx.x; e < RT * CT * ntaps; e += 256) {
+    const int k = e % ntaps, pr = e / ntaps;
+    const int rl = c_inner ? pr / CT : pr % RT, cl = c_inner ? pr % CT : pr / RT;
+    float* d = gw + (int64_t)(r0 + rl) * o.sr + (int64_t)(c0 + cl) * o.sc + k;
+    const float v = sm[(rl * CT + cl) * stride + inv[k]];
+    *d = o.accumulate ? *d + v : v;
   }
 }
 
@@ -840,7 +891,8 @@ int hpc_igemm_wgrad_umma(const hpc_igemm_wgrad_params* p, hpc_stream_t stream) {
   }
   auto st = (cudaStream_t)stream;
   HpcProfScope prof(HPC_PROF_IGEMM_WGRAD, 2.0 * p->N * p->GH * p->GW * (double)local.ntaps * p->R * p->Cc, stream);
-  igemm_wgrad_umma_kernel<<<local.nunits * local.nsplits, WG_THREADS, smem_bytes, st>>>(tmLo, tmHi, local);
+  HPC_CUDA(hpc_launch_pdl(igemm_wgrad_umma_kernel, dim3(local.nunits * local.nsplits), dim3(WG_THREADS), smem_bytes, st, tmLo,
+                          tmHi, local));
   HPC_LAUNCH_CHECK();
   const int64_t n = (int64_t)local.ntaps * p->R * p->Cc;
   WgOut o;
@@ -848,7 +900,22 @@ int hpc_igemm_wgrad_umma(const hpc_igemm_wgrad_params* p, hpc_stream_t stream) {
   o.mode = p->out_mode; o.accumulate = p->out_accumulate; o.R = p->R; o.Cc = p->Cc;
   o.sr = p->out_stride_r; o.sc = p->out_stride_c;
   for (int t = 0; t < local.ntaps && t < HPC_MAX_TAPS; ++t) o.tap_src[t] = p->out_tap_src[t];
-  wgrad_reduce_kernel<<<(int)((n + 127) / 128), 256, 0, st>>>(local.ws, local.nsplits, n, p->scale, p->gw_f32, o);
+  const int64_t smin = o.sr < o.sc ? o.sr : o.sc;
+  bool perm = o.mode == 1 && smin == local.ntaps && local.ntaps <= HPC_MAX_TAPS;
+  if (perm) {                                  // tap_src must be a permutation of [0, ntaps)
+    unsigned long long seen = 0;
+    for (int t = 0; t < local.ntaps; ++t)
+      if (o.tap_src[t] >= 0 && o.tap_src[t] < local.ntaps) seen |= 1ull << o.tap_src[t];
+    perm = seen == (1ull << local.ntaps) - 1;
+  }
+  if (perm) {
+    const int RT = o.sc < o.sr ? 4 : 16, CT = WGR_PAIRS / RT;       // R, Cc are multiples of 64
+    HPC_CUDA(hpc_launch_pdl(wgrad_reduce_tiled_kernel, dim3((p->R / RT) * (p->Cc / CT)), dim3(256), 0, st,
+                            (const float*)local.ws, local.nsplits, local.ntaps, p->scale, p->gw_f32, RT, CT, o));
+  } else {
+    HPC_CUDA(hpc_launch_pdl(wgrad_reduce_kernel, dim3((unsigned)((n + 127) / 128)), dim3(256), 0, st, (const float*)local.ws,
+                            local.nsplits, n, p->scale, p->gw_f32, o));
+  }
   HPC_LAUNCH_CHECK();
   return HPC_OK;
 }

@@ -169,7 +169,6 @@ conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_consta
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // zero the A buffers once: the padded K columns (k >= 80) are never written again
   for (int i = threadIdx.x; i < 2 * T1_A_BYTES / 16; i += T1_THREADS) reinterpret_cast<uint4*>(smem_a)[i] = make_uint4(0, 0, 0, 0);
-  for (int i = threadIdx.x; i < 256; i += T1_THREADS) bias_s[i] = (p.bias && i < CW) ? p.bias[i] : 0.f;
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmB);
     for (int s = 0; s < 2; ++s) { mbar_init(&full_a[s], 128); mbar_init(&empty_a[s], 1); mbar_init(&tfull[s], 1); mbar_init(&tempty[s], T1_EPI / 32); }
@@ -177,11 +176,14 @@ conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_consta
     fence_barrier_init();
   }
   if (warp == 0) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+  pdl_wait();                      // the prologue above overlaps the previous kernel's tail
+  for (int i = threadIdx.x; i < 256; i += T1_THREADS) bias_s[i] = (p.bias && i < CW) ? p.bias[i] : 0.f;
   fence_proxy_async();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
   const int tiles_per_img = p.tiles_w * p.tiles_h;
 
   if (warp == 0) {
@@ -322,7 +324,7 @@ int launch_t1(const CUtensorMap& tmB, const T1Params& kp, cudaStream_t st) {
     attr_set = true;
   }
   const int grid = kp.total_tiles < hpc_num_sms() ? kp.total_tiles : hpc_num_sms();
-  conv_c3_umma_kernel<CW><<<grid, T1_THREADS, Cfg::SMEM, st>>>(tmB, kp);
+  HPC_CUDA(hpc_launch_pdl(conv_c3_umma_kernel<CW>, dim3(grid), dim3(T1_THREADS), Cfg::SMEM, st, tmB, kp));
   HPC_LAUNCH_CHECK();
   return HPC_OK;
 }
@@ -421,6 +423,8 @@ deconv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                      // the prologue above overlaps the previous kernel's tail
+  pdl_launch_dependents();
   const int tiles_per_img = p.tiles_w * p.tiles_h;
 
   if (warp == 0) {
@@ -545,7 +549,7 @@ int launch_t2(const CUtensorMap& tmA, const CUtensorMap& tmB, const T2Params& kp
     attr_set = true;
   }
   const int grid = kp.total_tiles < hpc_num_sms() ? kp.total_tiles : hpc_num_sms();
-  deconv_c3_umma_kernel<CW><<<grid, T2_THREADS, Cfg::SMEM, st>>>(tmA, tmB, kp);
+  HPC_CUDA(hpc_launch_pdl(deconv_c3_umma_kernel<CW>, dim3(grid), dim3(T2_THREADS), Cfg::SMEM, st, tmA, tmB, kp));
   HPC_LAUNCH_CHECK();
   return HPC_OK;
 }
@@ -653,6 +657,8 @@ wgrad_c3_umma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                      // the prologue above overlaps the previous kernel's tail
+  pdl_launch_dependents();
 
   if (warp == 0) {
     if (lane < CW / 64) {               // lane c issues channel chunk c
@@ -755,6 +761,8 @@ wgrad_c3_umma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
 __global__ void wgrad_c3_umma_reduce(const float* __restrict__ ws, int nsplits, int Cw, float* __restrict__ gw, int64_t w_sr,
                                      int64_t w_sc) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  pdl_wait();
+  pdl_launch_dependents();
   if (i >= 75 * Cw) return;
   const int k = i / Cw, cw = i % Cw;
   float a = 0.f;
@@ -806,7 +814,7 @@ int hpc_wgrad_c3_umma(const void* wide_nhwc_bf16, const float* thin_nchw, int N,
                                     T3Cfg<CW_>::SMEM));                                                              \
       attr_set = true;                                                                                               \
     }                                                                                                                \
-    wgrad_c3_umma_kernel<CW_><<<kp.nsplits, T3_THREADS, T3Cfg<CW_>::SMEM, st>>>(tmW, kp);                            \
+    HPC_CUDA(hpc_launch_pdl(wgrad_c3_umma_kernel<CW_>, dim3(kp.nsplits), dim3(T3_THREADS), T3Cfg<CW_>::SMEM, st, tmW, kp)); \
   } while (0)
   switch (Cw) {
     case 64: LAUNCH_T3(64); break;
@@ -816,7 +824,8 @@ int hpc_wgrad_c3_umma(const void* wide_nhwc_bf16, const float* thin_nchw, int N,
   }
 #undef LAUNCH_T3
   HPC_LAUNCH_CHECK();
-  wgrad_c3_umma_reduce<<<(75 * Cw + 255) / 256, 256, 0, st>>>(kp.ws, kp.nsplits, Cw, gw, w_sr, w_sc);
+  HPC_CUDA(hpc_launch_pdl(wgrad_c3_umma_reduce, dim3((75 * Cw + 255) / 256), dim3(256), 0, st, (const float*)kp.ws, kp.nsplits,
+                          Cw, gw, w_sr, w_sc));
   HPC_LAUNCH_CHECK();
   return HPC_OK;
 }
