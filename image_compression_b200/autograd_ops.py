@@ -504,6 +504,7 @@ class Compressor2018Fn(torch.autograd.Function):
         g_raw = hp.clamp01_backward(raw, x if has_mse else None, g_xt, mse_coef, g, do_clamp=True)
         # --- g_s ---------------------------------------------------------------------------
         g_yt, gs_cg, gs_gg = B.gs_backward(Sgs, g_raw, need_input_grad=True)
+        hp.grads_ready(_join_ga(gs_cg, gs_gg))       # g_s gradients are final: their all-reduce may start now
         # --- conditional likelihood (+ exp/clamp of h_s fused) ------------------------------
         gy_partial, _, gpre = hp.conditional_backward(yt, sigma, m.dist, training, g, inv_np, None, g_yt,
                                                       fuse_exp_clamp=True, want_gs_f32=False, want_gs_lp=True,

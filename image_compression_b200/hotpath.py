@@ -194,6 +194,22 @@ def set_grad_sink(sink):
     _grad_sink = sink if sink else None
 
 
+_grad_ready_hook = None
+
+
+def set_grad_ready_hook(fn):
+    """fn(list of gradient tensors) or None.  The fused backward calls it as soon as every kernel writing the
+    gradients of a parameter group has been ENQUEUED on the current stream (today: the synthesis transform, whose
+    gradients are final ~45% into the backward), so sharding.FlatGradients can start their all-reduce early."""
+    global _grad_ready_hook
+    _grad_ready_hook = fn
+
+
+def grads_ready(grads):
+    if _grad_ready_hook is not None:
+        _grad_ready_hook([g for g in grads if g is not None])
+
+
 def grad_buffer(param, zero=False):
     """Output buffer for the gradient of `param` (fp32, param's shape)."""
     s = _grad_sink

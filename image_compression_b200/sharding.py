@@ -10,6 +10,8 @@ i % world and the per-image metrics are all-gathered at the end.
 
 torch.distributed is plumbing only (NCCL on the GPU box, gloo in the CPU tests).
 """
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -18,9 +20,11 @@ class FlatGradients:
     """Flat fp32 gradient buffer aliased by every parameter's `.grad` (state_dict order).
 
     usage per step:   fg.zero();  loss.backward();  fg.all_reduce_mean()
+    (with `overlap` -- the default on CUDA + NCCL -- exactly ONE backward between zero() and all_reduce_mean():
+    the synthesis-transform slice is all-reduced while the rest of the backward still runs)
     """
 
-    def __init__(self, params, device=None):
+    def __init__(self, params, device=None, overlap=None):
         self.params = [p for p in params if p.requires_grad]
         if not self.params:
             raise ValueError("FlatGradients: no trainable parameters")
@@ -37,6 +41,14 @@ class FlatGradients:
         self.numel = sum(p.numel() for p in self.params)
         self.offsets = offs
         self.direct = self.flat.is_cuda       # the CUDA backward writes into the slots itself (see zero())
+        # start the all-reduce of a parameter group as soon as the backward reports its gradients final
+        # (hotpath.set_grad_ready_hook); HPC_AR_OVERLAP=0 keeps the single all-reduce after backward
+        # With overlap EVERY rank must call all_reduce_mean() after each backward (the early all-reduce is a
+        # collective): pass overlap=False for a buffer whose gradients are not going to be reduced.
+        if overlap is None:
+            overlap = os.environ.get("HPC_AR_OVERLAP", "1") != "0"
+        self.overlap = self.direct and bool(overlap)
+        self._early = None
         self.copies = 0                       # slots that had to be filled by a copy in collect() (0 when direct)
         for p in self.params:
             p.grad = self._view(p)
@@ -63,6 +75,33 @@ class FlatGradients:
                 p.grad = None
                 sink[p.data_ptr()] = self._view(p)       # a fresh view object: autograd must be its only owner
             hp.set_grad_sink(sink)
+            self._early = None
+            hp.set_grad_ready_hook(self._reduce_early if self.overlap and self._multi_rank_nccl() else None)
+
+    @staticmethod
+    def _multi_rank_nccl(group=None):
+        return (dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+                and dist.get_backend(group) == "nccl")
+
+    def _reduce_early(self, grads):
+        """Asynchronous mean all-reduce of the contiguous slot range covered by `grads` (views of the flat buffer),
+        issued on NCCL's stream behind the kernels enqueued so far; all_reduce_mean() reduces the rest and waits."""
+        if self._early is not None or not grads:
+            return
+        base, total = self.flat.data_ptr(), self.flat.numel()
+        lo, hi = total, 0
+        for g in grads:
+            o = (g.data_ptr() - base) // 4
+            if g.dtype != torch.float32 or (g.data_ptr() - base) % 4 or not (0 <= o and o + g.numel() <= total):
+                return                                  # a stray gradient: keep the single all-reduce
+            lo, hi = min(lo, o), max(hi, (o + g.numel() + 3) // 4 * 4)
+        inside = sum(1 for o in self.offsets if lo <= o < hi)
+        if inside != len(grads):
+            return                                      # the range holds slots of other groups
+        from . import hotpath as hp
+        hp.set_grad_ready_hook(None)                    # one early reduce per zero(): a second backward before the next
+        work = dist.all_reduce(self.flat[lo:hi], op=dist.ReduceOp.AVG, async_op=True)   # zero() must not re-reduce
+        self._early = (lo, hi, work)
 
     def collect(self):
         """Re-establish `.grad is a view of the flat buffer` after backward (a no-op check when the backward wrote
@@ -70,6 +109,7 @@ class FlatGradients:
         if self.direct:
             from . import hotpath as hp
             hp.set_grad_sink(None)
+            hp.set_grad_ready_hook(None)
         for p, o in zip(self.params, self.offsets):
             g = p.grad
             if g is not None and g.data_ptr() == self.flat.data_ptr() + 4 * o:
@@ -89,6 +129,17 @@ class FlatGradients:
         if world == 1:
             return None
         if dist.get_backend(group) == "nccl":
+            if self._early is not None:
+                lo, hi, first = self._early
+                self._early = None
+                works = [first]
+                if lo > 0:
+                    works.append(dist.all_reduce(self.flat[:lo], op=dist.ReduceOp.AVG, group=group, async_op=True))
+                if hi < self.flat.numel():
+                    works.append(dist.all_reduce(self.flat[hi:], op=dist.ReduceOp.AVG, group=group, async_op=True))
+                for w in works:
+                    w.wait()                            # the current stream waits for NCCL's
+                return None
             return dist.all_reduce(self.flat, op=dist.ReduceOp.AVG, group=group, async_op=async_op)
         work = dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group, async_op=False)
         self.flat.mul_(1.0 / world)

@@ -19,7 +19,7 @@ from image_compression_b200 import sharding  # noqa: E402
 
 
 def flat_grad(model, x, nz, ny, mode, reduce):
-    fg = sharding.FlatGradients(model.parameters(), x.device)
+    fg = sharding.FlatGradients(model.parameters(), x.device, overlap=reduce)
     fg.zero()
     with pkg.compute_mode(mode):
         _, losses = model(x, nz, ny)
