@@ -446,7 +446,11 @@ class Compressor2018Fn(torch.autograd.Function):
         m = meta
         x = _f32c(x)
         N, C, H, W = x.shape
-        save = any(ctx.needs_input_grad)  # forward() itself always runs under no_grad
+        # forward() itself always runs under no_grad and needs_input_grad ignores the caller's grad mode, so the
+        # caller says whether a backward can follow (training = (mode flag, grad enabled)); without one nothing is
+        # saved and the GDN kernels skip their r output
+        training, grad_enabled = training if isinstance(training, tuple) else (training, True)
+        save = grad_enabled and any(ctx.needs_input_grad)
         i = 0
         ga_convs, ga_gdns = _split_ga(params[i:i + m.n_ga], len(m.strides)); i += m.n_ga
         ha_convs = _split_h(params[i:i + m.n_ha], m.ha_bias); i += m.n_ha

@@ -69,7 +69,7 @@ def ga_forward(x_nchw, convs, gdns, k=5, strides=(2, 2, 2, 2), want_abs=False, s
         if i < n - 1:
             gp, bp = gdns[i]
             gamma, beta = _gdn_params(gp, bp)
-            yv, nrm = hp.gdn_forward(cur, cur_sq, gamma, beta)
+            yv, nrm = hp.gdn_forward(cur, cur_sq, gamma, beta, want_nrm=save)
             S.layers.append(("gdn", (cur, cur_sq, nrm, gamma), None))
             cur = yv
     if n == 1 and want_abs:
@@ -137,7 +137,7 @@ def gs_forward(yt_lp, convs, gdns, k=5, strides=(2, 2, 2, 2), save=True):
             S.layers.append(("deconv", spec, cur))
             gp, bp = gdns[i]
             gamma, beta = _gdn_params(gp, bp)
-            yv, nrm = hp.gdn_forward(o["lp"], o.get("sq"), gamma, beta)
+            yv, nrm = hp.gdn_forward(o["lp"], o.get("sq"), gamma, beta, want_nrm=save)
             S.layers.append(("gdn", (o["lp"], o.get("sq"), nrm, gamma), None))
             cur = yv
     S.convs, S.gdns = convs, gdns

@@ -70,6 +70,7 @@ struct GdnParams {
   int64_t P;
   int tiles;
   int inverse;
+  int store_r;             // forward only: 0 = r is not wanted (no-grad evaluation): 2 HBM passes instead of 3
 };
 
 template <int C>
@@ -165,7 +166,7 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
   } else if (warp == 2) {
     // lanes 0..KC-1 store the r chunks, lanes KC..2KC-1 the y chunks (bulk groups are per thread); each group frees
     // its own buffer as soon as ITS stores have been read out of shared memory
-    if (lane < 2 * KC) {
+    if (lane < 2 * KC && (p.store_r || lane >= KC)) {
       const int c = lane % KC;
       int it = 0;
       for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
@@ -239,7 +240,7 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
       uint8_t* xt = xs + b * Cfg::TILE;
       mbar_wait(tfull, it & 1);
       tc_fence_after();
-      mbar_wait(rs_empty, (it & 1) ^ 1);          // r of the previous tile has left the staging buffer
+      if (p.store_r) mbar_wait(rs_empty, (it & 1) ^ 1);   // r of the previous tile has left the staging buffer
       const uint32_t taddr = tmem_base + lane_off + half * (C / 4);
       constexpr int GB = (C / 64) % 3 == 0 ? 3 : ((C / 64) % 2 == 0 ? 2 : 1);      // ld16 groups per batch
 #pragma unroll 1
@@ -269,7 +270,7 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
               y[e] = p.inverse ? x[e] * (n * r[e]) : x[e] * r[e];
             }
             *reinterpret_cast<uint4*>(xt + o) = pack8(y);
-            *reinterpret_cast<uint4*>(rs + o) = pack8(r);
+            if (p.store_r) *reinterpret_cast<uint4*>(rs + o) = pack8(r);
           }
         }
       }
@@ -1161,16 +1162,18 @@ static int gdn_check(const char* who, int64_t P, int C, std::initializer_list<co
 
 int hpc_gdn_fwd_umma(const void* x_bf16, const void* gamma_bf16, const float* beta, int64_t P, int C, int inverse,
                      void* y_bf16, void* rnorm_bf16, hpc_stream_t stream) {
-  int rc = gdn_check("hpc_gdn_fwd_umma", P, C, {x_bf16, gamma_bf16, beta, y_bf16, rnorm_bf16});
+  // rnorm_bf16 == NULL: r is not stored (evaluation under no_grad: nothing will run a backward)
+  int rc = gdn_check("hpc_gdn_fwd_umma", P, C, {x_bf16, gamma_bf16, beta, y_bf16, rnorm_bf16 ? rnorm_bf16 : y_bf16});
   if (rc) return rc;
   GdnParams kp;
   kp.beta = beta; kp.colsum_part = nullptr; kp.P = P; kp.tiles = (int)((P + 127) / 128); kp.inverse = inverse;
+  kp.store_r = rnorm_bf16 ? 1 : 0;
   CUtensorMap tmX, tmY, tmR, tmG;
   if ((rc = make_rows_tmap(&tmX, x_bf16, P, C, 128))) return rc;
   if ((rc = make_rows_tmap(&tmY, y_bf16, P, C, 128))) return rc;
-  if ((rc = make_rows_tmap(&tmR, rnorm_bf16, P, C, 128))) return rc;
+  if ((rc = make_rows_tmap(&tmR, rnorm_bf16 ? rnorm_bf16 : y_bf16, P, C, 128))) return rc;      // unused without r
   if ((rc = make_rows_tmap(&tmG, gamma_bf16, C, C, C))) return rc;
-  HpcProfScope prof(HPC_PROF_GDN, (double)P * C * 2 * 3, stream);
+  HpcProfScope prof(HPC_PROF_GDN, (double)P * C * 2 * (rnorm_bf16 ? 3 : 2), stream);
   auto st = (cudaStream_t)stream;
   GDN_DISPATCH(C, {
     static bool attr_set = false;

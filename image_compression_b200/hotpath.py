@@ -460,7 +460,7 @@ def gdn_prepare(gamma_param, beta_param, beta_min=1e-6):
     return ops
 
 
-def gdn_forward(x, xsq, gamma_eff, beta_eff, inverse=False):
+def gdn_forward(x, xsq, gamma_eff, beta_eff, inverse=False, want_nrm=True):
     """x (, xsq): NHWC lp; gamma_eff (C,C,1,1) fp32, beta_eff (C,) fp32 -> (y, nrm) NHWC lp.
     xsq may be None (computed here, or never materialised on the fused path).  gamma_eff may be a GdnOperands."""
     N, H, W, C = x.shape
@@ -469,9 +469,9 @@ def gdn_forward(x, xsq, gamma_eff, beta_eff, inverse=False):
             wp, beta_eff = gamma_eff.g, gamma_eff.beta
         else:
             wp = pack_weight(gamma_eff, _ONE_TAP[0], C, C, C, 1, x.dtype, cache=False)
-        y, nrm = torch.empty_like(x), torch.empty_like(x)
-        check(lib().hpc_gdn_fwd_umma(ptr(x), ptr(wp), ptr(beta_eff), N * H * W, C, int(inverse), ptr(y), ptr(nrm),
-                                     stream()))
+        y, nrm = torch.empty_like(x), (torch.empty_like(x) if want_nrm else None)   # no nrm: no backward will follow
+        check(lib().hpc_gdn_fwd_umma(ptr(x), ptr(wp), ptr(beta_eff), N * H * W, C, int(inverse), ptr(y),
+                                     ptr(nrm) if want_nrm else None, stream()))
         return y, nrm
     if xsq is None:
         xsq, _ = square(x)

@@ -73,7 +73,7 @@ class Compressor2018(nn.Module):
 
     def _forward_fused(self, x, noise_z, noise_y):
         self._meta.lmbda = float(self.distortion_loss_weight)
-        x_tilde, out = Compressor2018Fn.apply(x, self._meta, bool(self.training), noise_z, noise_y,
+        x_tilde, out = Compressor2018Fn.apply(x, self._meta, (bool(self.training), torch.is_grad_enabled()), noise_z, noise_y,
                                               *self._flat_params())
         det = out.detach()
         losses = {"z_entropy": det[0], "y_entropy": det[1], "bpp": det[2], "total_loss": out[3]}

@@ -395,6 +395,8 @@ size_t hpc_wgrad_c3_scratch_bytes(int N, int Cw, int Cs, int H, int W);
  *               one launch: beta_eff[C] fp32, gamma_bf16[i][k], gammaT_bf16[k][i]. */
 int hpc_gdn_prepare(const float* gamma_param, const float* beta_param, int C, float gamma_bound, float beta_bound,
                     float pedestal, float* beta_eff, void* gamma_bf16, void* gammaT_bf16, hpc_stream_t stream);
+/*  rnorm_bf16 may be NULL (evaluation under no_grad: r = n^-1/2 is only needed by the backward): the kernel then
+ *  makes 2 HBM passes (read x, write y) instead of 3. */
 int hpc_gdn_fwd_umma(const void* x_bf16, const void* gamma_bf16, const float* beta, int64_t P, int C, int inverse,
                      void* y_bf16, void* rnorm_bf16, hpc_stream_t stream);
 int hpc_gdn_bwd_umma_parts(int64_t P);
