@@ -123,6 +123,7 @@ _SIGNATURES = {
     "hpc_prof_enable": (c_int, [c_int]),
     "hpc_prof_pause": (c_int, [c_int]),
     "hpc_prof_read": (c_int, [c_int, POINTER(c_double), POINTER(ctypes.c_ulonglong), POINTER(c_double)]),
+    "hpc_prof_records": (c_int, [POINTER(c_int), POINTER(ctypes.c_float), POINTER(c_double), c_int]),
     "hpc_bound_fwd": (c_int, [c_void_p, c_void_p, c_int64, c_float, c_int, c_void_p]),
     "hpc_bound_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_float, c_int, c_void_p]),
     "hpc_nonneg_fwd": (c_int, [c_void_p, c_void_p, c_int64, c_float, c_float, c_void_p]),
@@ -262,6 +263,14 @@ def prof_read(cls):
     ms, n, w = c_double(), ctypes.c_ulonglong(), c_double()
     check(lib().hpc_prof_read(cls, byref(ms), byref(n), byref(w)))
     return ms.value, n.value, w.value
+
+
+def prof_records():
+    """[(class name, ms, work)] of every record since prof_enable(True), in call order."""
+    n = lib().hpc_prof_records(None, None, None, 0)
+    cls, ms, work = (c_int * n)(), (ctypes.c_float * n)(), (c_double * n)()
+    n = min(n, lib().hpc_prof_records(cls, ms, work, n))
+    return [(PROF_NAMES[cls[i]], float(ms[i]), float(work[i])) for i in range(n)]
 
 
 def ptr(t):

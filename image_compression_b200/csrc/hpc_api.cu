@@ -103,3 +103,20 @@ int hpc_prof_read(int cls, double* ms_total, unsigned long long* launches, doubl
   if (work_total) *work_total = work;
   return HPC_OK;
 }
+
+int hpc_prof_records(int* cls, float* ms, double* work, int max) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  int n = 0;
+  for (auto& r : g_prof) {
+    if (!r.closed) continue;
+    if (n < max) {
+      float t = 0.f;
+      if (cudaEventSynchronize(r.b) == cudaSuccess) cudaEventElapsedTime(&t, r.a, r.b);
+      if (cls) cls[n] = r.cls;
+      if (ms) ms[n] = t;
+      if (work) work[n] = r.work;
+    }
+    ++n;
+  }
+  return n;
+}

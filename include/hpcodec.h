@@ -63,6 +63,9 @@ int hpc_device_is_sm100(void);
 int hpc_prof_enable(int on); /* on!=0: clear the records and start; 0: stop recording (records kept) */
 int hpc_prof_pause(int paused); /* suspend / resume recording, records kept (needed around CUDA-graph capture) */
 int hpc_prof_read(int cls, double* ms_total, unsigned long long* launches, double* work_total);
+/* the individual records in call order: class, milliseconds and work of record i (returns the record count; fills at
+ * most `max` entries; any output pointer may be NULL) */
+int hpc_prof_records(int* cls, float* ms, double* work, int max);
 
 /* ------------------------------------------------------------------------------------------
  * Bounds and the GDN non-negative reparameterisation
