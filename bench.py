@@ -423,9 +423,42 @@ def run_ours(args):
     e2e_value = units / (e2e_ms / 1e3)
     h2d = B * 3 * H * W * 4
     d2h = 4 if training else 4 * (1 + 2 * B)
+    # ---- optimizer step (NOT part of `value` / `e2e`, which follow SURVEY 8d) ---------------
+    # fused clip + AdamW over the gradients the last step left, against eager torch (clip_grad_value_ +
+    # torch.optim.AdamW over the same 50 single-tensor groups: what solver/optim.py + engine/trainer.py run)
+    optim = None
+    if training:
+        from torch.nn.utils import clip_grad_value_
+        from image_compression_b200 import solver
+        cfg = pkg.get_recipe_cfg(RECIPE[args.workload])
+        opt = solver.make_optimizer(cfg, model)
+        shadow = [torch.nn.Parameter(p.detach().clone()) for p in model.parameters()]
+        for q, p in zip(shadow, model.parameters()):
+            q.grad = p.grad.detach().clone()
+        ropt = torch.optim.AdamW([{"params": [q], "lr": g["lr"], "weight_decay": g["weight_decay"]}
+                                  for q, g in zip(shadow, opt.param_groups)], cfg.SOLVER.BASE_LR, eps=cfg.SOLVER.EPS)
+
+        def ref_step(_):
+            clip_grad_value_(shadow, cfg.SOLVER.GRAD_CLIP)
+            ropt.step()
+        for _ in range(3):
+            opt.step(); ref_step(0)
+        k0 = _lib.lib().hpc_launch_count()
+        _lib.prof_enable(True)
+        ms_fused = timed(lambda i: opt.step(), args.steps)
+        _lib.prof_enable(False)
+        k1 = _lib.lib().hpc_launch_count()
+        oms, on, owork = _lib.prof_read(_lib.PROF_NAMES.index("optim"))
+        ms_torch = timed(ref_step, args.steps)
+        nparam = sum(p.numel() for p in model.parameters())
+        optim = {"fused_ms_per_step": ms_fused / args.steps, "kernel_ms": oms / max(on, 1),
+                 "kernel_gbs": owork / max(oms, 1e-9) / 1e6, "launches_per_step": (k1 - k0) / args.steps,
+                 "bytes_per_param": 28, "params": nparam, "torch_eager_ms_per_step": ms_torch / args.steps,
+                 "note": "fused clip_grad_value_ + AdamW (hpc_adamw_step) vs clip_grad_value_ + torch.optim.AdamW "
+                         "(foreach) over the same 50 single-tensor groups; outside `value`/`e2e`"}
     return dict(rank=rank, world=world, B=B, H=H, W=W, ms_total=ms_total, ms_events=ms_events, value=value, launches=launches, prof=prof,
                 clocks=clocks.summary(), e2e_value=e2e_value, e2e_ms=e2e_ms, h2d=h2d, d2h=d2h, n_rot=n_rot,
-                grad_bytes=fg.nbytes() if fg else 0, graphed=graphed is not None)
+                grad_bytes=fg.nbytes() if fg else 0, graphed=graphed is not None, optim=optim)
 
 
 _REAL_STDOUT = None
@@ -514,6 +547,10 @@ def main():
         "step_gemm_tflops_per_gpu": step_tflops,
         "step_frac_of_tensor_peak": step_tflops / peaks["bf16_tflops_sustained"],
     }
+    if r.get("optim"):
+        o = dict(r["optim"])
+        o["frac_of_hbm"] = o["kernel_gbs"] / peaks["hbm_gbs"]
+        line["optimizer_step"] = o
     if world == 1 and not args.no_cpu_baseline:
         n = args.cpu_sample if wl != "eval" else 1
         probe = time_cpu(wl, n, (H, W), 1, 1)

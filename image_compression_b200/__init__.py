@@ -7,9 +7,9 @@ hieu1999210/image_compression behind that repository's own module surface.
 """
 from . import _lib
 from .hotpath import compute_mode, get_compute_mode, set_compute_mode
-from . import modelling, utils
+from . import modelling, solver, utils
 from .modelling import build_model
 from .utils import get_cfg_defaults, get_recipe_cfg
 
-__all__ = ["modelling", "utils", "build_model", "get_cfg_defaults", "get_recipe_cfg", "set_compute_mode",
+__all__ = ["modelling", "solver", "utils", "build_model", "get_cfg_defaults", "get_recipe_cfg", "set_compute_mode",
            "get_compute_mode", "compute_mode"]

@@ -16,7 +16,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(_HERE, "libhpcodec_sm100a.so")
 SOURCES = ["hpc_api.cu", "entropy_kernels.cu", "loss_kernels.cu", "igemm_simt.cu", "thin_kernels.cu",
-           "igemm_umma.cu", "thin_umma.cu", "gdn_umma.cu", "misc_kernels.cu"]
+           "igemm_umma.cu", "thin_umma.cu", "gdn_umma.cu", "misc_kernels.cu", "optim_kernels.cu"]
 # no --use_fast_math: IEEE division / sqrt / expf are part of the parity contract
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC"]
@@ -29,7 +29,8 @@ MAX_TAPS, MAX_PHASES = 25, 4
  EPI_SIGN_ADD) = range(9)
 DIST_LAPLACE, DIST_GAUSS = 0, 1
 (PROF_IGEMM_FWD, PROF_IGEMM_WGRAD, PROF_CONDITIONAL, PROF_FACTORIZED, PROF_THIN, PROF_DISTORTION, PROF_GDN) = range(7)
-PROF_NAMES = ("igemm_fwd_umma", "igemm_wgrad_umma", "conditional", "factorized", "thin_c3", "distortion", "gdn_fused")
+PROF_NAMES = ("igemm_fwd_umma", "igemm_wgrad_umma", "conditional", "factorized", "thin_c3", "distortion", "gdn_fused",
+              "optim")
 MSSSIM_LOSS_LOG, MSSSIM_LOSS_PLAIN, MSSSIM_METRIC, SSIM_LOSS, SSIM_METRIC = range(5)
 
 
@@ -111,6 +112,11 @@ class IgemmWgradParams(Structure):
     ]
 
 
+class AdamwSeg(Structure):
+    _fields_ = [("p", c_void_p), ("g", c_void_p), ("m", c_void_p), ("v", c_void_p), ("n", c_int64),
+                ("decay", c_float), ("neg_step_size", c_float), ("bc2_sqrt", c_float), ("reserved", c_float)]
+
+
 class DistTerms(Structure):
     _fields_ = [("dist", c_void_p * 4), ("n", c_int * 4), ("scale", c_float * 4), ("n_terms", c_int)]
 
@@ -179,6 +185,7 @@ _SIGNATURES = {
     "hpc_nchw_to_nhwc": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "hpc_nhwc_to_nchw": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "hpc_cast": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int64, c_void_p]),
+    "hpc_adamw_step": (c_int, [POINTER(AdamwSeg), c_int, c_double, c_double, c_double, c_double, c_int, c_void_p]),
     "hpc_conv_c3_fwd": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_int, c_int, c_int, c_int,
                                 c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "hpc_deconv_c3_fwd": (c_int, [c_void_p, c_int, c_void_p, c_int64, c_int64, c_void_p, c_int, c_int, c_int,

@@ -73,7 +73,10 @@ def get_cfg_defaults():
                               "LOG_SCALE": False, "EPS": 1e-5},
                      "MS_SSIM_WEIGHTS": [0.0448, 0.2856, 0.3001, 0.2363, 0.1333]},
         },
-        "SOLVER": {"GD_STEPS": 1, "IMS_PER_BATCH": 2, "GRAD_CLIP": 0.0, "BASE_LR": 0.001},
+        # utils/config.py:86-127 of the reference (the keys solver/optim.py and engine/trainer.py read)
+        "SOLVER": {"GD_STEPS": 1, "IMS_PER_BATCH": 2, "GRAD_CLIP": 0.0, "BASE_LR": 0.001, "OPT_NAME": "sgd",
+                   "EPS": 1e-4, "WEIGHT_DECAY": 0.0005, "WEIGHT_DECAY_BIAS": 0.0, "BIAS_LR_FACTOR": 1.0,
+                   "MOMENTUM": 0.9, "USE_NESTEROV": False},
         "VAL": {"BATCH_SIZE": 1},
     })
 
@@ -81,11 +84,11 @@ def get_cfg_defaults():
 # the overrides the shipped recipes apply on top of the defaults (configs/*.yaml)
 RECIPES = {
     **{f"psnr_{l}": {"MODEL": {"LOSS": {"DISTORTION_LOSS_WEIGHT": float(l), "REDUCTION": "mean"}},
-                     "DATA": {"SIZE": 192}, "SOLVER": {"IMS_PER_BATCH": 64, "GRAD_CLIP": 5.0, "BASE_LR": 1e-4}}
+                     "DATA": {"SIZE": 192}, "SOLVER": {"IMS_PER_BATCH": 64, "GRAD_CLIP": 5.0, "BASE_LR": 1e-4, "OPT_NAME": "adamw"}}
        for l in (256, 512, 1024, 2048, 4096, 8192)},
     **{f"ssim_{l}": {"MODEL": {"LOSS": {"DISTORTION_LOSS_NAMES": ["MS_SSIMLoss"], "SSIM": {"LOG_SCALE": True},
                                         "DISTORTION_LOSS_WEIGHT": float(l), "REDUCTION": "mean"}},
-                     "DATA": {"SIZE": 192}, "SOLVER": {"IMS_PER_BATCH": 64, "GRAD_CLIP": 5.0, "BASE_LR": 1e-4}}
+                     "DATA": {"SIZE": 192}, "SOLVER": {"IMS_PER_BATCH": 64, "GRAD_CLIP": 5.0, "BASE_LR": 1e-4, "OPT_NAME": "adamw"}}
        for l in (8, 16, 32, 64, 128, 256, 512)},
 }
 

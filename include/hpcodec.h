@@ -59,7 +59,8 @@ int hpc_device_is_sm100(void);
 #define HPC_PROF_THIN 4        /* conv_c3 / deconv_c3 / wgrad_c3 (3-channel head and tail)        (bytes) */
 #define HPC_PROF_DISTORTION 5  /* clamp+SSE fwd/bwd, SSIM levels (K6/K7)                          (bytes) */
 #define HPC_PROF_GDN 6        /* fused GDN forward / backward (gdn_umma.cu)                      (bytes) */
-#define HPC_PROF_NCLASSES 7
+#define HPC_PROF_OPTIM 7      /* fused clip + AdamW step (optim_kernels.cu)                      (bytes) */
+#define HPC_PROF_NCLASSES 8
 int hpc_prof_enable(int on); /* on!=0: clear the records and start; 0: stop recording (records kept) */
 int hpc_prof_pause(int paused); /* suspend / resume recording, records kept (needed around CUDA-graph capture) */
 int hpc_prof_read(int cls, double* ms_total, unsigned long long* launches, double* work_total);
@@ -367,6 +368,22 @@ int hpc_nchw_to_nhwc(const float* src, void* dst, int dtype, int N, int C, int H
 int hpc_nhwc_to_nchw(const void* src, int dtype, float* dst, int N, int C, int H, int W, hpc_stream_t stream);
 /* elementwise cast between float and lp (n elements) */
 int hpc_cast(const void* src, int src_dtype, void* dst, int dst_dtype, int64_t n, hpc_stream_t stream);
+
+/* Fused clip_grad_value_ + AdamW step over every parameter tensor in one launch.
+ * Replaces engine/trainer.py:189-192 (clip_grad_value_(params, GRAD_CLIP); optimizer.step()) for the optimizer
+ * solver/optim.py:27-39 builds: torch.optim.AdamW over one parameter group per tensor, each with its own lr and
+ * weight decay.  One segment per tensor; the host passes the scalars torch derives in double per group and step t:
+ *   decay = 1 - lr*weight_decay,  neg_step_size = -lr / (1 - beta1^t),  bc2_sqrt = sqrt(1 - beta2^t).
+ * beta1, beta2, eps, clip are doubles (torch forms 1 - beta in double before the fp32 cast).  clip <= 0: no clipping.  write_clipped_grad != 0: the clamped gradient is also written back (what
+ * clip_grad_value_ leaves in .grad).  p, g, m (exp_avg), v (exp_avg_sq): fp32 device pointers, n elements each. */
+#define HPC_ADAMW_MAX_SEGS 56
+typedef struct {
+  float* p; float* g; float* m; float* v;
+  int64_t n;
+  float decay, neg_step_size, bc2_sqrt, reserved;
+} hpc_adamw_seg;
+int hpc_adamw_step(const hpc_adamw_seg* segs, int nseg, double beta1, double beta2, double eps, double clip,
+                   int write_clipped_grad, hpc_stream_t stream);
 
 /* Thin-channel layers (Cin=3 head of g_a, Cout=3 tail of g_s): K=75 is memory-bound.
  * conv_c3_fwd:   Conv2d(Cs->Cw,5,s2,p2): x NCHW float (N,Cs,H,W), w float (Cw,Cs,5,5) with

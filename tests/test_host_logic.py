@@ -87,3 +87,26 @@ def test_cpu_tensor_is_rejected_loudly():
     m = pkg.build_model(pkg.get_recipe_cfg("psnr_256"))
     with pytest.raises(RuntimeError, match="CUDA"):
         m(torch.rand(1, 3, 64, 64))
+
+
+def test_fused_adamw_host_logic():
+    """solver.make_optimizer mirrors solver/optim.py:20-46 (one group per tensor, the "bias" rule) and refuses CPU
+    tensors (no fallback); non-adamw optimizers are left to the reference."""
+    import image_compression_b200 as pkg
+    from image_compression_b200.solver import FusedAdamW, make_optimizer
+    cfg = pkg.get_recipe_cfg("psnr_256")
+    model = pkg.build_model(cfg)
+    opt = make_optimizer(cfg, model)
+    assert isinstance(opt, FusedAdamW) and len(opt.param_groups) == 50
+    names = [n for n, _ in model.named_parameters()]
+    for n, g in zip(names, opt.param_groups):
+        assert g["weight_decay"] == (cfg.SOLVER.WEIGHT_DECAY_BIAS if "bias" in n else cfg.SOLVER.WEIGHT_DECAY)
+        assert g["lr"] == cfg.SOLVER.BASE_LR and g["eps"] == cfg.SOLVER.EPS
+    assert sum("bias" in n for n in names) == 17
+    for p in model.parameters():
+        p.grad = torch.zeros_like(p)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        opt.step()
+    cfg.SOLVER.OPT_NAME = "sgd"
+    with pytest.raises(NotImplementedError):
+        make_optimizer(cfg, model)
