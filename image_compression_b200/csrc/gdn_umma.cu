@@ -854,6 +854,7 @@ gdn_bwd_dual_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
       int nset[2] = {(mine + 1) / 2, mine / 2};
       int jA[2] = {0, 0}, jD[2] = {0, 0};
       uint32_t dg_started = 0, spins = 0;
+      int nextD = 0;      // d(gamma) accumulates the half-tiles in index order (k = 2 j + s): bit-reproducible sums
       while (jD[0] < nset[0] || jD[1] < nset[1]) {
         bool progressed = false;
 #pragma unroll
@@ -871,7 +872,7 @@ gdn_bwd_dual_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
               ++jA[s];
               progressed = true;
             }
-          } else if (jD[s] < jA[s]) {
+          } else if (jD[s] < jA[s] && 2 * jD[s] + s == nextD) {
             if (mbar_try_wait(&out_full[s], jD[s] & 1)) {
               tc_fence_after();
 #pragma unroll
@@ -891,6 +892,7 @@ gdn_bwd_dual_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
               dg_started = 1;
               mma_commit(&in_empty[s]);
               ++jD[s];
+              ++nextD;
               progressed = true;
             }
           }

@@ -23,7 +23,7 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --
 timeout 900 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 3000 --csv --log-file $OUT/traffic.csv \
     python bench.py --steps 2 --warmup 1 --no-cpu-baseline > $OUT/ncu_traffic.log 2>&1; echo "ncu traffic rc=$?" | tee -a $OUT/summary.txt
 # full captures of the dominant kernels (one training step's worth of each)
-for spec in "igemm_fwd_umma:24:8" "igemm_wgrad_umma:12:4" "gdn_bwd_dual:6:3" "gdn_fwd_umma:6:3" "conv_c3_umma:2:2" "wgrad_c3_umma_kernel:1:1" "deconv_c3_umma:1:1"; do
+for spec in "igemm_fwd_umma:24:8" "igemm_wgrad_umma:12:4" "gdn_bwd_dual:6:3" "gdn_fwd_umma:6:3" "conv_c3_umma:2:2" "wgrad_c3_umma_kernel:1:1" "deconv_c3_umma:1:1" "conditional_:2:2" "adamw_step:3:1"; do
   IFS=: read RE SKIP CNT <<< "$spec"
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:$RE -s $SKIP -c $CNT -o $OUT/${RE}_full -f \
       python bench.py --steps 1 --warmup 1 --no-cpu-baseline > $OUT/ncu_full_$RE.log 2>&1; echo "ncu full $RE rc=$?" | tee -a $OUT/summary.txt
