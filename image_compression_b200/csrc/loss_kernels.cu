@@ -166,10 +166,12 @@ __device__ __forceinline__ SsimTerms ssim_terms(float mu1, float mu2, float e11,
   t.cs = cs;
   t.ssim = cs * lum;
   if (want_grad) {
-    float dcs_dmu2 = (-2.f * mu1 + 2.f * mu2 * cs) / dcs;
-    float dcs_dE22 = -cs / dcs;
-    float dcs_dE12 = 2.f / dcs;
-    float dlum_dmu2 = 2.f * (mu1 - lum * mu2) / dl;
+    // one reciprocal per denominator for the four gradient quotients (the loss VALUES above keep the true division)
+    const float inv_dcs = 1.f / dcs, inv_dl = 1.f / dl;
+    float dcs_dmu2 = (-2.f * mu1 + 2.f * mu2 * cs) * inv_dcs;
+    float dcs_dE22 = -cs * inv_dcs;
+    float dcs_dE12 = 2.f * inv_dcs;
+    float dlum_dmu2 = 2.f * (mu1 - lum * mu2) * inv_dl;
     t.dA_c = dcs_dmu2; t.dB_c = dcs_dE22; t.dC_c = dcs_dE12;
     t.dA_s = lum * dcs_dmu2 + cs * dlum_dmu2;
     t.dB_s = lum * dcs_dE22;
@@ -327,6 +329,257 @@ ssim_bwd_filter_kernel(const float* __restrict__ img1, const float* __restrict__
   }
 }
 
+// ---------------------------------------------------------------------------------------
+// Register-blocked SSIM level for the shipped 11-tap window (loss.py:57-66 / metric.py:47-56).  The kernels above
+// issue one shared-memory load per multiply-add (~120 LDS per output pixel: bound by shared-memory bandwidth at 5% of
+// HBM speed).  Here a block owns a 64x32 output tile (halo overhead 1.5x instead of 2.1x) and every thread produces
+// 8 outputs along the filtered direction from 18 loaded values:
+//   vertical pass   thread = (column, strip of 8 rows): 18 x 2 loads, the five products formed once per pixel;
+//   horizontal pass thread = (row, group of 8 columns): 18 x 5 loads (lanes differ in the ROW: the odd row pitch
+//                   makes the accesses conflict free), then the SSIM terms of its 8 pixels.
+// ~16 LDS and ~120 FMA per output pixel.  The filter taps sit in registers.  Same outputs as MODE 0 / 1 above.
+// ---------------------------------------------------------------------------------------
+constexpr int S2_TW = 64, S2_TH = 32, S2_R = 8, S2_FS = 11;
+constexpr int S2_PW = S2_TW + S2_FS - 1, S2_PH = S2_TH + S2_FS - 1, S2_PP = S2_PW | 1;     // 74, 42, pitch 75
+constexpr int S2_SMEM_FWD = (2 * S2_PH + 5 * S2_TH) * S2_PP * (int)sizeof(float);
+constexpr int S2_SMEM_BWD = (3 * S2_PH + 3 * S2_TH) * S2_PP * (int)sizeof(float);
+
+template <int MODE>
+__global__ void __launch_bounds__(256)
+ssim_level_rb_kernel(const float* __restrict__ img1, const float* __restrict__ img2, int C, int H, int W,
+                     const float* __restrict__ filt, float in_scale, float c1, float c2,
+                     unsigned long long* __restrict__ fx_sums, const float* __restrict__ g_ssim,
+                     const float* __restrict__ g_cs, float* __restrict__ maps) {
+  extern __shared__ float s2m[];
+  float* p1 = s2m;                          // [PH][PP]
+  float* p2 = p1 + S2_PH * S2_PP;           // [PH][PP]
+  float* vb = p2 + S2_PH * S2_PP;           // [5][TH][PP]   vertically filtered moments
+  __shared__ float red[32];
+  constexpr int FS = S2_FS, R = S2_R;
+  const int plane = blockIdx.z, n = plane / C;
+  const int OH = H - FS + 1, OW = W - FS + 1;
+  const int ox0 = blockIdx.x * S2_TW, oy0 = blockIdx.y * S2_TH;
+  const int tid = threadIdx.x;
+  float f[FS];
+#pragma unroll
+  for (int k = 0; k < FS; ++k) f[k] = __ldg(filt + k);
+  const float* a = img1 + (int64_t)plane * H * W;
+  const float* b = img2 + (int64_t)plane * H * W;
+  for (int i = tid; i < S2_PH * S2_PW; i += 256) {
+    const int r = i / S2_PW, c = i % S2_PW;
+    const int gy = oy0 + r, gx = ox0 + c;
+    float v1 = 0.f, v2 = 0.f;
+    if (gy < H && gx < W) {
+      v1 = a[(int64_t)gy * W + gx] * in_scale;
+      v2 = b[(int64_t)gy * W + gx] * in_scale;
+    }
+    p1[r * S2_PP + c] = v1;
+    p2[r * S2_PP + c] = v2;
+  }
+  __syncthreads();
+  // vertical pass
+  for (int i = tid; i < S2_PW * (S2_TH / R); i += 256) {
+    const int c = i % S2_PW, r0 = (i / S2_PW) * R;
+    float acc[5][R];
+#pragma unroll
+    for (int m = 0; m < 5; ++m)
+#pragma unroll
+      for (int j = 0; j < R; ++j) acc[m][j] = 0.f;
+#pragma unroll
+    for (int rr = 0; rr < R + FS - 1; ++rr) {
+      const float u = p1[(r0 + rr) * S2_PP + c], v = p2[(r0 + rr) * S2_PP + c];
+      const float q[5] = {u, v, u * u, v * v, u * v};
+#pragma unroll
+      for (int j = 0; j < R; ++j) {
+        const int k = rr - j;                       // compile-time after unrolling
+        if (k >= 0 && k < FS) {
+#pragma unroll
+          for (int m = 0; m < 5; ++m) acc[m][j] += f[k] * q[m];
+        }
+      }
+    }
+#pragma unroll
+    for (int m = 0; m < 5; ++m)
+#pragma unroll
+      for (int j = 0; j < R; ++j) vb[(m * S2_TH + r0 + j) * S2_PP + c] = acc[m][j];
+  }
+  __syncthreads();
+  // horizontal pass + SSIM terms: S2_TH rows x (S2_TW / R) groups = 256 tasks
+  float acc_s = 0.f, acc_c = 0.f, gs = 0.f, gc = 0.f;
+  if (MODE == 1) { gs = g_ssim[n]; gc = g_cs[n]; }
+  {
+    const int row = tid % S2_TH, x0 = (tid / S2_TH) * R;
+    float o[5][R];
+#pragma unroll
+    for (int m = 0; m < 5; ++m) {
+      float w[R + FS - 1];
+#pragma unroll
+      for (int j = 0; j < R + FS - 1; ++j) w[j] = vb[(m * S2_TH + row) * S2_PP + x0 + j];
+#pragma unroll
+      for (int j = 0; j < R; ++j) {
+        float t = 0.f;
+#pragma unroll
+        for (int k = 0; k < FS; ++k) t += f[k] * w[j + k];
+        o[m][j] = t;
+      }
+    }
+    const int oy = oy0 + row;
+    float mo[3][R];
+#pragma unroll
+    for (int j = 0; j < R; ++j) {
+      const int ox = ox0 + x0 + j;
+      mo[0][j] = mo[1][j] = mo[2][j] = 0.f;
+      if (oy < OH && ox < OW) {
+        const SsimTerms t = ssim_terms(o[0][j], o[1][j], o[2][j], o[3][j], o[4][j], c1, c2, MODE == 1);
+        if (MODE == 0) {
+          acc_s += t.ssim;
+          acc_c += t.cs;
+        } else {
+          mo[0][j] = gs * t.dA_s + gc * t.dA_c;
+          mo[1][j] = gs * t.dB_s + gc * t.dB_c;
+          mo[2][j] = gs * t.dC_s + gc * t.dC_c;
+        }
+      }
+    }
+    if (MODE == 1) {
+      // lanes of the pass above differ in the ROW: stage the three maps in shared memory (over the moments, once
+      // every thread has read them) and store them with the lanes along x
+      __syncthreads();
+#pragma unroll
+      for (int m = 0; m < 3; ++m)
+#pragma unroll
+        for (int j = 0; j < R; ++j) vb[(m * S2_TH + row) * S2_PP + x0 + j] = mo[m][j];
+      __syncthreads();
+      const int64_t msz = (int64_t)gridDim.z * OH * OW;
+      for (int i = tid; i < 3 * S2_TH * S2_TW; i += 256) {
+        const int x = i % S2_TW, r = (i / S2_TW) % S2_TH, m = i / (S2_TW * S2_TH);
+        const int yy = oy0 + r, xx = ox0 + x;
+        if (yy < OH && xx < OW)
+          maps[m * msz + (int64_t)plane * OH * OW + (int64_t)yy * OW + xx] = vb[(m * S2_TH + r) * S2_PP + x];
+      }
+    }
+  }
+  if (MODE == 0) {
+    const float ss = block_sum(acc_s, red);
+    const float cc = block_sum(acc_c, red);
+    if (tid == 0) {        // 32.32 fixed point (|partial| <= 2048): order-independent integer accumulation
+      atomicAdd(&fx_sums[2 * n], (unsigned long long)__double2ll_rn((double)ss * 4294967296.0));
+      atomicAdd(&fx_sums[2 * n + 1], (unsigned long long)__double2ll_rn((double)cc * 4294967296.0));
+    }
+  }
+}
+
+// backward filter, register blocked the same way: g_img2(p) = in_scale * (FA + 2 x2 FB + x1 FC), F* = full
+// correlation of the three maps with g (x) g
+__global__ void __launch_bounds__(256)
+ssim_bwd_filter_rb_kernel(const float* __restrict__ img1, const float* __restrict__ img2, int H, int W,
+                          const float* __restrict__ filt, float in_scale, const float* __restrict__ maps, int64_t msz,
+                          float* __restrict__ g_img2, int accumulate) {
+  extern __shared__ float s2m[];
+  float* pm = s2m;                          // [3][PH][PP]
+  float* vb = pm + 3 * S2_PH * S2_PP;       // [3][TH][PP]
+  constexpr int FS = S2_FS, R = S2_R;
+  const int plane = blockIdx.z;
+  const int OH = H - FS + 1, OW = W - FS + 1;
+  const int x0t = blockIdx.x * S2_TW, y0t = blockIdx.y * S2_TH;
+  const int tid = threadIdx.x;
+  float f[FS];
+#pragma unroll
+  for (int k = 0; k < FS; ++k) f[k] = __ldg(filt + k);
+  // patch covers map coords [y0-(FS-1), y0+TH) x [x0-(FS-1), x0+TW)
+  for (int i = tid; i < S2_PH * S2_PW; i += 256) {
+    const int r = i / S2_PW, c = i % S2_PW;
+    const int qy = y0t - (FS - 1) + r, qx = x0t - (FS - 1) + c;
+    const bool ok = (qy >= 0 && qy < OH && qx >= 0 && qx < OW);
+    const int64_t o = (int64_t)plane * OH * OW + (int64_t)qy * OW + qx;
+    pm[(0 * S2_PH + r) * S2_PP + c] = ok ? maps[o] : 0.f;
+    pm[(1 * S2_PH + r) * S2_PP + c] = ok ? maps[msz + o] : 0.f;
+    pm[(2 * S2_PH + r) * S2_PP + c] = ok ? maps[2 * msz + o] : 0.f;
+  }
+  __syncthreads();
+  // vertical: out row j (pixel y0+j) = sum_d f[d] M(y0+j-d): patch row of (y0+j-d) = j + FS-1 - d
+  for (int i = tid; i < S2_PW * (S2_TH / R); i += 256) {
+    const int c = i % S2_PW, r0 = (i / S2_PW) * R;
+    float acc[3][R];
+#pragma unroll
+    for (int m = 0; m < 3; ++m)
+#pragma unroll
+      for (int j = 0; j < R; ++j) acc[m][j] = 0.f;
+#pragma unroll
+    for (int rr = 0; rr < R + FS - 1; ++rr) {
+      float q[3];
+#pragma unroll
+      for (int m = 0; m < 3; ++m) q[m] = pm[(m * S2_PH + r0 + rr) * S2_PP + c];
+#pragma unroll
+      for (int j = 0; j < R; ++j) {
+        const int d = j + FS - 1 - rr;
+        if (d >= 0 && d < FS) {
+#pragma unroll
+          for (int m = 0; m < 3; ++m) acc[m][j] += f[d] * q[m];
+        }
+      }
+    }
+#pragma unroll
+    for (int m = 0; m < 3; ++m)
+#pragma unroll
+      for (int j = 0; j < R; ++j) vb[(m * S2_TH + r0 + j) * S2_PP + c] = acc[m][j];
+  }
+  __syncthreads();
+  {
+    const int row = tid % S2_TH, xg = (tid / S2_TH) * R;
+    float o[3][R];
+#pragma unroll
+    for (int m = 0; m < 3; ++m) {
+      float w[R + FS - 1];
+#pragma unroll
+      for (int j = 0; j < R + FS - 1; ++j) w[j] = vb[(m * S2_TH + row) * S2_PP + xg + j];
+#pragma unroll
+      for (int j = 0; j < R; ++j) {
+        float t = 0.f;
+#pragma unroll
+        for (int d = 0; d < FS; ++d) t += f[d] * w[j + FS - 1 - d];
+        o[m][j] = t;
+      }
+    }
+    // stage the filtered maps (lanes differ in the row) and finish with the lanes along x: coalesced image loads
+    // and gradient stores
+    __syncthreads();
+#pragma unroll
+    for (int m = 0; m < 3; ++m)
+#pragma unroll
+      for (int j = 0; j < R; ++j) vb[(m * S2_TH + row) * S2_PP + xg + j] = o[m][j];
+    __syncthreads();
+  }
+  for (int i = tid; i < S2_TH * S2_TW; i += 256) {
+    const int xl = i % S2_TW, r = i / S2_TW;
+    const int y = y0t + r, x = x0t + xl;
+    if (y < H && x < W) {
+      const int64_t o = (int64_t)plane * H * W + (int64_t)y * W + x;
+      const float x1 = img1[o] * in_scale, x2 = img2[o] * in_scale;
+      const float v = in_scale * (vb[(0 * S2_TH + r) * S2_PP + xl] + 2.f * x2 * vb[(1 * S2_TH + r) * S2_PP + xl] +
+                                  x1 * vb[(2 * S2_TH + r) * S2_PP + xl]);
+      g_img2[o] = accumulate ? (g_img2[o] + v) : v;
+    }
+  }
+}
+
+static int ssim_rb_attrs() {
+  static bool done = false;
+  if (!done) {
+    HPC_CUDA(cudaFuncSetAttribute(ssim_level_rb_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, S2_SMEM_FWD));
+    HPC_CUDA(cudaFuncSetAttribute(ssim_level_rb_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, S2_SMEM_FWD));
+    HPC_CUDA(cudaFuncSetAttribute(ssim_bwd_filter_rb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, S2_SMEM_BWD));
+    done = true;
+  }
+  return HPC_OK;
+}
+// the register-blocked kernels serve the 11-tap window on planes that give their 64x32 tiles something to do
+static bool ssim_use_rb(int H, int W, int fs) {
+  static int off = -1;
+  if (off < 0) { const char* e = getenv("HPC_SSIM_RB"); off = (e && e[0] == '0') ? 1 : 0; }
+  return !off && fs == S2_FS && H >= 24 && W >= 24;
+}
+
 static int ssim_check(int N, int C, int H, int W, int fs) {
   HPC_REQUIRE(N > 0 && C > 0, HPC_ERR_BAD_SHAPE, "ssim: empty batch");
   HPC_REQUIRE(fs >= 1 && fs <= SS_MAXF, HPC_ERR_UNSUPPORTED, "ssim: filter size %d not in [1,%d]", fs, SS_MAXF);
@@ -346,9 +599,16 @@ int hpc_ssim_level_fwd(const float* img1, const float* img2, int N, int C, int H
   auto* fx = (unsigned long long*)scratch;
   HPC_CUDA(cudaMemsetAsync(fx, 0, (size_t)N * 16, st));
   const int OH = H - fs + 1, OW = W - fs + 1;
-  dim3 grid((OW + SS_TW - 1) / SS_TW, (OH + SS_TH - 1) / SS_TH, N * C);
-  ssim_level_kernel<0><<<grid, dim3(32, 8), 0, st>>>(img1, img2, C, H, W, filt1d, fs, in_scale, c1, c2, fx, nullptr,
-                                                    nullptr, nullptr);
+  if (ssim_use_rb(H, W, fs)) {
+    if ((rc = ssim_rb_attrs())) return rc;
+    dim3 grid((OW + S2_TW - 1) / S2_TW, (OH + S2_TH - 1) / S2_TH, N * C);
+    ssim_level_rb_kernel<0><<<grid, 256, S2_SMEM_FWD, st>>>(img1, img2, C, H, W, filt1d, in_scale, c1, c2, fx, nullptr,
+                                                           nullptr, nullptr);
+  } else {
+    dim3 grid((OW + SS_TW - 1) / SS_TW, (OH + SS_TH - 1) / SS_TH, N * C);
+    ssim_level_kernel<0><<<grid, dim3(32, 8), 0, st>>>(img1, img2, C, H, W, filt1d, fs, in_scale, c1, c2, fx, nullptr,
+                                                      nullptr, nullptr);
+  }
   HPC_LAUNCH_CHECK();
   ssim_sums_finish_kernel<<<(N + 127) / 128, 128, 0, st>>>(fx, N, ssim_sum, cs_sum);
   HPC_LAUNCH_CHECK();
@@ -362,6 +622,18 @@ int hpc_ssim_level_bwd(const float* img1, const float* img2, int N, int C, int H
   if (rc) return rc;
   auto st = (cudaStream_t)stream;
   const int OH = H - fs + 1, OW = W - fs + 1;
+  if (ssim_use_rb(H, W, fs)) {
+    if ((rc = ssim_rb_attrs())) return rc;
+    dim3 grid((OW + S2_TW - 1) / S2_TW, (OH + S2_TH - 1) / S2_TH, N * C);
+    ssim_level_rb_kernel<1><<<grid, 256, S2_SMEM_FWD, st>>>(img1, img2, C, H, W, filt1d, in_scale, c1, c2, nullptr,
+                                                           g_ssim, g_cs, maps);
+    HPC_LAUNCH_CHECK();
+    dim3 grid2((W + S2_TW - 1) / S2_TW, (H + S2_TH - 1) / S2_TH, N * C);
+    ssim_bwd_filter_rb_kernel<<<grid2, 256, S2_SMEM_BWD, st>>>(img1, img2, H, W, filt1d, in_scale, maps,
+                                                               (int64_t)N * C * OH * OW, g_img2, accumulate);
+    HPC_LAUNCH_CHECK();
+    return HPC_OK;
+  }
   dim3 grid((OW + SS_TW - 1) / SS_TW, (OH + SS_TH - 1) / SS_TH, N * C);
   ssim_level_kernel<1><<<grid, dim3(32, 8), 0, st>>>(img1, img2, C, H, W, filt1d, fs, in_scale, c1, c2, nullptr,
                                                     g_ssim, g_cs, maps);
@@ -378,48 +650,41 @@ int hpc_ssim_level_bwd(const float* img1, const float* img2, int N, int C, int H
 // ---------------------------------------------------------------------------------------
 __device__ __forceinline__ int reflect_idx(int i, int n) { return i < n ? i : 2 * n - 2 - i; }
 
-__global__ void avgpool2_fwd_kernel(const float* __restrict__ in, float* __restrict__ out, int64_t total, int H, int W,
-                                    int OH, int OW, float scale) {
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    int ox = (int)(i % OW);
-    int64_t t = i / OW;
-    int oy = (int)(t % OH);
-    int64_t pl = t / OH;
-    const float* p = in + pl * (int64_t)H * W;
-    int y0 = 2 * oy, y1 = reflect_idx(2 * oy + 1, H), x0 = 2 * ox, x1 = reflect_idx(2 * ox + 1, W);
-    // F.avg_pool2d sums the window then divides
-    float s = p[(int64_t)y0 * W + x0] + p[(int64_t)y0 * W + x1] + p[(int64_t)y1 * W + x0] + p[(int64_t)y1 * W + x1];
-    out[i] = scale * (s * 0.25f);
-  }
+// grid = (ceil(OW / 256), OH, planes): no 64-bit index arithmetic per element
+__global__ void avgpool2_fwd_kernel(const float* __restrict__ in, float* __restrict__ out, int H, int W, int OH, int OW,
+                                    float scale) {
+  const int ox = blockIdx.x * blockDim.x + threadIdx.x, oy = blockIdx.y;
+  if (ox >= OW) return;
+  const float* p = in + (int64_t)blockIdx.z * H * W;
+  const int y0 = 2 * oy, y1 = reflect_idx(2 * oy + 1, H), x0 = 2 * ox, x1 = reflect_idx(2 * ox + 1, W);
+  // F.avg_pool2d sums the window then divides
+  const float s = p[(int64_t)y0 * W + x0] + p[(int64_t)y0 * W + x1] + p[(int64_t)y1 * W + x0] + p[(int64_t)y1 * W + x1];
+  out[((int64_t)blockIdx.z * OH + oy) * OW + ox] = scale * (s * 0.25f);
 }
 // gather form of the backward: each input pixel collects from the (<=2x2) outputs it fed
-__global__ void avgpool2_bwd_kernel(const float* __restrict__ gout, float* __restrict__ gin, int64_t total, int H,
-                                    int W, int OH, int OW, float scale, int accumulate) {
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    int x = (int)(i % W);
-    int64_t t = i / W;
-    int y = (int)(t % H);
-    int64_t pl = t / H;
-    const float* g = gout + pl * (int64_t)OH * OW;
-    // rows of the padded image that map to y: y itself, plus the reflected row H (== H-2) when H is odd
-    float wy_main = 1.f, wx_main = 1.f;
-    float v = 0.f;
-    int oy = y >> 1, ox = x >> 1;
-    float acc = g[(int64_t)oy * OW + ox] * wy_main * wx_main;
-    bool ry = (H & 1) && (y == H - 2);  // padded row H reads row H-2, belongs to output row (H)/2 = OH-1
-    bool rx = (W & 1) && (x == W - 2);
-    if (ry) acc += g[(int64_t)(OH - 1) * OW + ox];
-    if (rx) acc += g[(int64_t)oy * OW + (OW - 1)];
-    if (ry && rx) acc += g[(int64_t)(OH - 1) * OW + (OW - 1)];
-    v = scale * 0.25f * acc;
-    gin[i] = accumulate ? gin[i] + v : v;
-  }
+__global__ void avgpool2_bwd_kernel(const float* __restrict__ gout, float* __restrict__ gin, int H, int W, int OH,
+                                    int OW, float scale, int accumulate) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= W) return;
+  const float* g = gout + (int64_t)blockIdx.z * OH * OW;
+  const int oy = y >> 1, ox = x >> 1;
+  float acc = g[(int64_t)oy * OW + ox];
+  // rows of the padded image that map to y: y itself, plus the reflected row H (== H-2) when H is odd
+  const bool ry = (H & 1) && (y == H - 2);  // padded row H reads row H-2, belongs to output row (H)/2 = OH-1
+  const bool rx = (W & 1) && (x == W - 2);
+  if (ry) acc += g[(int64_t)(OH - 1) * OW + ox];
+  if (rx) acc += g[(int64_t)oy * OW + (OW - 1)];
+  if (ry && rx) acc += g[(int64_t)(OH - 1) * OW + (OW - 1)];
+  const float v = scale * 0.25f * acc;
+  const int64_t i = ((int64_t)blockIdx.z * H + y) * W + x;
+  gin[i] = accumulate ? gin[i] + v : v;
 }
 int hpc_avgpool2_fwd(const float* in, float* out, int NC, int H, int W, float scale, hpc_stream_t stream) {
   HPC_REQUIRE(NC > 0 && H >= 2 && W >= 2, HPC_ERR_BAD_SHAPE, "hpc_avgpool2_fwd: bad shape NC=%d H=%d W=%d", NC, H, W);
   int OH = (H + 1) / 2, OW = (W + 1) / 2;
-  int64_t total = (int64_t)NC * OH * OW;
-  avgpool2_fwd_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(in, out, total, H, W, OH, OW, scale);
+  HPC_REQUIRE(NC <= 65535 && OH <= 65535, HPC_ERR_UNSUPPORTED, "hpc_avgpool2_fwd: NC=%d or OH=%d > 65535", NC, OH);
+  const int th = OW >= 256 ? 256 : (OW >= 128 ? 128 : 64);
+  avgpool2_fwd_kernel<<<dim3((OW + th - 1) / th, OH, NC), th, 0, (cudaStream_t)stream>>>(in, out, H, W, OH, OW, scale);
   HPC_LAUNCH_CHECK();
   return HPC_OK;
 }
@@ -427,9 +692,10 @@ int hpc_avgpool2_bwd(const float* gout, float* gin, int NC, int H, int W, float 
                      hpc_stream_t stream) {
   HPC_REQUIRE(NC > 0 && H >= 2 && W >= 2, HPC_ERR_BAD_SHAPE, "hpc_avgpool2_bwd: bad shape");
   int OH = (H + 1) / 2, OW = (W + 1) / 2;
-  int64_t total = (int64_t)NC * H * W;
-  avgpool2_bwd_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(gout, gin, total, H, W, OH, OW, scale,
-                                                                            accumulate);
+  HPC_REQUIRE(NC <= 65535 && H <= 65535, HPC_ERR_UNSUPPORTED, "hpc_avgpool2_bwd: NC=%d or H=%d > 65535", NC, H);
+  const int th = W >= 256 ? 256 : (W >= 128 ? 128 : 64);
+  avgpool2_bwd_kernel<<<dim3((W + th - 1) / th, H, NC), th, 0, (cudaStream_t)stream>>>(gout, gin, H, W, OH, OW, scale,
+                                                                                    accumulate);
   HPC_LAUNCH_CHECK();
   return HPC_OK;
 }
