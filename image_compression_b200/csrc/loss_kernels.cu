@@ -365,16 +365,17 @@ ssim_level_rb_kernel(const float* __restrict__ img1, const float* __restrict__ i
   for (int k = 0; k < FS; ++k) f[k] = __ldg(filt + k);
   const float* a = img1 + (int64_t)plane * H * W;
   const float* b = img2 + (int64_t)plane * H * W;
-  for (int i = tid; i < S2_PH * S2_PW; i += 256) {
-    const int r = i / S2_PW, c = i % S2_PW;
-    const int gy = oy0 + r, gx = ox0 + c;
-    float v1 = 0.f, v2 = 0.f;
-    if (gy < H && gx < W) {
-      v1 = a[(int64_t)gy * W + gx] * in_scale;
-      v2 = b[(int64_t)gy * W + gx] * in_scale;
+  // patch load: a warp per row, lanes along x (no per-element division, one row pointer per row)
+  for (int r = tid >> 5; r < S2_PH; r += 8) {
+    const int gy = oy0 + r;
+    const float* ar = a + (int64_t)gy * W + ox0;
+    const float* br = b + (int64_t)gy * W + ox0;
+#pragma unroll
+    for (int c = tid & 31; c < S2_PW; c += 32) {
+      const bool ok = gy < H && ox0 + c < W;
+      p1[r * S2_PP + c] = ok ? ar[c] * in_scale : 0.f;
+      p2[r * S2_PP + c] = ok ? br[c] * in_scale : 0.f;
     }
-    p1[r * S2_PP + c] = v1;
-    p2[r * S2_PP + c] = v2;
   }
   __syncthreads();
   // vertical pass
@@ -451,11 +452,16 @@ ssim_level_rb_kernel(const float* __restrict__ img1, const float* __restrict__ i
         for (int j = 0; j < R; ++j) vb[(m * S2_TH + row) * S2_PP + x0 + j] = mo[m][j];
       __syncthreads();
       const int64_t msz = (int64_t)gridDim.z * OH * OW;
-      for (int i = tid; i < 3 * S2_TH * S2_TW; i += 256) {
-        const int x = i % S2_TW, r = (i / S2_TW) % S2_TH, m = i / (S2_TW * S2_TH);
-        const int yy = oy0 + r, xx = ox0 + x;
-        if (yy < OH && xx < OW)
-          maps[m * msz + (int64_t)plane * OH * OW + (int64_t)yy * OW + xx] = vb[(m * S2_TH + r) * S2_PP + x];
+      for (int r = tid >> 5; r < S2_TH; r += 8) {
+        const int yy = oy0 + r;
+        if (yy >= OH) break;
+        float* mr = maps + (int64_t)plane * OH * OW + (int64_t)yy * OW + ox0;
+#pragma unroll
+        for (int x = tid & 31; x < S2_TW; x += 32)
+          if (ox0 + x < OW) {
+#pragma unroll
+            for (int m = 0; m < 3; ++m) mr[m * msz + x] = vb[(m * S2_TH + r) * S2_PP + x];
+          }
       }
     }
   }
@@ -487,14 +493,18 @@ ssim_bwd_filter_rb_kernel(const float* __restrict__ img1, const float* __restric
 #pragma unroll
   for (int k = 0; k < FS; ++k) f[k] = __ldg(filt + k);
   // patch covers map coords [y0-(FS-1), y0+TH) x [x0-(FS-1), x0+TW)
-  for (int i = tid; i < S2_PH * S2_PW; i += 256) {
-    const int r = i / S2_PW, c = i % S2_PW;
-    const int qy = y0t - (FS - 1) + r, qx = x0t - (FS - 1) + c;
-    const bool ok = (qy >= 0 && qy < OH && qx >= 0 && qx < OW);
-    const int64_t o = (int64_t)plane * OH * OW + (int64_t)qy * OW + qx;
-    pm[(0 * S2_PH + r) * S2_PP + c] = ok ? maps[o] : 0.f;
-    pm[(1 * S2_PH + r) * S2_PP + c] = ok ? maps[msz + o] : 0.f;
-    pm[(2 * S2_PH + r) * S2_PP + c] = ok ? maps[2 * msz + o] : 0.f;
+  for (int r = tid >> 5; r < S2_PH; r += 8) {
+    const int qy = y0t - (FS - 1) + r;
+    const bool oky = qy >= 0 && qy < OH;
+    const float* m0 = maps + (int64_t)plane * OH * OW + (int64_t)qy * OW + (x0t - (FS - 1));
+#pragma unroll
+    for (int c = tid & 31; c < S2_PW; c += 32) {
+      const int qx = x0t - (FS - 1) + c;
+      const bool ok = oky && qx >= 0 && qx < OW;
+      pm[(0 * S2_PH + r) * S2_PP + c] = ok ? m0[c] : 0.f;
+      pm[(1 * S2_PH + r) * S2_PP + c] = ok ? m0[msz + c] : 0.f;
+      pm[(2 * S2_PH + r) * S2_PP + c] = ok ? m0[2 * msz + c] : 0.f;
+    }
   }
   __syncthreads();
   // vertical: out row j (pixel y0+j) = sum_d f[d] M(y0+j-d): patch row of (y0+j-d) = j + FS-1 - d
@@ -550,16 +560,18 @@ ssim_bwd_filter_rb_kernel(const float* __restrict__ img1, const float* __restric
       for (int j = 0; j < R; ++j) vb[(m * S2_TH + row) * S2_PP + xg + j] = o[m][j];
     __syncthreads();
   }
-  for (int i = tid; i < S2_TH * S2_TW; i += 256) {
-    const int xl = i % S2_TW, r = i / S2_TW;
-    const int y = y0t + r, x = x0t + xl;
-    if (y < H && x < W) {
-      const int64_t o = (int64_t)plane * H * W + (int64_t)y * W + x;
-      const float x1 = img1[o] * in_scale, x2 = img2[o] * in_scale;
-      const float v = in_scale * (vb[(0 * S2_TH + r) * S2_PP + xl] + 2.f * x2 * vb[(1 * S2_TH + r) * S2_PP + xl] +
-                                  x1 * vb[(2 * S2_TH + r) * S2_PP + xl]);
-      g_img2[o] = accumulate ? (g_img2[o] + v) : v;
-    }
+  for (int r = tid >> 5; r < S2_TH; r += 8) {
+    const int y = y0t + r;
+    if (y >= H) break;
+    const int64_t ro = (int64_t)plane * H * W + (int64_t)y * W + x0t;
+#pragma unroll
+    for (int xl = tid & 31; xl < S2_TW; xl += 32)
+      if (x0t + xl < W) {
+        const float x1 = img1[ro + xl] * in_scale, x2 = img2[ro + xl] * in_scale;
+        const float v = in_scale * (vb[(0 * S2_TH + r) * S2_PP + xl] + 2.f * x2 * vb[(1 * S2_TH + r) * S2_PP + xl] +
+                                    x1 * vb[(2 * S2_TH + r) * S2_PP + xl]);
+        g_img2[ro + xl] = accumulate ? (g_img2[ro + xl] + v) : v;
+      }
   }
 }
 
