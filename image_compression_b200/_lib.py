@@ -138,7 +138,9 @@ _SIGNATURES = {
                                    c_uint64, c_uint64, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
                                    c_void_p]),
     "hpc_factorized_bwd": (c_int, [c_void_p, POINTER(CdfParams), c_int64, c_int, c_int, c_float, c_void_p,
-                                   c_float, c_void_p, c_void_p, c_void_p, POINTER(CdfParams), c_void_p]),
+                                   c_float, c_void_p, c_void_p, c_void_p, POINTER(CdfParams), c_void_p, c_size_t,
+                                   c_void_p]),
+    "hpc_factorized_bwd_scratch_bytes": (c_size_t, [c_int64, c_int]),
     "hpc_cdf_logits_fwd": (c_int, [c_void_p, POINTER(CdfParams), c_int64, c_int, c_void_p, c_void_p]),
     "hpc_cdf_logits_bwd": (c_int, [c_void_p, POINTER(CdfParams), c_int64, c_int, c_void_p, c_void_p,
                                    POINTER(CdfParams), c_void_p]),

@@ -704,8 +704,10 @@ def factorized_backward(zt, cdf, training, g_bits, g_scale, g_probs=None, g_zt=N
     gz = torch.empty_like(zt)
     grads = {k: grad_buffer(v, zero=True) for k, v in cdf.items()}
     s, gs = _cdf_struct(cdf), _cdf_struct(grads)
+    nb = lib().hpc_factorized_bwd_scratch_bytes(P, C)      # per-row-block partials: fixed-order (reproducible) sums
+    part = torch.empty(nb // 4, dtype=torch.float32, device=zt.device)
     check(lib().hpc_factorized_bwd(ptr(zt), byref(s), P, C, int(training), bin_, ptr(g_bits), g_scale, ptr(g_probs),
-                                   ptr(g_zt), ptr(gz), byref(gs), stream()))
+                                   ptr(g_zt), ptr(gz), byref(gs), ptr(part), nb, stream()))
     return gz, grads
 
 

@@ -117,11 +117,15 @@ int hpc_factorized_fwd(const float* z, const float* noise, const hpc_cdf_params*
                        hpc_stream_t stream);
 /* backward of the above (autograd in the reference).  g_bits: device scalar dL/dbits (may be
  * NULL), g_probs: optional (P,C) dL/dprobs, g_zt: optional (P,C) dL/dz_tilde (float).
- * gz (P,C) out; gparams accumulated with atomics into caller-zeroed buffers.  g_scale
+ * gz (P,C) out; gparams accumulated into caller-zeroed buffers.  g_scale
  * multiplies *g_bits (e.g. 1/num_pixels). */
 int hpc_factorized_bwd(const float* z_tilde, const hpc_cdf_params* params, int64_t P, int C, int mode,
                        float bin, const float* g_bits, float g_scale, const float* g_probs, const float* g_zt,
-                       float* gz, const hpc_cdf_params* gparams, hpc_stream_t stream);
+                       float* gz, const hpc_cdf_params* gparams, void* scratch, size_t scratch_bytes,
+                       hpc_stream_t stream);
+/* scratch (optional, >= hpc_factorized_bwd_scratch_bytes(P, C)): per-row-block partials of the 43 x C parameter
+ * gradients, summed in block order by a finishing kernel (bit-reproducible); NULL: float atomics into gparams. */
+size_t hpc_factorized_bwd_scratch_bytes(int64_t P, int C);
 
 /* CDFEstimator.forward stand-alone: logits of the per-channel MLP at x (P,C) (entropy_model.py:101-114)
  * and its backward (g (P,C) upstream; gx may be NULL; gparams accumulated into zeroed buffers). */
