@@ -28,4 +28,6 @@ for spec in "igemm_fwd_umma:24:8" "igemm_wgrad_umma:12:4" "gdn_bwd_dual:6:3" "gd
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:$RE -s $SKIP -c $CNT -o $OUT/${RE}_full -f \
       python bench.py --steps 1 --warmup 1 --no-cpu-baseline > $OUT/ncu_full_$RE.log 2>&1; echo "ncu full $RE rc=$?" | tee -a $OUT/summary.txt
 done
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:"ssim_level_rb_kernel|ssim_bwd_filter_rb" -c 3 -o $OUT/ssim_rb_full -f \
+    python bench.py --workload train_ssim --steps 1 --warmup 0 --no-cpu-baseline > $OUT/ncu_full_ssim_rb.log 2>&1; echo "ncu full ssim rc=$?" | tee -a $OUT/summary.txt
 ls -la $OUT
