@@ -199,6 +199,42 @@ def cpu_step_fn(workload, n, hw):
     return (eval_step if workload == "eval" else train_step), n
 
 
+def time_torch_gpu(workload, n, hw, steps, warmup):
+    """The same oracle port in eager PyTorch (cuDNN / ATen, fp32 tensors, torch's default TF32 flags) on cuda:0: what a user of the reference runs
+    on this GPU today (BASELINE.md "second baseline, same box").  A reported baseline like `cpu_baseline`; the
+    product path never touches it.  Returns None when the port cannot run on the device."""
+    import torch
+    from oracle import hyperprior_oracle as O
+    try:
+        cfg = O.default_cfg(lmbda=256.0)     # torch's default precision flags, as the reference runs: cuDNN TF32 allowed
+        torch.manual_seed(0)
+        params = {k: v.detach().cuda().requires_grad_(True) for k, v in O.init_params(cfg, seed=0).items()}
+        x = torch.rand(n, 3, *hw, device="cuda")
+
+        def step():
+            for p in params.values():
+                p.grad = None
+            if workload == "eval":
+                with torch.no_grad():
+                    return O.compressor2018_forward(params, x, cfg, False)[1]["bpp"]
+            losses = O.compressor2018_forward(params, x, cfg, True)[1]
+            losses["total_loss"].backward()
+            return losses["total_loss"].detach()
+        for _ in range(warmup):
+            step()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        return {"value": n / (ms / 1e3), "ms_per_step": ms, "units": n}
+    except Exception as e:           # e.g. a CPU-only helper tensor inside the port
+        return {"value": None, "error": f"{type(e).__name__}: {str(e)[:160]}"}
+
+
 def time_cpu(workload, n, hw, steps, warmup):
     import torch
     cores = os.cpu_count() or 1
@@ -551,6 +587,15 @@ def main():
         o = dict(r["optim"])
         o["frac_of_hbm"] = o["kernel_gbs"] / peaks["hbm_gbs"]
         line["optimizer_step"] = o
+    if world == 1 and not args.no_cpu_baseline and wl in ("train", "eval"):
+        g = time_torch_gpu(wl, B, (H, W), 5, 2)
+        if g is not None:
+            g.update(unit=UNIT[wl], kind="port", sample=f"5 steps of {B} x {H}x{W} after 2 warm-ups, eager torch on the same B200 "
+                     "(fp32 tensors, cuDNN, default flags: cudnn.allow_tf32=%s, matmul.allow_tf32=%s): the oracle port of "
+                     "the reference modules, " % (__import__("torch").backends.cudnn.allow_tf32,
+                                                  __import__("torch").backends.cuda.matmul.allow_tf32)
+                     + ("fwd+loss+bwd" if wl == "train" else "forward in rounding mode"))
+            line["torch_gpu_baseline"] = g
     if world == 1 and not args.no_cpu_baseline:
         n = args.cpu_sample if wl != "eval" else 1
         probe = time_cpu(wl, n, (H, W), 1, 1)

@@ -278,7 +278,7 @@ conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_consta
             const float a = v[2 * e] + bias_s[cc * 64 + cb + 2 * e];
             const float b = v[2 * e + 1] + bias_s[cc * 64 + cb + 2 * e + 1];
             lo[e] = pack2_bf16(a, b);
-            sq[e] = pack2_bf16(a * a, b * b);
+            if (p.out_sq) sq[e] = pack2_bf16(a * a, b * b);      // (uniform branch: the fused GDN path never asks for x^2)
           }
           uint4* d0 = reinterpret_cast<uint4*>(st_lp + row * T1_ST_ROW + cb * 2);
           d0[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
