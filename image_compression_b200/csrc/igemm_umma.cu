@@ -587,11 +587,18 @@ struct WgKParams {
   int tw, th, nb, tiles_w, tiles_h, tiles_n, kblocks;
   int nunits, nsplits, rchunks, cchunks, ntaps;
   int stages;
+  int epi_smem;                                // stage the accumulators in shared memory and bulk-copy whole rows out
   hpc_igemm_phase phase[HPC_MAX_PHASES];
   int dh[HPC_MAX_TAPS], dw[HPC_MAX_TAPS];
   WgUnit unit[WG_MAX_UNITS];
   float* ws;                                   // [nsplits][ntaps][R][Cc]
 };
+
+// one contiguous row shared -> global (cp.async.bulk, bulk-group completion); 16-byte aligned, bytes % 16 == 0
+__device__ __forceinline__ void bulk_store_row(void* gdst, const void* ssrc, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(ssrc)), "r"(bytes)
+               : "memory");
+}
 
 __global__ void __launch_bounds__(WG_THREADS, 1)
 igemm_wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmLo, const __grid_constant__ CUtensorMap tmHi,
@@ -681,6 +688,47 @@ igemm_wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmLo, const __grid_c
       }
       mma_commit(done_bar);
     }
+  } else if (p.epi_smem) {
+    // Epilogue through shared memory: a thread owns one accumulator ROW, so direct global stores would be 16-byte
+    // pieces of 32 different rows per instruction.  The operand stages are free once the last MMA has retired:
+    // the rows are staged there (pitch Cc*4 + 16 bytes: conflict-free float4 writes) and every row leaves as ONE
+    // bulk copy of Cc*4 contiguous bytes into the split-K workspace.
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const int pitch = p.Cc * 4 + 16;
+    mbar_wait(done_bar, 0);
+    tc_fence_after();
+    const int nmma = (U.natoms + 1) / 2;
+    for (int m = 0; m < nmma; ++m) {
+      uint8_t* srow = smem + (size_t)(m * 128 + row) * pitch;
+      const uint32_t taddr = tmem_base + m * 256 + ((uint32_t)(q * 32) << 16);
+      for (int c0 = 0; c0 < p.Cc; c0 += 16) {
+        float v[16];
+        if (nkb > 0) {
+          tmem_ld16(taddr + c0, v);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = 0.f;
+        }
+        float4* d = reinterpret_cast<float4*>(srow + c0 * 4);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) d[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+      }
+    }
+    fence_proxy_async();                    // generic-proxy writes -> visible to the bulk-copy (async proxy) reads
+    // each thread copies out the rows it wrote itself: no cross-thread hand-off is needed
+    for (int m = 0; m < nmma; ++m) {
+      const int a = 2 * m + row / 64;
+      if (a < U.natoms) {
+        const int atom = U.atom_begin + a;
+        const int t = P.tap_begin + atom / p.rchunks, r = (atom % p.rchunks) * 64 + (row & 63);
+        float* dst = p.ws + (((int64_t)split * p.ntaps + t) * p.R + r) * p.Cc;
+        bulk_store_row(dst, smem + (size_t)(m * 128 + row) * pitch, (uint32_t)(p.Cc * 4));
+      }
+    }
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   } else {
     const int q = warp & 3;
     const int row = q * 32 + lane;
@@ -883,6 +931,11 @@ int hpc_igemm_wgrad_umma(const hpc_igemm_wgrad_params* p, hpc_stream_t stream) {
   local.stages = local.cchunks <= 3 ? WG_MAX_STAGES : 3;       // 224 KB for C = 192, 192 KB for C = 256
   { const char* e = getenv("HPC_WG_STAGES"); if (e && atoi(e) >= 2 && atoi(e) <= local.stages) local.stages = atoi(e); }
   const int smem_bytes = local.stages * (4 + local.cchunks) * WG_ATOM_BYTES + 1024 + 256;
+  {  // staged epilogue when 256 padded rows fit in the operand stages (C <= 192); HPC_WG_EPI_SMEM=0 keeps direct stores
+    static int want = -1;
+    if (want < 0) { const char* e = getenv("HPC_WG_EPI_SMEM"); want = (e && e[0] == '0') ? 0 : 1; }
+    local.epi_smem = want && 256 * (p->Cc * 4 + 16) <= local.stages * (4 + local.cchunks) * WG_ATOM_BYTES;
+  }
   static bool attr_set = false;
   if (!attr_set) {
     HPC_CUDA(cudaFuncSetAttribute(igemm_wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
