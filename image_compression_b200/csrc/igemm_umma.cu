@@ -18,6 +18,15 @@
 
 using namespace umma;
 
+// one contiguous row shared -> global (cp.async.bulk, bulk-group completion); 16-byte aligned, bytes % 16 == 0
+__device__ __forceinline__ void bulk_store_row(void* gdst, const void* ssrc, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(ssrc)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_group_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_group_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_group_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
 // ---------------------------------------------------------------------------------------
 // forward kernel
 // ---------------------------------------------------------------------------------------
@@ -34,6 +43,8 @@ struct FwdKParams {
   hpc_igemm_phase phase[HPC_MAX_PHASES];
   int dh[HPC_MAX_TAPS], dw[HPC_MAX_TAPS];
   int kchunks;               // Ci / 64
+  int stage_out;             // CTA-pair kernel, plain bias epilogue with the bf16 output only: rows staged in shared
+                             // memory and written with one bulk copy each
   int ksplit;                // > 1: work item = (tile, K slice); raw fp32 partials go to ws[slice][N,OH,OW,Co]
   float* ws;
   int64_t out_elems;
@@ -45,10 +56,15 @@ struct FwdCfg {
   static constexpr int A_BYTES = FW_BM * FW_BK * 2;        // 16 KB
   static constexpr int B_BYTES = (BLOCK_N / NCTA) * FW_BK * 2;   // a CTA of a pair holds half of the weight tile
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (200 * 1024 / STAGE_BYTES) > 8 ? 8 : (200 * 1024 / STAGE_BYTES);
+  // CTA-pair kernel: one [128 rows x (BLOCK_N bf16 + 16 B pad)] output staging tile (rows leave as single bulk copies)
+  static constexpr int STG_PITCH = BLOCK_N * 2 + 16;
+  static constexpr int STG_BYTES = NCTA == 2 ? FW_BM * STG_PITCH : 0;
+  static constexpr int FIXED_BYTES = 1024 /*align*/ + 256 /*barriers*/ + 1024 /*bias*/;
+  static constexpr int BUDGET = NCTA == 2 ? (232448 - FIXED_BYTES - STG_BYTES) : 200 * 1024;
+  static constexpr int STAGES = (BUDGET / STAGE_BYTES) > 8 ? 8 : (BUDGET / STAGE_BYTES);
   static constexpr int ACC_STRIDE = BLOCK_N <= 32 ? 32 : (BLOCK_N <= 64 ? 64 : (BLOCK_N <= 128 ? 128 : 256));
   static constexpr int TMEM_COLS = 2 * ACC_STRIDE;          // 64..512, power of two
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + 1024 /*bias*/;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + FIXED_BYTES + STG_BYTES;
 };
 
 // Work item `w` of the persistent loop -> (phase, tile origin).  NCTA == 1: w is a tile.  NCTA == 2: w is a PAIR of
@@ -199,6 +215,7 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
   uint64_t* tempty_bar = tfull_bar + 2;         // [2]       epilogue -> MMA (pair: both CTAs arrive at the leader's)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
   float* bias_s = reinterpret_cast<float*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256);   // bias staged once per CTA
+  uint8_t* stg = smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256 + 1024;                        // output staging (pair kernel)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int rank = NCTA == 2 ? (int)cluster_ctarank() : 0;
@@ -325,6 +342,37 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + acc * Cfg::ACC_STRIDE + ((uint32_t)(q * 32) << 16);
+      if (NCTA == 2 && p.stage_out) {
+        // a thread owns one output ROW (pixel): direct stores are 16-byte pieces of 32 different rows per instruction.
+        // Stage the bf16 row in shared memory (pitch BLOCK_N*2 + 16 B: conflict-free) and write it with ONE bulk copy.
+        uint8_t* srow = stg + row * Cfg::STG_PITCH;
+        bulk_group_wait_read();                  // the previous tile's copy has finished reading this row
+#pragma unroll 1
+        for (int c0 = 0; c0 < BLOCK_N; c0 += 16) {
+          float v[16];
+          tmem_ld16(taddr + c0, v);
+          tmem_ld_wait();
+          if (epi.bias) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] += epi.bias[c0 + i];
+          }
+          uint4 u[2];
+          __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(u);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+          *reinterpret_cast<uint4*>(srow + c0 * 2) = u[0];
+          *reinterpret_cast<uint4*>(srow + c0 * 2 + 16) = u[1];
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&tempty_bar[acc]), 0));    // accumulator drained
+        fence_proxy_async();
+        if (valid)
+          bulk_store_row(reinterpret_cast<__nv_bfloat16*>(epi.out_lp) + obase, srow, (uint32_t)(BLOCK_N * 2));
+        bulk_group_commit();
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        continue;
+      }
 #pragma unroll 1
       for (int c0 = 0; c0 < BLOCK_N; c0 += 16) {
         float v[16];
@@ -349,6 +397,7 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+    if (NCTA == 2 && p.stage_out) bulk_group_wait_all();
   }
   tc_fence_before();
   if (NCTA == 2) cluster_sync_all(); else __syncthreads();
@@ -508,6 +557,12 @@ int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
   }
 
   const bool pair = fwd_use_pair(kp);
+  {  // staged bulk-copy epilogue: plain (bias) epilogue whose only output is the bf16 tensor; HPC_FWD_STAGE_OUT=0 disables
+    static int want = -1;
+    if (want < 0) { const char* e = getenv("HPC_FWD_STAGE_OUT"); want = (e && e[0] == '0') ? 0 : 1; }
+    kp.stage_out = want && pair && kp.epi.epi == HPC_EPI_LINEAR && kp.epi.out_lp && !kp.epi.out_f32 && !kp.epi.out_sq_lp &&
+                   !kp.epi.out_abs_lp && !kp.epi.out_nrm_lp && hpc_aligned16(kp.epi.out_lp) && (p->Co * 2) % 16 == 0;
+  }
   kp.ksplit = 1;
   if (!pair) {
     const int ks = fwd_ksplit(p, kp.total_tiles);
@@ -593,12 +648,6 @@ struct WgKParams {
   WgUnit unit[WG_MAX_UNITS];
   float* ws;                                   // [nsplits][ntaps][R][Cc]
 };
-
-// one contiguous row shared -> global (cp.async.bulk, bulk-group completion); 16-byte aligned, bytes % 16 == 0
-__device__ __forceinline__ void bulk_store_row(void* gdst, const void* ssrc, uint32_t bytes) {
-  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(ssrc)), "r"(bytes)
-               : "memory");
-}
 
 __global__ void __launch_bounds__(WG_THREADS, 1)
 igemm_wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmLo, const __grid_constant__ CUtensorMap tmHi,
