@@ -52,30 +52,41 @@ class FusedAdamW(torch.optim.Optimizer):
         if closure is not None:
             with torch.enable_grad():
                 loss = closure()
-        segs = []
         beta1, beta2 = self.param_groups[0]["betas"]
         eps = self.param_groups[0]["eps"]
+        # the segment table (pointers, sizes) is rebuilt only when a tensor moved: with FlatGradients the parameter,
+        # gradient and moment addresses are stable, so a step is one pass over the groups updating three scalars each
+        live, key = [], []
         for group in self.param_groups:
-            lr, wd = float(group["lr"]), float(group["weight_decay"])
             for p in group["params"]:
-                if p.grad is None:
-                    continue
+                if p.grad is not None:
+                    st = self._state(p)
+                    live.append((group, p, st))
+                    key.append((p.data_ptr(), p.grad.data_ptr(), st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr()))
+        if not live:
+            return loss
+        cache = getattr(self, "_seg_cache", None)
+        if cache is None or cache[0] != key:
+            for _, p, _ in live:
                 _lib.require_cuda(p, p.grad)
                 if p.dtype != torch.float32 or p.grad.dtype != torch.float32:
                     raise TypeError("FusedAdamW: parameters and gradients must be fp32 (the reference trains in fp32)")
                 if p.grad.is_sparse or not p.is_contiguous() or not p.grad.is_contiguous():
                     raise RuntimeError("FusedAdamW: dense contiguous parameters and gradients only")
-                st = self._state(p)
-                st["step"] += 1
-                t = float(st["step"])
-                bc1 = 1.0 - beta1 ** t
-                bc2 = 1.0 - beta2 ** t
-                segs.append(AdamwSeg(ptr(p), ptr(p.grad), ptr(st["exp_avg"]), ptr(st["exp_avg_sq"]), p.numel(),
-                                     1.0 - lr * wd, -(lr / bc1), math.sqrt(bc2), 0.0))
-        if segs:
-            arr = (AdamwSeg * len(segs))(*segs)
-            check(lib().hpc_adamw_step(arr, len(segs), beta1, beta2, eps, self.grad_clip,
-                                       int(self.write_clipped_grad), stream()))
+            arr = (AdamwSeg * len(live))(*[AdamwSeg(k[0], k[1], k[2], k[3], p.numel(), 1.0, 0.0, 1.0, 0.0)
+                                            for k, (_, p, _) in zip(key, live)])
+            cache = self._seg_cache = (key, arr)
+        arr = cache[1]
+        for i, (group, p, st) in enumerate(live):
+            lr, wd = float(group["lr"]), float(group["weight_decay"])
+            st["step"] += 1
+            t = float(st["step"])
+            seg = arr[i]
+            seg.decay = 1.0 - lr * wd
+            seg.neg_step_size = -(lr / (1.0 - beta1 ** t))
+            seg.bc2_sqrt = math.sqrt(1.0 - beta2 ** t)
+        check(lib().hpc_adamw_step(arr, len(live), beta1, beta2, eps, self.grad_clip, int(self.write_clipped_grad),
+                                   stream()))
         return loss
 
 
