@@ -110,3 +110,32 @@ def test_fused_adamw_host_logic():
     cfg.SOLVER.OPT_NAME = "sgd"
     with pytest.raises(NotImplementedError):
         make_optimizer(cfg, model)
+
+
+def test_early_all_reduce_slot_range(monkeypatch):
+    """FlatGradients._reduce_early (the hook the fused backward calls when the g_s gradients are final) reduces exactly
+    the contiguous slot range of the tensors it is given, and declines when a gradient is not a view of the flat buffer
+    or when the range would swallow another group's slot."""
+    import torch.distributed as dist
+    from image_compression_b200 import sharding
+    params = [torch.nn.Parameter(torch.zeros(n)) for n in (5, 16, 7, 9, 3)]
+    fg = sharding.FlatGradients(params, torch.device("cpu"), overlap=False)
+    calls = []
+
+    class _Work:
+        def wait(self):
+            return True
+
+    def fake_all_reduce(t, op=None, group=None, async_op=False):
+        calls.append((t.data_ptr() - fg.flat.data_ptr()) // 4)
+        calls.append(t.numel())
+        return _Work()
+    monkeypatch.setattr(dist, "all_reduce", fake_all_reduce)
+    views = [fg._view(p) for p in params]
+    fg._reduce_early([views[2], views[3]])                     # slots 2 and 3 are neighbours
+    assert calls == [fg.offsets[2], fg.offsets[4] - fg.offsets[2]] and fg._early[:2] == (fg.offsets[2], fg.offsets[4])
+    calls.clear(); fg._early = None
+    fg._reduce_early([views[1], views[3]])                     # slot 2 lies between them: not this group's to reduce
+    assert calls == [] and fg._early is None
+    fg._reduce_early([views[1], torch.zeros(7)])               # a stray gradient (not a view of the flat buffer)
+    assert calls == [] and fg._early is None
