@@ -57,7 +57,10 @@ def parse():
     ap.add_argument("--kernel-events", default="after", choices=["timed", "after"],
                     help="per-kernel-class event pairs: inside the timed region, or over the same number of steps right "
                          "after it (an event record between two kernels serialises their programmatic dependent launch)")
-    ap.add_argument("--cpu-sample", type=int, default=8, help="crops per CPU-baseline step")
+    ap.add_argument("--cpu-sample", type=int, default=0,
+                    help="crops per CPU step (0: the reference arm uses the full per-GPU batch, the cpu_baseline leg 16)")
+    ap.add_argument("--sustained", type=int, default=200, help="steps of the sustained sub-record (train workload)")
+    ap.add_argument("--quick", action="store_true", help="headline measurement only (no extra / sustained / trainer records)")
     return ap.parse_args()
 
 
@@ -251,87 +254,123 @@ def time_cpu(workload, n, hw, steps, warmup):
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU path (oracle port) on this box's host cores."""
+    """--impl reference: the reference's CPU path (oracle port) on this box's host cores, on the own arm's config:
+    every step is the full per-GPU batch of the workload (64 crops / 3 images), --steps and --warmup honoured; only
+    if the probe step says the run would not end within the arm's time budget are the steps cut (and the line says so)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return  # rank 0 alone runs it
-    _, hw = workload_shape(args)
-    n = args.cpu_sample if args.workload != "eval" else 1
-    steps, warmup = args.steps, max(1, min(args.warmup, 2))
-    # bound the run: a step of 8 crops costs seconds on a host; cap the timed steps to keep it within minutes
-    probe = time_cpu(args.workload, n, hw, 1, 1)
-    budget_s = 120.0
-    max_steps = max(1, int(budget_s / max(probe["ms_per_step"] / 1e3, 1e-3)))
-    steps_run = min(steps, max_steps)
-    r = time_cpu(args.workload, n, hw, steps_run, warmup)
+    n, hw = workload_shape(args)
+    if args.cpu_sample:
+        n = args.cpu_sample
+    steps, warmup = args.steps, args.warmup
+    budget_s = float(os.environ.get("HPC_REF_BUDGET_S", "300"))
+    probe = time_cpu(args.workload, n, hw, 1, 1)                 # (counts as the first warm-up step)
+    per = probe["ms_per_step"] / 1e3
+    cut = None
+    if per * (steps + warmup) > budget_s:
+        warmup_run = min(warmup, 1)
+        steps_run = max(1, min(steps, int((budget_s - per * warmup_run) / per)))
+        cut = f"cut from {steps} steps / {warmup} warm-ups to {steps_run} / {warmup_run + 1}: {per:.1f} s per step, {budget_s:.0f} s budget"
+    else:
+        steps_run, warmup_run = steps, max(warmup - 1, 0)
+    r = time_cpu(args.workload, n, hw, steps_run, warmup_run)
     sample = (f"{steps_run} step(s) of {n} x {hw[0]}x{hw[1]} synthetic "
-              f"{'crops fwd+loss+bwd' if args.workload != 'eval' else 'image fwd+metrics'} in fp32, torch-CPU, "
-              f"{r['cores']} threads, after {warmup} warm-up")
+              f"{'crops fwd+loss+bwd' if args.workload != 'eval' else 'images fwd+metrics'} in fp32, torch-CPU, "
+              f"{r['cores']} threads, after {warmup_run + 1} warm-up step(s)" + (f" ({cut})" if cut else ""))
     line = {
         "impl": "reference", "metric": METRIC[args.workload], "value": r["value"], "unit": UNIT[args.workload],
-        "n_gpus": args.gpus, "steps": steps_run, "warmup": warmup, "ms_per_step": r["ms_per_step"],
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": config_dict(args, per_gpu=workload_shape(args)[0],
-                              note=f"CPU reference arm: each step is a bounded sample of {n} unit(s) of this workload"),
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": DATA_NOTE,
+        "config": config_dict(args),
         "cpu_baseline": {"value": r["value"], "unit": UNIT[args.workload], "cores": r["cores"], "kind": "port",
                          "sample": sample},
         "e2e": {"value": r["value"], "unit": UNIT[args.workload], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
+        "gpu_launches": 0, "steps_timed": steps_run,
     }
     emit(line)
 
 
-def config_dict(args, per_gpu, note=None):
-    _, hw = workload_shape(args)
+DATA_NOTE = "synthetic (torch.rand images, random-init weights of the reference architecture)"
+
+
+def config_dict(args, workload=None):
+    """Names the workload; a function of the command line only, so both arms print the same `config`."""
+    wl = workload or args.workload
+    a = argparse.Namespace(**vars(args))
+    a.workload = wl
+    if wl != args.workload:
+        a.batch = a.size = None
+    per_gpu, hw = workload_shape(a)
     names = {"train": "psnr_256 training step (fwd+bwd, noise quantisation), 256x256 synthetic crops",
              "train_ssim": "ssim_64 MS-SSIM-distortion training step (fwd+bwd), 256x256 synthetic crops",
              "eval": "eval sweep: 768x512 Kodak-shaped synthetic images, rounding quantisation, bpp/PSNR/MS-SSIM"}
-    d = {"workload": names[args.workload], "recipe": RECIPE[args.workload], "per_gpu_batch": per_gpu,
-         "global_batch": per_gpu * args.gpus, "height": hw[0], "width": hw[1], "channels": 192,
-         "parallelism": f"dp{args.gpus}" if args.workload != "eval" else f"per-image x{args.gpus}"}
-    if note:
-        d["note"] = note
-    return d
+    return {"workload": names[wl], "recipe": RECIPE[wl], "per_gpu_batch": per_gpu,
+            "global_batch": per_gpu * args.gpus, "height": hw[0], "width": hw[1], "channels": 192,
+            "parallelism": f"dp{args.gpus}" if wl != "eval" else f"per-image x{args.gpus}",
+            "l2": "GPU arm: inputs rotate over resident batches totalling > 126 MB (L2); one step streams > 1 GB of "
+                  "activations.  CPU arm: not applicable",
+            "timing": "GPU arm: CUDA events on the launching stream, max over ranks; CPU arm: perf_counter",
+            "step": ("one pass of the hot path over one per-GPU batch: zero_grad, forward, RD loss, backward, gradient "
+                     "all-reduce for N>1; every weight is marked updated before each step, so the bf16 operand copies of "
+                     "all weights are re-packed in every step as in real training; optimizer step excluded (SURVEY 8d), "
+                     "reported separately as `with_optimizer`") if wl != "eval" else
+                    "one pass over one per-GPU batch of images: forward (rounding), bpp, PSNR, MS-SSIM; per-image results "
+                    "all-gathered inside the step for N>1"}
 
 
 # ------------------------------------------------------------------------------------------
 # own arm
 # ------------------------------------------------------------------------------------------
-def run_ours(args):
+class Ctx:
+    pass
+
+
+def setup_dist():
     import torch
     import torch.distributed as dist
-    import image_compression_b200 as pkg
-    from image_compression_b200 import _lib, sharding
-    from image_compression_b200.utils.metric import image_metrics
-
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
+    c = Ctx()
+    c.rank = int(os.environ.get("RANK", "0"))
+    c.world = int(os.environ.get("WORLD_SIZE", "1"))
+    c.local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the hot path has no CPU fallback (use --impl reference for the CPU arm)")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
+    torch.cuda.set_device(c.local)
+    c.dev = torch.device("cuda", c.local)
+    if c.world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         # (NCCL prints its version banner on file descriptor 1; main() has pointed fd 1 at stderr for the whole run
         # and emit() writes the one JSON line to the saved stdout)
-        dist.init_process_group("nccl", device_id=dev)
-    _lib.lib()  # fail loudly here if the extension is missing
-    pkg.set_compute_mode(args.mode)
+        dist.init_process_group("nccl", device_id=c.dev)
+    return c
 
-    B, (H, W) = workload_shape(args)
-    training = args.workload != "eval"
+
+def measure(args, c, wl, steps, warmup, with_clocks=False, with_optimizer=False, sustained_steps=0,
+            trainer_sequence=False):
+    """Time one workload on this rank's GPU.  Returns a dict (see main() for how it becomes the JSON line)."""
+    import torch
+    import torch.distributed as dist
+    import image_compression_b200 as pkg
+    from image_compression_b200 import _lib, hotpath as hp, sharding
+    from image_compression_b200.utils.metric import image_metrics
+
+    rank, world, dev = c.rank, c.world, c.dev
+    a = argparse.Namespace(**vars(args))
+    a.workload = wl
+    if wl != args.workload:
+        a.batch = a.size = None
+    B, (H, W) = workload_shape(a)
+    training = wl != "eval"
     torch.manual_seed(0)                       # identical random-init weights on every rank
-    model = pkg.build_model(pkg.get_recipe_cfg(RECIPE[args.workload])).to(dev)
+    cfg = pkg.get_recipe_cfg(RECIPE[wl])
+    model = pkg.build_model(cfg).to(dev)
     model.train(training)
     sharding.broadcast_parameters(model)
     torch.manual_seed(1000 + rank)             # per-rank inputs and in-kernel Philox noise streams
     n_rot = max(2, -(-int(1.6 * L2_BYTES) // (B * 3 * H * W * 4)))   # resident input batches: > L2 in total
     host = [torch.rand(B, 3, H, W).pin_memory() for _ in range(n_rot)]
     resident = [h.to(dev) for h in host]
-    fg = sharding.FlatGradients(model.parameters(), dev) if training else None
-    stage = torch.empty(B, 3, H, W, device=dev)
-    loss_host = torch.empty(1 + 2 * B, dtype=torch.float32).pin_memory()
+    params = [p for p in model.parameters()]
 
     def eval_eager(x):
         with torch.no_grad():
@@ -344,27 +383,37 @@ def run_ours(args):
         # evaluation is launch bound (3 images per step, ~60 short kernels): replay the step as one CUDA graph
         from image_compression_b200.utils.graphs import GraphedCallable
         graphed = GraphedCallable(eval_eager, resident[0])
+    table = torch.empty((B, 2), device=dev)
 
     def step(x):
         if training:
-            fg.zero()
+            # what engine/trainer.py:176-194 does around the model, minus the optimizer arithmetic: zero_grad
+            # (set_to_none), forward, backward.  The model's GradientReducer writes the gradients into its flat buffer
+            # and (N>1) all-reduces them from inside the backward.  bump_versions stands in for the optimizer's update
+            # of the weights: the packed bf16 operand copies of ALL weights are rebuilt in every step.
+            for p in params:
+                p.grad = None
+            hp.bump_versions(params)
             _, losses = model(x)
             losses["total_loss"].backward()
-            fg.all_reduce_mean()
             return losses["total_loss"]
-        return graphed(x) if graphed is not None else eval_eager(x)
+        out = graphed(x) if graphed is not None else eval_eager(x)
+        if world > 1:           # per-image sharding: the per-image results of all ranks, in image order, on every rank
+            table[:, 0].copy_(out[1]); table[:, 1].copy_(out[2])
+            sharding.gather_per_image(table, B * world, rank, world)
+        return out
 
     def sync_all():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, steps):
-        """EXACTLY `steps` calls bracketed by barrier+synchronize; device time, max over ranks."""
+    def timed(fn, nsteps):
+        """EXACTLY `nsteps` calls bracketed by barrier+synchronize; device time, max over ranks."""
         sync_all()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for i in range(steps):
+        for i in range(nsteps):
             fn(i)
         e1.record()
         torch.cuda.synchronize()
@@ -375,35 +424,41 @@ def run_ours(args):
         return float(ms)
 
     # ---- resident-input throughput (`value`) ------------------------------------------------
-    for i in range(args.warmup):
+    for i in range(warmup):
         step(resident[i % n_rot])
     events_in_timed = args.kernel_events == "timed"
-    with ClockSampler(local) as clocks:
-        n0 = _lib.lib().hpc_launch_count()
-        if events_in_timed:
-            _lib.prof_enable(True)
-        ms_total = timed(lambda i: step(resident[i % n_rot]), args.steps)
+    clocks = ClockSampler(c.local) if with_clocks else None
+    if clocks:
+        clocks.__enter__()
+    n0 = _lib.lib().hpc_launch_count()
+    if events_in_timed:
+        _lib.prof_enable(True)
+    ms_total = timed(lambda i: step(resident[i % n_rot]), steps)
+    _lib.prof_enable(False)
+    launches = _lib.lib().hpc_launch_count() - n0
+    ms_events = ms_total
+    if not events_in_timed:
+        _lib.prof_enable(True)
+        ms_events = timed(lambda i: step(resident[i % n_rot]), steps)
         _lib.prof_enable(False)
-        launches = _lib.lib().hpc_launch_count() - n0
-        ms_events = ms_total
-        if not events_in_timed:
-            _lib.prof_enable(True)
-            ms_events = timed(lambda i: step(resident[i % n_rot]), args.steps)
-            _lib.prof_enable(False)
+    if clocks:
+        clocks.__exit__()
     if graphed is not None:
         # kernels inside a replayed graph are neither counted nor event-timed by the library: take the launch
         # count and the kernel-class times from the same number of eager steps, outside the timed region
         sync_all()
         n0 = _lib.lib().hpc_launch_count()
         _lib.prof_enable(True)
-        for i in range(args.steps):
+        for i in range(steps):
             eval_eager(resident[i % n_rot])
         torch.cuda.synchronize()
         _lib.prof_enable(False)
         launches = _lib.lib().hpc_launch_count() - n0
-    prof = {name: _lib.prof_read(c) for c, name in enumerate(_lib.PROF_NAMES)}
-    units = B * world * args.steps
-    value = units / (ms_total / 1e3)
+    prof = {name: _lib.prof_read(k) for k, name in enumerate(_lib.PROF_NAMES)}
+    units = B * world * steps
+    r = dict(wl=wl, rank=rank, world=world, B=B, H=H, W=W, steps=steps, warmup=warmup, ms_total=ms_total,
+             ms_events=ms_events, value=units / (ms_total / 1e3), launches=launches, prof=prof,
+             clocks=clocks.summary() if clocks else None, n_rot=n_rot, graphed=graphed is not None)
 
     # ---- end to end through the module API with host inputs (`e2e`) --------------------------
     # Every step's input is copied host->device INSIDE the timed region (on a side stream, one step ahead of the
@@ -413,7 +468,7 @@ def run_ours(args):
     # synchronize of the timed region.  Three staging buffers: the copy for step i+1 overwrites the input of step
     # i-2, whose loss the host has already read.
     copy_stream = torch.cuda.Stream(device=dev)
-    stages = [stage, torch.empty_like(stage), torch.empty_like(stage)]
+    stages = [torch.empty(B, 3, H, W, device=dev) for _ in range(3)]
     copied = [torch.cuda.Event() for _ in range(3)]
     nres = 1 if training else 1 + 2 * B
     res_host = [torch.empty(nres, dtype=torch.float32).pin_memory() for _ in range(2)]
@@ -451,23 +506,45 @@ def run_ours(args):
             if i + 1 == nsteps:
                 read_result(i)
         return e2e_step
-    nw = max(2, args.warmup // 2)
+    nw = max(2, warmup // 2)
     warm = make_e2e(nw)
     for i in range(nw):
         warm(i)
-    e2e_ms = timed(make_e2e(args.steps), args.steps)
-    e2e_value = units / (e2e_ms / 1e3)
-    h2d = B * 3 * H * W * 4
-    d2h = 4 if training else 4 * (1 + 2 * B)
-    # ---- optimizer step (NOT part of `value` / `e2e`, which follow SURVEY 8d) ---------------
-    # fused clip + AdamW over the gradients the last step left, against eager torch (clip_grad_value_ +
-    # torch.optim.AdamW over the same 50 single-tensor groups: what solver/optim.py + engine/trainer.py run)
-    optim = None
-    if training:
+    e2e_ms = timed(make_e2e(steps), steps)
+    r.update(e2e_value=units / (e2e_ms / 1e3), e2e_ms=e2e_ms, h2d=B * 3 * H * W * 4,
+             d2h=4 if training else 4 * (1 + 2 * B),
+             grad_bytes=model.gradient_reducer().fg.nbytes() if training else 0)
+
+    # ---- a sustained run: >= 200 steps back to back (clocks settle under the power cap) -----------------------
+    if sustained_steps:
+        cs = ClockSampler(c.local)
+        cs.__enter__()
+        ms_s = timed(lambda i: step(resident[i % n_rot]), sustained_steps)
+        cs.__exit__()
+        r["sustained"] = {"steps": sustained_steps, "ms_per_step": ms_s / sustained_steps,
+                          "value": B * world * sustained_steps / (ms_s / 1e3), "unit": UNIT[wl], "clocks": cs.summary()}
+
+    # ---- the full training iteration: + fused clip + AdamW ----------------------------------
+    if training and with_optimizer:
         from torch.nn.utils import clip_grad_value_
         from image_compression_b200 import solver
-        cfg = pkg.get_recipe_cfg(RECIPE[args.workload])
         opt = solver.make_optimizer(cfg, model)
+
+        def full_step(i):
+            opt.zero_grad(set_to_none=True)
+            _, losses = model(resident[i % n_rot])
+            losses["total_loss"].backward()
+            opt.step()                  # fused clip_grad_value_ + AdamW; bumps the weight versions -> re-pack next step
+        for i in range(3):
+            full_step(i)
+        ms_full = timed(full_step, steps)
+        k0 = _lib.lib().hpc_launch_count()
+        _lib.prof_enable(True)
+        ms_fused = timed(lambda i: opt.step(), steps)
+        _lib.prof_enable(False)
+        k1 = _lib.lib().hpc_launch_count()
+        oms, on, owork = _lib.prof_read(_lib.PROF_NAMES.index("optim"))
+        # eager torch on a shadow copy: clip_grad_value_ + torch.optim.AdamW over the same 50 single-tensor groups
         shadow = [torch.nn.Parameter(p.detach().clone()) for p in model.parameters()]
         for q, p in zip(shadow, model.parameters()):
             q.grad = p.grad.detach().clone()
@@ -478,23 +555,111 @@ def run_ours(args):
             clip_grad_value_(shadow, cfg.SOLVER.GRAD_CLIP)
             ropt.step()
         for _ in range(3):
-            opt.step(); ref_step(0)
-        k0 = _lib.lib().hpc_launch_count()
-        _lib.prof_enable(True)
-        ms_fused = timed(lambda i: opt.step(), args.steps)
-        _lib.prof_enable(False)
-        k1 = _lib.lib().hpc_launch_count()
-        oms, on, owork = _lib.prof_read(_lib.PROF_NAMES.index("optim"))
-        ms_torch = timed(ref_step, args.steps)
-        nparam = sum(p.numel() for p in model.parameters())
-        optim = {"fused_ms_per_step": ms_fused / args.steps, "kernel_ms": oms / max(on, 1),
-                 "kernel_gbs": owork / max(oms, 1e-9) / 1e6, "launches_per_step": (k1 - k0) / args.steps,
-                 "bytes_per_param": 28, "params": nparam, "torch_eager_ms_per_step": ms_torch / args.steps,
-                 "note": "fused clip_grad_value_ + AdamW (hpc_adamw_step) vs clip_grad_value_ + torch.optim.AdamW "
-                         "(foreach) over the same 50 single-tensor groups; outside `value`/`e2e`"}
-    return dict(rank=rank, world=world, B=B, H=H, W=W, ms_total=ms_total, ms_events=ms_events, value=value, launches=launches, prof=prof,
-                clocks=clocks.summary(), e2e_value=e2e_value, e2e_ms=e2e_ms, h2d=h2d, d2h=d2h, n_rot=n_rot,
-                grad_bytes=fg.nbytes() if fg else 0, graphed=graphed is not None, optim=optim)
+            ref_step(0)
+        ms_torch = timed(ref_step, steps)
+        r["with_optimizer"] = {
+            "value": units / (ms_full / 1e3), "unit": UNIT[wl], "ms_per_step": ms_full / steps,
+            "what": "zero_grad + forward + backward (+ all-reduce) + FusedAdamW.step() (fused clip_grad_value_ + AdamW, "
+                    "one launch) per step: the whole of engine/trainer.py:176-194",
+            "optimizer_only_ms": ms_fused / steps, "optimizer_kernel_ms": oms / max(on, 1),
+            "optimizer_kernel_gbs": owork / max(oms, 1e-9) / 1e6, "optimizer_launches_per_step": (k1 - k0) / steps,
+            "bytes_per_param": 28, "params": sum(p.numel() for p in model.parameters()),
+            "torch_eager_optimizer_ms": ms_torch / steps}
+
+    # ---- the reference trainer's own call sequence around the model (tests/trainer_replay.py) ------------------
+    if training and trainer_sequence:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        from trainer_replay import Monitor, train_step
+        from image_compression_b200 import solver, utils as U
+        dp = torch.nn.DataParallel(model, device_ids=[c.local])
+        opt = solver.make_optimizer(cfg, dp)
+        mon = Monitor(model.loss_names, {"psnr": U.psnr, "ms_ssim": U.MS_SSIM()})
+
+        def seq_step(i):
+            torch.cuda.current_stream().wait_event(copied[i % 3])
+            train_step(dp, opt, stages[i % 3], mon, grad_clip=cfg.SOLVER.GRAD_CLIP, it=1)
+            h2d_async(i + 1)
+        h2d_async(0)
+        for i in range(3):
+            seq_step(i)
+        ms_seq = timed(lambda i: seq_step(i + 3), steps)
+        torch.cuda.synchronize()
+        r["trainer_sequence"] = {
+            "value": units / (ms_seq / 1e3), "unit": UNIT[wl], "ms_per_step": ms_seq / steps,
+            "what": "engine/trainer.py:176-208 replayed call for call around nn.DataParallel(model): forward, .mean(), "
+                    "isnan check, backward, clip_grad_value_, FusedAdamW.step, zero_grad, Monitor.update_metric "
+                    "(PSNR + 5-level MS-SSIM of the batch) and update_loss (float() of 4 loss values); inputs copied "
+                    "from pinned host memory every step"}
+    del model, graphed
+    torch.cuda.empty_cache()
+    return r
+
+
+def record_of(r, peaks, args, headline=False):
+    """JSON sub-record of one measured workload (roofline of its dominant kernel class, kernel classes, e2e)."""
+    wl, steps = r["wl"], r["steps"]
+    B, H, W, world = r["B"], r["H"], r["W"], r["world"]
+    ms, n, flops = r["prof"]["igemm_fwd_umma"]
+    roofline = None
+    if n:
+        ach = flops / (ms * 1e-3) / 1e12
+        peak = peaks["bf16_tflops_sustained"]   # kernel timed inside a long step -> sustained figure
+        roofline = {"bound": "tensor", "kernel": "igemm_fwd_umma_pair_kernel + igemm_fwd_umma_kernel (one class: the "
+                    "CTA-pair and single-CTA builds of the implicit-GEMM forward engine)", "achieved": ach, "peak": peak,
+                    "unit": "TFLOP/s", "frac": ach / peak,
+                    "traffic": ncu_traffic("igemm_fwd_umma_pair_kernel", "igemm_fwd_umma_kernel") if wl == "train" else None,
+                    "peak_source": f"{peaks['source']} (bf16 sustained)", "launches": n,
+                    "avg_launch_ms": ms / n, "share_of_step": ms / r["ms_events"],
+                    "algorithmic_flops_per_launch": flops / n}
+    kernels = {}
+    for name, (kms, kn, work) in r["prof"].items():
+        if not kn:
+            continue
+        gemm = name.startswith("igemm")
+        rate = work / (kms * 1e-3) / (1e12 if gemm else 1e9)
+        pk = peaks["bf16_tflops_sustained"] if gemm else peaks["hbm_gbs"]
+        kernels[name] = {"ms_per_step": kms / steps, "launches_per_step": kn / steps,
+                         "achieved": rate, "unit": "TFLOP/s" if gemm else "GB/s", "frac": rate / pk,
+                         "share_of_step": kms / r["ms_events"]}
+    # the entropy path as one figure (north_star: >= 70 % of HBM): K4 + K5 + K6 together
+    ent = [r["prof"][k] for k in ("conditional", "factorized", "distortion") if r["prof"][k][1]]
+    entropy_path = None
+    if ent:
+        ems, ework = sum(e[0] for e in ent), sum(e[2] for e in ent)
+        entropy_path = {"ms_per_step": ems / steps, "achieved": ework / (ems * 1e-3) / 1e9, "unit": "GB/s",
+                        "frac": ework / (ems * 1e-3) / 1e9 / peaks["hbm_gbs"], "target_frac": 0.70,
+                        "kernels": "factorized + conditional + distortion (K4 + K5 + K6)"}
+    gflop_unit = TRAIN_GFLOP_PER_CROP if wl != "eval" else EVAL_GFLOP_PER_IMAGE
+    if (H, W) != ((256, 256) if wl != "eval" else (512, 768)):
+        gflop_unit *= (H * W) / ((256 * 256) if wl != "eval" else (512 * 768))
+    step_tflops = r["value"] / world * gflop_unit / 1e3
+    rec = {
+        "metric": METRIC[wl], "value": r["value"], "unit": UNIT[wl], "n_gpus": world, "steps": steps,
+        "warmup": r["warmup"], "ms_per_step": r["ms_total"] / steps,
+        "e2e": {"value": r["e2e_value"], "unit": UNIT[wl], "h2d_bytes_per_step": r["h2d"],
+                "d2h_bytes_per_step": r["d2h"], "ms_per_step": r["e2e_ms"] / steps},
+        "gpu_launches": int(r["launches"]),
+        "roofline": roofline,
+        "kernels": kernels,
+        "entropy_path": entropy_path,
+        "step_gemm_tflops_per_gpu": step_tflops,
+        "step_frac_of_tensor_peak": step_tflops / peaks["bf16_tflops_sustained"],
+        "kernel_events": ("event pairs around every kernel class inside the timed region"
+                          if args.kernel_events == "timed" else
+                          "event pairs around every kernel class over %d further steps right after the timed "
+                          "region (%.3f ms/step with the events; an event record between two kernels "
+                          "serialises their programmatic dependent launch, so `value` is timed without them)"
+                          % (steps, r["ms_events"] / steps)),
+    }
+    if r["graphed"]:
+        rec["cuda_graph"] = ("each step replays one captured graph of the package's kernels; kernel-class times and "
+                             "gpu_launches come from the same number of eager steps run after the timed region")
+    for k in ("sustained", "with_optimizer", "trainer_sequence"):
+        if r.get(k):
+            rec[k] = r[k]
+    if not headline:
+        rec["config"] = config_dict(args, wl)
+    return rec
 
 
 _REAL_STDOUT = None
@@ -521,92 +686,56 @@ def main():
     args = parse()
     if args.impl == "reference":
         return run_reference(args)
-    r = run_ours(args)
-    if r["rank"] != 0:
+    import torch
+    c = setup_dist()
+    import image_compression_b200 as pkg
+    from image_compression_b200 import _lib
+    _lib.lib()  # fail loudly here if the extension is missing
+    pkg.set_compute_mode(args.mode)
+    wl = args.workload
+    full = wl == "train" and not args.quick
+    r = measure(args, c, wl, args.steps, args.warmup, with_clocks=True, with_optimizer=wl != "eval",
+                sustained_steps=args.sustained if full else 0, trainer_sequence=full)
+    extras = {}
+    if full:
+        # the rest of BASELINE's metric in front of the driver: C4 (ssim_64 training) and C5 (768x512 eval sweep) from
+        # short runs after the headline timing, at the same N
+        for w2 in ("train_ssim", "eval"):
+            extras[w2] = measure(args, c, w2, max(5, min(args.steps, 10)), 3)
+    if c.rank != 0:
+        _finish_dist()
         return
     peaks = measured_peaks()
-    wl = args.workload
     B, H, W, world = r["B"], r["H"], r["W"], r["world"]
-    ms_per_step = r["ms_total"] / args.steps
-    # dominant kernel: the tcgen05 implicit-GEMM forward kernel (conv / deconv phases / dgrads / GDN contractions)
-    ms, n, flops = r["prof"]["igemm_fwd_umma"]
-    roofline = None
-    if n:
-        ach = flops / (ms * 1e-3) / 1e12
-        peak = peaks["bf16_tflops_sustained"]   # kernel timed inside a long step -> sustained figure
-        roofline = {"bound": "tensor", "kernel": "igemm_fwd_umma_pair_kernel + igemm_fwd_umma_kernel (one class: the "
-                    "CTA-pair and single-CTA builds of the implicit-GEMM forward engine)", "achieved": ach, "peak": peak,
-                    "unit": "TFLOP/s", "frac": ach / peak,
-                    "traffic": ncu_traffic("igemm_fwd_umma_pair_kernel", "igemm_fwd_umma_kernel"),
-                    "peak_source": f"{peaks['source']} (bf16 sustained)", "launches": n,
-                    "avg_launch_ms": ms / n, "share_of_step": ms / r["ms_events"],
-                    "algorithmic_flops_per_launch": flops / n}
-    kernels = {}
-    for name, (kms, kn, work) in r["prof"].items():
-        if not kn:
-            continue
-        gemm = name.startswith("igemm")
-        rate = work / (kms * 1e-3) / (1e12 if gemm else 1e9)
-        pk = peaks["bf16_tflops_sustained"] if gemm else peaks["hbm_gbs"]
-        kernels[name] = {"ms_per_step": kms / args.steps, "launches_per_step": kn / args.steps,
-                         "achieved": rate, "unit": "TFLOP/s" if gemm else "GB/s", "frac": rate / pk,
-                         "share_of_step": kms / r["ms_events"]}
-    gflop_unit = TRAIN_GFLOP_PER_CROP if wl != "eval" else EVAL_GFLOP_PER_IMAGE
-    if (H, W) != ((256, 256) if wl != "eval" else (512, 768)):
-        gflop_unit *= (H * W) / ((256 * 256) if wl != "eval" else (512 * 768))
-    step_tflops = r["value"] / world * gflop_unit / 1e3
-    line = {
-        "metric": METRIC[wl], "value": r["value"], "unit": UNIT[wl], "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": {"bf16": "bf16", "fp32": "f32", "bf16_simt": "bf16"}[args.mode],
-        "data": "synthetic (torch.rand images, random-init weights of the reference architecture)",
-        "config": dict(config_dict(args, per_gpu=B),
-                       l2="inputs rotate over %d resident batches (%.0f MB > 126 MB L2); one step streams >1 GB of "
-                          "activations" % (r["n_rot"], r["n_rot"] * r["h2d"] / 1e6),
-                       timing="CUDA events on the launching stream, max over ranks",
-                       optimizer="excluded (SURVEY 8d); gradient all-reduce included for N>1",
-                       kernel_events=("event pairs around every kernel class inside the timed region"
-                                      if args.kernel_events == "timed" else
-                                      "event pairs around every kernel class over %d further steps right after the timed "
-                                      "region (%.3f ms/step with the events; an event record between two kernels "
-                                      "serialises their programmatic dependent launch, so `value` is timed without them)"
-                                      % (args.steps, r["ms_events"] / args.steps)),
-                       **({"cuda_graph": "each step replays one captured graph of the package's kernels; kernel-class "
-                                         "times and gpu_launches come from the same number of eager steps run after "
-                                         "the timed region"} if r["graphed"] else {})),
-        "clocks": r["clocks"],
-        "e2e": {"value": r["e2e_value"], "unit": UNIT[wl], "h2d_bytes_per_step": r["h2d"],
-                "d2h_bytes_per_step": r["d2h"], "ms_per_step": r["e2e_ms"] / args.steps},
-        "gpu_launches": int(r["launches"]),
-        "roofline": roofline,
-        "kernels": kernels,
-        "step_gemm_tflops_per_gpu": step_tflops,
-        "step_frac_of_tensor_peak": step_tflops / peaks["bf16_tflops_sustained"],
-    }
-    if r.get("optim"):
-        o = dict(r["optim"])
-        o["frac_of_hbm"] = o["kernel_gbs"] / peaks["hbm_gbs"]
-        line["optimizer_step"] = o
+    line = {"higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": {"bf16": "bf16", "fp32": "f32", "bf16_simt": "bf16"}[args.mode], "data": DATA_NOTE,
+            "config": config_dict(args), "clocks": r["clocks"]}
+    line.update(record_of(r, peaks, args, headline=True))
+    if extras:
+        line["extra"] = {k: record_of(v, peaks, args) for k, v in extras.items()}
     if world == 1 and not args.no_cpu_baseline and wl in ("train", "eval"):
         g = time_torch_gpu(wl, B, (H, W), 5, 2)
         if g is not None:
             g.update(unit=UNIT[wl], kind="port", sample=f"5 steps of {B} x {H}x{W} after 2 warm-ups, eager torch on the same B200 "
                      "(fp32 tensors, cuDNN, default flags: cudnn.allow_tf32=%s, matmul.allow_tf32=%s): the oracle port of "
-                     "the reference modules, " % (__import__("torch").backends.cudnn.allow_tf32,
-                                                  __import__("torch").backends.cuda.matmul.allow_tf32)
+                     "the reference modules, " % (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
                      + ("fwd+loss+bwd" if wl == "train" else "forward in rounding mode"))
             line["torch_gpu_baseline"] = g
     if world == 1 and not args.no_cpu_baseline:
-        n = args.cpu_sample if wl != "eval" else 1
+        n = (args.cpu_sample or 16) if wl != "eval" else 1
         probe = time_cpu(wl, n, (H, W), 1, 1)
         steps = max(1, min(5, int(20.0 / max(probe["ms_per_step"] / 1e3, 1e-3))))
-        c = time_cpu(wl, n, (H, W), steps, 0)
+        cb = time_cpu(wl, n, (H, W), steps, 0)
         line["cpu_baseline"] = {
-            "value": c["value"], "unit": UNIT[wl], "cores": c["cores"], "kind": "port",
+            "value": cb["value"], "unit": UNIT[wl], "cores": cb["cores"], "kind": "port",
             "sample": f"{steps} step(s) of {n} x {H}x{W} synthetic "
                       f"{'crops, fwd+loss+bwd' if wl != 'eval' else 'image, fwd+metrics'}, fp32 torch-CPU oracle port of "
-                      f"the reference modules, {c['cores']} threads, after 2 warm-up steps"}
+                      f"the reference modules, {cb['cores']} threads, after 2 warm-up steps"}
     emit(line)
+    _finish_dist()
+
+
+def _finish_dist():
     import torch.distributed as dist
     if dist.is_available() and dist.is_initialized():
         dist.destroy_process_group()

@@ -117,6 +117,16 @@ class AdamwSeg(Structure):
                 ("decay", c_float), ("neg_step_size", c_float), ("bc2_sqrt", c_float), ("reserved", c_float)]
 
 
+class PackJob(Structure):
+    _fields_ = [("kind", c_int), ("ntaps", c_int), ("rows", c_int), ("cols", c_int), ("stride_r", c_int64),
+                ("stride_c", c_int64), ("src", c_void_p), ("src2", c_void_p), ("dst", c_void_p), ("dst2", c_void_p),
+                ("dst3", c_void_p), ("f0", c_float), ("f1", c_float), ("f2", c_float), ("tap_src", ctypes.c_ubyte * 28)]
+
+
+PACK_TAPS, PACK_C3_K, PACK_C3_N, PACK_GDN = range(4)
+PACK_MAX_JOBS = 48
+
+
 class DistTerms(Structure):
     _fields_ = [("dist", c_void_p * 4), ("n", c_int * 4), ("scale", c_float * 4), ("n_terms", c_int)]
 
@@ -144,6 +154,9 @@ _SIGNATURES = {
     "hpc_cdf_logits_fwd": (c_int, [c_void_p, POINTER(CdfParams), c_int64, c_int, c_void_p, c_void_p]),
     "hpc_cdf_logits_bwd": (c_int, [c_void_p, POINTER(CdfParams), c_int64, c_int, c_void_p, c_void_p,
                                    POINTER(CdfParams), c_void_p]),
+    "hpc_cdf_layer_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "hpc_cdf_layer_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p,
+                                  c_void_p, c_void_p, c_void_p, c_void_p]),
     "hpc_conditional_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_float, c_float,
                                     c_uint64, c_uint64, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
                                     c_void_p]),
@@ -178,6 +191,7 @@ _SIGNATURES = {
     "hpc_igemm_wgrad_workspace_bytes": (c_size_t, [POINTER(IgemmWgradParams)]),
     "hpc_pack_weight": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int64, c_int64,
                                 POINTER(c_int), c_void_p]),
+    "hpc_pack_multi": (c_int, [POINTER(PackJob), c_int, c_int, c_void_p]),
     "hpc_unpack_wgrad": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_int64, POINTER(c_int),
                                  c_int, c_void_p]),
     "hpc_colsum": (c_int, [c_void_p, c_int, c_int64, c_int, c_float, c_void_p, c_void_p, c_size_t, c_void_p]),

@@ -433,6 +433,47 @@ class ModelMeta:
         return _lib.SSIM_LOSS, (1 if s.LOG_SCALE else 0), (s.EPS if s.LOG_SCALE else 0.0), (1.0,), c1, c2
 
 
+def _split_model_params(m, params):
+    i = 0
+    ga_convs, ga_gdns = _split_ga(params[i:i + m.n_ga], len(m.strides)); i += m.n_ga
+    ha_convs = _split_h(params[i:i + m.n_ha], m.ha_bias); i += m.n_ha
+    hs_convs = _split_h(params[i:i + m.n_hs], [True] * len(m.hk)); i += m.n_hs
+    gs_convs, gs_gdns = _split_ga(params[i:i + m.n_gs], len(m.strides)); i += m.n_gs
+    cdf = dict(zip(CDF_KEYS, params[i:i + m.n_cdf]))
+    return ga_convs, ga_gdns, ha_convs, hs_convs, gs_convs, gs_gdns, cdf
+
+
+def build_pack_plan(m, params):
+    """hotpath.PackPlan with every packed operand the fused forward + backward of this model read (the same
+    ConvSpec geometry blocks_impl builds layer by layer), for the current compute mode."""
+    ga_convs, ga_gdns, ha_convs, hs_convs, gs_convs, gs_gdns, _ = _split_model_params(m, params)
+    dt = hp.lp_dtype()
+    plan = hp.PackPlan(dt)
+    n = len(m.strides)
+    for i, (w, _) in enumerate(ga_convs):
+        if i == 0:
+            if hp._thin_umma_ok(w.shape[0], w.shape[1], dt):
+                plan.add_c3(w, "k")
+        else:
+            plan.add_spec(hp.ConvSpec(False, w.shape[1], w.shape[0], m.k, m.strides[i]), w)
+    for i, (w, _) in enumerate(ha_convs):
+        plan.add_spec(hp.ConvSpec(False, w.shape[1], w.shape[0], m.hk[i], m.hs[i]), w)
+    for i, (w, _) in enumerate(hs_convs):
+        plan.add_spec(hp.ConvSpec(True, w.shape[0], w.shape[1], m.hk[::-1][i], m.hs[::-1][i]), w)
+    for i, (w, _) in enumerate(gs_convs):
+        if i == n - 1:
+            if hp._thin_umma_ok(w.shape[0], w.shape[1], dt):
+                if w.shape[0] <= 192:
+                    plan.add_c3(w, "n")
+                plan.add_c3(w, "k")
+        else:
+            plan.add_spec(hp.ConvSpec(True, w.shape[0], w.shape[1], m.k, m.strides[i]), w)
+    for gp, bp in list(ga_gdns) + list(gs_gdns):
+        if hp.gdn_fused_ok(dt, bp.numel()):
+            plan.add_gdn(gp, bp, 1e-6)
+    return plan
+
+
 def _nhwc_noise(noise):
     return None if noise is None else _f32c(noise.permute(0, 2, 3, 1))
 
@@ -451,12 +492,8 @@ class Compressor2018Fn(torch.autograd.Function):
         # saved and the GDN kernels skip their r output
         training, grad_enabled = training if isinstance(training, tuple) else (training, True)
         save = grad_enabled and any(ctx.needs_input_grad)
-        i = 0
-        ga_convs, ga_gdns = _split_ga(params[i:i + m.n_ga], len(m.strides)); i += m.n_ga
-        ha_convs = _split_h(params[i:i + m.n_ha], m.ha_bias); i += m.n_ha
-        hs_convs = _split_h(params[i:i + m.n_hs], [True] * len(m.hk)); i += m.n_hs
-        gs_convs, gs_gdns = _split_ga(params[i:i + m.n_gs], len(m.strides)); i += m.n_gs
-        cdf = {k: v.contiguous() for k, v in zip(CDF_KEYS, params[i:i + m.n_cdf])}
+        ga_convs, ga_gdns, ha_convs, hs_convs, gs_convs, gs_gdns, cdf = _split_model_params(m, params)
+        cdf = {k: v.contiguous() for k, v in cdf.items()}
 
         y, yabs, Sga = B.ga_forward(x, ga_convs, ga_gdns, m.k, m.strides, want_abs=True, save=save)
         z, Sha = B.ha_forward(yabs, ha_convs, m.hk, m.hs, save=save)
@@ -508,7 +545,8 @@ class Compressor2018Fn(torch.autograd.Function):
         g_raw = hp.clamp01_backward(raw, x if has_mse else None, g_xt, mse_coef, g, do_clamp=True)
         # --- g_s ---------------------------------------------------------------------------
         g_yt, gs_cg, gs_gg = B.gs_backward(Sgs, g_raw, need_input_grad=True)
-        hp.grads_ready(_join_ga(gs_cg, gs_gg))       # g_s gradients are final: their all-reduce may start now
+        # (every layer above reported its gradients through hp.grads_ready: finished slot ranges of
+        #  sharding.FlatGradients are being all-reduced while the rest of this backward runs)
         # --- conditional likelihood (+ exp/clamp of h_s fused) ------------------------------
         gy_partial, _, gpre = hp.conditional_backward(yt, sigma, m.dist, training, g, inv_np, None, g_yt,
                                                       fuse_exp_clamp=True, want_gs_f32=False, want_gs_lp=True,
@@ -516,6 +554,7 @@ class Compressor2018Fn(torch.autograd.Function):
         # --- h_s -> z~ -> factorised prior -> z ---------------------------------------------
         g_zt, hs_cg = B.hs_backward(Shs, gpre, need_input_grad=True, want_f32=True)
         gz, cdf_grads = hp.factorized_backward(zt, cdf, training, g, inv_np, None, g_zt, m.bin)
+        hp.grads_ready(list(cdf_grads.values()))
         # --- h_a, with d|y|/dy and the three-way sum fused into its last dgrad ---------------
         gy, ha_cg = B.ha_backward(Sha, hp.cast(gz, hp.lp_dtype()), sign_add=(y, gy_partial))
         # --- g_a ---------------------------------------------------------------------------
@@ -556,6 +595,34 @@ class CdfLogitsFn(torch.autograd.Function):
         check(lib().hpc_cdf_logits_bwd(ptr(xl), _lib.byref(s), xl.numel() // C, C, ptr(gl), ptr(gx), _lib.byref(gs),
                                        stream()))
         return (gx.permute(*inv), *[grads[k] for k in CDF_KEYS])
+
+
+class CdfLayerFn(torch.autograd.Function):
+    """CDFLayer.forward stand-alone (entropy_model.py:67-78): x (N,C,D,1) -> (N,C,D',1)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, factor):
+        _lib.require_cuda(x, weight, bias)
+        _, C, dout, din = weight.shape
+        if x.dim() != 4 or x.shape[1] != C or x.shape[2] != din or x.shape[3] != 1:
+            raise ValueError(f"CDFLayer: expected x of shape (N,{C},{din},1), got {tuple(x.shape)}")
+        xc, w, b = _f32c(x), _f32c(weight), _f32c(bias)
+        f = _f32c(factor) if factor is not None else None
+        out = torch.empty((x.shape[0], C, dout, 1), dtype=torch.float32, device=x.device)
+        check(lib().hpc_cdf_layer_fwd(ptr(xc), ptr(w), ptr(b), ptr(f), x.shape[0], C, din, dout, ptr(out), stream()))
+        ctx.save_for_backward(xc, w, b, f)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        xc, w, b, f = ctx.saved_tensors
+        _, C, dout, din = w.shape
+        gx = torch.empty_like(xc) if ctx.needs_input_grad[0] else None
+        gw, gb = torch.empty_like(w), torch.empty_like(b)
+        gf = torch.empty_like(f) if f is not None else None
+        check(lib().hpc_cdf_layer_bwd(ptr(xc), ptr(w), ptr(b), ptr(f), xc.shape[0], C, din, dout, ptr(_f32c(g)), ptr(gx),
+                                      ptr(gw), ptr(gb), ptr(gf), stream()))
+        return gx, gw, gb, gf
 
 
 class AbsFn(torch.autograd.Function):

@@ -92,6 +92,7 @@ def ga_backward(S, gy_lp):
             gsum = None
             gw = spec.wgrad(inp, g, w)
             conv_grads[ci] = (gw, gb)
+            hp.grads_ready((gw, gb))
             g = spec.dgrad(g, w, inp.shape[1:3])["lp"]
             ci -= 1
         elif kind == "gdn":
@@ -102,6 +103,7 @@ def ga_backward(S, gy_lp):
                 g, x, xsq, nrm, gamma, want_dxsum=True, reparam=(gp, bp, 1e-6),
                 dxsum_out=hp.grad_buffer(b_prod) if b_prod is not None and hp.gdn_bwd_has_dxsum(x) else None)
             gdn_grads[gi] = (ggamma, gbeta)
+            hp.grads_ready((ggamma, gbeta, gsum))
             g = dx
             gi -= 1
         else:  # head conv: weight + bias grads only (the image needs no gradient)
@@ -109,6 +111,7 @@ def ga_backward(S, gy_lp):
             gw = hp.wgrad_c3(g, S.x, w.shape[0], w.shape[1], w)
             gb = (gsum if gsum is not None else hp.colsum(g, out=hp.grad_buffer(b))) if b is not None else None
             conv_grads[0] = (gw, gb)
+            hp.grads_ready((gw, gb), flush=True)
     return conv_grads, gdn_grads
 
 
@@ -157,6 +160,7 @@ def gs_backward(S, g_raw_nchw, need_input_grad=True):
             w, b = S.convs[ci]
             g, gw, gb = hp.deconv_c3_backward(g_raw_nchw, inp, w, need_dx=(not first) or need_input_grad, bias=b)
             conv_grads[ci] = (gw, gb if b is not None else None)
+            hp.grads_ready((gw, gb))
             ci -= 1
         elif kind == "gdn":
             x, xsq, nrm, gamma = a
@@ -166,6 +170,7 @@ def gs_backward(S, g_raw_nchw, need_input_grad=True):
                 g, x, xsq, nrm, gamma, want_dxsum=True, reparam=(gp, bp, 1e-6),
                 dxsum_out=hp.grad_buffer(b_prod) if b_prod is not None and hp.gdn_bwd_has_dxsum(x) else None)
             gdn_grads[gi] = (ggamma, gbeta)
+            hp.grads_ready((ggamma, gbeta, gsum))
             g = dx
             gi -= 1
         else:
@@ -175,6 +180,7 @@ def gs_backward(S, g_raw_nchw, need_input_grad=True):
             gsum = None
             gw = spec.wgrad(inp, g, w)
             conv_grads[ci] = (gw, gb)
+            hp.grads_ready((gw, gb), flush=first)
             g = spec.dgrad(g, w, inp.shape[1:3])["lp"] if (not first or need_input_grad) else None
             ci -= 1
     return g, conv_grads, gdn_grads
@@ -215,6 +221,7 @@ def ha_backward(S, gz_lp, sign_add=None, need_input_grad=True):
         gb = hp.colsum(g, out=hp.grad_buffer(b)) if b is not None else None
         gw = spec.wgrad(inp, g, w)
         conv_grads[i] = (gw, gb)
+        hp.grads_ready((gw, gb), flush=(i == 0))
         if i > 0:
             # inp is the ReLU output of layer i-1: mask the gradient in the dgrad epilogue
             g = spec.dgrad(g, w, inp.shape[1:3], EPI_RELU_MASK, aux0=inp)["lp"]
@@ -265,6 +272,7 @@ def hs_backward(S, gpre_lp, need_input_grad=True, want_f32=False):
         gb = hp.colsum(g, out=hp.grad_buffer(b)) if b is not None else None
         gw = spec.wgrad(inp, g, w)
         conv_grads[i] = (gw, gb)
+        hp.grads_ready((gw, gb))
         if i > 0:
             g = spec.dgrad(g, w, inp.shape[1:3], EPI_RELU_MASK, aux0=inp)["lp"]
         elif need_input_grad:

@@ -31,3 +31,129 @@ int hpc_abs_bwd(const float* x, const float* g, float* gx, int64_t n, hpc_stream
   HPC_LAUNCH_CHECK();
   return HPC_OK;
 }
+
+// ---------------------------------------------------------------------------------------
+// hpc_pack_multi: every packed bf16 operand copy a training step needs (the [tap][row][col] copies of the
+// 192 -> 192 conv / transposed-conv weights for the forward and the dgrad engines, the K-major / N-major copies of
+// the 3-channel head and tail, the effective gamma / gamma^T / beta of every GDN layer) in ONE launch.
+// A block owns one tile of one job; the job table travels by value in the kernel parameters.
+// Same arithmetic as hpc_pack_weight / hpc_pack_c3_weight / hpc_gdn_prepare (pure data movement + the
+// NonNegativeParam reparametrisation of gdn.py:59-62), so the engines see bit-identical operands.
+// ---------------------------------------------------------------------------------------
+namespace {
+constexpr int PK_TR = 8, PK_TC = 32, PK_THREADS = 256;
+constexpr int PK_FLAT = 2048;                 // dst elements per block of the flat job kinds
+
+struct PackTable {
+  hpc_pack_job job[HPC_PACK_MAX_JOBS];
+  int block_begin[HPC_PACK_MAX_JOBS + 1];
+  int njobs;
+  int dtype;
+};
+
+template <typename T>
+__device__ __forceinline__ void pack_taps_tile(const hpc_pack_job& J, int b, float* sm) {
+  const int K = J.ntaps, rows = J.rows, cols = J.cols;
+  const int tiles_c = (cols + PK_TC - 1) / PK_TC;
+  const int tr0 = (b / tiles_c) * PK_TR, tc0 = (b % tiles_c) * PK_TC;
+  const float* __restrict__ src = J.src;
+  const int64_t sr = J.stride_r, sc = J.stride_c;
+  const bool c_inner = sc <= sr;               // the (r | c) index whose K taps follow each other in memory goes second
+  const int n = PK_TR * PK_TC * K;
+  for (int i = threadIdx.x; i < n; i += PK_THREADS) {
+    const int k = i % K, q = i / K;
+    const int c = c_inner ? q % PK_TC : q / PK_TR;
+    const int r = c_inner ? q / PK_TC : q % PK_TR;
+    const bool in = tr0 + r < rows && tc0 + c < cols;
+    sm[(r * PK_TC + c) * K + k] = in ? src[(tr0 + r) * sr + (tc0 + c) * sc + k] : 0.f;
+  }
+  __syncthreads();
+  T* __restrict__ dst = (T*)J.dst;
+  for (int i = threadIdx.x; i < n; i += PK_THREADS) {
+    const int c = i % PK_TC, r = (i / PK_TC) % PK_TR, j = i / (PK_TC * PK_TR);
+    if (tr0 + r < rows && tc0 + c < cols)
+      st_from_float<T>(dst, ((size_t)j * rows + tr0 + r) * cols + tc0 + c, sm[(r * PK_TC + c) * K + J.tap_src[j]]);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(PK_THREADS)
+pack_multi_kernel(const __grid_constant__ PackTable t) {
+  __shared__ float sm[PK_TR * PK_TC * HPC_MAX_TAPS];
+  int lo = 0, hi = t.njobs;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if ((int)blockIdx.x >= t.block_begin[mid]) lo = mid; else hi = mid;
+  }
+  const hpc_pack_job& J = t.job[lo];
+  const int b = (int)blockIdx.x - t.block_begin[lo];
+  if (J.kind == HPC_PACK_TAPS) {
+    pack_taps_tile<T>(J, b, sm);
+  } else if (J.kind == HPC_PACK_C3_K || J.kind == HPC_PACK_C3_N) {
+    // w[cw*stride_r + cs*stride_c + tap] -> kmaj[cw][128] (k = cs*25+tap, zero padded) or nmaj[80][cw]; always bf16
+    const int Cw = J.rows, total = J.kind == HPC_PACK_C3_K ? Cw * 128 : 80 * Cw;
+    __nv_bfloat16* __restrict__ dst = (__nv_bfloat16*)J.dst;
+    for (int i = b * PK_FLAT + threadIdx.x; i < min(total, (b + 1) * PK_FLAT); i += PK_THREADS) {
+      const int cw = J.kind == HPC_PACK_C3_K ? i / 128 : i % Cw, k = J.kind == HPC_PACK_C3_K ? i % 128 : i / Cw;
+      dst[i] = __float2bfloat16_rn(k < 75 ? J.src[cw * J.stride_r + (k / 25) * J.stride_c + (k % 25)] : 0.f);
+    }
+  } else {  // HPC_PACK_GDN: gdn.py:59-62 for gamma and beta + both bf16 operand copies of gamma (== gdn_prepare_kernel)
+    const int C = J.rows, total = C * C;
+    __nv_bfloat16* __restrict__ g = (__nv_bfloat16*)J.dst;
+    __nv_bfloat16* __restrict__ gT = (__nv_bfloat16*)J.dst2;
+    for (int i = b * PK_FLAT + threadIdx.x; i < min(total, (b + 1) * PK_FLAT); i += PK_THREADS) {
+      const float v = fmaxf(J.src[i], J.f0);
+      const __nv_bfloat16 h = __float2bfloat16_rn(v * v - J.f2);
+      g[i] = h;
+      gT[(i % C) * C + i / C] = h;
+      if (i < C) {
+        const float w = fmaxf(J.src2[i], J.f1);
+        J.dst3[i] = w * w - J.f2;
+      }
+    }
+  }
+}
+}  // namespace
+
+int hpc_pack_multi(const hpc_pack_job* jobs, int njobs, int dtype, hpc_stream_t stream) {
+  HPC_REQUIRE(jobs && njobs > 0, HPC_ERR_BAD_SHAPE, "hpc_pack_multi: no jobs");
+  HPC_REQUIRE(dtype == HPC_BF16 || dtype == HPC_F32, HPC_ERR_UNSUPPORTED, "hpc_pack_multi: dtype %d", dtype);
+  for (int base = 0; base < njobs; base += HPC_PACK_MAX_JOBS) {
+    PackTable t;
+    memset(&t, 0, sizeof(t));
+    t.njobs = njobs - base < HPC_PACK_MAX_JOBS ? njobs - base : HPC_PACK_MAX_JOBS;
+    t.dtype = dtype;
+    int blocks = 0;
+    for (int i = 0; i < t.njobs; ++i) {
+      const hpc_pack_job& J = jobs[base + i];
+      HPC_REQUIRE(J.src && J.dst && J.rows > 0, HPC_ERR_BAD_SHAPE, "hpc_pack_multi: job %d has a NULL pointer or no rows", base + i);
+      t.job[i] = J;
+      t.block_begin[i] = blocks;
+      switch (J.kind) {
+        case HPC_PACK_TAPS:
+          HPC_REQUIRE(J.ntaps >= 1 && J.ntaps <= HPC_MAX_TAPS && J.cols > 0 && (J.stride_r == J.ntaps || J.stride_c == J.ntaps),
+                      HPC_ERR_BAD_SHAPE, "hpc_pack_multi: job %d: taps=%d cols=%d strides (%lld,%lld): the taps of one "
+                      "(row, col) must be contiguous", base + i, J.ntaps, J.cols, (long long)J.stride_r, (long long)J.stride_c);
+          for (int k = 0; k < J.ntaps; ++k)
+            HPC_REQUIRE(J.tap_src[k] < J.ntaps, HPC_ERR_BAD_SHAPE, "hpc_pack_multi: job %d: tap_src[%d] out of range", base + i, k);
+          blocks += ((J.rows + PK_TR - 1) / PK_TR) * ((J.cols + PK_TC - 1) / PK_TC);
+          break;
+        case HPC_PACK_C3_K: blocks += (J.rows * 128 + PK_FLAT - 1) / PK_FLAT; break;
+        case HPC_PACK_C3_N: blocks += (J.rows * 80 + PK_FLAT - 1) / PK_FLAT; break;
+        case HPC_PACK_GDN:
+          HPC_REQUIRE(J.src2 && J.dst2 && J.dst3 && J.rows <= PK_FLAT, HPC_ERR_BAD_SHAPE, "hpc_pack_multi: job %d: GDN job needs beta, "
+                      "gamma^T and beta_eff pointers and C <= %d", base + i, PK_FLAT);
+          blocks += (J.rows * J.rows + PK_FLAT - 1) / PK_FLAT;
+          break;
+        default: HPC_FAIL(HPC_ERR_UNSUPPORTED, "hpc_pack_multi: job %d: kind %d", base + i, J.kind);
+      }
+    }
+    t.block_begin[t.njobs] = blocks;
+    if (dtype == HPC_BF16)
+      pack_multi_kernel<__nv_bfloat16><<<blocks, PK_THREADS, 0, (cudaStream_t)stream>>>(t);
+    else
+      pack_multi_kernel<float><<<blocks, PK_THREADS, 0, (cudaStream_t)stream>>>(t);
+    HPC_LAUNCH_CHECK();
+  }
+  return HPC_OK;
+}

@@ -186,28 +186,38 @@ _capturing = False
 _grad_sink = None
 
 
-def set_grad_sink(sink):
+_grad_sink_owner = None
+
+
+def set_grad_sink(sink, owner=None):
     """sink: {param.data_ptr(): zero-filled fp32 view shaped like the parameter} or None.  While armed, the
     backward functions below take the OUTPUT buffer of a parameter's gradient from the sink (each entry once), so
     the kernels write into the caller's flat gradient buffer (sharding.FlatGradients) instead of fresh tensors."""
-    global _grad_sink
+    global _grad_sink, _grad_sink_owner
     _grad_sink = sink if sink else None
+    _grad_sink_owner = owner if sink else None
+
+
+def grad_sink_owner():
+    return _grad_sink_owner if _grad_sink else None
 
 
 _grad_ready_hook = None
 
 
 def set_grad_ready_hook(fn):
-    """fn(list of gradient tensors) or None.  The fused backward calls it as soon as every kernel writing the
-    gradients of a parameter group has been ENQUEUED on the current stream (today: the synthesis transform, whose
-    gradients are final ~45% into the backward), so sharding.FlatGradients can start their all-reduce early."""
+    """fn(list of gradient tensors, flush) or None.  The backward schedules call it as soon as every kernel writing
+    the gradients of a layer has been ENQUEUED on the current stream, so sharding.FlatGradients can start the
+    all-reduce of finished slot ranges while the rest of the backward still runs."""
     global _grad_ready_hook
     _grad_ready_hook = fn
 
 
-def grads_ready(grads):
+def grads_ready(grads, flush=False):
+    """Called by the backward schedules (blocks_impl, autograd_ops) after every layer: the kernels writing these
+    parameter gradients have all been enqueued.  flush: a parameter group ends here (start its all-reduce now)."""
     if _grad_ready_hook is not None:
-        _grad_ready_hook([g for g in grads if g is not None])
+        _grad_ready_hook([g for g in grads if g is not None], flush)
 
 
 def grad_buffer(param, zero=False):
@@ -222,32 +232,154 @@ def grad_buffer(param, zero=False):
     return torch.empty(param.shape, dtype=torch.float32, device=param.device)
 
 
+_captured_keys = set()
+
+
 def set_capturing(flag):
     """While a CUDA graph is being captured the packed-weight cache is bypassed, so that the pack kernels are
-    nodes of the graph and replays always see the current weights."""
+    nodes of the graph and replays always see the current weights (operands a PackPlan re-packed INSIDE this
+    capture are the exception: its launch is the graph node, and its persistent buffers are what later calls read)."""
     global _capturing
     _capturing = bool(flag)
+    _captured_keys.clear()
+
+
+def _plan_filled(key):
+    return key in _captured_keys
+
+
+def _pack_key(w, taps, rows, cols, stride_r, stride_c, dtype):
+    return (id(w), rows, cols, stride_r, stride_c, dtype, tuple(t[2] for t in taps))
+
+
+def _cache_get(key, w):
+    """Cached operand copy of the live tensor `w` (or None).  Valid only for the very same tensor object at the same
+    version and storage: ids and device addresses are both recycled after a model is freed.  The version check is
+    what makes weight updates visible: torch's in-place ops bump `_version`; code that writes parameters through raw
+    device pointers (solver.FusedAdamW) must bump it itself (`bump_versions`)."""
+    hit = _pack_cache.get(key)
+    if hit is not None and hit[0]() is w and hit[1] == w._version and hit[2] == w.data_ptr():
+        return hit[3]
+    return None
+
+
+def _cache_put(key, w, out):
+    if len(_pack_cache) > 512:
+        _pack_cache.clear()
+    _pack_cache[key] = (weakref.ref(w), w._version, w.data_ptr(), out)
+
+
+def bump_versions(tensors):
+    """Tell autograd (and every cache keyed on `_version`, the packed-operand cache above included) that `tensors`
+    were modified in place by a kernel that got raw pointers."""
+    torch._C._increment_version(list(tensors))
+
+
+def invalidate_packs():
+    """Drop every cached packed operand (e.g. after parameters were written behind torch's back)."""
+    _pack_cache.clear()
+
+
+class PackPlan:
+    """Every packed operand copy a model's forward + backward consume -- the [tap][row][col] copies of the conv /
+    transposed-conv weights for the forward and the dgrad engines, the K-/N-major copies of the 3-channel head and tail,
+    the effective gamma / gamma^T / beta of the GDN layers -- rebuilt by ONE launch (hpc_pack_multi) into persistent
+    buffers whenever a source parameter changed (a training step changes all of them: 33 launches otherwise).
+    `ensure()` publishes the copies in the packed-operand cache, where pack_weight / pack_c3_weight / gdn_prepare find
+    them.  While a CUDA graph is being captured the launch is always issued, so it becomes a node of the graph."""
+
+    def __init__(self, dtype):
+        self.dtype = dtype
+        self.entries = []          # (key, sources, out object, job index)
+        self.jobs = []
+        self._sig = None
+        self._arr = None
+
+    def _job(self, kind, src, dst, rows, cols=0, ntaps=0, sr=0, sc=0, tap_src=(), src2=None, dst2=None, dst3=None,
+             f=(0.0, 0.0, 0.0)):
+        self.jobs.append(dict(kind=kind, src=src, dst=dst, rows=rows, cols=cols, ntaps=ntaps, sr=sr, sc=sc,
+                              tap_src=tuple(tap_src), src2=src2, dst2=dst2, dst3=dst3, f=f))
+        self._arr = None
+
+    def add_taps(self, w, taps, rows, cols, sr, sc):
+        key = _pack_key(w, taps, rows, cols, sr, sc, self.dtype)
+        if any(e[0] == key for e in self.entries):
+            return
+        out = torch.empty((len(taps), rows, cols), dtype=self.dtype, device=w.device)
+        self.entries.append((key, (w,), out))
+        self._job(_lib.PACK_TAPS, w, out, rows, cols, len(taps), sr, sc, [t[2] for t in taps])
+
+    def add_spec(self, spec, w, dgrad=True):
+        self.add_taps(w, *spec.fwd_pack())
+        if dgrad:
+            self.add_taps(w, *spec.dgrad_pack())
+
+    def add_c3(self, w, kind):
+        Cw, Cs = w.shape[0], w.shape[1]
+        out = torch.empty((Cw, 128) if kind == "k" else (80, Cw), dtype=torch.bfloat16, device=w.device)
+        self.entries.append(((id(w), "c3", kind), (w,), out))
+        self._job(_lib.PACK_C3_K if kind == "k" else _lib.PACK_C3_N, w, out, Cw, sr=Cs * 25, sc=25)
+
+    def add_gdn(self, gamma_param, beta_param, beta_min=1e-6):
+        C = beta_param.numel()
+        ops = GdnOperands()
+        ops.beta = torch.empty((C,), dtype=torch.float32, device=beta_param.device)
+        both = torch.empty((2, C, C), dtype=torch.bfloat16, device=beta_param.device)
+        ops.g, ops.gT = both[0], both[1]
+        self.entries.append(((id(gamma_param), "gdn", float(beta_min)), (gamma_param, beta_param), ops))
+        self._job(_lib.PACK_GDN, gamma_param, ops.g, C, src2=beta_param, dst2=ops.gT, dst3=ops.beta,
+                  f=(GAMMA_BOUND, beta_bound(beta_min), PEDESTAL))
+
+    def _signature(self):
+        return tuple((t._version, t.data_ptr()) for e in self.entries for t in e[1])
+
+    def ensure(self):
+        if not self.jobs:
+            return
+        sig = self._signature()
+        if sig != self._sig or _capturing:
+            ptrs = tuple(s[1] for s in sig)
+            if self._arr is None or self._ptrs != ptrs:
+                arr = (_lib.PackJob * len(self.jobs))()
+                for a, j in zip(arr, self.jobs):
+                    a.kind, a.ntaps, a.rows, a.cols, a.stride_r, a.stride_c = (j["kind"], j["ntaps"], j["rows"],
+                                                                              j["cols"], j["sr"], j["sc"])
+                    a.src, a.src2, a.dst, a.dst2, a.dst3 = (ptr(j["src"]), ptr(j["src2"]), ptr(j["dst"]),
+                                                            ptr(j["dst2"]), ptr(j["dst3"]))
+                    a.f0, a.f1, a.f2 = j["f"]
+                    for i, t in enumerate(j["tap_src"]):
+                        a.tap_src[i] = t
+                self._arr, self._ptrs = arr, ptrs
+            check(lib().hpc_pack_multi(self._arr, len(self.jobs), _lib.dtype_code(self.dtype), stream()))
+            self._sig = sig
+            if _capturing:
+                _captured_keys.update(e[0] for e in self.entries)
+        elif self.entries[0][0] in _pack_cache and _pack_cache[self.entries[0][0]][3] is self.entries[0][2]:
+            return                      # still published
+        for key, srcs, out in self.entries:
+            if len(srcs) == 1:
+                _cache_put(key, srcs[0], out)
+            else:        # GDN: validated on both parameters
+                _pack_cache[key] = (weakref.ref(srcs[0]), tuple(t._version for t in srcs),
+                                    tuple(t.data_ptr() for t in srcs), out, weakref.ref(srcs[1]))
 
 
 def pack_weight(w, taps, rows, cols, stride_r, stride_c, dtype, cache=True):
     """Packed (ntaps, rows, cols) copy of a reference-layout weight in `dtype` (hpc_pack_weight).
-    Cached on (storage, version) so evaluation loops do not repack unchanged weights."""
-    key = (id(w), rows, cols, stride_r, stride_c, dtype, tuple(t[2] for t in taps))
-    cache = cache and not _capturing
+    Cached on (tensor, version, storage) so unchanged weights are not repacked; a model's PackPlan fills the cache
+    for all of its layers with one launch."""
+    key = _pack_key(w, taps, rows, cols, stride_r, stride_c, dtype)
     if cache:
-        hit = _pack_cache.get(key)
-        # valid only for the very same live tensor object at the same version and storage: ids and
-        # device addresses are both recycled after a model is freed
-        if hit is not None and hit[0]() is w and hit[1] == w._version and hit[2] == w.data_ptr():
-            return hit[3]
+        hit = _cache_get(key, w)        # (during a graph capture the plan has just re-issued the pack as a graph node)
+        if hit is not None and (not _capturing or _plan_filled(key)):
+            return hit
+        cache = not _capturing
     out = torch.empty((len(taps), rows, cols), dtype=dtype, device=w.device)
     src = (c_int * len(taps))(*[t[2] for t in taps])
     check(lib().hpc_pack_weight(ptr(w), ptr(out), _lib.dtype_code(out), len(taps), rows, cols, stride_r, stride_c,
                                 src, stream()))
     if cache:
-        if len(_pack_cache) > 256:
-            _pack_cache.clear()
-        _pack_cache[key] = (weakref.ref(w), w._version, w.data_ptr(), out)
+        _cache_put(key, w, out)
     return out
 
 
@@ -358,32 +490,42 @@ class ConvSpec:
             return (H - 1) * s - 2 * p + k + (s - 1), (W - 1) * s - 2 * p + k + (s - 1)
         return (H + 2 * p - k) // s + 1, (W + 2 * p - k) // s + 1
 
+    # ---- packed operand geometry: (taps, rows, cols, stride_r, stride_c) of pack_weight ----------
+    def fwd_pack(self):
+        K, Ci, Co = self.K, self.cin, self.cout
+        if self.transposed:   # weight (Ci,Co,k,k); rows=Co cols=Ci
+            return self.deconv_taps[0], Co, Ci, K, Co * K
+        return self.conv_taps[0], Co, Ci, Ci * K, K          # weight (Co,Ci,k,k)
+
+    def dgrad_pack(self):
+        K, Ci, Co = self.K, self.cin, self.cout
+        if self.transposed:   # conv-type over the input grid; rows=Ci cols=Co from W[ci][co][k]
+            return self.conv_taps[0], Ci, Co, Co * K, K
+        return self.deconv_taps[0], Ci, Co, K, Ci * K        # rows=Ci cols=Co from W[co][ci][k]
+
     # ---- forward -------------------------------------------------------------------
     def forward(self, x, weight, bias, epi=EPI_LINEAR, **wants):
         N, H, W, Ci = x.shape
         assert Ci == self.cin, (Ci, self.cin)
         OH, OW = self.out_hw(H, W)
-        K, Ci_, Co = self.K, self.cin, self.cout
-        if self.transposed:   # weight (Ci,Co,k,k); rows=Co cols=Ci
+        wp = pack_weight(weight, *self.fwd_pack(), x.dtype)
+        if self.transposed:
             taps, phases = self.deconv_taps
-            wp = pack_weight(weight, taps, Co, Ci_, K, Co * K, x.dtype)
-            return igemm_fwd(x, wp, taps, phases, (H, W), 1, self.s, (OH, OW), Co, epi, bias, **wants)
-        taps, phases = self.conv_taps  # weight (Co,Ci,k,k)
-        wp = pack_weight(weight, taps, Co, Ci_, Ci_ * K, K, x.dtype)
-        return igemm_fwd(x, wp, taps, phases, (OH, OW), self.s, 1, (OH, OW), Co, epi, bias, **wants)
+            return igemm_fwd(x, wp, taps, phases, (H, W), 1, self.s, (OH, OW), self.cout, epi, bias, **wants)
+        taps, phases = self.conv_taps
+        return igemm_fwd(x, wp, taps, phases, (OH, OW), self.s, 1, (OH, OW), self.cout, epi, bias, **wants)
 
     # ---- backward ------------------------------------------------------------------
     def dgrad(self, g, weight, in_hw, epi=EPI_LINEAR, **kw):
         """g: NHWC lp gradient wrt this layer's output -> gradient wrt its input."""
         N, GH_, GW_, _ = g.shape
         H, W = in_hw
-        K, Ci, Co = self.K, self.cin, self.cout
-        if self.transposed:   # conv-type over the input grid; rows=Ci cols=Co from W[ci][co][k]
+        Ci = self.cin
+        wp = pack_weight(weight, *self.dgrad_pack(), g.dtype)
+        if self.transposed:
             taps, phases = self.conv_taps
-            wp = pack_weight(weight, taps, Ci, Co, Co * K, K, g.dtype)
             return igemm_fwd(g, wp, taps, phases, (H, W), self.s, 1, (H, W), Ci, epi, None, **kw)
-        taps, phases = self.deconv_taps  # rows=Ci cols=Co from W[co][ci][k]
-        wp = pack_weight(weight, taps, Ci, Co, K, Ci * K, g.dtype)
+        taps, phases = self.deconv_taps
         return igemm_fwd(g, wp, taps, phases, (GH_, GW_), 1, self.s, (H, W), Ci, epi, None, **kw)
 
     def wgrad(self, x, g, weight_shape_like):
@@ -448,7 +590,14 @@ class GdnOperands:
 
 
 def gdn_prepare(gamma_param, beta_param, beta_min=1e-6):
-    """gdn.py:59-62 for both parameters + both operand copies in one launch (fused path only)."""
+    """gdn.py:59-62 for both parameters + both operand copies in one launch (fused path only).  A model's PackPlan
+    publishes them for all of its GDN layers at once; this is the stand-alone path."""
+    key = (id(gamma_param), "gdn", float(beta_min))
+    hit = _pack_cache.get(key)
+    if (hit is not None and len(hit) == 5 and hit[0]() is gamma_param and hit[4]() is beta_param
+            and hit[1] == (gamma_param._version, beta_param._version)
+            and hit[2] == (gamma_param.data_ptr(), beta_param.data_ptr()) and (not _capturing or _plan_filled(key))):
+        return hit[3]
     C = beta_param.numel()
     ops = GdnOperands()
     ops.beta = torch.empty((C,), dtype=torch.float32, device=beta_param.device)
@@ -563,17 +712,15 @@ def pack_c3_weight(weight, kind):
     """bf16 operand of the tcgen05 thin kernels from a (Cw,3,5,5)-laid-out weight (Conv2d(3->Cw) weight or
     ConvTranspose2d(Cw->3) weight): kind "k" -> [Cw][128] (k contiguous), "n" -> [80][Cw].  Cached like pack_weight."""
     key = (id(weight), "c3", kind)
-    hit = None if _capturing else _pack_cache.get(key)
-    if hit is not None and hit[0]() is weight and hit[1] == weight._version and hit[2] == weight.data_ptr():
-        return hit[3]
+    hit = _cache_get(key, weight)
+    if hit is not None and (not _capturing or _plan_filled(key)):
+        return hit
     Cw, Cs = weight.shape[0], weight.shape[1]
     out = torch.empty((Cw, 128) if kind == "k" else (80, Cw), dtype=torch.bfloat16, device=weight.device)
     check(lib().hpc_pack_c3_weight(ptr(weight), Cs * 25, 25, Cw, ptr(out) if kind == "k" else None,
                                    ptr(out) if kind == "n" else None, stream()))
     if not _capturing:
-        if len(_pack_cache) > 256:
-            _pack_cache.clear()
-        _pack_cache[key] = (weakref.ref(weight), weight._version, weight.data_ptr(), out)
+        _cache_put(key, weight, out)
     return out
 
 
@@ -673,11 +820,20 @@ def _check_cdf_dims(t):
                                   "(utils/config.py:66); got " + str([tuple(t[f'w{i}'].shape) for i in range(4)]))
 
 
+def _rank_salt():
+    """Ranks of a data-parallel job are usually seeded identically (the reference seeds every process with cfg.SEED,
+    utils/deterministic.py:21-29): mix the rank into the Philox key so replicas draw different quantisation noise."""
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized():
+        return (dist.get_rank() * 0x9E3779B97F4A7C15) & (2 ** 62 - 1)
+    return 0
+
+
 def next_seed():
     """(seed, offset) for the in-kernel Philox stream, drawn from torch's CPU generator so that
-    torch.manual_seed() makes runs reproducible (no device sync)."""
+    torch.manual_seed() makes runs reproducible (no device sync); the rank is mixed into the seed."""
     v = torch.randint(0, 2 ** 62, (2,), dtype=torch.int64)
-    return int(v[0]), int(v[1])
+    return int(v[0]) ^ _rank_salt(), int(v[1])
 
 
 def factorized_forward(z, cdf, training, noise=None, bin_=1.0, want_probs=True, want_lp=False):

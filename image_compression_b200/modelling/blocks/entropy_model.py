@@ -6,7 +6,7 @@ import torch
 import torch.nn as nn
 
 from ... import _lib
-from ...autograd_ops import BitsFn, CdfLogitsFn, ConditionalFn, EntropyModelFn
+from ...autograd_ops import BitsFn, CdfLayerFn, CdfLogitsFn, ConditionalFn, EntropyModelFn
 from .build import ENTROPY_MODEL_REGISTRY
 
 
@@ -24,8 +24,9 @@ class CDFLayer(nn.Module):
             self.factor = nn.Parameter(nn.init.zeros_(torch.empty(1, channels, out_dim, 1)))
 
     def forward(self, x):
-        raise NotImplementedError("CDFLayer is evaluated inside the fused per-channel MLP kernel; call "
-                                  "CDFEstimator / EntropyModel instead")
+        """x (N,C,D,1) -> (N,C,D',1)  (entropy_model.py:67-78).  Stand-alone layer kernel for module parity; the
+        hot path (CDFEstimator / EntropyModel) evaluates all four layers inside one fused per-channel MLP kernel."""
+        return CdfLayerFn.apply(x, self.weight, self.bias, self.factor if self.act else None)
 
 
 class CDFEstimator(nn.Module):

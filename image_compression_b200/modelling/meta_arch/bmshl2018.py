@@ -12,7 +12,9 @@ Two execution paths, both on the hand-written kernels only:
 import torch
 import torch.nn as nn
 
-from ...autograd_ops import Compressor2018Fn, ModelMeta
+from ... import _lib
+
+from ...autograd_ops import Compressor2018Fn, ModelMeta, build_pack_plan
 from ..blocks import (ENTROPY_MODEL_REGISTRY, AnalysisTransform, HyperpriorAnalysisTransform,
                       HyperpriorSynthesisTransform, SynthesisTransform)
 from ..layers import LowerBound, UpperBound
@@ -42,6 +44,18 @@ class Compressor2018(nn.Module):
         self.fused = True
         self.cuda_graphs = False      # opt-in: replay evaluation forwards (no_grad, eval mode) as one CUDA graph
         self._graphs = {}
+        self._plans = {}              # compute mode -> hotpath.PackPlan (packed bf16 operand copies of the weights)
+        # trainer-transparent gradient handling (sharding.GradientReducer): in training mode the backward writes every
+        # gradient into one flat buffer and, under torchrun (an initialised process group with > 1 rank), all-reduces it
+        # from inside the backward, so engine/trainer.py:176-194 runs unchanged.  False: plain autograd gradients.
+        self.flat_gradients = True
+        self._reducer = None
+
+    def __getstate__(self):
+        # copy.deepcopy / pickling: per-process device state (flat gradient buffer, packed operands, CUDA graphs) stays behind
+        d = self.__dict__.copy()
+        d["_reducer"], d["_plans"], d["_graphs"] = None, {}, {}
+        return d
 
     # ------------------------------------------------------------------------------
     def _flat_params(self):
@@ -49,14 +63,45 @@ class Compressor2018(nn.Module):
                 self.prior_synthesis.flat_params() + self.synthesis_transform.flat_params() +
                 self.entropy_model._cdf_estimator.flat_params())
 
+    def gradient_reducer(self):
+        """The model's sharding.GradientReducer (built on first use, rebuilt when the parameters moved).  Slot order of
+        its flat buffer = the order the backward finishes gradients in (g_s last layer first ... g_a first layer last),
+        so finished ranges are all-reduced while the rest of the backward runs."""
+        from ...sharding import GradientReducer
+        params = [p for p in self.backward_order_parameters() if p.requires_grad]
+        r = self._reducer
+        if r is None or r.fg.flat.device != params[0].device or len(r.fg.params) != len(params) or any(
+                a is not b for a, b in zip(r.fg.params, params)):
+            r = self._reducer = GradientReducer(params, module=self)
+        return r
+
+    def backward_order_parameters(self):
+        out = []
+        for block in (self.synthesis_transform, self.prior_synthesis):
+            out += list(block.parameters())[::-1]
+        out += list(self.entropy_model.parameters())
+        for block in (self.prior_analysis, self.analysis_transform):
+            out += list(block.parameters())[::-1]
+        seen = {id(p) for p in out}
+        return out + [p for p in self.parameters() if id(p) not in seen]
+
     def forward(self, x, noise_z=None, noise_y=None):
         """noise_z / noise_y: optional U[0,1) tensors shaped like z / y (NCHW) replacing the in-kernel
         Philox noise of training mode (parity tests inject the reference's draws here)."""
+        reducer = None
+        if self.flat_gradients and self.training and torch.is_grad_enabled() and x.is_cuda:
+            reducer = self.gradient_reducer()
+            if not reducer.before_forward():
+                reducer = None
         if self.fused and self._meta.fusable():
             if self.cuda_graphs and not self.training and not torch.is_grad_enabled() and noise_z is None:
                 return self._forward_graphed(x)
-            return self._forward_fused(x, noise_z, noise_y)
-        return self._forward_composed(x, noise_z, noise_y)
+            out = self._forward_fused(x, noise_z, noise_y)
+        else:
+            out = self._forward_composed(x, noise_z, noise_y)
+        if reducer is not None:
+            reducer.watch(out[1]["total_loss"])
+        return out
 
     def _forward_graphed(self, x):
         """Static-shape evaluation forward replayed as a CUDA graph (outputs are static tensors: consume them
@@ -71,8 +116,22 @@ class Compressor2018(nn.Module):
             g = self._graphs[key] = GraphedCallable(lambda t: self._forward_fused(t, None, None), x.contiguous())
         return g(x.contiguous())
 
+    def pack_plan(self):
+        """The model's packed-operand plan for the current compute mode and parameter placement (one
+        hpc_pack_multi launch per weight update instead of one pack launch per layer and use)."""
+        from ...hotpath import get_compute_mode
+        params = self._flat_params()
+        key = (get_compute_mode(), params[0].device)
+        plan = self._plans.get(key)
+        if plan is None or plan.owner_ids != tuple(id(p) for p in params):
+            plan = self._plans[key] = build_pack_plan(self._meta, params)
+            plan.owner_ids = tuple(id(p) for p in params)
+        return plan
+
     def _forward_fused(self, x, noise_z, noise_y):
         self._meta.lmbda = float(self.distortion_loss_weight)
+        _lib.require_cuda(x, self.analysis_transform.layers[0].weight)      # no CPU fallback: fail before any launch
+        self.pack_plan().ensure()
         x_tilde, out = Compressor2018Fn.apply(x, self._meta, (bool(self.training), torch.is_grad_enabled()), noise_z, noise_y,
                                               *self._flat_params())
         det = out.detach()

@@ -87,6 +87,10 @@ class FusedAdamW(torch.optim.Optimizer):
             seg.bc2_sqrt = math.sqrt(1.0 - beta2 ** t)
         check(lib().hpc_adamw_step(arr, len(live), beta1, beta2, eps, self.grad_clip, int(self.write_clipped_grad),
                                    stream()))
+        # the kernel wrote the parameters (and moments) through raw pointers: bump their version counters like an
+        # in-place torch op would, so autograd's saved-tensor checks and the packed-operand cache
+        # (hotpath.PackPlan / pack_weight, keyed on `_version`) see the update
+        torch._C._increment_version([p for _, p, _ in live])
         return loss
 
 

@@ -101,6 +101,16 @@ typedef struct {
   float* f[3]; /* (C,3) x3 */
 } hpc_cdf_params;
 
+/* CDFLayer.forward stand-alone (one layer of the MLP): x (N,C,din,1) -> out (N,C,dout,1),
+ *   pre = softplus(w[c]) x + b[c];  out = f ? pre + tanh(pre)*tanh(f[c]) : pre   (f == NULL: the last layer, act=False)
+ * w (C,dout,din), b (C,dout), f (C,dout) in the reference's layouts; din, dout <= 4.
+ * Replaces modelling/blocks/entropy_model.py:67-78 (module-surface parity; the hot path evaluates the whole MLP in
+ * hpc_factorized_fwd / hpc_cdf_logits_fwd).  bwd: gx may be NULL; gw, gb, gf are overwritten (fixed-order sums). */
+int hpc_cdf_layer_fwd(const float* x, const float* w, const float* b, const float* f, int64_t N, int C, int din,
+                      int dout, float* out, hpc_stream_t stream);
+int hpc_cdf_layer_bwd(const float* x, const float* w, const float* b, const float* f, int64_t N, int C, int din,
+                      int dout, const float* g, float* gx, float* gw, float* gb, float* gf, hpc_stream_t stream);
+
 /* EntropyModel.forward: quantise, pmf = s*(sigmoid(s*u)-sigmoid(s*l)), bits.
  * Replaces modelling/blocks/entropy_model.py:204-214 (_quantize :216-236, _prob_mass :259-269,
  * CDFLayer.forward :67-78, CDFEstimator.forward :101-114, _ce_loss :185).
@@ -347,6 +357,30 @@ int hpc_pack_weight(const float* src, void* dst, int dtype, int ntaps, int rows,
 /* inverse for gradients: dst(r,c,tap_src[t]) (+)= src[t][r][c]; float both sides. */
 int hpc_unpack_wgrad(const float* src, float* dst, int ntaps, int rows, int cols, int64_t stride_r,
                      int64_t stride_c, const int* tap_src_host, int accumulate, hpc_stream_t stream);
+
+/* All packed operand copies of a model in ONE launch (a training step changes every weight, so every copy is
+ * rebuilt once per step: 27 pack + 6 gdn_prepare launches otherwise).  Job kinds:
+ *   HPC_PACK_TAPS  dst[t][r][c] = src(r, c, tap_src[t]) as hpc_pack_weight (`dtype` of the call); the taps of one
+ *                  (r, c) pair must be contiguous in src (stride_r == ntaps or stride_c == ntaps)
+ *   HPC_PACK_C3_K  as hpc_pack_c3_weight's kmaj (rows = Cw; bf16)    HPC_PACK_C3_N  its nmaj (rows = Cw; bf16)
+ *   HPC_PACK_GDN   as hpc_gdn_prepare: src = gamma_param, src2 = beta_param, rows = C, f0 = gamma_bound,
+ *                  f1 = beta_bound, f2 = pedestal; dst = gamma_bf16, dst2 = gammaT_bf16, dst3 = beta_eff
+ * Replaces the same reference code as those three entries (weights are read by F.conv2d / conv_transpose2d in
+ * place: analysis.py:55, synthesis.py:55-57, prior_*.py:54-56; gdn.py:59-62). */
+#define HPC_PACK_TAPS 0
+#define HPC_PACK_C3_K 1
+#define HPC_PACK_C3_N 2
+#define HPC_PACK_GDN 3
+#define HPC_PACK_MAX_JOBS 48
+typedef struct {
+  int kind, ntaps, rows, cols;
+  int64_t stride_r, stride_c;
+  const float* src; const float* src2;
+  void* dst; void* dst2; float* dst3;
+  float f0, f1, f2;
+  unsigned char tap_src[28];
+} hpc_pack_job;
+int hpc_pack_multi(const hpc_pack_job* jobs_host, int njobs, int dtype, hpc_stream_t stream);
 
 /* out[c] = scale * sum_p x[p][c]  (bias gradients; GDN beta gradient).  x (P,C) lp. */
 int hpc_colsum(const void* x, int dtype, int64_t P, int C, float scale, float* out, void* scratch,

@@ -1,5 +1,7 @@
-"""BASELINE.json's full sizes (64 x 256x256 training crops; 768x512 Kodak-shaped evaluation images), where the CPU
-oracle would take minutes: checked through size-independent properties of the path instead --
+"""BASELINE.json's full sizes (64 x 256x256 training crops; 768x512 Kodak-shaped evaluation images).
+Second half of this file: the product path against the CPU oracle AT those sizes (a 64-crop oracle step is a few seconds
+of host time: run in chunks of 16 crops, whose loss / gradient mean is the batch's, bmshl2018.py:70,88).
+First half: size-independent properties of the path --
   * the returned losses are consistent with each other (bpp = y_entropy + z_entropy; total = lambda*D + bpp);
   * batch linearity: every replica normalises by its own pixel count (bmshl2018.py:70,88), so the gradient of a
     batch is the MEAN of the gradients of its halves (the data-parallel identity, at the benchmark size);
@@ -13,7 +15,8 @@ import torch
 
 import image_compression_b200 as pkg
 from image_compression_b200 import sharding, utils as U
-from util import make_pair, perturb, rel_l2
+from oracle import hyperprior_oracle as O
+from util import cosine, grad_margins, make_pair, perturb, record_parity, rel_l2
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
@@ -112,3 +115,96 @@ def test_smallest_and_non_square_shapes(N, hw):
     assert xt.shape == x.shape and math.isfinite(float(losses["total_loss"]))
     for k, p in model.named_parameters():
         assert p.grad is not None and bool(torch.isfinite(p.grad).all()), k
+
+
+# ------------------------------------------------------------------------------------------------------------
+# oracle parity at BASELINE's own sizes (configs[1], [3], [4]); tolerances: BASELINE.json north_star
+# ------------------------------------------------------------------------------------------------------------
+def _oracle_train_chunked(params, ocfg, x, nz, ny, chunk):
+    """Oracle loss dict and gradients of the whole batch = mean over equal chunks (every term of the loss is a mean
+    over the batch: lambda * MSE-mean (or the per-image-mean MS-SSIM loss) + bits / (N*H*W))."""
+    pl = O.leaf_params(params)
+    n = x.shape[0]
+    assert n % chunk == 0
+    k = n // chunk
+    acc, xts = {}, []
+    for i in range(0, n, chunk):
+        xt, lo = O.compressor2018_forward(pl, x[i:i + chunk], ocfg, True, nz[i:i + chunk], ny[i:i + chunk])
+        (lo["total_loss"] / k).backward()
+        for name, v in lo.items():
+            acc[name] = acc.get(name, 0.0) + float(v) / k
+        xts.append(xt.detach())
+    return pl, acc, torch.cat(xts)
+
+
+@pytest.mark.parametrize("recipe,N,chunk", [("psnr_256", 64, 16), ("ssim_64", 8, 8)])
+def test_train_step_full_size_against_oracle(recipe, N, chunk):
+    model, params, ocfg = make_pair(recipe, 192)
+    params = perturb(params)
+    model.load_state_dict(params)
+    model.train()
+    H = W = 256
+    g = torch.Generator().manual_seed(31)
+    x = torch.rand(N, 3, H, W, generator=g)
+    nz = torch.rand(N, 192, H // 64, W // 64, generator=g)
+    ny = torch.rand(N, 192, H // 16, W // 16, generator=g)
+    with pkg.compute_mode("bf16"):
+        xt, losses = model(x.to(DEV), nz.to(DEV), ny.to(DEV))
+        losses["total_loss"].backward()
+        torch.cuda.synchronize()
+    pl, lo, xto = _oracle_train_chunked(params, ocfg, x, nz, ny, chunk)
+    rep = {k: (float(losses[k]), lo[k]) for k in lo}
+    assert abs(rep["bpp"][0] - rep["bpp"][1]) <= 1e-3 * rep["bpp"][1], rep                       # bpp: 1e-3 relative
+    assert abs(rep["total_loss"][0] - rep["total_loss"][1]) <= 2e-3 * abs(rep["total_loss"][1]), rep
+    p1 = U.psnr(xt * 255, x.to(DEV) * 255).cpu()
+    p0 = O.psnr(xto * 255, x * 255)
+    assert float((p1 - p0).abs().max()) <= 0.01, float((p1 - p0).abs().max())                    # PSNR: 0.01 dB
+    marg = grad_margins(model, pl)
+    worst_c = min(marg.items(), key=lambda kv: kv[1][0])
+    worst_r = max(marg.items(), key=lambda kv: kv[1][1])
+    record_parity(f"fullsize_train_{recipe}_{N}x{H}x{W}_bf16_vs_oracle", {
+        "losses_product_vs_oracle": rep, "psnr_max_abs_diff_db": float((p1 - p0).abs().max()),
+        "worst_cosine": [worst_c[0], worst_c[1][0]], "worst_rel_l2": [worst_r[0], worst_r[1][1]],
+        "per_tensor_cos_relL2": {k: list(v) for k, v in marg.items()}})
+    for k, (c, r) in marg.items():
+        assert c >= GRAD_COS_MIN and r <= GRAD_REL_L2_MAX, (k, c, r)
+
+
+GRAD_COS_MIN, GRAD_REL_L2_MAX = 0.995, 0.10      # measured floor + margin: profiles/r02_parity.json
+
+
+def test_eval_full_size_against_oracle():
+    model, params, ocfg = make_pair("psnr_256", 192)
+    model.eval()
+    g = torch.Generator().manual_seed(32)
+    x = torch.rand(3, 3, 512, 768, generator=g)
+    with torch.no_grad(), pkg.compute_mode("bf16"):
+        xd = x.to(DEV)
+        xt, losses = model(xd)
+        ps, ms = U.image_metrics(xt, xd)
+        y = model.analysis_transform(xd)
+        singles = [float(model(xd[i:i + 1])[1]["bpp"]) for i in range(3)]
+    ps0, ms0, bpp0, mism_rates, ok_all = [], [], [], [], True
+    for i in range(3):       # the oracle image by image (0.7 s each); per-image bpp is what BASELINE's tolerance is on
+        with torch.no_grad():
+            xto, lo, inter = O.compressor2018_forward(params, x[i:i + 1], ocfg, False, return_intermediates=True)
+        ps0.append(float(O.psnr(xto * 255, x[i:i + 1] * 255)))
+        ms0.append(float(O.ms_ssim_metric(xto * 255, x[i:i + 1] * 255)))
+        bpp0.append(float(lo["bpp"]))
+        with torch.no_grad(), pkg.compute_mode("bf16"):
+            yt, _ = model.conditional_model(y[i:i + 1], inter["sigma"].to(DEV))
+        mism = yt.cpu() != inter["y_tilde"]
+        d = (y[i:i + 1].cpu() - inter["y"]).abs()
+        frac = (inter["y"] - inter["y"].floor() - 0.5).abs()
+        ok_all = ok_all and bool((frac[mism] <= d[mism] + 1e-6).all())      # mismatches only across a .5 boundary
+        mism_rates.append(float(mism.float().mean()))
+    rec = {"bpp_product_per_image": singles, "bpp_oracle_per_image": bpp0, "psnr_product": ps.cpu().tolist(), "psnr_oracle": ps0,
+           "msssim_db_product": ms.cpu().tolist(), "msssim_db_oracle": ms0, "symbol_mismatch_rate": mism_rates,
+           "batch_bpp_product": float(losses["bpp"]), "batch_bpp_oracle_mean": sum(bpp0) / 3}
+    record_parity("fullsize_eval_psnr_256_3x512x768_bf16_vs_oracle", rec)
+    for i in range(3):
+        assert abs(singles[i] - bpp0[i]) <= 1e-3 * bpp0[i], rec                       # per-image bpp: 1e-3 relative
+        assert abs(float(ps[i]) - ps0[i]) <= 0.01, rec                                # PSNR: 0.01 dB
+        assert abs(float(ms[i]) - ms0[i]) <= 0.02, rec                                # MS-SSIM: 0.02 dB
+    assert abs(float(losses["bpp"]) - sum(bpp0) / 3) <= 1e-3 * sum(bpp0) / 3
+    assert ok_all and max(mism_rates) < 0.02, rec

@@ -87,6 +87,97 @@ def test_state_dict_round_trip_and_clipped_grad_writeback():
         assert float((p - q).abs().max()) <= 2e-6 * float(q.abs().max())
 
 
+def _train(model, opt, xs, noises, clip=None):
+    losses = []
+    for x, (nz, ny) in zip(xs, noises):
+        opt.zero_grad(set_to_none=True)
+        _, out = model(x, nz, ny)
+        out["total_loss"].backward()
+        if clip is not None:
+            clip_grad_value_(model.parameters(), clip)       # engine/trainer.py:189-190
+        opt.step()
+        losses.append(float(out["total_loss"]))
+    return losses
+
+
+def test_fused_adamw_updates_reach_the_forward_and_match_torch_adamw():
+    """Round-1 bug: FusedAdamW wrote the weights through raw pointers without bumping `_version`, so the cached bf16
+    operand packs of every conv stayed at step 0.  Now: (a) after N fused steps the next forward is bit-equal to a
+    FRESH model built from state_dict() (nothing stale anywhere); (b) the parameter and loss trajectories equal
+    clip_grad_value_ + torch.optim.AdamW (engine/trainer.py:188-194, solver/optim.py:27-39) driving an identical model."""
+    cfg = pkg.get_recipe_cfg("psnr_256")
+    torch.manual_seed(0)
+    ours = pkg.build_model(cfg).to(DEV).train()
+    ref = copy.deepcopy(ours)
+    w0 = ours.analysis_transform.layers[2].weight.detach().clone()
+    opt = make_optimizer(cfg, ours)
+    ropt = torch.optim.AdamW(_ref_groups(ref, cfg), cfg.SOLVER.BASE_LR, eps=cfg.SOLVER.EPS)
+    g = torch.Generator(device=DEV).manual_seed(11)
+    steps = 6
+    xs = [torch.rand(4, 3, 128, 128, device=DEV, generator=g) for _ in range(steps)]
+    noises = [(torch.rand(4, 192, 2, 2, device=DEV, generator=g), torch.rand(4, 192, 8, 8, device=DEV, generator=g))
+              for _ in range(steps)]
+    with pkg.compute_mode("bf16"):
+        lo = _train(ours, opt, xs, noises)
+        lr = _train(ref, ropt, xs, noises, clip=cfg.SOLVER.GRAD_CLIP)
+        # the conv weights really moved (lr 1e-4, 6 steps of Adam: ~6e-4 per element)
+        moved = float((ours.analysis_transform.layers[2].weight - w0).abs().max())
+        assert moved > 1e-4, moved
+        worst = 0.0
+        for (n, p), q in zip(ours.named_parameters(), ref.parameters()):
+            err = float((p - q).abs().max() / q.abs().max().clamp_min(1e-12))
+            worst = max(worst, err)
+            assert err <= 5e-6, (n, err)
+        for a, b in zip(lo, lr):
+            assert abs(a - b) <= 2e-5 * abs(b), (lo, lr)
+        # (a) a fresh model from the state_dict computes the very same forward, bit for bit
+        fresh = pkg.build_model(cfg).to(DEV).train()
+        fresh.load_state_dict(ours.state_dict(), strict=True)
+        xt_a, la = ours(xs[0], *noises[0])
+        xt_b, lb = fresh(xs[0], *noises[0])
+        assert torch.equal(xt_a, xt_b)
+        for k in la:
+            assert float(la[k]) == float(lb[k]), (k, float(la[k]), float(lb[k]))
+        # and the loss after training differs from the step-0 loss by more than the biases alone explain:
+        # the same input through the ORIGINAL weights
+        torch.manual_seed(0)
+        init = pkg.build_model(cfg).to(DEV).train()
+        _, l0 = init(xs[0], *noises[0])
+        assert float(la["total_loss"]) < float(l0["total_loss"])
+    print("worst relative parameter deviation FusedAdamW vs clip+torch.AdamW through the model after", steps, "steps:", worst)
+
+
+def test_pack_plan_tracks_every_kind_of_weight_update():
+    """The packed-operand cache follows torch in-place updates, load_state_dict, raw-pointer writes announced through
+    bump_versions, and hp.invalidate_packs(); one hpc_pack_multi launch per update."""
+    from image_compression_b200 import _lib, hotpath as hp
+    cfg = pkg.get_recipe_cfg("psnr_256")
+    torch.manual_seed(0)
+    model = pkg.build_model(cfg).to(DEV).eval()
+    x = torch.rand(1, 3, 128, 128, device=DEV)
+    with pkg.compute_mode("bf16"), torch.no_grad():
+        base = float(model(x)[1]["bpp"])
+        n0 = _lib.lib().hpc_launch_count()
+        assert float(model(x)[1]["bpp"]) == base
+        per_fwd = _lib.lib().hpc_launch_count() - n0            # no repack: weights unchanged
+        w = model.analysis_transform.layers[2].weight
+        w.mul_(1.5)                                             # torch in-place op: version bump
+        n0 = _lib.lib().hpc_launch_count()
+        b1 = float(model(x)[1]["bpp"])
+        assert _lib.lib().hpc_launch_count() - n0 == per_fwd + 1            # exactly one pack launch
+        assert b1 != base
+        w.data.mul_(1.0 / 1.5)                                  # .data write: no version bump (torch semantics) ...
+        hp.bump_versions([w])                                   # ... so the writer announces it
+        w.copy_(torch.nn.Parameter(w.detach().clone()))         # and an ordinary copy_ on top
+        b2 = float(model(x)[1]["bpp"])
+        sd = {k: v.clone() for k, v in model.state_dict().items()}
+        fresh = pkg.build_model(cfg).to(DEV).eval()
+        fresh.load_state_dict(sd)
+        assert float(fresh(x)[1]["bpp"]) == b2
+        hp.invalidate_packs()
+        assert float(model(x)[1]["bpp"]) == b2
+
+
 def test_train_steps_reduce_the_loss():
     cfg = pkg.get_recipe_cfg("psnr_256")
     torch.manual_seed(0)

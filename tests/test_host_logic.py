@@ -113,13 +113,15 @@ def test_fused_adamw_host_logic():
 
 
 def test_early_all_reduce_slot_range(monkeypatch):
-    """FlatGradients._reduce_early (the hook the fused backward calls when the g_s gradients are final) reduces exactly
-    the contiguous slot range of the tensors it is given, and declines when a gradient is not a view of the flat buffer
-    or when the range would swallow another group's slot."""
+    """FlatGradients._reduce_early (the hook the backward schedules call after every layer): slots become reducible in
+    buffer order -- the range between the frontier and the first slot not yet reported is all-reduced once it holds
+    >= min_bucket elements or at a flush; a gradient that is not a slot view is left to the final all-reduce, which
+    covers everything beyond the frontier."""
     import torch.distributed as dist
     from image_compression_b200 import sharding
     params = [torch.nn.Parameter(torch.zeros(n)) for n in (5, 16, 7, 9, 3)]
     fg = sharding.FlatGradients(params, torch.device("cpu"), overlap=False)
+    fg.min_bucket = 20
     calls = []
 
     class _Work:
@@ -127,15 +129,25 @@ def test_early_all_reduce_slot_range(monkeypatch):
             return True
 
     def fake_all_reduce(t, op=None, group=None, async_op=False):
-        calls.append((t.data_ptr() - fg.flat.data_ptr()) // 4)
-        calls.append(t.numel())
+        calls.append(((t.data_ptr() - fg.flat.data_ptr()) // 4, t.numel()))
         return _Work()
     monkeypatch.setattr(dist, "all_reduce", fake_all_reduce)
+    monkeypatch.setattr(dist, "is_initialized", lambda: True)
+    monkeypatch.setattr(dist, "get_world_size", lambda group=None: 2)
+    monkeypatch.setattr(dist, "get_backend", lambda group=None: "nccl")
     views = [fg._view(p) for p in params]
-    fg._reduce_early([views[2], views[3]])                     # slots 2 and 3 are neighbours
-    assert calls == [fg.offsets[2], fg.offsets[4] - fg.offsets[2]] and fg._early[:2] == (fg.offsets[2], fg.offsets[4])
-    calls.clear(); fg._early = None
-    fg._reduce_early([views[1], views[3]])                     # slot 2 lies between them: not this group's to reduce
-    assert calls == [] and fg._early is None
-    fg._reduce_early([views[1], torch.zeros(7)])               # a stray gradient (not a view of the flat buffer)
-    assert calls == [] and fg._early is None
+    fg._reduce_early([views[2], views[3]])                     # slots 2, 3 ready, but slot 0 is the frontier: nothing yet
+    assert calls == [] and fg._frontier == 0
+    fg._reduce_early([views[0]])                               # slot 0 alone: 8 padded elements < min_bucket
+    assert calls == [] and fg._frontier == 0
+    fg._reduce_early([views[1]])                               # 0..3 contiguous now: one all-reduce up to slot 4's offset
+    assert calls == [(0, fg.offsets[4])] and fg._frontier == 4
+    fg._reduce_early([torch.zeros(3)])                         # a stray gradient (not a view of the flat buffer): ignored
+    assert len(calls) == 1 and fg._frontier == 4
+    for p, v in zip(params, views):
+        p.grad = v
+    fg.all_reduce_mean()                                       # the rest: slot 4 to the end of the buffer; state reset
+    assert calls[1] == (fg.offsets[4], fg.flat.numel() - fg.offsets[4]) and fg._frontier == 0 and not fg._early
+    calls.clear()
+    fg._reduce_early([views[0]], flush=True)                   # a flush starts the reduce of whatever is contiguous
+    assert calls == [(0, fg.offsets[1])] and fg._frontier == 1

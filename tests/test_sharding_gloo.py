@@ -61,6 +61,51 @@ def test_flat_gradients_and_eval_sharding_world2():
         assert numel == 5 * 7 + 7 + 7 * 3 + 3 and flat >= numel and flat % 4 == 0
 
 
+def _reducer_worker(rank, world, port, results):
+    """The trainer-transparent path: the model arms the reducer in forward, a hook on the loss queues the all-reduce at
+    the end of backward; the caller only runs the reference's sequence (engine/trainer.py:179-194)."""
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.manual_seed(rank)                  # different initial weights per rank: the reducer broadcasts rank 0's
+        net = torch.nn.Sequential(torch.nn.Linear(5, 7), torch.nn.Tanh(), torch.nn.Linear(7, 3))
+        red = sharding.GradientReducer(list(net.parameters())[::-1], module=net)
+        opt = torch.optim.SGD(net.parameters(), lr=0.1)
+        torch.manual_seed(0)
+        ref = torch.nn.Sequential(torch.nn.Linear(5, 7), torch.nn.Tanh(), torch.nn.Linear(7, 3))
+        ropt = torch.optim.SGD(ref.parameters(), lr=0.1)
+        w0 = max(float((p - q).abs().max()) for p, q in zip(net.parameters(), ref.parameters()))
+        x = torch.randn(4 * world, 5, generator=torch.Generator().manual_seed(1))
+        err = 0.0
+        for it in range(1, 5):                   # GD_STEPS = 2: backward, backward, step, zero_grad
+            xs = x[rank * 4:(rank + 1) * 4] * it
+            assert red.before_forward()
+            loss = net(xs).pow(2).mean() / 2
+            red.watch(loss)
+            loss.backward()
+            sum(ref(x[r * 4:(r + 1) * 4] * it).pow(2).mean() / 2 for r in range(world)).div(world).backward()
+            err = max(err, max(float((p.grad - q.grad).abs().max()) for p, q in zip(net.parameters(), ref.parameters())))
+            if it % 2 == 0:
+                opt.step(); ropt.step()
+                opt.zero_grad(); ropt.zero_grad()
+        werr = max(float((p - q).abs().max()) for p, q in zip(net.parameters(), ref.parameters()))
+        results[rank] = (w0, err, werr)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gradient_reducer_transparent_world2():
+    world = 2
+    mgr = mp.Manager()
+    results = mgr.dict()
+    mp.spawn(_reducer_worker, args=(world, _free_port(), results), nprocs=world, join=True)
+    assert len(results) == world
+    for rank in range(world):
+        w0, err, werr = results[rank]
+        assert w0 == 0.0            # broadcast from rank 0 at attach
+        assert err < 1e-6 and werr < 1e-6, (err, werr)
+
+
 def test_shard_indices_cover_everything_once():
     for n, w in ((24, 8), (7, 2), (3, 4), (1, 1)):
         seen = sorted(i for r in range(w) for i in sharding.shard_indices(n, r, w))

@@ -41,3 +41,31 @@ def perturb(params, seed=1, scale=0.05):
         else:
             out[k] = v.clone()
     return out
+
+
+def record_parity(tag, data):
+    """Append measured parity margins (worst cosine / rel-L2 per tensor, loss errors ...) to the round's parity
+    record: gpurun_out/r02_parity.json on the GPU box (merged back by gpurun; the committed copy is
+    profiles/r02_parity.json)."""
+    import json
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    d = os.path.join(root, "gpurun_out")
+    try:
+        os.makedirs(d, exist_ok=True)
+        path = os.path.join(d, "r02_parity.json")
+        rec = {}
+        if os.path.exists(path):
+            with open(path) as f:
+                rec = json.load(f)
+        rec[tag] = data
+        with open(path, "w") as f:
+            json.dump(rec, f, indent=1, sort_keys=True)
+    except OSError:
+        pass
+
+
+def grad_margins(model, oracle_leaf_params):
+    """{name: (cosine, rel_l2)} of every parameter gradient against the oracle's."""
+    return {k: (cosine(p.grad, oracle_leaf_params[k].grad), rel_l2(p.grad, oracle_leaf_params[k].grad))
+            for k, p in model.named_parameters()}
