@@ -552,11 +552,13 @@ class Compressor2018Fn(torch.autograd.Function):
                                                       fuse_exp_clamp=True, want_gs_f32=False, want_gs_lp=True,
                                                       bin_=m.bin, mean=0.0)
         # --- h_s -> z~ -> factorised prior -> z ---------------------------------------------
-        g_zt, hs_cg = B.hs_backward(Shs, gpre, need_input_grad=True, want_f32=True)
+        # (the small-K weight gradients of h_s and h_a run on a side stream beside the dgrad chain; joined at the end
+        #  of h_a's backward, where their gradients are reported ready)
+        g_zt, hs_cg = B.hs_backward(Shs, gpre, need_input_grad=True, want_f32=True, join=False)
         gz, cdf_grads = hp.factorized_backward(zt, cdf, training, g, inv_np, None, g_zt, m.bin)
-        hp.grads_ready(list(cdf_grads.values()))
         # --- h_a, with d|y|/dy and the three-way sum fused into its last dgrad ---------------
-        gy, ha_cg = B.ha_backward(Sha, hp.cast(gz, hp.lp_dtype()), sign_add=(y, gy_partial))
+        gy, ha_cg = B.ha_backward(Sha, hp.cast(gz, hp.lp_dtype()), sign_add=(y, gy_partial), also_ready=hs_cg[::-1])
+        hp.grads_ready(list(cdf_grads.values()), flush=True)
         # --- g_a ---------------------------------------------------------------------------
         ga_cg, ga_gg = B.ga_backward(Sga, gy)
         grads = (_join_ga(ga_cg, ga_gg) + _join_h(ha_cg, m.ha_bias) + _join_h(hs_cg, [True] * len(hs_cg)) +

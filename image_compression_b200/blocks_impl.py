@@ -209,7 +209,7 @@ def ha_forward(yabs_lp, convs, kernels=(3, 5, 5), strides=(1, 2, 2), save=True):
     return z, (S if save else None)
 
 
-def ha_backward(S, gz_lp, sign_add=None, need_input_grad=True):
+def ha_backward(S, gz_lp, sign_add=None, need_input_grad=True, also_ready=()):
     """gz_lp: NHWC lp gradient wrt z.  sign_add=(y_f32, gy_partial_f32): fuse d|y|/dy and the sum with
     the other two gradient streams of y (bmshl2018.py:72) into the last dgrad epilogue.
     Returns (g wrt input (lp), conv grads)."""
@@ -218,10 +218,12 @@ def ha_backward(S, gz_lp, sign_add=None, need_input_grad=True):
     for i in range(len(S.convs) - 1, -1, -1):
         spec, inp = S.layers[i]
         w, b = S.convs[i]
-        gb = hp.colsum(g, out=hp.grad_buffer(b)) if b is not None else None
-        gw = spec.wgrad(inp, g, w)
+        with hp.side_stream(g.device) as on_side:       # small-K weight gradient: off the critical path, beside the dgrad chain
+            gb = hp.colsum(g, out=hp.grad_buffer(b)) if b is not None else None
+            gw = spec.wgrad(inp, g, w)
+        if on_side:
+            hp.hold_until_join(g.device, g, inp)
         conv_grads[i] = (gw, gb)
-        hp.grads_ready((gw, gb), flush=(i == 0))
         if i > 0:
             # inp is the ReLU output of layer i-1: mask the gradient in the dgrad epilogue
             g = spec.dgrad(g, w, inp.shape[1:3], EPI_RELU_MASK, aux0=inp)["lp"]
@@ -233,6 +235,10 @@ def ha_backward(S, gz_lp, sign_add=None, need_input_grad=True):
                 g = spec.dgrad(g, w, inp.shape[1:3])["lp"]
         else:
             g = None
+    hp.join_side_stream(gz_lp.device)
+    for gw, gb in list(also_ready) + conv_grads[::-1]:
+        hp.grads_ready((gw, gb))
+    hp.grads_ready((), flush=True)
     return g, conv_grads
 
 
@@ -260,7 +266,7 @@ def hs_forward(zt_lp, convs, kernels=(5, 5, 3), strides=(2, 2, 1), save=True):
     return sigma, (S if save else None)
 
 
-def hs_backward(S, gpre_lp, need_input_grad=True, want_f32=False):
+def hs_backward(S, gpre_lp, need_input_grad=True, want_f32=False, join=True):
     """gpre_lp: NHWC lp gradient wrt the pre-exp activation (the exp/clamp chain rule is applied by the
     caller: hpc_conditional_bwd(fuse_exp_clamp) or hpc_exp_clamp_bwd).
     Returns (g wrt z~ (lp or fp32), conv grads)."""
@@ -269,10 +275,12 @@ def hs_backward(S, gpre_lp, need_input_grad=True, want_f32=False):
     for i in range(len(S.convs) - 1, -1, -1):
         spec, inp = S.layers[i]
         w, b = S.convs[i]
-        gb = hp.colsum(g, out=hp.grad_buffer(b)) if b is not None else None
-        gw = spec.wgrad(inp, g, w)
+        with hp.side_stream(g.device) as on_side:       # small-K weight gradient: off the critical path, beside the dgrad chain
+            gb = hp.colsum(g, out=hp.grad_buffer(b)) if b is not None else None
+            gw = spec.wgrad(inp, g, w)
+        if on_side:
+            hp.hold_until_join(g.device, g, inp)
         conv_grads[i] = (gw, gb)
-        hp.grads_ready((gw, gb))
         if i > 0:
             g = spec.dgrad(g, w, inp.shape[1:3], EPI_RELU_MASK, aux0=inp)["lp"]
         elif need_input_grad:
@@ -280,4 +288,8 @@ def hs_backward(S, gpre_lp, need_input_grad=True, want_f32=False):
             g = o["f32"] if want_f32 else o["lp"]
         else:
             g = None
+    if join:
+        hp.join_side_stream(gpre_lp.device)
+        for gw, gb in conv_grads[::-1]:
+            hp.grads_ready((gw, gb))
     return g, conv_grads

@@ -494,6 +494,7 @@ struct GdnFusedParams {
   int64_t P;
   int tiles;
   int inverse;
+  int prefetch;            // dual kernel: L2 prefetch of the next half-tile of each set
 };
 
 template <int C>
@@ -837,8 +838,12 @@ gdn_bwd_dual_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
       const int s = lane / (3 * KC), rem = lane % (3 * KC), which = rem / KC, c = rem % KC;
       uint8_t* dst = (which == 0 ? bg : (which == 1 ? bx : bn)) + c * G_CHUNK + s * HBYTES;
       const CUtensorMap* tm = which == 0 ? &tmGr : (which == 1 ? &tmX : &tmR);
+      // L2 prefetch one half-tile of this set ahead: the load that follows the buffer release then pays L2 latency
+      // instead of HBM latency (the buffers, not the bandwidth, bound the bytes in flight: HPC_GDN_PREFETCH=0 disables)
+      if (p.prefetch && s < mine) tma_prefetch_2d(tm, c * 64, (blockIdx.x + s * gridDim.x) * HROWS);
       for (int k = s, j = 0; k < mine; k += 2, ++j) {
         const int h = blockIdx.x + k * gridDim.x;
+        if (p.prefetch && k + 2 < mine) tma_prefetch_2d(tm, c * 64, (h + 2 * (int)gridDim.x) * HROWS);
         mbar_wait(&in_empty[s], (j & 1) ^ 1);
         if (rem == 0) mbar_arrive_expect_tx(&in_full[s], 3 * Cfg::TILE / 2);
         tma_load_2d(dst, tm, &in_full[s], c * 64, h * HROWS);
@@ -1244,6 +1249,9 @@ int hpc_gdn_bwd_fused_umma(const void* g_bf16, const void* x_bf16, const void* r
   kp.colsum_part = kp.dgamma_part + (size_t)grid * C * C;
   kp.dxsum_part = kp.colsum_part + (size_t)grid * C;
   kp.tiles = (int)((P + 127) / 128); kp.inverse = inverse; kp.P = P;
+  static int prefetch = -1;
+  if (prefetch < 0) { const char* e = getenv("HPC_GDN_PREFETCH"); prefetch = e ? (atoi(e) ? 1 : 0) : 1; }
+  kp.prefetch = prefetch;
   const int box_rows = dual ? 64 : 128;
   CUtensorMap tmGr, tmX, tmR, tmDx, tmG;
   if ((rc = make_rows_tmap(&tmGr, g_bf16, P, C, box_rows))) return rc;

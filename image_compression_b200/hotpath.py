@@ -235,6 +235,68 @@ def grad_buffer(param, zero=False):
 _captured_keys = set()
 
 
+# ----------------------------------------------------------------------------------------
+# side stream for work off the backward's critical path (the small-K weight gradients of h_a / h_s / the 16x16
+# layers: each uses a fraction of the SMs, and so do the dgrads they would otherwise serialise with)
+# ----------------------------------------------------------------------------------------
+import os as _os
+
+_side_enabled = _os.environ.get("HPC_SIDE_WGRAD", "0") != "0"      # measured r02b: 6.68 ms with, 6.60 ms without -> off
+_side_state = {}
+
+
+def set_side_wgrad(flag):
+    global _side_enabled
+    _side_enabled = bool(flag)
+
+
+class side_stream:
+    """`with side_stream(dev) as on: ...` runs the body on the device's side stream, ordered after everything enqueued
+    on the current stream so far (fork).  `join_side_stream(dev)` makes the current stream wait for it.  Inactive (body
+    runs on the current stream) when disabled or while a CUDA graph is being captured."""
+
+    def __init__(self, device):
+        self.active = _side_enabled and not _capturing
+        if not self.active:
+            return
+        st = _side_state.get(device)
+        if st is None:
+            st = _side_state[device] = {"stream": torch.cuda.Stream(device=device), "fork": torch.cuda.Event(),
+                                        "join": torch.cuda.Event(), "dirty": False, "held": []}
+        self.st = st
+
+    def __enter__(self):
+        if self.active:
+            st = self.st
+            st["fork"].record()
+            st["stream"].wait_event(st["fork"])
+            st["dirty"] = True
+            self.ctx = torch.cuda.stream(st["stream"])
+            self.ctx.__enter__()
+        return self.active
+
+    def __exit__(self, *a):
+        if self.active:
+            self.ctx.__exit__(*a)
+
+
+def hold_until_join(device, *tensors):
+    """Tensors allocated on the main stream that side-stream work reads: keep them alive until the join, or the caching
+    allocator may hand their storage to a later main-stream kernel while the side stream still reads it."""
+    st = _side_state.get(device)
+    if st is not None:
+        st["held"].extend(tensors)
+
+
+def join_side_stream(device):
+    st = _side_state.get(device)
+    if st is not None and st["dirty"]:
+        st["join"].record(st["stream"])
+        torch.cuda.current_stream(device).wait_event(st["join"])
+        st["dirty"] = False
+        st["held"].clear()
+
+
 def set_capturing(flag):
     """While a CUDA graph is being captured the packed-weight cache is bypassed, so that the pack kernels are
     nodes of the graph and replays always see the current weights (operands a PackPlan re-packed INSIDE this

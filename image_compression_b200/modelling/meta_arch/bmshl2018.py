@@ -13,6 +13,7 @@ import torch
 import torch.nn as nn
 
 from ... import _lib
+from ...utils import lazy
 
 from ...autograd_ops import Compressor2018Fn, ModelMeta, build_pack_plan
 from ..blocks import (ENTROPY_MODEL_REGISTRY, AnalysisTransform, HyperpriorAnalysisTransform,
@@ -50,6 +51,10 @@ class Compressor2018(nn.Module):
         # from inside the backward, so engine/trainer.py:176-194 runs unchanged.  False: plain autograd gradients.
         self.flat_gradients = True
         self._reducer = None
+        # lazily synchronised outputs for the unchanged trainer / monitor (utils/lazy.py); defer_nan_check: answer the
+        # trainer's `torch.isnan(loss).any()` at once and run the check at the step's first host read instead
+        self.lazy_sync = True
+        self.defer_nan_check = True
 
     def __getstate__(self):
         # copy.deepcopy / pickling: per-process device state (flat gradient buffer, packed operands, CUDA graphs) stays behind
@@ -113,8 +118,8 @@ class Compressor2018(nn.Module):
         if g is None:
             if len(self._graphs) >= 8:
                 self._graphs.clear()
-            g = self._graphs[key] = GraphedCallable(lambda t: self._forward_fused(t, None, None), x.contiguous())
-        return g(x.contiguous())
+            g = self._graphs[key] = GraphedCallable(lambda t: self._forward_fused_raw(t, None, None), x.contiguous())
+        return self._wrap_outputs(*g(x.contiguous()))
 
     def pack_plan(self):
         """The model's packed-operand plan for the current compute mode and parameter placement (one
@@ -129,16 +134,34 @@ class Compressor2018(nn.Module):
         return plan
 
     def _forward_fused(self, x, noise_z, noise_y):
+        return self._wrap_outputs(*self._forward_fused_raw(x, noise_z, noise_y))
+
+    def _forward_fused_raw(self, x, noise_z, noise_y):
         self._meta.lmbda = float(self.distortion_loss_weight)
         _lib.require_cuda(x, self.analysis_transform.layers[0].weight)      # no CPU fallback: fail before any launch
         self.pack_plan().ensure()
-        x_tilde, out = Compressor2018Fn.apply(x, self._meta, (bool(self.training), torch.is_grad_enabled()), noise_z, noise_y,
-                                              *self._flat_params())
+        return Compressor2018Fn.apply(x, self._meta, (bool(self.training), torch.is_grad_enabled()), noise_z, noise_y,
+                                      *self._flat_params())
+
+    def _wrap_outputs(self, x_tilde, out):
+        """(x_tilde, (8,) loss vector of hpc_rd_combine) -> the reference's return value (bmshl2018.py:91-98)."""
         det = out.detach()
         losses = {"z_entropy": det[0], "y_entropy": det[1], "bpp": det[2], "total_loss": out[3]}
         for i, name in enumerate(self.distortion_loss_fns.keys()):
             losses[name] = det[4 + i]
-        return x_tilde.detach(), losses
+        x_tilde = x_tilde.detach()
+        if self.lazy_sync and lazy.enabled and not torch.cuda.is_current_stream_capturing():
+            # SURVEY 8f rank 2: one asynchronous device-to-host copy of the 8 loss values right behind the forward; the
+            # reference's float(value) / isnan / preds.max() reads are then served without further stream stalls
+            mirror = lazy.HostMirror(det)
+            for i, k in enumerate(("z_entropy", "y_entropy", "bpp")):
+                losses[k] = lazy.LazyScalar.wrap(losses[k], mirror, i)
+            for i, name in enumerate(self.distortion_loss_fns.keys()):
+                losses[name] = lazy.LazyScalar.wrap(losses[name], mirror, 4 + i)
+            lazy.LossTensor.defer_nan_check = bool(self.defer_nan_check)
+            losses["total_loss"] = lazy.LossTensor.wrap(losses["total_loss"], mirror, 3)
+            x_tilde = lazy.ReconImage.wrap(x_tilde)
+        return x_tilde, losses
 
     def _forward_composed(self, x, noise_z=None, noise_y=None):
         N, C, H, W = x.size()

@@ -193,12 +193,21 @@ class GradientReducer:
         else:
             # gradients are being accumulated (SOLVER.GD_STEPS > 1) or the caller keeps zero-filled .grad tensors: this
             # backward adds into `.grad` the ordinary way; the reduce at its end covers the whole buffer
+            if not self._multi_rank():
+                if owner is fg:
+                    hp.set_grad_sink(None)
+                    hp.set_grad_ready_hook(None)
+                self.active = self.armed = False     # one process: nothing to reduce, the gradients stay where they are
+                return False
             if owner is fg:
                 hp.set_grad_sink(None)
                 hp.set_grad_ready_hook(None)
             fg._early, fg._ready, fg._frontier = [], set(), 0
             self.armed = False
         return True
+
+    def _multi_rank(self):
+        return dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1
 
     def watch(self, loss):
         """Hook the (scalar) loss the caller will call backward() on."""

@@ -170,7 +170,7 @@ def test_train_step_full_size_against_oracle(recipe, N, chunk):
         assert c >= GRAD_COS_MIN and r <= GRAD_REL_L2_MAX, (k, c, r)
 
 
-GRAD_COS_MIN, GRAD_REL_L2_MAX = 0.995, 0.10      # measured floor + margin: profiles/r02_parity.json
+GRAD_COS_MIN, GRAD_REL_L2_MAX = 0.999, 0.03      # SURVEY 8c's proposal; measured floor 0.99977 / 0.0213 (profiles/r02_parity.json)
 
 
 def test_eval_full_size_against_oracle():

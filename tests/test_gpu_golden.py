@@ -154,13 +154,19 @@ def test_whole_model_against_reference_outputs(name, mode):
     p0 = O.psnr(g["x_tilde"].float() * 255, x * 255)
     assert float((p1 - p0).abs().max()) <= (1e-3 if tight else 0.01), (p1, p0)           # PSNR: 0.01 dB
     if training:
+        worst = ("", 0.0)
         for k, p in model.named_parameters():
             ref = g["grad." + k]
             d = digest(p.grad.float().cpu())
             nrm, nrm0 = float(d[0]), float(ref[0])
-            assert abs(nrm - nrm0) <= (2e-3 if tight else 0.15) * max(nrm0, 1e-12), (k, nrm, nrm0)
+            dev_ = abs(nrm - nrm0) / max(nrm0, 1e-12)
+            worst = max(worst, (k, dev_), key=lambda t: t[1])
+            # bf16: golden shapes hold 4-16 z positions, see tests/test_gpu_model_bf16.py::grad_tolerance
+            assert dev_ <= (2e-3 if tight else 0.15), (k, nrm, nrm0)
             if tight:
                 close(d[2:], ref[2:], 5e-3, k)
+        from util import record_parity
+        record_parity(f"golden_{name}_{mode}_grad_norm_rel_dev", {"worst": list(worst), "shape": [N, C, H, W]})
     else:
         close(ps.cpu(), g["psnr"], 1e-5 if tight else 3e-4)
         assert float((ms.cpu() - g["msssim_db"]).abs().max()) <= (1e-3 if tight else 0.02)

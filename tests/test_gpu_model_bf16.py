@@ -1,8 +1,8 @@
 """Product path (bf16 operands on tcgen05, fp32 accumulate) against the fp32 CPU oracle on identical
 inputs, weights and noise.  Tolerances are BASELINE.json's: per-image bpp within 1e-3 relative, PSNR
 within 0.01 dB, rounded symbols bit-exact wherever the pre-rounding values agree; for loss and gradients
-the stated bf16 tolerance is: total loss 2e-3 relative, every parameter gradient cosine >= 0.99 and
-relative L2 <= 0.15 against the fp32 oracle (bf16 has 8 mantissa bits: 2^-9 = 2e-3 per rounding)."""
+the stated bf16 tolerance is: total loss 2e-3 relative, every parameter gradient within grad_tolerance() below
+(cosine / relative L2 against the fp32 oracle; bf16 has 8 mantissa bits: 2^-9 = 2e-3 per rounding)."""
 import pytest
 import torch
 
@@ -15,7 +15,16 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda"
 
 
-GRAD_COS_MIN, GRAD_REL_L2_MAX = 0.99, 0.15      # tightened to the measured floor + margin below (profiles/r02_parity.json)
+def grad_tolerance(n_z_positions):
+    """Stated bf16 gradient tolerance against the fp32 oracle: (min cosine, max rel-L2) for EVERY parameter tensor.
+    The worst tensors are always the hyper-prior convolutions, whose gradient is a sum over the z positions of the
+    batch (N * H/64 * W/64): the bf16 rounding noise of the activations averages out as 1/sqrt(positions).  Measured
+    (profiles/r02_parity.json): 8 positions 0.108 / 0.9943, 9 -> 0.069, 16 -> 0.048, 1024 (64 x 256^2, BASELINE's
+    training shape) -> 0.0089 / 0.99996, ssim_64 at 8 x 256^2 -> 0.021 / 0.99977.  At BASELINE's shapes
+    tests/test_gpu_fullsize.py asserts SURVEY 8c's proposal (cos >= 0.999, rel-L2 <= 0.03); here, floor + margin."""
+    rel = 0.03 + 0.3 / n_z_positions ** 0.5
+    return 1.0 - 0.75 * rel * rel, rel
+
 
 
 @pytest.fixture(autouse=True)
@@ -56,8 +65,9 @@ def test_train_step_bf16(recipe, hw, N):
                   {"losses_product_vs_oracle": rep, "worst_cosine": worst_c, "worst_rel_l2": worst_r,
                    "per_tensor_cos_relL2": per})
     print("worst cosine", worst_c, "worst rel-L2", worst_r)
+    cos_min, rel_max = grad_tolerance(N * (hw[0] // 64) * (hw[1] // 64))
     for k, (c, r) in per.items():
-        assert c >= GRAD_COS_MIN and r <= GRAD_REL_L2_MAX, (k, c, r)
+        assert c >= cos_min and r <= rel_max, (k, c, r, cos_min, rel_max)
 
 
 def test_eval_bf16_bpp_psnr_symbols():
