@@ -577,8 +577,8 @@ def measure(args, c, wl, steps, warmup, with_clocks=False, with_optimizer=False,
 
         def seq_step(i):
             torch.cuda.current_stream().wait_event(copied[i % 3])
+            h2d_async(i + 1)            # the loader's prefetch of the next batch overlaps this step (as in the e2e leg)
             train_step(dp, opt, stages[i % 3], mon, grad_clip=cfg.SOLVER.GRAD_CLIP, it=1)
-            h2d_async(i + 1)
         h2d_async(0)
         for i in range(3):
             seq_step(i)

@@ -190,6 +190,9 @@ class LossTensor(torch.Tensor):
     def __float__(self):
         return float(self.item())
 
+    def __format__(self, spec):
+        return format(self.item(), spec)
+
 
 class _KnownUpperBound:
     """`recon.max()` of a reconstruction the clamp kernel produced: comparisons against anything >= the bound are
