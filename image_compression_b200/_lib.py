@@ -15,7 +15,7 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(_HERE, "libhpcodec_sm100a.so")
-SOURCES = ["hpc_api.cu", "entropy_kernels.cu", "loss_kernels.cu", "igemm_simt.cu", "thin_kernels.cu",
+SOURCES = ["hpc_api.cu", "rans_kernels.cu", "entropy_kernels.cu", "loss_kernels.cu", "igemm_simt.cu", "thin_kernels.cu",
            "igemm_umma.cu", "thin_umma.cu", "gdn_umma.cu", "misc_kernels.cu", "optim_kernels.cu"]
 # no --use_fast_math: IEEE division / sqrt / expf are part of the parity contract
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -227,6 +227,14 @@ _SIGNATURES = {
                                   c_size_t, c_void_p]),
     "hpc_wgrad_c3_umma_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "hpc_nchw_channel_sum": (c_int, [c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p, c_void_p]),
+    "hpc_rans_stream_capacity": (c_int, [c_int, c_int]),
+    "hpc_rans_encode": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
+                                c_void_p, c_void_p]),
+    "hpc_rans_compact": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "hpc_rans_decode": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
+                                c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "hpc_scale_levels": (c_int, [c_void_p, c_int64, c_float, c_float, c_int, c_void_p, c_void_p]),
+    "hpc_minmax_rint": (c_int, [c_void_p, c_int64, c_void_p, c_void_p]),
     "hpc_rd_combine": (c_int, [c_void_p, c_void_p, POINTER(DistTerms), c_float, c_float, c_void_p, c_void_p]),
 }
 

@@ -122,13 +122,25 @@ int hpc_pack_c3_weight(const float* w, int64_t w_sr, int64_t w_sc, int Cw, void*
 //   bound by the epilogue: K = 80 makes the MMA negligible, so two warps share each TMEM lane quarter)
 // ---------------------------------------------------------------------------------------
 namespace {
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, const void* src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(m)),
+               "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_group_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void bulk_wait_group_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
 constexpr int T1_TH = 8, T1_TW = 16;                      // 128 output pixels per tile
 constexpr int T1_PH = 2 * T1_TH + 3, T1_PWV = 2 * T1_TW + 3, T1_PW = T1_PWV + 1;   // 19 x 35 (+1 pad)
 constexpr int T1_THREADS = 416;
 constexpr int T1_EPI = 256;                               // epilogue threads
 constexpr int T1_A_BYTES = 2 * 16384;                     // two 64-wide K chunks of [128 x 128 B]
-constexpr int T1_ST_ROW = 144;                            // staging row pitch: 64 bf16 + 16 B pad
-constexpr int T1_ST_BYTES = 128 * T1_ST_ROW;              // one tensor, one 64-channel chunk
+constexpr int T1_ST_BYTES = 128 * 128;                    // staging tile of one tensor, one 64-channel chunk: [128 pixels x 128 B],
+                                                          // SWIZZLE_128B (the layout a TMA tensor store reads)
+constexpr int T1_NSTAGE = 3;                              // staging tiles in flight (see the epilogue)
 
 struct T1Params {
   const float* x; const float* bias;
@@ -142,13 +154,14 @@ struct T1Cfg {
   static constexpr int B_BYTES = 2 * CW * 128;
   static constexpr int ACC_STRIDE = CW <= 64 ? 64 : (CW <= 128 ? 128 : 256);
   static constexpr int TMEM_COLS = 2 * ACC_STRIDE;
-  static constexpr int PATCH_BYTES = ((TCS * T1_PH * T1_PW * 4 + 127) / 128) * 128;
-  static constexpr int SMEM = 1024 + 2 * T1_A_BYTES + B_BYTES + PATCH_BYTES + 4 * T1_ST_BYTES + 1024 /*bias*/ + 256;
+  static constexpr int PATCH_BYTES = ((TCS * T1_PH * T1_PW * 4 + 1023) / 1024) * 1024;     // keeps `stage` 1 KB aligned
+  static constexpr int SMEM = 1024 + 2 * T1_A_BYTES + B_BYTES + PATCH_BYTES + 2 * T1_NSTAGE * T1_ST_BYTES + 1024 /*bias*/ + 256;
 };
 
 template <int CW>
 __global__ void __launch_bounds__(T1_THREADS, 1)
-conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constant__ T1Params p) {
+conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmOut,
+                    const __grid_constant__ CUtensorMap tmSq, const __grid_constant__ T1Params p) {
   using Cfg = T1Cfg<CW>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1 KB aligned; pointer arithmetic keeps the
@@ -156,8 +169,8 @@ conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_consta
   uint8_t* smem_a = smem;                                   // 2 x 32 KB
   uint8_t* smem_b = smem_a + 2 * T1_A_BYTES;                // 2 chunks x [CW x 128 B]
   float* patch = reinterpret_cast<float*>(smem_b + Cfg::B_BYTES);
-  uint8_t* stage = reinterpret_cast<uint8_t*>(patch) + Cfg::PATCH_BYTES;     // [2 parity][2 tensors][128 x 144]
-  float* bias_s = reinterpret_cast<float*>(stage + 4 * T1_ST_BYTES);
+  uint8_t* stage = reinterpret_cast<uint8_t*>(patch) + Cfg::PATCH_BYTES;     // [T1_NSTAGE][2 tensors][128 x 128 B]
+  float* bias_s = reinterpret_cast<float*>(stage + 2 * T1_NSTAGE * T1_ST_BYTES);
   uint64_t* bars = reinterpret_cast<uint64_t*>(bias_s + 256);
   uint64_t* full_a = bars;          // [2] builders -> MMA   (128 arrivals)
   uint64_t* empty_a = bars + 2;     // [2] MMA -> builders   (tcgen05.commit)
@@ -170,7 +183,7 @@ conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_consta
   // zero the A buffers once: the padded K columns (k >= 80) are never written again
   for (int i = threadIdx.x; i < 2 * T1_A_BYTES / 16; i += T1_THREADS) reinterpret_cast<uint4*>(smem_a)[i] = make_uint4(0, 0, 0, 0);
   if (threadIdx.x == 0) {
-    prefetch_tmap(&tmB);
+    prefetch_tmap(&tmB); prefetch_tmap(&tmOut); prefetch_tmap(&tmSq);
     for (int s = 0; s < 2; ++s) { mbar_init(&full_a[s], 128); mbar_init(&empty_a[s], 1); mbar_init(&tfull[s], 1); mbar_init(&tempty[s], T1_EPI / 32); }
     mbar_init(b_full, 1);
     fence_barrier_init();
@@ -260,9 +273,15 @@ conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_consta
       const uint32_t taddr = tmem_base + buf * Cfg::ACC_STRIDE + ((uint32_t)(q * 32) << 16);
 #pragma unroll 1
       for (int cc = 0; cc < CW / 64; ++cc) {
-        // staging buffers alternate on the RUNNING chunk count (3 chunks per tile: a per-tile parity would
-        // reuse buffer 0 back to back across tiles), so one barrier per chunk orders writers after readers
-        uint8_t* st_lp = stage + ((it * (CW / 64) + cc) & 1) * 2 * T1_ST_BYTES;
+        // A thread owns one pixel (= TMEM lane) and 32 channels of the chunk: it writes them as four 16-byte units of its
+        // 128-byte row of a SWIZZLE_128B staging tile (unit u of row r at (u ^ (r & 7)) * 16: the 8 lanes of a store
+        // wavefront hit 8 different bank groups), and ONE thread then hands the whole [8 x 16 pixels][64 channels] tile to
+        // the TMA (one tensor store per tile and chunk; rows past the image edge are clipped by the tensor map).
+        // Three staging tiles rotate on the running chunk count: the issuing thread waits, after committing the store of
+        // chunk j, until the store of chunk j-1 has been read out of shared memory, and only then joins the barrier of
+        // chunk j+1 -- whose passing is what lets the writers of chunk j+2 start on the tile chunk j-1 used.
+        const int j = it * (CW / 64) + cc;
+        uint8_t* st_lp = stage + (j % T1_NSTAGE) * 2 * T1_ST_BYTES;
         uint8_t* st_sq = st_lp + T1_ST_BYTES;
         float v2[2][16];
 #pragma unroll
@@ -280,13 +299,13 @@ conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_consta
             lo[e] = pack2_bf16(a, b);
             if (p.out_sq) sq[e] = pack2_bf16(a * a, b * b);      // (uniform branch: the fused GDN path never asks for x^2)
           }
-          uint4* d0 = reinterpret_cast<uint4*>(st_lp + row * T1_ST_ROW + cb * 2);
-          d0[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-          d0[1] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+          const int u0 = cb >> 3;                            // 16-byte unit of the first 8 channels
+          const uint32_t o0 = row * 128 + (((u0) ^ (row & 7)) << 4), o1 = row * 128 + (((u0 + 1) ^ (row & 7)) << 4);
+          *reinterpret_cast<uint4*>(st_lp + o0) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+          *reinterpret_cast<uint4*>(st_lp + o1) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
           if (p.out_sq) {
-            uint4* d1 = reinterpret_cast<uint4*>(st_sq + row * T1_ST_ROW + cb * 2);
-            d1[0] = make_uint4(sq[0], sq[1], sq[2], sq[3]);
-            d1[1] = make_uint4(sq[4], sq[5], sq[6], sq[7]);
+            *reinterpret_cast<uint4*>(st_sq + o0) = make_uint4(sq[0], sq[1], sq[2], sq[3]);
+            *reinterpret_cast<uint4*>(st_sq + o1) = make_uint4(sq[4], sq[5], sq[6], sq[7]);
           }
         }
         if (cc == CW / 64 - 1) {                           // accumulator fully read: hand it back early
@@ -294,21 +313,17 @@ conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_consta
           __syncwarp();
           if (lane == 0) mbar_arrive(&tempty[buf]);
         }
+        fence_proxy_async();                               // the staged rows must be visible to the TMA (async proxy)
         named_bar(2, T1_EPI);
-        // coalesced copy-out: 8 lanes cover one pixel's 128-byte channel chunk
-#pragma unroll
-        for (int i = 0; i < 1024 / T1_EPI; ++i) {
-          const int idx = t + T1_EPI * i, rr = idx >> 3, u = idx & 7;
-          const int oh = i0 + (rr >> 4), ow = j0 + (rr & 15);
-          if (oh < p.OH && ow < p.OW) {
-            const int64_t o = (((int64_t)n * p.OH + oh) * p.OW + ow) * CW + cc * 64 + u * 8;
-            *reinterpret_cast<uint4*>(p.out_lp + o) = *reinterpret_cast<const uint4*>(st_lp + rr * T1_ST_ROW + u * 16);
-            if (p.out_sq)
-              *reinterpret_cast<uint4*>(p.out_sq + o) = *reinterpret_cast<const uint4*>(st_sq + rr * T1_ST_ROW + u * 16);
-          }
+        if (t == 0) {
+          tma_store_4d(&tmOut, st_lp, cc * 64, j0, i0, n);
+          if (p.out_sq) tma_store_4d(&tmSq, st_sq, cc * 64, j0, i0, n);
+          bulk_commit_group();
+          bulk_wait_group_read<1>();
         }
       }
     }
+    if (t == 0) bulk_wait_group_all();
   }
   tc_fence_before();
   __syncthreads();
@@ -316,7 +331,7 @@ conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_consta
 }
 
 template <int CW>
-int launch_t1(const CUtensorMap& tmB, const T1Params& kp, cudaStream_t st) {
+int launch_t1(const CUtensorMap& tmB, const CUtensorMap& tmOut, const CUtensorMap& tmSq, const T1Params& kp, cudaStream_t st) {
   using Cfg = T1Cfg<CW>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -324,7 +339,7 @@ int launch_t1(const CUtensorMap& tmB, const T1Params& kp, cudaStream_t st) {
     attr_set = true;
   }
   const int grid = kp.total_tiles < hpc_num_sms() ? kp.total_tiles : hpc_num_sms();
-  HPC_CUDA(hpc_launch_pdl(conv_c3_umma_kernel<CW>, dim3(grid), dim3(T1_THREADS), Cfg::SMEM, st, tmB, kp));
+  HPC_CUDA(hpc_launch_pdl(conv_c3_umma_kernel<CW>, dim3(grid), dim3(T1_THREADS), Cfg::SMEM, st, tmB, tmOut, tmSq, kp));
   HPC_LAUNCH_CHECK();
   return HPC_OK;
 }
@@ -351,14 +366,22 @@ int hpc_conv_c3_fwd_umma(const float* x_nchw, const void* w_kmaj_bf16, const flo
   uint32_t estr[2] = {1, 1};
   int rc = make_tmap(&tmB, w_kmaj_bf16, 2, dims, strides, box, estr);
   if (rc) return rc;
+  // output tiles leave through TMA tensor stores: NHWC as a 4-D map (C, OW, OH, N), box = 64 channels x 16 x 8 pixels
+  CUtensorMap tmOut, tmSq;
+  uint64_t odims[4] = {(uint64_t)Cw, (uint64_t)kp.OW, (uint64_t)kp.OH, (uint64_t)N};
+  uint64_t ostr[3] = {(uint64_t)Cw * 2, (uint64_t)kp.OW * Cw * 2, (uint64_t)kp.OH * kp.OW * Cw * 2};
+  uint32_t obox[4] = {64, T1_TW, T1_TH, 1};
+  uint32_t oestr[4] = {1, 1, 1, 1};
+  if ((rc = make_tmap(&tmOut, out_lp_bf16, 4, odims, ostr, obox, oestr))) return rc;
+  if ((rc = make_tmap(&tmSq, out_sq_bf16 ? out_sq_bf16 : out_lp_bf16, 4, odims, ostr, obox, oestr))) return rc;
   const double opix = (double)N * kp.OH * kp.OW * Cw;
   HpcProfScope prof(HPC_PROF_THIN, (double)N * TCS * H * W * 4 + opix * (2 + (out_sq_bf16 ? 2 : 0)), stream);
   auto st = (cudaStream_t)stream;
   switch (Cw) {
-    case 64: return launch_t1<64>(tmB, kp, st);
-    case 128: return launch_t1<128>(tmB, kp, st);
-    case 192: return launch_t1<192>(tmB, kp, st);
-    default: return launch_t1<256>(tmB, kp, st);
+    case 64: return launch_t1<64>(tmB, tmOut, tmSq, kp, st);
+    case 128: return launch_t1<128>(tmB, tmOut, tmSq, kp, st);
+    case 192: return launch_t1<192>(tmB, tmOut, tmSq, kp, st);
+    default: return launch_t1<256>(tmB, tmOut, tmSq, kp, st);
   }
 }
 
@@ -600,12 +623,14 @@ int hpc_deconv_c3_fwd_umma(const void* x_nhwc_bf16, const void* w_nmaj_bf16, con
 //   ([64 pixels] x [64 values]): `wide` straight from NHWC by TMA, the im2col of `thin` written by 4 warps.
 //   Split-K over 64-pixel blocks across the grid; partials go to the workspace, a second kernel reduces them
 //   in a fixed order (deterministic) into the reference weight layout.
-//   warp 0: TMA | warp 1: MMA, TMEM | warps 2-5: im2col builders, then the TMEM -> workspace epilogue
+//   warp 0: TMA | warp 1: MMA, TMEM | warps 2-9: two im2col builder groups; group 0 then runs the TMEM -> workspace epilogue
 // ---------------------------------------------------------------------------------------
 namespace {
 constexpr int T3_TH = 4, T3_TW = 16;                      // 64 pixels per K block
 constexpr int T3_PH = 2 * T3_TH + 3, T3_PWV = 2 * T3_TW + 3, T3_PW = T3_PWV + 1;   // 11 x 35 (+1)
-constexpr int T3_THREADS = 192;
+constexpr int T3_GROUPS = 2;                              // independent im2col builder groups (128 threads each): the
+                                                          // kernel is bound by the builders, not by TMA or the MMAs
+constexpr int T3_THREADS = 64 + 128 * T3_GROUPS;
 constexpr int T3_STAGES = 4;
 
 struct T3Params {
@@ -618,7 +643,7 @@ template <int CW>
 struct T3Cfg {
   static constexpr int STAGE_BYTES = (2 + CW / 64) * ATOM_BYTES;
   static constexpr int PATCH_BYTES = ((TCS * T3_PH * T3_PW * 4 + 127) / 128) * 128;
-  static constexpr int SMEM = 1024 + T3_STAGES * STAGE_BYTES + PATCH_BYTES + 256;
+  static constexpr int SMEM = 1024 + T3_STAGES * STAGE_BYTES + T3_GROUPS * PATCH_BYTES + 256;
 };
 
 template <int CW>
@@ -629,7 +654,7 @@ wgrad_c3_umma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1 KB aligned; pointer arithmetic keeps the
                                                                                   // shared address space (LDS/STS, not generic LD/ST)
   float* patch = reinterpret_cast<float*>(smem + T3_STAGES * Cfg::STAGE_BYTES);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(patch) + Cfg::PATCH_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(patch) + T3_GROUPS * Cfg::PATCH_BYTES);
   uint64_t* full_bar = bars;                    // [STAGES] 1 TMA arrival (+tx) + 128 builder arrivals
   uint64_t* empty_bar = bars + T3_STAGES;       // [STAGES] tcgen05.commit
   uint64_t* done_bar = bars + 2 * T3_STAGES;
@@ -694,22 +719,27 @@ wgrad_c3_umma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
       mma_commit(done_bar);
     }
   } else {
-    const int t = threadIdx.x - 64;
+    // Builder group g (128 threads, its own patch buffer and named barrier) takes the K blocks kb0 + g, kb0 + g + 2, ...;
+    // the pipeline stage of a block follows from its index, so TMA, MMA and both groups agree without talking.
+    const int grp = (threadIdx.x - 64) >> 7;
+    const int t = (threadIdx.x - 64) & 127;
     const int px = t & 63, half = t >> 6;                  // pixel of the K block, which half of its 10 units
     const int il = px >> 4, jl = px & 15;
-    int stage = 0; uint32_t phase = 0;
+    float* mypatch = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(patch) + grp * Cfg::PATCH_BYTES);
     constexpr int NPF = (TCS * T3_PH * T3_PWV + 127) / 128;
     float pf[NPF];
-    if (kb0 < kb1) {
-      const int n = kb0 / tiles_per_img, r = kb0 % tiles_per_img;
+    if (kb0 + grp < kb1) {
+      const int n = (kb0 + grp) / tiles_per_img, r = (kb0 + grp) % tiles_per_img;
       patch_fetch<T3_PH, T3_PWV, NPF>(pf, p.thin, n, 2 * p.H, 2 * p.W, (r / p.tiles_w) * T3_TH, (r % p.tiles_w) * T3_TW, t);
     }
-    for (int kb = kb0; kb < kb1; ++kb) {
-      named_bar(1, 128);
-      patch_commit<T3_PH, T3_PWV, T3_PW, NPF>(patch, pf, t);
-      named_bar(1, 128);
-      if (kb + 1 < kb1) {
-        const int n = (kb + 1) / tiles_per_img, r = (kb + 1) % tiles_per_img;
+    for (int kb = kb0 + grp; kb < kb1; kb += T3_GROUPS) {
+      const int seq = kb - kb0, stage = seq % T3_STAGES;
+      const uint32_t phase = (uint32_t)(seq / T3_STAGES) & 1;
+      named_bar(1 + grp, 128);
+      patch_commit<T3_PH, T3_PWV, T3_PW, NPF>(mypatch, pf, t);
+      named_bar(1 + grp, 128);
+      if (kb + T3_GROUPS < kb1) {
+        const int n = (kb + T3_GROUPS) / tiles_per_img, r = (kb + T3_GROUPS) % tiles_per_img;
         patch_fetch<T3_PH, T3_PWV, NPF>(pf, p.thin, n, 2 * p.H, 2 * p.W, (r / p.tiles_w) * T3_TH, (r % p.tiles_w) * T3_TW, t);
       }
       mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -717,17 +747,17 @@ wgrad_c3_umma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
       if (half == 0) {                                    // units 0..4 | 5..9 of the 80-long row (compile-time k)
 #pragma unroll
         for (int u = 0; u < 5; ++u)
-          *reinterpret_cast<uint4*>(arow + (((u & 7) ^ (px & 7)) << 4)) = im2col_unit<T3_PH, T3_PW>(patch, il, jl, u);
+          *reinterpret_cast<uint4*>(arow + (((u & 7) ^ (px & 7)) << 4)) = im2col_unit<T3_PH, T3_PW>(mypatch, il, jl, u);
       } else {
 #pragma unroll
         for (int u = 5; u < 10; ++u)
           *reinterpret_cast<uint4*>(arow + (u >> 3) * ATOM_BYTES + (((u & 7) ^ (px & 7)) << 4)) =
-              im2col_unit<T3_PH, T3_PW>(patch, il, jl, u);
+              im2col_unit<T3_PH, T3_PW>(mypatch, il, jl, u);
       }
       fence_proxy_async();
       mbar_arrive(&full_bar[stage]);
-      if (++stage == T3_STAGES) { stage = 0; phase ^= 1; }
     }
+    if (grp == 0) {
     // epilogue: row = k (TMEM lane); rows >= 80 are padding
     const int q = warp & 3;
     const int row = q * 32 + lane;
@@ -751,6 +781,7 @@ wgrad_c3_umma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
         }
       }
     }
+    }   // grp == 0
   }
   tc_fence_before();
   __syncthreads();

@@ -423,6 +423,34 @@ typedef struct {
 int hpc_adamw_step(const hpc_adamw_seg* segs, int nseg, double beta1, double beta2, double eps, double clip,
                    int write_clipped_grad, hpc_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Entropy coding of the quantised latents: what the reference's `compress` / `decompress` /
+ * "symbol" stubs stand for (modelling/meta_arch/bmshl2018.py:106-110, modelling/blocks/entropy_model.py:157-169,
+ * 235-251).  Parity unpinned by the reference; the format is stated in csrc/rans_kernels.cu and restated in
+ * oracle/rans_oracle.py.  rANS, 32-bit state, 16-bit words, 16-bit probabilities; one stream per image and group of
+ * `cpg` consecutive channels; one thread codes one stream.
+ *   symbols   (n_img*npos, C) float, NHWC rows, integer valued (the rounded latent)
+ *   level     optional (n_img*npos, C) table index per symbol (conditional model: quantised scale); NULL: table = channel
+ *   cum       (T, A+1) uint32 cumulative frequencies, cum[t][0] = 0, cum[t][A] = 65536, strictly increasing
+ *   encode -> stream_buf (n_img*C/cpg, capacity) uint16, the stream's words in its LAST lengths[s] slots;
+ *   compact -> words[offsets[s] .. + lengths[s]);  decode reads that layout.  err_flag: device int, set non-zero on a
+ *   symbol outside the alphabet (encode) or a malformed stream (decode); the caller zeroes and checks it. */
+int hpc_rans_stream_capacity(int npos, int cpg);
+int hpc_rans_encode(const float* symbols, const unsigned char* level, const uint32_t* cum, int n_img, int npos, int C,
+                    int cpg, int A, int vmin, unsigned short* stream_buf, int* lengths, int* err_flag,
+                    hpc_stream_t stream);
+int hpc_rans_compact(const unsigned short* stream_buf, int cap, const int* lengths, const int64_t* offsets, int nstreams,
+                     unsigned short* words, hpc_stream_t stream);
+int hpc_rans_decode(const unsigned short* words, const int64_t* offsets, const int* lengths, const unsigned char* level,
+                    const uint32_t* cum, int n_img, int npos, int C, int cpg, int A, int vmin, float* symbols,
+                    void* symbols_lp, int lp_dtype, int* err_flag, hpc_stream_t stream);
+/* level[i] = smallest l in [0, nlevels) with sigma[i] <= scale_min * (scale_max/scale_min)^(l/(nlevels-1)) (the scale
+ * table of the conditional model's coder; the likelihood itself is entropy_model.py:341-352 at those scales) */
+int hpc_scale_levels(const float* sigma, int64_t n, float scale_min, float scale_max, int nlevels, unsigned char* level,
+                     hpc_stream_t stream);
+/* out2[0] = min, out2[1] = max over rint(x[i]) (int32); the caller initialises out2 to {INT_MAX, INT_MIN} */
+int hpc_minmax_rint(const float* x, int64_t n, int* out2, hpc_stream_t stream);
+
 /* Thin-channel layers (Cin=3 head of g_a, Cout=3 tail of g_s): K=75 is memory-bound.
  * conv_c3_fwd:   Conv2d(Cs->Cw,5,s2,p2): x NCHW float (N,Cs,H,W), w float (Cw,Cs,5,5) with
  *                strides (w_sr, w_sc) for (Cw,Cs) so the same kernel serves the dgrad of the tail

@@ -32,6 +32,23 @@ def flat_grad(model, x, nz, ny, mode, reduce):
     return fg.flat.clone(), float(losses["total_loss"].detach())
 
 
+def transparent_grad(model, x, nz, ny, mode):
+    """The trainer's own sequence, nothing else (engine/trainer.py:179-194): zero_grad (set_to_none), forward, .mean(),
+    backward.  The model's GradientReducer arms the flat buffer in forward and all-reduces from inside backward."""
+    model.zero_grad(set_to_none=True)
+    with pkg.compute_mode(mode):
+        _, losses = model(x, nz, ny)
+        loss = losses.pop("total_loss").mean()
+        loss.backward()
+    torch.cuda.synchronize()
+    red = model.gradient_reducer()
+    order = {id(p): i for i, p in enumerate(model.parameters())}
+    # back to state_dict order for the comparison with FlatGradients(model.parameters())
+    flat = torch.cat([p.grad.reshape(-1) if p.numel() % 4 == 0 else
+                      torch.cat([p.grad.reshape(-1), p.grad.new_zeros((-p.numel()) % 4)]) for p in model.parameters()])
+    return flat, len(red.fg._early), float(loss.detach())
+
+
 def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -59,6 +76,16 @@ def main():
                   f"rel-L2 {rel:.3e} (tol {tol:.0e}); mean replica loss {float(losses):.6f} vs {loss_all:.6f} "
                   f"(rel {lrel:.2e})", flush=True)
             ok = ok and rel <= tol and lrel <= 1e-4
+        dist.barrier()
+        # trainer-transparent path (no FlatGradients in the caller)
+        got2, _, loss2 = transparent_grad(model, X[sl].to(dev), NZ[sl].to(dev), NY[sl].to(dev), mode)
+        same = torch.tensor([float((got2 - got).abs().max())], device=dev)
+        dist.all_reduce(same, op=dist.ReduceOp.MAX)
+        if rank == 0:
+            print(f"mode {mode}: in-model reducer vs explicit FlatGradients: max abs difference {float(same):.3e}; "
+                  f"flat order of the reducer = backward completion order, min_bucket {model.gradient_reducer().fg.min_bucket}",
+                  flush=True)
+            ok = ok and float(same) <= 1e-6 * float(got.abs().max())
         dist.barrier()
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.broadcast(flag, src=0)
