@@ -10,9 +10,10 @@ the probability MODEL is the reference's (`_prob_mass`, :259-269 and :341-352), 
     z~ with the same kernels, image by image (batch-independent arithmetic), so both sides pick identical tables;
   * rANS streams (csrc/rans_kernels.cu): one per image and group of 8 channels, coded by one GPU thread each.
 
-Byte layout of one image's string (little endian):
-  "HPC1" | u16 H | u16 W | u16 C | u8 channels per stream | u8 flags (1: gauss) | i16 zmin | i16 zmax | i16 ymin | i16 ymax
-  | u32 length (in 16-bit words) of each z stream, then of each y stream | z words | y words
+Byte layout (little endian).  Latent string (one image, one latent):
+  i16 vmin | i16 vmax | u32 length in 16-bit words of each of the C/8 streams | the streams' words
+Image string:  "HPC1" | u16 H | u16 W | u16 C | u8 channels per stream | u8 flags (1: gauss) | u32 bytes of the z string
+  | z latent string | y latent string
 Torch is plumbing here too (memory, copies); table quantisation is host numpy on a few thousand numbers.
 """
 import struct
@@ -28,7 +29,8 @@ MAGIC = b"HPC1"
 PREC_TOTAL = 1 << 16
 SCALE_MIN, SCALE_MAX, SCALE_LEVELS = 0.11, 256.0, 64
 CHANNELS_PER_STREAM = 8
-_HEADER = struct.Struct("<4sHHHBBhhhh")
+_HEADER = struct.Struct("<4sHHHBBI")
+_RANGE = struct.Struct("<hh")
 
 
 def quantise_pmf(p):
@@ -86,14 +88,18 @@ def factorized_tables(entropy_model, vmin, vmax):
     return quantise_pmf(probs.t().cpu().numpy())                     # (C, A)
 
 
+def _cum_to_device(cum_np, dev):
+    """(T, A+1) uint32 table -> device tensor (values <= 65536, carried as int32: same bits)."""
+    return torch.from_numpy(np.ascontiguousarray(cum_np).astype(np.int32)).to(dev)
+
+
 def _encode(sym, level, cum_np, n_img, vmin):
     """sym (n_img*npos, C) fp32 integer valued -> (lengths (n_img, S) numpy, words numpy uint16 in stream order)."""
     P, C = sym.shape
     npos, cpg = P // n_img, CHANNELS_PER_STREAM
     S, A = C // cpg, cum_np.shape[1] - 1
     dev = sym.device
-    cum = torch.from_numpy(cum_np.astype(np.int64)).to(torch.int32 if False else torch.int64)      # uint32 values
-    cum = cum.to(dev).to(torch.int32) if cum_np.max() < 2 ** 31 else None
+    cum = _cum_to_device(cum_np, dev)
     cap = lib().hpc_rans_stream_capacity(npos, cpg)
     buf = torch.empty((n_img * S, cap), dtype=torch.int16, device=dev)
     lengths = torch.empty((n_img * S,), dtype=torch.int32, device=dev)
@@ -118,7 +124,7 @@ def _decode(words_np, lengths_np, level, cum_np, n_img, npos, C, vmin, dev, want
     offs = torch.zeros(ln.shape, dtype=torch.int64)
     offs[1:] = torch.cumsum(ln[:-1].to(torch.int64), 0)
     words = torch.from_numpy(words_np.view(np.int16).copy()).to(dev)
-    cum = torch.from_numpy(cum_np.astype(np.int64)).to(dev).to(torch.int32)
+    cum = _cum_to_device(cum_np, dev)
     sym = torch.empty((n_img * npos, C), dtype=torch.float32, device=dev)
     sym_lp = torch.empty((n_img * npos, C), dtype=hp.lp_dtype(), device=dev) if want_lp else None
     err = torch.zeros((1,), dtype=torch.int32, device=dev)
@@ -134,3 +140,118 @@ def scale_levels(sigma):
     level = torch.empty(sigma.shape, dtype=torch.uint8, device=sigma.device)
     check(lib().hpc_scale_levels(ptr(sigma), sigma.numel(), SCALE_MIN, SCALE_MAX, SCALE_LEVELS, ptr(level), stream()))
     return level
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# one latent <-> byte strings
+# ----------------------------------------------------------------------------------------------------------------
+def encode_latent(sym, level, cum_np, vmin, vmax):
+    """sym (N, ..., C) fp32 integer valued, NHWC -> list of N latent strings."""
+    N, C = sym.shape[0], sym.shape[-1]
+    lens, words, offs = _encode(sym.reshape(-1, C), None if level is None else level.reshape(-1, C), cum_np, N, vmin)
+    out = []
+    for n in range(N):
+        body = words[offs[n, 0]:offs[n, -1] + lens[n, -1]].astype("<u2").tobytes()
+        out.append(_RANGE.pack(vmin, vmax) + lens[n].astype("<u4").tobytes() + body)
+    return out
+
+
+def parse_latent(string, C):
+    S = C // CHANNELS_PER_STREAM
+    vmin, vmax = _RANGE.unpack_from(string, 0)
+    lens = np.frombuffer(string, dtype="<u4", count=S, offset=_RANGE.size).astype(np.int64)
+    o = _RANGE.size + 4 * S
+    if len(string) != o + 2 * int(lens.sum()):
+        raise ValueError("latent string: truncated or over-long")
+    return vmin, vmax, lens, np.frombuffer(string, dtype="<u2", count=int(lens.sum()), offset=o)
+
+
+def decode_latent(strings, level, table_fn, npos, C, dev, want_lp=False):
+    """strings of N images (one value range) -> (sym (N*npos, C) fp32, lp copy | None).  table_fn(vmin, vmax) -> cum."""
+    parsed = [parse_latent(s, C) for s in strings]
+    vmin, vmax = parsed[0][0], parsed[0][1]
+    if any((p[0], p[1]) != (vmin, vmax) for p in parsed):
+        raise ValueError("latent strings with different value ranges: decode them call by call")
+    lens = np.stack([p[2] for p in parsed])
+    words = np.concatenate([p[3] for p in parsed])
+    return _decode(words, lens, None if level is None else level.reshape(-1, C), table_fn(vmin, vmax), len(strings), npos, C,
+                   vmin, dev, want_lp)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# whole-model compress / decompress
+# ----------------------------------------------------------------------------------------------------------------
+def _sigma_per_image(model, zt_lp):
+    """sigma = h_s(z~) image by image: the few-tile layers choose their split-K factor from the grid size, so a batched
+    launch would make sigma -- and with it the decoder's table choice -- depend on what else is in the batch."""
+    from . import blocks_impl as B
+    m = model._meta
+    layers = model.prior_synthesis._layers
+    convs = [(layers[i].weight, layers[i].bias) for i in range(0, len(layers), 2)]
+    outs = [B.hs_forward(zt_lp[i:i + 1].contiguous(), convs, m.hk[::-1], m.hs[::-1], save=False)[0]
+            for i in range(zt_lp.shape[0])]
+    if len(outs) == 1:
+        return outs[0]
+    out = torch.empty((len(outs),) + tuple(outs[0].shape[1:]), dtype=outs[0].dtype, device=outs[0].device)
+    for i, t in enumerate(outs):
+        out[i:i + 1].copy_(t)
+    return out
+
+
+def compress(model, x):
+    """x (N,3,H,W) in [0,1], H and W multiples of 64 -> list of N image strings (layout in the module docstring).
+    Rounding quantisation as in evaluation mode (entropy_model.py:232-234, :335-337), whatever model.training says."""
+    from . import blocks_impl as B
+    from .autograd_ops import _split_model_params
+    _lib.require_cuda(x)
+    N, _, H, W = x.shape
+    if H % 64 or W % 64:
+        raise ValueError(f"compress: image size {H}x{W} is not a multiple of 64 (the reference does not pad either)")
+    m = model._meta
+    gauss = m.dist == _lib.DIST_GAUSS
+    with torch.no_grad():
+        model.pack_plan().ensure()
+        ga_convs, ga_gdns, ha_convs, _, _, _, cdf = _split_model_params(m, model._flat_params())
+        cdf = {k: v.detach().contiguous() for k, v in cdf.items()}
+        y, yabs, _ = B.ga_forward(hp.contiguous_f32(x), ga_convs, ga_gdns, m.k, m.strides, want_abs=True, save=False)
+        z, _ = B.ha_forward(yabs, ha_convs, m.hk, m.hs, save=False)
+        zt, ztl, _, _ = hp.factorized_forward(z, cdf, False, None, m.bin, want_probs=False, want_lp=True)
+        sigma = _sigma_per_image(model, ztl)
+        yt, _, _, _ = hp.conditional_forward(y, sigma, m.dist, False, None, m.bin, 0.0, want_probs=False)
+        C = zt.shape[-1]
+        zmin, zmax = _value_range(zt)
+        ymin, ymax = _value_range(yt)
+        zs = encode_latent(zt, None, factorized_tables(model.entropy_model, zmin, zmax), zmin, zmax)
+        ys = encode_latent(yt, scale_levels(sigma), quantise_pmf(conditional_pmf(ymin, ymax, gauss)), ymin, ymax)
+    return [_HEADER.pack(MAGIC, H, W, C, CHANNELS_PER_STREAM, int(gauss), len(a)) + a + b for a, b in zip(zs, ys)]
+
+
+def decompress(model, strings, device=None):
+    """list of image strings (one size and value range, e.g. the output of ONE compress call) -> x~ (N,3,H,W) fp32
+    in [0,1]: the reconstruction evaluation mode computes (bmshl2018.py:79-81)."""
+    from . import blocks_impl as B
+    from .autograd_ops import _split_model_params
+    heads = [_HEADER.unpack_from(s, 0) for s in strings]
+    magic, H, W, C, cpg, flags, _ = heads[0]
+    if any(h[:6] != heads[0][:6] for h in heads) or magic != MAGIC or cpg != CHANNELS_PER_STREAM:
+        raise ValueError("decompress: not bitstreams of this codec, or of different image sizes")
+    m = model._meta
+    gauss = bool(flags & 1)
+    if gauss != (m.dist == _lib.DIST_GAUSS):
+        raise ValueError("decompress: the bitstream was written with the other conditional model")
+    o = _HEADER.size
+    zs = [s[o:o + h[6]] for s, h in zip(strings, heads)]
+    ys = [s[o + h[6]:] for s, h in zip(strings, heads)]
+    N = len(strings)
+    dev = device or model.analysis_transform.layers[0].weight.device
+    with torch.no_grad():
+        model.pack_plan().ensure()
+        _, _, _, _, gs_convs, gs_gdns, _ = _split_model_params(m, model._flat_params())
+        zpos, ypos = (H // 64) * (W // 64), (H // 16) * (W // 16)
+        zt, ztl = decode_latent(zs, None, lambda a, b: factorized_tables(model.entropy_model, a, b), zpos, C, dev, True)
+        sigma = _sigma_per_image(model, ztl.view(N, H // 64, W // 64, C))
+        yt, ytl = decode_latent(ys, scale_levels(sigma), lambda a, b: quantise_pmf(conditional_pmf(a, b, gauss)), ypos, C,
+                                dev, True)
+        raw, _ = B.gs_forward(ytl.view(N, H // 16, W // 16, C), gs_convs, gs_gdns, m.k, m.strides, save=False)
+        xt, _ = hp.clamp01_sse(raw, raw, 1.0, do_clamp=True, want_xt=True)
+    return xt

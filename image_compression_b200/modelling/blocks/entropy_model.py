@@ -56,14 +56,10 @@ class BaseEntropyModel(nn.Module):
         """sum clamp(-log2(p+1e-10),0,50)  (entropy_model.py:171-185)"""
         return BitsFn.apply(probs)
 
-    def compress(self, x):
-        raise NotImplementedError()
-
-    def decompress(self, x):
-        raise NotImplementedError()
-
     def _dequantize(self, x):
-        raise NotImplementedError()
+        """symbols -> values: the identity for bin = 1 and mean = 0, the only configuration the reference runs
+        (entropy_model.py:165-169 is a stub there)."""
+        return x
 
 
 @ENTROPY_MODEL_REGISTRY.register()
@@ -85,6 +81,25 @@ class EntropyModel(BaseEntropyModel):
     def _logit_cumulative(self, x):
         return self._cdf_estimator(x)
 
+    def compress(self, x):
+        """x (N,C,h,w) -> list of N byte strings coding round(x) with the per-channel tables of this prior (the
+        reference's stub, entropy_model.py:157-160; rANS coder: image_compression_b200/codec.py)."""
+        from ... import codec, hotpath as hp
+        with torch.no_grad():
+            sym = hp.to_nhwc(x.detach(), torch.float32)
+            lo, hi = codec._value_range(sym)
+            return codec.encode_latent(sym, None, codec.factorized_tables(self, lo, hi), lo, hi)
+
+    def decompress(self, strings, shape):
+        """strings from compress(), shape = (h, w) -> the rounded symbols (N,C,h,w) fp32 (entropy_model.py:162-163)."""
+        from ... import codec, hotpath as hp
+        C = self._cdf_estimator.layers[0].weight.shape[1]
+        dev = self._cdf_estimator.layers[0].weight.device
+        with torch.no_grad():
+            sym, _ = codec.decode_latent(strings, None, lambda a, b: codec.factorized_tables(self, a, b),
+                                         shape[0] * shape[1], C, dev)
+        return hp.as_nchw(sym.view(len(strings), shape[0], shape[1], C))
+
 
 class SymmetricConditionalModel(BaseEntropyModel):
     DIST = None
@@ -98,6 +113,29 @@ class SymmetricConditionalModel(BaseEntropyModel):
             raise NotImplementedError("tensor-valued mean: the reference only ever passes mean=0 "
                                       "(bmshl2018.py:76)")
         return ConditionalFn.apply(x, scale, float(mean), float(self.bin), bool(self.training), self.DIST, noise)
+
+
+    def compress(self, x, scale):
+        """x, scale (N,C,h,w) -> list of N byte strings coding round(x) under this model at the quantised scales
+        (scale table of codec.py; the reference's stub: entropy_model.py:157-160, "symbol" mode :235-236)."""
+        from ... import codec, hotpath as hp
+        with torch.no_grad():
+            xs, ss = hp.to_nhwc(x.detach(), torch.float32), hp.to_nhwc(scale.detach(), torch.float32)
+            sym, _, _, _ = hp.conditional_forward(xs, ss, self.DIST, False, None, float(self.bin), 0.0, want_probs=False)
+            lo, hi = codec._value_range(sym)
+            cum = codec.quantise_pmf(codec.conditional_pmf(lo, hi, self.DIST == _lib.DIST_GAUSS))
+            return codec.encode_latent(sym, codec.scale_levels(ss), cum, lo, hi)
+
+    def decompress(self, strings, scale):
+        """strings from compress(), the same scale tensor -> the rounded symbols (N,C,h,w) fp32."""
+        from ... import codec, hotpath as hp
+        with torch.no_grad():
+            ss = hp.to_nhwc(scale.detach(), torch.float32)
+            N, h, w, C = ss.shape
+            gauss = self.DIST == _lib.DIST_GAUSS
+            sym, _ = codec.decode_latent(strings, codec.scale_levels(ss),
+                                         lambda a, b: codec.quantise_pmf(codec.conditional_pmf(a, b, gauss)), h * w, C, ss.device)
+        return hp.as_nchw(sym.view(N, h, w, C))
 
 
 @ENTROPY_MODEL_REGISTRY.register()

@@ -187,11 +187,16 @@ class Compressor2018(nn.Module):
     def distortion_loss(self, img1, img2):
         return {name: fn(img1, img2) for name, fn in self.distortion_loss_fns.items()}
 
-    def compress(self, x):   # stubs in the reference too (bmshl2018.py:106-110)
-        pass
+    def compress(self, x):
+        """x (N,3,H,W) in [0,1] -> list of N byte strings: the rANS bitstreams of z~ and y~ (the reference's stub,
+        bmshl2018.py:106-107; format and coder in image_compression_b200/codec.py)."""
+        from ... import codec
+        return codec.compress(self, x)
 
     def decompress(self, x):
-        pass
+        """list of byte strings from compress() -> reconstruction (N,3,H,W) in [0,1] (bmshl2018.py:109-110)."""
+        from ... import codec
+        return codec.decompress(self, x)
 
 
 def _abs(y):
