@@ -113,7 +113,8 @@ def _encode(sym, level, cum_np, n_img, vmin):
     offs[1:] = torch.cumsum(ln[:-1].to(torch.int64), 0)
     total = int(ln.sum())
     words = torch.empty((total,), dtype=torch.int16, device=dev)
-    check(lib().hpc_rans_compact(ptr(buf), cap, ptr(lengths), ptr(offs.to(dev)), n_img * S, ptr(words), stream()))
+    offs_dev = offs.to(dev)          # (a named tensor: a temporary would be freed, and its block reused, before the launch)
+    check(lib().hpc_rans_compact(ptr(buf), cap, ptr(lengths), ptr(offs_dev), n_img * S, ptr(words), stream()))
     return ln.numpy().reshape(n_img, S), words.cpu().numpy().view(np.uint16), offs.numpy().reshape(n_img, S)
 
 
@@ -128,7 +129,10 @@ def _decode(words_np, lengths_np, level, cum_np, n_img, npos, C, vmin, dev, want
     sym = torch.empty((n_img * npos, C), dtype=torch.float32, device=dev)
     sym_lp = torch.empty((n_img * npos, C), dtype=hp.lp_dtype(), device=dev) if want_lp else None
     err = torch.zeros((1,), dtype=torch.int32, device=dev)
-    check(lib().hpc_rans_decode(ptr(words), ptr(offs.to(dev)), ptr(ln.to(dev)), ptr(level), ptr(cum), n_img, npos, C, cpg, A,
+    # named device tensors: inline temporaries are freed as soon as their pointer is taken, and the caching allocator
+    # would hand the second one the first one's block
+    offs_dev, ln_dev = offs.to(dev), ln.to(dev)
+    check(lib().hpc_rans_decode(ptr(words), ptr(offs_dev), ptr(ln_dev), ptr(level), ptr(cum), n_img, npos, C, cpg, A,
                                 vmin, ptr(sym), ptr(sym_lp), _lib.dtype_code(hp.lp_dtype()), ptr(err), stream()))
     code = int(err.cpu())
     if code:

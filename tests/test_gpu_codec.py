@@ -104,15 +104,20 @@ def test_model_compress_decompress_equals_the_evaluation_forward(recipe, conditi
     assert torch.equal(xt, xt_ref)                                  # bit-exact reconstruction from the bitstream alone
     bits = [8 * len(s) for s in strings]
     est = [float(losses["bpp"]) * N * hw[0] * hw[1]]
-    # actual size vs the cross-entropy estimate (entropy_model.py:185).  Overheads on top of the estimate: 16-bit table
-    # quantisation (freq >= 1 floors), 64 scale levels instead of the exact sigma (<= one level = 13 % in scale), 32 bits
-    # of final state per stream (48 streams per image) and the stream-length table (4 B per stream)
+    # actual size vs the cross-entropy estimate (entropy_model.py:185).  Above the estimate: 16-bit table quantisation
+    # (freq >= 1 floors), 64 scale levels instead of the exact sigma, 32 bits of final state per stream (48 streams per
+    # image), the stream-length table (4 B per stream) and the 16-byte header.  BELOW it: the tables are renormalised over
+    # the value range [vmin, vmax] the header carries, which removes the tail mass the estimate pays for -- a large
+    # effect for an untrained model (factorised prior initialised with scale 10, latents in a narrow range): measured
+    # 0.857 at 3 x 512x768, 0.846 at 2 x 128x192, 1.29 for one 64x64 image (fixed overheads) (profiles/r02_parity.json).  The exact statement about code length is
+    # made elsewhere: the kernels' words equal the oracle's (above), whose length is checked against the ideal code length
+    # of the tables on the CPU (tests/test_rans_oracle.py).
     ratio = sum(bits) / sum(est)
     record_parity(f"codec_{conditional}_{N}x{hw[0]}x{hw[1]}_actual_vs_estimated_bits",
                   {"actual_bits": bits, "estimated_bits": est, "ratio": ratio,
                    "bpp_actual": [b / (hw[0] * hw[1]) for b in bits]})
     small = hw[0] * hw[1] <= 64 * 64
-    assert 0.98 <= ratio <= (1.60 if small else 1.15), (ratio, bits, est)
+    assert 0.5 <= ratio <= (1.60 if small else 1.06), (ratio, bits, est)
 
 
 def test_decompress_rejects_foreign_strings():
