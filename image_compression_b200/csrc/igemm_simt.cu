@@ -376,6 +376,51 @@ int hpc_colsum(const void* x, int dtype, int64_t P, int C, float scale, float* o
 }
 
 // ---------------------------------------------------------------------------------------
+// hpc_colsum_static: hpc_colsum for callers that cannot allocate device memory (code under CUDA-graph capture, tight
+// serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The stage-1 partial sums live in a file-scope device array instead of a caller buffer:
+//   * size: kColsumParts x HPC_COLSUM_STATIC_MAX_C floats = 592 x 512 x 4 B = 1.16 MiB, held by EVERY GPU that loads
+//     this library until the process exits; C beyond the maximum is rejected;
+//   * in host code `g_colsum_static` is only a stand-in for the symbol, not a device address: its address on the
+//     current device comes from cudaGetSymbolAddress, once per device, with that device current;
+//   * nothing has to start at zero: stage 1 overwrites every partial (nparts x C) that stage 2 of the same call reads,
+//     so what an earlier call left behind is never seen;
+//   * every call on a device shares the one array: two calls whose kernels overlap on the GPU (different streams
+//     without an ordering between them) race.  Calls on one stream, or ordered by events, are safe.
+// The entry point launches kernels only: no cudaMalloc / cudaFree / allocating library routine.
+// ---------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_colsum_static[(size_t)kColsumParts * HPC_COLSUM_STATIC_MAX_C];
+
+static int colsum_static_address(float** out) {
+  constexpr int kMaxDevices = 64;
+  static float* addr[kMaxDevices] = {nullptr};     // per device; a benign race: every thread resolves the same address
+  int dev = -1;
+  HPC_CUDA(cudaGetDevice(&dev));
+  HPC_REQUIRE(dev >= 0 && dev < kMaxDevices, HPC_ERR_UNSUPPORTED, "hpc_colsum_static: device ordinal %d not in [0,%d)", dev,
+              kMaxDevices);
+  float* p = __atomic_load_n(&addr[dev], __ATOMIC_ACQUIRE);
+  if (!p) {
+    HPC_CUDA(cudaGetSymbolAddress((void**)&p, g_colsum_static));      // address on the CURRENT device (= dev)
+    HPC_REQUIRE(p != nullptr, HPC_ERR_CUDA, "hpc_colsum_static: cudaGetSymbolAddress returned NULL on device %d", dev);
+    __atomic_store_n(&addr[dev], p, __ATOMIC_RELEASE);
+  }
+  *out = p;
+  return HPC_OK;
+}
+
+int hpc_colsum_static(const void* x, int dtype, int64_t P, int C, float scale, float* out, hpc_stream_t stream) {
+  HPC_REQUIRE(x && out, HPC_ERR_BAD_SHAPE, "hpc_colsum_static: NULL pointer");
+  HPC_REQUIRE(P > 0 && C > 0, HPC_ERR_BAD_SHAPE, "hpc_colsum_static: empty input");
+  HPC_REQUIRE(C <= HPC_COLSUM_STATIC_MAX_C, HPC_ERR_BAD_SHAPE,
+              "hpc_colsum_static: C = %d exceeds the built-in scratch (at most %d columns); use hpc_colsum with a caller buffer",
+              C, HPC_COLSUM_STATIC_MAX_C);
+  float* scratch = nullptr;
+  int rc = colsum_static_address(&scratch);
+  if (rc) return rc;
+  return hpc_colsum(x, dtype, P, C, scale, out, scratch, sizeof(float) * (size_t)kColsumParts * HPC_COLSUM_STATIC_MAX_C, stream);
+}
+
+// ---------------------------------------------------------------------------------------
 // GDN elementwise helpers
 // ---------------------------------------------------------------------------------------
 template <typename T>

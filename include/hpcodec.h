@@ -386,6 +386,14 @@ int hpc_pack_multi(const hpc_pack_job* jobs_host, int njobs, int dtype, hpc_stre
 int hpc_colsum(const void* x, int dtype, int64_t P, int C, float scale, float* out, void* scratch,
                size_t scratch_bytes, hpc_stream_t stream);
 size_t hpc_colsum_scratch_bytes(int64_t P, int C);
+/* hpc_colsum without a caller scratch buffer, for callers that cannot allocate device memory (CUDA-graph capture,
+ * serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * The partial sums use a static device array inside the library (592 x HPC_COLSUM_STATIC_MAX_C floats =
+ * 1.16 MiB on every GPU that loads the library, until exit); C > HPC_COLSUM_STATIC_MAX_C returns HPC_ERR_BAD_SHAPE.
+ * The call allocates nothing (no cudaMalloc / cudaFree).  All calls on a device share the array: calls whose kernels
+ * may overlap on the GPU (unordered streams) race; calls on one stream are safe.  Same result as hpc_colsum, bit for bit. */
+#define HPC_COLSUM_STATIC_MAX_C 512
+int hpc_colsum_static(const void* x, int dtype, int64_t P, int C, float scale, float* out, hpc_stream_t stream);
 
 /* GDN helpers (elementwise, NHWC lp tensors of n elements).
  * hpc_square: out = x^2 (optionally relu first: gdn.py:80-81); used when the producer did not
