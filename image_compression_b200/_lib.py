@@ -215,6 +215,9 @@ _SIGNATURES = {
     "hpc_gdn_bwd_fused_umma": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p,
                                        c_void_p, c_float, c_void_p, c_float, c_void_p, c_void_p, c_void_p,
                                        c_void_p, c_size_t, c_void_p]),
+    "hpc_gdn_bwd_fused_rc_umma": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p,
+                                       c_void_p, c_float, c_void_p, c_float, c_void_p, c_void_p, c_void_p,
+                                       c_void_p, c_size_t, c_void_p]),
     "hpc_gdn_prepare": (c_int, [c_void_p, c_void_p, c_int, c_float, c_float, c_float, c_void_p, c_void_p, c_void_p,
                                 c_void_p]),
     "hpc_gdn_bwd_umma_parts": (c_int, [c_int64]),

@@ -495,6 +495,7 @@ struct GdnFusedParams {
   int tiles;
   int inverse;
   int prefetch;            // dual kernel: L2 prefetch of the next half-tile of each set
+  const float* beta;       // recompute form (RC): effective beta[C]; r = rsqrt(beta + x^2 . gamma^T) is rebuilt in the kernel
 };
 
 template <int C>
@@ -777,12 +778,20 @@ gdn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_cons
 // disable-output-lane mask of the other half, so the two sets share one accumulator; the d(gamma) UMMAs contract over
 // the 64 rows of their own set only (K = 64).  TMEM budget unchanged (512 columns for C = 192).
 // ---------------------------------------------------------------------------------------
-template <int C>
+//
+// RC = true ("recompute"): r is NOT read from HBM (and the forward never writes it: 7 -> 5 HBM passes per layer and
+// step).  The workers first write x^2 into the r buffer; an extra UMMA n = x^2 . gamma^T reads it as its A operand and
+// the RESIDENT gamma^T tile through an MN-major descriptor as its B operand (element (N = i, K = k) of gamma is
+// gammaT[k][i]: i contiguous), accumulating into the `a` columns, which are time-shared: n, read out as
+// r = rsqrt(beta + n), then a = t . gamma.  TMEM stays at 512 columns; r is the forward's fp32 value instead of its
+// bf16 rounding.
+template <int C, bool RC>
 __global__ void __launch_bounds__(G_THREADS, 1)
 gdn_bwd_dual_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_constant__ CUtensorMap tmX,
                     const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmDx,
                     const __grid_constant__ CUtensorMap tmG, const __grid_constant__ GdnFusedParams p) {
   static_assert(C == 128 || C == 192, "fused d(gamma): C in {128, 192}");
+  constexpr int NT = RC ? 2 : 3;                            // tensors loaded per half-tile: g, x (, r)
   using Cfg = GCfg<C>;
   constexpr int KC = Cfg::KC;
   constexpr int REM = C - 128;
@@ -795,16 +804,19 @@ gdn_bwd_dual_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
   uint8_t* gam = smem;                           // gamma^T as the K-major B operand
   uint8_t* bg = gam + Cfg::GAMMA;                // g   -> u = g r -> dx
   uint8_t* bx = bg + Cfg::TILE;                  // x   -> x^2
-  uint8_t* bn = bx + Cfg::TILE;                  // r   -> t
+  uint8_t* bn = bx + Cfg::TILE;                  // r   -> t          (RC: x^2 -> t)
+  float* beta_s = reinterpret_cast<float*>(bn + Cfg::TILE);              // RC: 256 floats
   uint64_t* bars = reinterpret_cast<uint64_t*>(bn + Cfg::TILE + 1024);
   uint64_t* g_full = bars;
-  uint64_t* in_full = bars + 1;     // [2] TMA: g, x, r half-tiles landed
+  uint64_t* in_full = bars + 1;     // [2] TMA: g, x (, r) half-tiles landed
   uint64_t* in_empty = bars + 3;    // [2] KC store lanes + d(gamma) MMA commit + 8 worker warps
   uint64_t* a_full = bars + 5;      // [2] workers of the set: t (and u) written
   uint64_t* tfull = bars + 7;       // [2]
   uint64_t* out_full = bars + 9;    // [2] workers of the set: dx, x^2 written
   uint64_t* dg_done = bars + 11;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+  uint64_t* sq_full = bars + 12;    // [2] RC: workers of the set: x^2 written
+  uint64_t* nfull = bars + 14;      // [2] RC: n = x^2 . gamma^T is in TMEM
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nh = (int)((p.P + HROWS - 1) / HROWS);                              // half-tiles in the tensor
@@ -816,26 +828,31 @@ gdn_bwd_dual_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
     for (int s = 0; s < 2; ++s) {
       mbar_init(&in_full[s], 1); mbar_init(&in_empty[s], KC + 1 + GW / 32);
       mbar_init(&a_full[s], GW); mbar_init(&tfull[s], 1); mbar_init(&out_full[s], GW);
+      mbar_init(&sq_full[s], GW); mbar_init(&nfull[s], 1);
     }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, TCOLS);
+  if constexpr (RC) {
+    pdl_wait();                    // beta was written by an earlier kernel of the stream
+    for (int i = threadIdx.x; i < 256; i += G_THREADS) beta_s[i] = i < C ? p.beta[i] : 1.f;
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  pdl_wait();                      // the prologue above overlaps the previous kernel's tail
+  if constexpr (!RC) pdl_wait();   // the prologue above overlaps the previous kernel's tail
   pdl_launch_dependents();
 
   if (warp == 0) {
-    // lane l: set l / 3KC, tensor (l % 3KC) / KC, chunk l % KC.  The lanes run independently (a complete_tx may
+    // lane l: set l / (NT KC), tensor (l % (NT KC)) / KC, chunk l % KC.  The lanes run independently (a complete_tx may
     // precede the expect_tx of its phase: the phase cannot complete before the expecting arrival).
     if (lane == 0) {
       mbar_arrive_expect_tx(g_full, Cfg::GAMMA);
       for (int c = 0; c < KC; ++c) tma_load_2d(gam + c * (C * 128), &tmG, g_full, c * 64, 0);
     }
-    if (lane < 6 * KC) {
-      const int s = lane / (3 * KC), rem = lane % (3 * KC), which = rem / KC, c = rem % KC;
+    if (lane < 2 * NT * KC) {
+      const int s = lane / (NT * KC), rem = lane % (NT * KC), which = rem / KC, c = rem % KC;
       uint8_t* dst = (which == 0 ? bg : (which == 1 ? bx : bn)) + c * G_CHUNK + s * HBYTES;
       const CUtensorMap* tm = which == 0 ? &tmGr : (which == 1 ? &tmX : &tmR);
       // L2 prefetch one half-tile of this set ahead: the load that follows the buffer release then pays L2 latency
@@ -845,7 +862,7 @@ gdn_bwd_dual_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
         const int h = blockIdx.x + k * gridDim.x;
         if (p.prefetch && k + 2 < mine) tma_prefetch_2d(tm, c * 64, (h + 2 * (int)gridDim.x) * HROWS);
         mbar_wait(&in_empty[s], (j & 1) ^ 1);
-        if (rem == 0) mbar_arrive_expect_tx(&in_full[s], 3 * Cfg::TILE / 2);
+        if (rem == 0) mbar_arrive_expect_tx(&in_full[s], NT * Cfg::TILE / 2);
         tma_load_2d(dst, tm, &in_full[s], c * 64, h * HROWS);
       }
     }
@@ -856,29 +873,46 @@ gdn_bwd_dual_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
       constexpr uint32_t idesc_dgb = make_idesc_bf16(128, 64, 1, 1);
       mbar_wait(g_full, 0);
       const uint32_t t_addr = smem_u32(bn), sq_addr = smem_u32(bx), b_addr = smem_u32(gam);
+      constexpr uint32_t idesc_n = make_idesc_bf16(128, C, 0, 1);       // RC: A = x^2 K-major, B = gamma^T read MN-major
       int nset[2] = {(mine + 1) / 2, mine / 2};
-      int jA[2] = {0, 0}, jD[2] = {0, 0};
+      // per set, the MMAs of half-tile j go out in the order N (RC only), A, D; st = which one is due
+      int j[2] = {0, 0}, st[2] = {RC ? 0 : 1, RC ? 0 : 1};
       uint32_t dg_started = 0, spins = 0;
       int nextD = 0;      // d(gamma) accumulates the half-tiles in index order (k = 2 j + s): bit-reproducible sums
-      while (jD[0] < nset[0] || jD[1] < nset[1]) {
+      while (j[0] < nset[0] || j[1] < nset[1]) {
         bool progressed = false;
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
-          if (jA[s] < nset[s] && jA[s] == jD[s]) {
-            if (mbar_try_wait(&a_full[s], jA[s] & 1)) {
+          if (j[s] >= nset[s]) continue;
+          const uint32_t keep = s ? 0u : 0xFFFFFFFFu;       // disable the OTHER set's lanes
+          if (RC && st[s] == 0) {
+            if (mbar_try_wait(&sq_full[s], j[s] & 1)) {
               tc_fence_after();
-              const uint32_t keep = s ? 0u : 0xFFFFFFFFu;   // disable the OTHER set's lanes
+              // n[p][i] = sum_k x^2[p][k] gamma[i][k]: K = k runs over the ROWS of the resident gamma^T tile (16 rows =
+              // 2 KB per step), N = i over its KC chunks (leading byte offset = chunk stride)
+#pragma unroll
+              for (int k = 0; k < C / 16; ++k)
+                mma_bf16_ss_masked(tmem_base, make_smem_desc_sw128(t_addr + (k >> 2) * G_CHUNK + (k & 3) * 32, 16, 1024),
+                                   make_smem_desc_sw128(b_addr + k * 2048, C * 128, 1024), idesc_n, k != 0, ~keep, ~keep,
+                                   keep, keep);
+              mma_commit(&nfull[s]);
+              st[s] = 1;
+              progressed = true;
+            }
+          } else if (st[s] == 1) {
+            if (mbar_try_wait(&a_full[s], j[s] & 1)) {
+              tc_fence_after();
 #pragma unroll
               for (int k = 0; k < C / 16; ++k)
                 mma_bf16_ss_masked(tmem_base, make_smem_desc_sw128(t_addr + (k >> 2) * G_CHUNK + (k & 3) * 32, 16, 1024),
                                    make_smem_desc_sw128(b_addr + (k >> 2) * (C * 128) + (k & 3) * 32, 16, 1024), idesc,
                                    k != 0, ~keep, ~keep, keep, keep);
               mma_commit(&tfull[s]);
-              ++jA[s];
+              st[s] = 2;
               progressed = true;
             }
-          } else if (jD[s] < jA[s] && 2 * jD[s] + s == nextD) {
-            if (mbar_try_wait(&out_full[s], jD[s] & 1)) {
+          } else if (st[s] == 2 && 2 * j[s] + s == nextD) {
+            if (mbar_try_wait(&out_full[s], j[s] & 1)) {
               tc_fence_after();
 #pragma unroll
               for (int ks = 0; ks < HROWS / 16; ++ks) {     // K = the 64 rows of this set
@@ -896,7 +930,8 @@ gdn_bwd_dual_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
               }
               dg_started = 1;
               mma_commit(&in_empty[s]);
-              ++jD[s];
+              st[s] = RC ? 0 : 1;
+              ++j[s];
               ++nextD;
               progressed = true;
             }
@@ -935,6 +970,60 @@ gdn_bwd_dual_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
       const int h = blockIdx.x + k * gridDim.x;
       mbar_wait(&in_full[s], j & 1);
       constexpr int UB = UH % 4 == 0 ? 4 : (UH % 3 == 0 ? 3 : (UH % 2 == 0 ? 2 : 1));
+      if constexpr (RC) {
+        // phase 1: x^2 -> the r buffer (A operand of n = x^2 . gamma^T)
+#pragma unroll 1
+        for (int ub = 0; ub < UH; ub += UB) {
+          uint4 rx[UB];
+#pragma unroll
+          for (int jj = 0; jj < UB; ++jj) rx[jj] = *reinterpret_cast<const uint4*>(bx + unit_off(row, half * UH + ub + jj));
+#pragma unroll
+          for (int jj = 0; jj < UB; ++jj) {
+            float x[8];
+            unpack8(rx[jj], x);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) x[e] *= x[e];
+            *reinterpret_cast<uint4*>(bn + unit_off(row, half * UH + ub + jj)) = pack8(x);
+          }
+        }
+        fence_proxy_async();
+        tc_fence_before();          // (the accumulator reads of the previous half-tile precede this arrival)
+        mbar_arrive(&sq_full[s]);
+        mbar_wait(&nfull[s], j & 1);
+        tc_fence_after();
+        // phase 2: r = rsqrt(beta + n) from TMEM;  t = g x r^3 (over x^2),  u = g r (over g)
+        const uint32_t naddr = tmem_base + ((uint32_t)(q * 32) << 16) + half * (C / 4);
+#pragma unroll 1
+        for (int gb = 0; gb < C / 64; ++gb) {
+          float v[16];
+          uint4 gr[2], xr[2];
+          tmem_ld16(naddr + gb * 16, v);
+          const int c0 = half * (C / 4) + gb * 16;
+#pragma unroll
+          for (int hh = 0; hh < 2; ++hh) {
+            const uint32_t o = unit_off(row, (c0 >> 3) + hh);
+            gr[hh] = *reinterpret_cast<const uint4*>(bg + o);
+            xr[hh] = *reinterpret_cast<const uint4*>(bx + o);
+          }
+          tmem_ld_wait();
+#pragma unroll
+          for (int hh = 0; hh < 2; ++hh) {
+            const uint32_t o = unit_off(row, (c0 >> 3) + hh);
+            float g[8], x[8], t[8], u[8];
+            unpack8(gr[hh], g);
+            unpack8(xr[hh], x);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const float n = v[hh * 8 + e] + beta_s[c0 + hh * 8 + e];
+              const float r = rsqrtf(n);
+              t[e] = g[e] * x[e] * (p.inverse ? r : r * r * r);
+              u[e] = p.inverse ? g[e] * (n * r) : g[e] * r;        // g / r = g sqrt(n) = g n r
+            }
+            *reinterpret_cast<uint4*>(bn + o) = pack8(t);
+            *reinterpret_cast<uint4*>(bg + o) = pack8(u);
+          }
+        }
+      } else {
 #pragma unroll 1
       for (int ub = 0; ub < UH; ub += UB) {
         uint4 rg[UB], rx[UB], rr[UB];
@@ -960,6 +1049,7 @@ gdn_bwd_dual_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
           *reinterpret_cast<uint4*>(bn + o) = pack8(t);
           *reinterpret_cast<uint4*>(bg + o) = pack8(u);
         }
+      }
       }
       fence_proxy_async();
       tc_fence_before();            // (the accumulator reads of the previous half-tile precede this arrival)
@@ -1230,12 +1320,16 @@ size_t hpc_gdn_bwd_fused_umma_workspace_bytes(int64_t P, int C) {
   return (size_t)gdn_grid((int)((P + 63) / 64)) * (C * C + 2 * C) * sizeof(float);   // >= the single-pipeline grid
 }
 
-int hpc_gdn_bwd_fused_umma(const void* g_bf16, const void* x_bf16, const void* rnorm_bf16, const void* gammaT_bf16,
-                           int64_t P, int C, int inverse, void* dx_bf16, const float* gamma_param, float gamma_bound,
-                           const float* beta_param, float beta_bound, float* dgamma, float* dbeta, float* dbias,
-                           void* workspace, size_t workspace_bytes, hpc_stream_t stream) {
+// rnorm_bf16 != NULL: r is read (4 HBM passes);  rnorm_bf16 == NULL: beta_eff given, r is recomputed in the kernel (3 passes)
+static int gdn_bwd_fused_launch(const void* g_bf16, const void* x_bf16, const void* rnorm_bf16, const float* beta_eff,
+                                const void* gammaT_bf16, int64_t P, int C, int inverse, void* dx_bf16,
+                                const float* gamma_param, float gamma_bound, const float* beta_param, float beta_bound,
+                                float* dgamma, float* dbeta, float* dbias, void* workspace, size_t workspace_bytes,
+                                hpc_stream_t stream) {
+  const bool recompute = rnorm_bf16 == nullptr;
   int rc = gdn_check("hpc_gdn_bwd_fused_umma", P, C,
-                     {g_bf16, x_bf16, rnorm_bf16, gammaT_bf16, dx_bf16, dgamma, dbeta, workspace});
+                     {g_bf16, x_bf16, recompute ? (const void*)beta_eff : rnorm_bf16, gammaT_bf16, dx_bf16, dgamma, dbeta,
+                      workspace});
   if (rc) return rc;
   HPC_REQUIRE(C == 128 || C == 192, HPC_ERR_UNSUPPORTED, "hpc_gdn_bwd_fused_umma: C=%d not in {128,192}", C);
   HPC_REQUIRE(workspace_bytes >= hpc_gdn_bwd_fused_umma_workspace_bytes(P, C), HPC_ERR_BAD_SHAPE,
@@ -1243,8 +1337,11 @@ int hpc_gdn_bwd_fused_umma(const void* g_bf16, const void* x_bf16, const void* r
   HPC_REQUIRE(!dbias || hpc_aligned16(dbias), HPC_ERR_BAD_ALIGNMENT, "hpc_gdn_bwd_fused_umma: dbias must be 16B aligned");
   static int dual = -1;                          // HPC_GDN_BWD_DUAL=0 selects the single-pipeline kernel (A/B measurements)
   if (dual < 0) { const char* e = getenv("HPC_GDN_BWD_DUAL"); dual = e ? (atoi(e) ? 1 : 0) : 1; }
+  HPC_REQUIRE(dual || !recompute, HPC_ERR_UNSUPPORTED, "the recompute form of the GDN backward exists for the dual-pipeline "
+              "kernel only (HPC_GDN_BWD_DUAL=0 is set)");
   const int grid = dual ? gdn_grid((int)((P + 63) / 64)) : gdn_grid((int)((P + 127) / 128));
   GdnFusedParams kp;
+  kp.beta = beta_eff;
   kp.dgamma_part = (float*)workspace;
   kp.colsum_part = kp.dgamma_part + (size_t)grid * C * C;
   kp.dxsum_part = kp.colsum_part + (size_t)grid * C;
@@ -1256,24 +1353,28 @@ int hpc_gdn_bwd_fused_umma(const void* g_bf16, const void* x_bf16, const void* r
   CUtensorMap tmGr, tmX, tmR, tmDx, tmG;
   if ((rc = make_rows_tmap(&tmGr, g_bf16, P, C, box_rows))) return rc;
   if ((rc = make_rows_tmap(&tmX, x_bf16, P, C, box_rows))) return rc;
-  if ((rc = make_rows_tmap(&tmR, rnorm_bf16, P, C, box_rows))) return rc;
+  if ((rc = make_rows_tmap(&tmR, recompute ? x_bf16 : rnorm_bf16, P, C, box_rows))) return rc;      // unused when recomputing
   if ((rc = make_rows_tmap(&tmDx, dx_bf16, P, C, box_rows))) return rc;
   if ((rc = make_rows_tmap(&tmG, gammaT_bf16, C, C, C))) return rc;
-  HpcProfScope prof(HPC_PROF_GDN, (double)P * C * 2 * 4, stream);
+  HpcProfScope prof(HPC_PROF_GDN, (double)P * C * 2 * (recompute ? 3 : 4), stream);
   auto st = (cudaStream_t)stream;
-#define GDN_BWD_LAUNCH(KERNEL, CC)                                                                              \
+#define GDN_BWD_LAUNCH(...)                                                                                     \
   do {                                                                                                          \
+    auto kfn = __VA_ARGS__;                                                                                     \
     static bool attr_set = false;                                                                               \
     if (!attr_set) {                                                                                            \
-      HPC_CUDA(cudaFuncSetAttribute(KERNEL<CC>, cudaFuncAttributeMaxDynamicSharedMemorySize, GCfg<CC>::SMEM));  \
+      HPC_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));                   \
       attr_set = true;                                                                                          \
     }                                                                                                           \
-    HPC_CUDA(hpc_launch_pdl(KERNEL<CC>, dim3(grid), dim3(G_THREADS), GCfg<CC>::SMEM, st, tmGr, tmX, tmR, tmDx, tmG, kp)); \
+    HPC_CUDA(hpc_launch_pdl(kfn, dim3(grid), dim3(G_THREADS), smem, st, tmGr, tmX, tmR, tmDx, tmG, kp));        \
   } while (0)
-  if (dual) {
-    if (C == 128) GDN_BWD_LAUNCH(gdn_bwd_dual_kernel, 128); else GDN_BWD_LAUNCH(gdn_bwd_dual_kernel, 192);
+  const size_t smem = C == 128 ? GCfg<128>::SMEM : GCfg<192>::SMEM;
+  if (dual && recompute) {
+    if (C == 128) GDN_BWD_LAUNCH(gdn_bwd_dual_kernel<128, true>); else GDN_BWD_LAUNCH(gdn_bwd_dual_kernel<192, true>);
+  } else if (dual) {
+    if (C == 128) GDN_BWD_LAUNCH(gdn_bwd_dual_kernel<128, false>); else GDN_BWD_LAUNCH(gdn_bwd_dual_kernel<192, false>);
   } else {
-    if (C == 128) GDN_BWD_LAUNCH(gdn_bwd_fused_kernel, 128); else GDN_BWD_LAUNCH(gdn_bwd_fused_kernel, 192);
+    if (C == 128) GDN_BWD_LAUNCH(gdn_bwd_fused_kernel<128>); else GDN_BWD_LAUNCH(gdn_bwd_fused_kernel<192>);
   }
 #undef GDN_BWD_LAUNCH
   HPC_LAUNCH_CHECK();
@@ -1286,6 +1387,25 @@ int hpc_gdn_bwd_fused_umma(const void* g_bf16, const void* x_bf16, const void* r
   HPC_CUDA(hpc_launch_pdl(gdn_bwd_finish_kernel, dim3(f.ng + f.nc + (dbias ? f.nc : 0)), dim3(256), 0, st, f));
   HPC_LAUNCH_CHECK();
   return HPC_OK;
+}
+
+int hpc_gdn_bwd_fused_umma(const void* g_bf16, const void* x_bf16, const void* rnorm_bf16, const void* gammaT_bf16,
+                           int64_t P, int C, int inverse, void* dx_bf16, const float* gamma_param, float gamma_bound,
+                           const float* beta_param, float beta_bound, float* dgamma, float* dbeta, float* dbias,
+                           void* workspace, size_t workspace_bytes, hpc_stream_t stream) {
+  HPC_REQUIRE(rnorm_bf16, HPC_ERR_BAD_SHAPE, "hpc_gdn_bwd_fused_umma: rnorm is NULL (use hpc_gdn_bwd_fused_rc_umma to "
+              "recompute it)");
+  return gdn_bwd_fused_launch(g_bf16, x_bf16, rnorm_bf16, nullptr, gammaT_bf16, P, C, inverse, dx_bf16, gamma_param,
+                              gamma_bound, beta_param, beta_bound, dgamma, dbeta, dbias, workspace, workspace_bytes, stream);
+}
+
+int hpc_gdn_bwd_fused_rc_umma(const void* g_bf16, const void* x_bf16, const float* beta_eff, const void* gammaT_bf16,
+                              int64_t P, int C, int inverse, void* dx_bf16, const float* gamma_param, float gamma_bound,
+                              const float* beta_param, float beta_bound, float* dgamma, float* dbeta, float* dbias,
+                              void* workspace, size_t workspace_bytes, hpc_stream_t stream) {
+  HPC_REQUIRE(beta_eff, HPC_ERR_BAD_SHAPE, "hpc_gdn_bwd_fused_rc_umma: beta_eff is NULL");
+  return gdn_bwd_fused_launch(g_bf16, x_bf16, nullptr, beta_eff, gammaT_bf16, P, C, inverse, dx_bf16, gamma_param,
+                              gamma_bound, beta_param, beta_bound, dgamma, dbeta, dbias, workspace, workspace_bytes, stream);
 }
 
 // gdn.py:59-62 for both parameters of a layer + both bf16 operand copies of gamma, one launch:

@@ -508,6 +508,15 @@ int hpc_gdn_bwd_fused_umma(const void* g_bf16, const void* x_bf16, const void* r
                            int64_t P, int C, int inverse, void* dx_bf16, const float* gamma_param, float gamma_bound,
                            const float* beta_param, float beta_bound, float* dgamma, float* dbeta, float* dbias,
                            void* workspace, size_t workspace_bytes, hpc_stream_t stream);
+/*  gdn_bwd_fused_rc_umma: the same without the saved r = n^-1/2: the kernel rebuilds n = beta_eff + x^2 . gamma^T on the
+ *                tensor cores (the resident gamma^T tile read through an MN-major descriptor) and uses the forward's
+ *                fp32 r instead of its bf16 rounding; the forward then need not write r at all (hpc_gdn_fwd_umma with
+ *                rnorm_bf16 == NULL): 5 HBM passes per layer and step instead of 7.  beta_eff: C floats (hpc_gdn_prepare).
+ *                Same reference code: modelling/layers/gdn.py:79-88 and its autograd. */
+int hpc_gdn_bwd_fused_rc_umma(const void* g_bf16, const void* x_bf16, const float* beta_eff, const void* gammaT_bf16,
+                           int64_t P, int C, int inverse, void* dx_bf16, const float* gamma_param, float gamma_bound,
+                           const float* beta_param, float beta_bound, float* dgamma, float* dbeta, float* dbias,
+                           void* workspace, size_t workspace_bytes, hpc_stream_t stream);
 int hpc_gdn_bwd_umma(const void* g_bf16, const void* x_bf16, const void* rnorm_bf16, const void* gammaT_bf16, int64_t P,
                      int C, int inverse, void* dx_bf16, void* t_bf16, void* xsq_bf16, float* colsum_part,
                      hpc_stream_t stream);
