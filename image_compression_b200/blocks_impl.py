@@ -69,7 +69,8 @@ def ga_forward(x_nchw, convs, gdns, k=5, strides=(2, 2, 2, 2), want_abs=False, s
         if i < n - 1:
             gp, bp = gdns[i]
             gamma, beta = _gdn_params(gp, bp)
-            yv, nrm = hp.gdn_forward(cur, cur_sq, gamma, beta, want_nrm=save)
+            yv, nrm = hp.gdn_forward(cur, cur_sq, gamma, beta,
+                                     want_nrm=save and not hp.gdn_bwd_recomputes(cur.dtype, cur.shape[-1], gamma))
             S.layers.append(("gdn", (cur, cur_sq, nrm, gamma), None))
             cur = yv
     if n == 1 and want_abs:
@@ -140,7 +141,8 @@ def gs_forward(yt_lp, convs, gdns, k=5, strides=(2, 2, 2, 2), save=True):
             S.layers.append(("deconv", spec, cur))
             gp, bp = gdns[i]
             gamma, beta = _gdn_params(gp, bp)
-            yv, nrm = hp.gdn_forward(o["lp"], o.get("sq"), gamma, beta, want_nrm=save)
+            yv, nrm = hp.gdn_forward(o["lp"], o.get("sq"), gamma, beta,
+                                     want_nrm=save and not hp.gdn_bwd_recomputes(o["lp"].dtype, o["lp"].shape[-1], gamma))
             S.layers.append(("gdn", (o["lp"], o.get("sq"), nrm, gamma), None))
             cur = yv
     S.convs, S.gdns = convs, gdns

@@ -692,6 +692,26 @@ def gdn_forward(x, xsq, gamma_eff, beta_eff, inverse=False, want_nrm=True):
     return o["lp"], o["nrm"]
 
 
+# Measured (r02i, one box visit, 64 x 256^2 training step): saved r 6.70 ms / gdn class 1.88 ms; recompute 6.73 ms / 1.98 ms.
+# The backward kernel is bound by instruction issue and latency (ncu: 210 M warp instructions in 420 us at the 128^2 layer,
+# issue slots 51 % busy, 19 warps resident), not by HBM, so two HBM passes fewer do not pay for ~25 % more instructions.
+# Off by default; on, it saves the r tensors (~1 GB of saved activations at batch 64).
+_gdn_recompute = _os.environ.get("HPC_GDN_RECOMPUTE", "0") != "0"
+
+
+def set_gdn_recompute(flag):
+    global _gdn_recompute
+    _gdn_recompute = bool(flag)
+
+
+def gdn_bwd_recomputes(dtype, C, gamma_eff):
+    """True when the backward of this GDN layer rebuilds r = n^-1/2 itself (hpc_gdn_bwd_fused_rc_umma): the forward
+    then need not write r and the backward need not read it (5 HBM passes per layer and step instead of 7).
+    Opt-in with HPC_GDN_RECOMPUTE=1 or hotpath.set_gdn_recompute(True)."""
+    return (_gdn_recompute and gdn_fused_ok(dtype, C) and C in (128, 192) and isinstance(gamma_eff, GdnOperands)
+            and not _capturing)
+
+
 def gdn_bwd_has_dxsum(x):
     """True when gdn_backward(x, ..., want_dxsum=True) will return the column sums of dx."""
     return gdn_fused_ok(x.dtype, x.shape[-1]) and x.shape[-1] in (128, 192)
@@ -739,8 +759,15 @@ def _gdn_backward_eff(g, x, xsq, nrm, gamma_eff, inverse, need_dx, dxsum_out, re
             dxsum = dxsum_out if dxsum_out is not None else torch.empty((C,), dtype=torch.float32, device=dev)
             wsb = lib().hpc_gdn_bwd_fused_umma_workspace_bytes(P, C)
             ws = torch.empty(wsb, dtype=torch.uint8, device=dev)
-            check(lib().hpc_gdn_bwd_fused_umma(ptr(g), ptr(x), ptr(nrm), ptr(wp), P, C, int(inverse), ptr(dx), gpp, gb,
-                                               bpp, bb, ptr(dgamma), ptr(dbeta), ptr(dxsum), ptr(ws), wsb, stream()))
+            if nrm is None:       # the forward kept no r: the kernel rebuilds it from x, gamma and beta
+                if not isinstance(gamma_eff, GdnOperands):
+                    raise RuntimeError("gdn_backward: r was not saved and the effective beta is not at hand")
+                check(lib().hpc_gdn_bwd_fused_rc_umma(ptr(g), ptr(x), ptr(gamma_eff.beta), ptr(wp), P, C, int(inverse),
+                                                      ptr(dx), gpp, gb, bpp, bb, ptr(dgamma), ptr(dbeta), ptr(dxsum),
+                                                      ptr(ws), wsb, stream()))
+            else:
+                check(lib().hpc_gdn_bwd_fused_umma(ptr(g), ptr(x), ptr(nrm), ptr(wp), P, C, int(inverse), ptr(dx), gpp, gb,
+                                                   bpp, bb, ptr(dgamma), ptr(dbeta), ptr(dxsum), ptr(ws), wsb, stream()))
             return dx, dgamma, dbeta, dxsum, True
         dx, t, sq = torch.empty_like(x), torch.empty_like(x), torch.empty_like(x)
         parts = torch.empty((lib().hpc_gdn_bwd_umma_parts(P), C), dtype=torch.float32, device=x.device)

@@ -120,7 +120,9 @@ int hpc_cdf_layer_bwd(const float* x, const float* w, const float* b, const floa
  *   z_tilde_f32  (P,C) out;  z_tilde_lp optional copy in `lp_dtype` (feeds h_s)
  *   probs        optional (P,C) out (NHWC; the reference's (N,W,C,H) result is a view of it)
  *   bits_out     1 float: sum of clamp(-log2(p+1e-10),0,50); deterministic reduction
- *   scratch      >= hpc_reduce_scratch_bytes() bytes, zero-initialised once by the caller */
+ *   scratch      >= hpc_reduce_scratch_bytes() bytes, zero-initialised once by the caller; required: besides the
+ *                reduction state it holds the transformed-parameter table (67 x C floats, C <= 1024) that a small
+ *                pre-kernel of this call fills (calls sharing one scratch buffer must be stream ordered) */
 int hpc_factorized_fwd(const float* z, const float* noise, const hpc_cdf_params* params, int64_t P, int C,
                        int mode, float bin, uint64_t seed, uint64_t offset, float* z_tilde_f32,
                        void* z_tilde_lp, int lp_dtype, float* probs, float* bits_out, void* scratch,
@@ -133,8 +135,8 @@ int hpc_factorized_bwd(const float* z_tilde, const hpc_cdf_params* params, int64
                        float bin, const float* g_bits, float g_scale, const float* g_probs, const float* g_zt,
                        float* gz, const hpc_cdf_params* gparams, void* scratch, size_t scratch_bytes,
                        hpc_stream_t stream);
-/* scratch (optional, >= hpc_factorized_bwd_scratch_bytes(P, C)): per-row-block partials of the 43 x C parameter
- * gradients, summed in block order by a finishing kernel (bit-reproducible); NULL: float atomics into gparams. */
+/* scratch (required, >= hpc_factorized_bwd_scratch_bytes(P, C)): per-row-block partials of the 43 x C parameter
+ * gradients, summed in a fixed order by a finishing kernel (bit-reproducible), and the transformed-parameter table. */
 size_t hpc_factorized_bwd_scratch_bytes(int64_t P, int C);
 
 /* CDFEstimator.forward stand-alone: logits of the per-channel MLP at x (P,C) (entropy_model.py:101-114)

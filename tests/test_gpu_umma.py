@@ -245,3 +245,48 @@ def test_wgrad_c3_umma(N, H, W, C):
     torch.nn.functional.conv2d(xw, wt, None, stride=2, padding=2).backward(wide.float().permute(0, 3, 1, 2))
     err = float((a - wt.grad).abs().max()) / float(wt.grad.abs().max())
     assert err < 1e-2, err
+
+
+def _rel(a, b):
+    return float((a.double() - b.double()).norm() / (b.double().norm() + 1e-30))
+
+
+# ---------------------------------------------------------------------------------------------
+# GDN backward with r = n^-1/2 recomputed in the kernel (hpc_gdn_bwd_fused_rc_umma) against the saved-r form and fp64
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("P,C,inverse", [(64, 192, False), (200, 192, False), (148 * 64 * 5 + 37, 192, False),
+                                         (148 * 64 * 3 + 64, 192, True), (1000, 128, False), (148 * 64 * 2 + 1, 128, True)])
+def test_gdn_backward_recompute_matches_saved_r_and_fp64(P, C, inverse):
+    torch.manual_seed(P % 1000 + C)
+    dev = DEV
+    x = (torch.randn(1, 1, P, C, device=dev) * 1.5).to(torch.bfloat16)
+    g = torch.randn(1, 1, P, C, device=dev).to(torch.bfloat16)
+    gp = (torch.rand(C, C, 1, 1, device=dev) * 0.05 + 0.02 * torch.eye(C, device=dev).view(C, C, 1, 1)).sqrt()
+    bp = (torch.rand(C, device=dev) * 0.5 + 0.5).sqrt()
+    with pkg.compute_mode("bf16"):
+        ops = hp.gdn_prepare(gp, bp)
+        y, nrm = hp.gdn_forward(x, None, ops, None, inverse, want_nrm=True)
+        y2, none = hp.gdn_forward(x, None, ops, None, inverse, want_nrm=False)
+        assert none is None and torch.equal(y, y2)
+        a = hp.gdn_backward(g, x, None, nrm, ops, inverse, want_dxsum=True, reparam=(gp, bp, 1e-6))
+        b = hp.gdn_backward(g, x, None, None, ops, inverse, want_dxsum=True, reparam=(gp, bp, 1e-6))
+        b2 = hp.gdn_backward(g, x, None, None, ops, inverse, want_dxsum=True, reparam=(gp, bp, 1e-6))
+    torch.cuda.synchronize()
+    # fp64 reference through autograd on the same bf16-rounded operands (gdn.py:59-62, 79-88)
+    xd = x.double().view(P, C).requires_grad_(True)
+    gpd, bpd = gp.double().requires_grad_(True), bp.double().requires_grad_(True)
+    ped = hp.PEDESTAL
+    gam = (torch.maximum(gpd, torch.tensor(hp.GAMMA_BOUND, device=dev, dtype=torch.float64)) ** 2 - ped).view(C, C)
+    gam = gam.detach().to(torch.bfloat16).double() + (gam - gam.detach())  # the kernels' bf16 gamma; gradient passes ONCE
+    bet = torch.maximum(bpd, torch.tensor(hp.beta_bound(1e-6), device=dev, dtype=torch.float64)) ** 2 - ped
+    n = bet + (xd * xd) @ gam.t()
+    yd = xd * n.sqrt() if inverse else xd / n.sqrt()
+    yd.backward(g.double().view(P, C))
+    names = ("dx", "dgamma", "dbeta", "dxsum")
+    refs = (xd.grad.view(1, 1, P, C), gpd.grad, bpd.grad, xd.grad.sum(0))
+    for name, u, v, w, r in zip(names, a, b, b2, refs):
+        assert torch.equal(v, w), name                                   # bit-reproducible
+        ea, eb = _rel(u.double(), r), _rel(v.double(), r)
+        # bf16 rounding of t, u, dx in both kernels; the saved-r form also rounds r to bf16
+        assert eb <= 8e-3 and eb <= ea * 1.10 + 1e-4, (name, ea, eb)
+        assert _rel(v.double(), u.double()) <= 1.2e-2, (name, _rel(v.double(), u.double()))
