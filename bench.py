@@ -27,6 +27,8 @@ import sys
 import threading
 import time
 
+import numpy as np
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
@@ -515,6 +517,55 @@ def measure(args, c, wl, steps, warmup, with_clocks=False, with_optimizer=False,
              d2h=4 if training else 4 * (1 + 2 * B),
              grad_bytes=model.gradient_reducer().fg.nbytes() if training else 0)
 
+    # ---- the same end-to-end loop fed by data_utils.Batch: uint8 pixels over PCIe, normalised on the GPU (8f rank 4) ----
+    # The Batch objects are collated ahead of time (the DataLoader workers' job in the reference as well: the collate
+    # function runs there); the timed region holds, per step, Batch.to(device) -- the uint8 H2D copy and the
+    # crop/normalise kernel, one step ahead on the copy stream -- the step itself and the loss read-back.
+    if training:
+        from image_compression_b200 import data_utils as DU
+        mean, std = tuple(cfg.DATA.MEAN), tuple(cfg.DATA.STD)
+        rng_u8 = np.random.RandomState(1234 + rank)
+        u8_host = [[("%d" % k, DU.U8Image(rng_u8.randint(0, 256, size=(H, W, 3)).astype(np.uint8), mean, std))
+                    for k in range(B)] for _ in range(min(n_rot, 3))]
+        ready = [DU.Batch(items, cfg).pin_memmory() for items in u8_host]
+        ring = [None, None, None]
+
+        def u8_async(i):
+            b = ready[i % len(ready)]
+            with torch.cuda.stream(copy_stream):
+                b.to(dev)
+                copied[i % 3].record(copy_stream)
+            ring[i % 3] = b.imgs              # kept alive until step i's loss has been read (three steps later)
+
+        def make_u8(nsteps):
+            def u8_step(i):
+                if i == 0:
+                    u8_async(0)
+                torch.cuda.current_stream().wait_event(copied[i % 3])
+                if i + 1 < nsteps:
+                    u8_async(i + 1)
+                out = step(ring[i % 3])
+                res_host[i & 1].copy_(out.detach().reshape(1), non_blocking=True)
+                res_ready[i & 1].record()
+                if i > 0:
+                    read_result(i - 1)
+                if i + 1 == nsteps:
+                    read_result(i)
+            return u8_step
+        warm = make_u8(nw)
+        for i in range(nw):
+            warm(i)
+        k0 = _lib.lib().hpc_launch_count()
+        u8_ms = timed(make_u8(steps), steps)
+        r["e2e_u8_batch"] = {
+            "value": units / (u8_ms / 1e3), "unit": UNIT[wl], "ms_per_step": u8_ms / steps,
+            "h2d_bytes_per_step": B * 3 * H * W, "d2h_bytes_per_step": 4,
+            "launches_per_step": (_lib.lib().hpc_launch_count() - k0) / steps,
+            "what": "the e2e loop fed through data_utils.Batch (the reference's collate object, data_utils/batch.py:19-29): "
+                    "uint8 HWC pixels from pinned host memory, ToTensor/ChannelFirst/Normalize by hpc_u8_crop_normalize "
+                    "inside Batch.to(device), bit-identical to the reference's fp32 batch"}
+        del ring, ready, u8_host
+
     # ---- a sustained run: >= 200 steps back to back (clocks settle under the power cap) -----------------------
     if sustained_steps:
         cs = ClockSampler(c.local)
@@ -654,7 +705,7 @@ def record_of(r, peaks, args, headline=False):
     if r["graphed"]:
         rec["cuda_graph"] = ("each step replays one captured graph of the package's kernels; kernel-class times and "
                              "gpu_launches come from the same number of eager steps run after the timed region")
-    for k in ("sustained", "with_optimizer", "trainer_sequence"):
+    for k in ("sustained", "with_optimizer", "trainer_sequence", "e2e_u8_batch"):
         if r.get(k):
             rec[k] = r[k]
     if not headline:

@@ -192,6 +192,8 @@ _SIGNATURES = {
     "hpc_pack_weight": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int64, c_int64,
                                 POINTER(c_int), c_void_p]),
     "hpc_pack_multi": (c_int, [POINTER(PackJob), c_int, c_int, c_void_p]),
+    "hpc_u8_crop_normalize": (c_int, [c_void_p, c_int64, c_int64, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
+                                      POINTER(c_float), POINTER(c_float), c_void_p, c_void_p]),
     "hpc_colsum_static": (c_int, [c_void_p, c_int, c_int64, c_int, c_float, c_void_p, c_void_p]),
     "hpc_unpack_wgrad": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_int64, POINTER(c_int),
                                  c_int, c_void_p]),

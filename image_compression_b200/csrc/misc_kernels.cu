@@ -157,3 +157,67 @@ int hpc_pack_multi(const hpc_pack_job* jobs, int njobs, int dtype, hpc_stream_t 
   }
   return HPC_OK;
 }
+
+// ---------------------------------------------------------------------------------------
+// hpc_u8_crop_normalize: the reference's per-image input pipeline on the device:
+//   RandomCrop window -> ToTensor (float) -> ChannelFirst -> Normalize = (v / 255 - mean) / std, stacked like Batch
+//   (data_utils/transforms/transforms.py:23-35, 64-75, 84-127, 143-166; data_utils/batch.py:19-29).
+// The host sends uint8 HWC pixels (4x fewer bytes than the fp32 NCHW batch the reference copies) and the crop offsets it
+// drew; every arithmetic step is fp32 with IEEE division, like torch's, so the result is bit-identical.
+// One thread per output pixel: a warp reads 32 consecutive pixels (96 B for RGB) and writes 32 consecutive floats to
+// each channel plane.  A window that leaves the source image is never read (zeros are written): the host validates.
+// ---------------------------------------------------------------------------------------
+namespace {
+struct CropNorm {
+  const uint8_t* src; int64_t img_stride, row_stride;
+  const int* offs;                 // device (N, 2) [y0, x0] or NULL
+  const int* index;                // device (N) source image of output n, or NULL (= n)
+  int n_src, src_h, src_w, N, C, oh, ow;
+  float mean[4], std[4];
+  float* out;
+};
+__global__ void u8_crop_normalize_kernel(const __grid_constant__ CropNorm p) {
+  const int64_t plane = (int64_t)p.oh * p.ow, total = plane * p.N;
+  for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int n = (int)(t / plane);
+    const int r = (int)(t % plane), i = r / p.ow, j = r % p.ow;
+    const int y = i + (p.offs ? p.offs[2 * n] : 0), x = j + (p.offs ? p.offs[2 * n + 1] : 0);
+    const int m = p.index ? p.index[n] : n;
+    const bool in = m >= 0 && m < p.n_src && y >= 0 && y < p.src_h && x >= 0 && x < p.src_w;
+    const uint8_t* s = p.src + m * p.img_stride + (int64_t)y * p.row_stride + (int64_t)x * p.C;
+    float* o = p.out + (int64_t)n * p.C * plane + r;
+#pragma unroll 4
+    for (int c = 0; c < p.C; ++c) {
+      const float v = in ? (float)s[c] : 0.f;
+      o[c * plane] = (v / 255.0f - p.mean[c]) / p.std[c];
+    }
+  }
+}
+}  // namespace
+
+int hpc_u8_crop_normalize(const unsigned char* src_u8_hwc, int64_t img_stride_bytes, int64_t row_stride_bytes, int n_src,
+                          int src_h, int src_w, const int* src_index_dev, const int* offsets_yx_dev, int N, int C, int out_h, int out_w, const float* mean_host,
+                          const float* std_host, float* out_nchw, hpc_stream_t stream) {
+  HPC_REQUIRE(src_u8_hwc && out_nchw, HPC_ERR_BAD_SHAPE, "hpc_u8_crop_normalize: NULL pointer");
+  HPC_REQUIRE(n_src > 0 && (src_index_dev || n_src >= N), HPC_ERR_BAD_SHAPE,
+              "hpc_u8_crop_normalize: %d source images for %d outputs and no index", n_src, N);
+  HPC_REQUIRE(N > 0 && C >= 1 && C <= 4 && out_h > 0 && out_w > 0 && src_h >= out_h && src_w >= out_w, HPC_ERR_BAD_SHAPE,
+              "hpc_u8_crop_normalize: bad shape (N %d, C %d, source %dx%d, output %dx%d; the reference does not pad "
+              "under-sized images either: transforms.py:158-159)", N, C, src_h, src_w, out_h, out_w);
+  HPC_REQUIRE(row_stride_bytes >= (int64_t)src_w * C && img_stride_bytes >= 0, HPC_ERR_BAD_SHAPE,
+              "hpc_u8_crop_normalize: row stride %lld smaller than a row (%d bytes)", (long long)row_stride_bytes, src_w * C);
+  CropNorm p;
+  memset(&p, 0, sizeof(p));
+  p.src = src_u8_hwc; p.img_stride = img_stride_bytes; p.row_stride = row_stride_bytes; p.offs = offsets_yx_dev;
+  p.index = src_index_dev; p.n_src = n_src;
+  p.src_h = src_h; p.src_w = src_w; p.N = N; p.C = C; p.oh = out_h; p.ow = out_w; p.out = out_nchw;
+  for (int c = 0; c < C; ++c) {
+    p.mean[c] = mean_host ? mean_host[c] : 0.f;
+    p.std[c] = std_host ? std_host[c] : 1.f;
+    HPC_REQUIRE(p.std[c] != 0.f, HPC_ERR_BAD_SHAPE, "hpc_u8_crop_normalize: std[%d] is zero", c);
+  }
+  const int64_t total = (int64_t)N * out_h * out_w;
+  u8_crop_normalize_kernel<<<grid_for(total, 256, 148 * 16), 256, 0, (cudaStream_t)stream>>>(p);
+  HPC_LAUNCH_CHECK();
+  return HPC_OK;
+}

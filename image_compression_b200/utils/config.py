@@ -61,7 +61,7 @@ def get_cfg_defaults():
     """Defaults of every key the hot path reads (same values as the reference's `_C`)."""
     return CfgNode({
         "SEED": 0,
-        "DATA": {"IN_CHANNELS": 3, "SIZE": 256},
+        "DATA": {"IN_CHANNELS": 3, "SIZE": 256, "MEAN": [0., 0., 0.], "STD": [1., 1., 1.], "NUM_WORKERS": 4},
         "MODEL": {
             "META_ARCHITECTURE": "Compressor2018",
             "STRIDES": [2, 2, 2, 2], "CONV_KERNEL": 5, "INTER_CHANNELS": 192, "LATENT_CHANNELS": 192,

@@ -360,6 +360,22 @@ int hpc_pack_weight(const float* src, void* dst, int dtype, int ntaps, int rows,
 int hpc_unpack_wgrad(const float* src, float* dst, int ntaps, int rows, int cols, int64_t stride_r,
                      int64_t stride_c, const int* tap_src_host, int accumulate, hpc_stream_t stream);
 
+/* The reference's per-image input pipeline on the device: crop window -> float -> channels first
+ * -> (v / 255 - mean[c]) / std[c], stacked into the (N,C,out_h,out_w) fp32 batch.  Bit-identical to the reference
+ * (fp32 steps, IEEE division).  Replaces data_utils/transforms/transforms.py:23-35 (RandomCrop :143-166 with the
+ * offsets the HOST drew, ToTensor :64-75, ChannelFirst :84-100, Normalize :103-127) and the stack + fp32 host-to-device
+ * copy of data_utils/batch.py:19-29: the host sends uint8 pixels, 4x fewer bytes.
+ *   src_u8_hwc      device uint8, n_src images; pixel (m,y,x,c) at m*img_stride_bytes + y*row_stride_bytes + x*C + c
+ *                   (C <= 4)
+ *   src_index_dev   device int32 (N): output n is cut from source image src_index[n] (a uint8 image set kept resident
+ *                   in HBM, sampled by index); NULL = image n
+ *   offsets_yx_dev  device int32 (N,2) = (y0, x0) per image, or NULL for (0,0); a window or index that leaves the source is
+ *                   not read (zeros are written): the host validates its offsets (the reference asserts, :158-159)
+ *   mean_host, std_host   HOST arrays of C floats (cfg.DATA.MEAN / STD), NULL = 0 / 1 */
+int hpc_u8_crop_normalize(const unsigned char* src_u8_hwc, int64_t img_stride_bytes, int64_t row_stride_bytes, int n_src,
+                          int src_h, int src_w, const int* src_index_dev, const int* offsets_yx_dev, int N, int C, int out_h, int out_w, const float* mean_host,
+                          const float* std_host, float* out_nchw, hpc_stream_t stream);
+
 /* All packed operand copies of a model in ONE launch (a training step changes every weight, so every copy is
  * rebuilt once per step: 27 pack + 6 gdn_prepare launches otherwise).  Job kinds:
  *   HPC_PACK_TAPS  dst[t][r][c] = src(r, c, tap_src[t]) as hpc_pack_weight (`dtype` of the call); the taps of one
