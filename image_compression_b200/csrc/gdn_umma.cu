@@ -1273,10 +1273,11 @@ int hpc_gdn_fwd_umma(const void* x_bf16, const void* gamma_bf16, const float* be
   HpcProfScope prof(HPC_PROF_GDN, (double)P * C * 2 * (rnorm_bf16 ? 3 : 2), stream);
   auto st = (cudaStream_t)stream;
   GDN_DISPATCH(C, {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static HpcOncePerDevice attr_once;
+    int attr_dev;
+    if (attr_once.need(&attr_dev)) {
       HPC_CUDA(cudaFuncSetAttribute(gdn_fwd_umma_kernel<CC>, cudaFuncAttributeMaxDynamicSharedMemorySize, GCfg<CC>::SMEM));
-      attr_set = true;
+      attr_once.mark(attr_dev);
     }
     HPC_CUDA(hpc_launch_pdl(gdn_fwd_umma_kernel<CC>, dim3(gdn_grid(kp.tiles)), dim3(G_THREADS), GCfg<CC>::SMEM, st, tmX, tmY, tmR, tmG, kp));
   });
@@ -1304,10 +1305,11 @@ int hpc_gdn_bwd_umma(const void* g_bf16, const void* x_bf16, const void* rnorm_b
   HpcProfScope prof(HPC_PROF_GDN, (double)P * C * 2 * 6, stream);
   auto st = (cudaStream_t)stream;
   GDN_DISPATCH(C, {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static HpcOncePerDevice attr_once;
+    int attr_dev;
+    if (attr_once.need(&attr_dev)) {
       HPC_CUDA(cudaFuncSetAttribute(gdn_bwd_umma_kernel<CC>, cudaFuncAttributeMaxDynamicSharedMemorySize, GCfg<CC>::SMEM));
-      attr_set = true;
+      attr_once.mark(attr_dev);
     }
     gdn_bwd_umma_kernel<CC><<<gdn_grid(kp.tiles), G_THREADS, GCfg<CC>::SMEM, st>>>(tmGr, tmX, tmR, tmDx, tmT, tmSq, tmG, kp);
   });
@@ -1361,10 +1363,11 @@ static int gdn_bwd_fused_launch(const void* g_bf16, const void* x_bf16, const vo
 #define GDN_BWD_LAUNCH(...)                                                                                     \
   do {                                                                                                          \
     auto kfn = __VA_ARGS__;                                                                                     \
-    static bool attr_set = false;                                                                               \
-    if (!attr_set) {                                                                                            \
+    static HpcOncePerDevice attr_once;                                                                               \
+    int attr_dev;                                                                               \
+    if (attr_once.need(&attr_dev)) {                                                                                            \
       HPC_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));                   \
-      attr_set = true;                                                                                          \
+      attr_once.mark(attr_dev);                                                                                          \
     }                                                                                                           \
     HPC_CUDA(hpc_launch_pdl(kfn, dim3(grid), dim3(G_THREADS), smem, st, tmGr, tmX, tmR, tmDx, tmG, kp));        \
   } while (0)

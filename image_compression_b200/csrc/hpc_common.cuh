@@ -90,6 +90,21 @@ static inline bool hpc_aligned16(const void* p) { return (reinterpret_cast<uintp
 // number of SMs of the current device (cached per thread)
 int hpc_num_sms();
 
+// One-time set-up that CUDA keeps PER DEVICE (cudaFuncSetAttribute: the opt-in dynamic shared memory size belongs to the
+// function on one device).  A process-wide `static bool` would skip every device after the first when one process
+// drives several GPUs (nn.DataParallel, a test that switches devices) and the launch there would fail with
+// "invalid argument".  One bit per device ordinal; racing threads at worst repeat the idempotent set-up.
+struct HpcOncePerDevice {
+  unsigned long long bits[4] = {0, 0, 0, 0};          // ordinals 0..255
+  bool need(int* dev) {
+    if (cudaGetDevice(dev) != cudaSuccess || *dev < 0 || *dev >= 256) { *dev = -1; return true; }   // unknown: always set
+    return !((__atomic_load_n(&bits[*dev >> 6], __ATOMIC_ACQUIRE) >> (*dev & 63)) & 1ull);
+  }
+  void mark(int dev) {
+    if (dev >= 0) __atomic_fetch_or(&bits[dev >> 6], 1ull << (dev & 63), __ATOMIC_RELEASE);
+  }
+};
+
 // ---------------------------------------------------------------------------------------
 // low-precision element access (T = float or __nv_bfloat16)
 // ---------------------------------------------------------------------------------------

@@ -451,22 +451,24 @@ template <int BLOCK_N>
 static int launch_fwd(const CUtensorMap& tmA, const CUtensorMap& tmB, const FwdKParams& kp, bool pair, cudaStream_t st) {
   if (pair) {
     using Cfg = FwdCfg<BLOCK_N, 2>;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static HpcOncePerDevice attr_once;
+    int attr_dev;
+    if (attr_once.need(&attr_dev)) {
       HPC_CUDA(cudaFuncSetAttribute(igemm_fwd_umma_pair_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     Cfg::SMEM_BYTES));
-      attr_set = true;
+      attr_once.mark(attr_dev);
     }
     const int pairs = (kp.tiles_per_phase + 1) / 2 * kp.nphases, tpcs = hpc_num_sms() / 2;
     const int grid = 2 * (pairs < tpcs ? pairs : tpcs);
     HPC_CUDA(hpc_launch_pdl(igemm_fwd_umma_pair_kernel<BLOCK_N>, dim3(grid), dim3(FW_THREADS), Cfg::SMEM_BYTES, st, tmA, tmB, kp));
   } else {
     using Cfg = FwdCfg<BLOCK_N, 1>;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static HpcOncePerDevice attr_once;
+    int attr_dev;
+    if (attr_once.need(&attr_dev)) {
       HPC_CUDA(cudaFuncSetAttribute(igemm_fwd_umma_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     Cfg::SMEM_BYTES));
-      attr_set = true;
+      attr_once.mark(attr_dev);
     }
     const int work = kp.total_tiles * kp.ksplit;
     const int grid = work < hpc_num_sms() ? work : hpc_num_sms();
@@ -985,11 +987,12 @@ int hpc_igemm_wgrad_umma(const hpc_igemm_wgrad_params* p, hpc_stream_t stream) {
     if (want < 0) { const char* e = getenv("HPC_WG_EPI_SMEM"); want = (e && e[0] == '0') ? 0 : 1; }
     local.epi_smem = want && 256 * (p->Cc * 4 + 16) <= local.stages * (4 + local.cchunks) * WG_ATOM_BYTES;
   }
-  static bool attr_set = false;
-  if (!attr_set) {
+  static HpcOncePerDevice attr_once;
+  int attr_dev;
+  if (attr_once.need(&attr_dev)) {
     HPC_CUDA(cudaFuncSetAttribute(igemm_wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   WG_MAX_STAGES * 7 * WG_ATOM_BYTES + 1024 + 256));
-    attr_set = true;
+    attr_once.mark(attr_dev);
   }
   auto st = (cudaStream_t)stream;
   HpcProfScope prof(HPC_PROF_IGEMM_WGRAD, 2.0 * p->N * p->GH * p->GW * (double)local.ntaps * p->R * p->Cc, stream);

@@ -576,12 +576,13 @@ ssim_bwd_filter_rb_kernel(const float* __restrict__ img1, const float* __restric
 }
 
 static int ssim_rb_attrs() {
-  static bool done = false;
-  if (!done) {
+  static HpcOncePerDevice once;
+  int dev;
+  if (once.need(&dev)) {
     HPC_CUDA(cudaFuncSetAttribute(ssim_level_rb_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, S2_SMEM_FWD));
     HPC_CUDA(cudaFuncSetAttribute(ssim_level_rb_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, S2_SMEM_FWD));
     HPC_CUDA(cudaFuncSetAttribute(ssim_bwd_filter_rb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, S2_SMEM_BWD));
-    done = true;
+    once.mark(dev);
   }
   return HPC_OK;
 }

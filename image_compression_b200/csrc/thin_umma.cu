@@ -333,10 +333,11 @@ conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_consta
 template <int CW>
 int launch_t1(const CUtensorMap& tmB, const CUtensorMap& tmOut, const CUtensorMap& tmSq, const T1Params& kp, cudaStream_t st) {
   using Cfg = T1Cfg<CW>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static HpcOncePerDevice attr_once;
+  int attr_dev;
+  if (attr_once.need(&attr_dev)) {
     HPC_CUDA(cudaFuncSetAttribute(conv_c3_umma_kernel<CW>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
-    attr_set = true;
+    attr_once.mark(attr_dev);
   }
   const int grid = kp.total_tiles < hpc_num_sms() ? kp.total_tiles : hpc_num_sms();
   HPC_CUDA(hpc_launch_pdl(conv_c3_umma_kernel<CW>, dim3(grid), dim3(T1_THREADS), Cfg::SMEM, st, tmB, tmOut, tmSq, kp));
@@ -566,10 +567,11 @@ deconv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
 template <int CW>
 int launch_t2(const CUtensorMap& tmA, const CUtensorMap& tmB, const T2Params& kp, cudaStream_t st) {
   using Cfg = T2Cfg<CW>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static HpcOncePerDevice attr_once;
+  int attr_dev;
+  if (attr_once.need(&attr_dev)) {
     HPC_CUDA(cudaFuncSetAttribute(deconv_c3_umma_kernel<CW>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
-    attr_set = true;
+    attr_once.mark(attr_dev);
   }
   const int grid = kp.total_tiles < hpc_num_sms() ? kp.total_tiles : hpc_num_sms();
   HPC_CUDA(hpc_launch_pdl(deconv_c3_umma_kernel<CW>, dim3(grid), dim3(T2_THREADS), Cfg::SMEM, st, tmA, tmB, kp));
@@ -839,11 +841,12 @@ int hpc_wgrad_c3_umma(const void* wide_nhwc_bf16, const float* thin_nchw, int N,
   auto st = (cudaStream_t)stream;
 #define LAUNCH_T3(CW_)                                                                                               \
   do {                                                                                                               \
-    static bool attr_set = false;                                                                                    \
-    if (!attr_set) {                                                                                                 \
+    static HpcOncePerDevice attr_once;                                                                                    \
+    int attr_dev;                                                                                    \
+    if (attr_once.need(&attr_dev)) {                                                                                                 \
       HPC_CUDA(cudaFuncSetAttribute(wgrad_c3_umma_kernel<CW_>, cudaFuncAttributeMaxDynamicSharedMemorySize,          \
                                     T3Cfg<CW_>::SMEM));                                                              \
-      attr_set = true;                                                                                               \
+      attr_once.mark(attr_dev);                                                                                               \
     }                                                                                                                \
     HPC_CUDA(hpc_launch_pdl(wgrad_c3_umma_kernel<CW_>, dim3(kp.nsplits), dim3(T3_THREADS), T3Cfg<CW_>::SMEM, st, tmW, kp)); \
   } while (0)
