@@ -51,28 +51,43 @@ struct FwdKParams {
   EpiArgs epi;
 };
 
-template <int BLOCK_N, int NCTA>
+// MT = M tiles per CTA and work item (CTA-pair kernel only).  MT == 2: a CTA holds TWO 128-pixel tiles per stage and both
+// of its accumulators belong to the same work item, so every weight box is used for twice the rows.  ncu on the
+// 64x64x64-pixel 5x5 layer (r02p): 4.40 GB cross the L2 -> SM crossbar in 408 us = 10.8 TB/s, the chip's L2 output cap,
+// with the tensor pipe 63 % busy -- the MT == 1 pair kernel is bound by operand bytes, 43 % of them weights.  MT == 2
+// halves the weight bytes per flop (4.40 -> 3.46 GB) at the price of an epilogue that no longer overlaps the next
+// tile's MMAs (TMEM holds 2 x 256 columns: both are in use).
+template <int BLOCK_N, int NCTA, int MT = 1>
 struct FwdCfg {
-  static constexpr int A_BYTES = FW_BM * FW_BK * 2;        // 16 KB
+  static_assert(MT == 1 || NCTA == 2, "two M tiles per CTA: CTA-pair kernel only");
+  static constexpr int A_BYTES = FW_BM * FW_BK * 2;        // 16 KB per M tile
   static constexpr int B_BYTES = (BLOCK_N / NCTA) * FW_BK * 2;   // a CTA of a pair holds half of the weight tile
-  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGE_BYTES = MT * A_BYTES + B_BYTES;
   // CTA-pair kernel: one [128 rows x (BLOCK_N bf16 + 16 B pad)] output staging tile (rows leave as single bulk copies)
   static constexpr int STG_PITCH = BLOCK_N * 2 + 16;
   static constexpr int STG_BYTES = NCTA == 2 ? FW_BM * STG_PITCH : 0;
-  static constexpr int FIXED_BYTES = 1024 /*align*/ + 256 /*barriers*/ + 1024 /*bias*/;
+  // MT == 2 needs every byte for its 4th stage (C = 192: 4 x 44 KB + 50 KB staging + 1 KB = 227 KB exactly): no
+  // alignment slack (the kernel traps if the dynamic shared memory window is not 1 KB aligned) and a bias area of
+  // BLOCK_N floats
+  static constexpr int ALIGN_SLACK = MT == 2 ? 0 : 1024;
+  static constexpr int BIAS_BYTES = MT == 2 ? BLOCK_N * 4 : 1024;
+  static constexpr int FIXED_BYTES = ALIGN_SLACK + 256 /*barriers*/ + BIAS_BYTES;
   static constexpr int BUDGET = NCTA == 2 ? (232448 - FIXED_BYTES - STG_BYTES) : 200 * 1024;
   static constexpr int STAGES = (BUDGET / STAGE_BYTES) > 8 ? 8 : (BUDGET / STAGE_BYTES);
   static constexpr int ACC_STRIDE = BLOCK_N <= 32 ? 32 : (BLOCK_N <= 64 ? 64 : (BLOCK_N <= 128 ? 128 : 256));
   static constexpr int TMEM_COLS = 2 * ACC_STRIDE;          // 64..512, power of two
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + FIXED_BYTES + STG_BYTES;
+  static_assert(SMEM_BYTES <= 232448, "shared memory budget");
+  static_assert((2 * STAGES + 4) * 8 + 4 <= 256, "barrier area");
 };
 
 // Work item `w` of the persistent loop -> (phase, tile origin).  NCTA == 1: w is a tile.  NCTA == 2: w is a PAIR of
 // consecutive tiles of one phase (so both CTAs run the same tap sequence) and `rank` picks the tile; a phase with an
-// odd tile count ends in a phantom tile whose batch origin n0 >= N (TMA zero fill, no rows stored).
-template <int NCTA>
-__device__ __forceinline__ void tile_coords(const FwdKParams& p, int ph, int idx, int rank, int& n0, int& i0, int& j0) {
-  int r = idx * NCTA + rank;
+// odd tile count ends in a phantom tile whose batch origin n0 >= N (TMA zero fill, no rows stored).  MT == 2: w is a
+// group of FOUR consecutive tiles, two per CTA.
+template <int NCTA, int MT = 1>
+__device__ __forceinline__ void tile_coords(const FwdKParams& p, int ph, int idx, int rank, int& n0, int& i0, int& j0, int m = 0) {
+  int r = (idx * MT + m) * NCTA + rank;         // MT == 2: accumulator m of the pair = tiles (2 m, 2 m + 1) of the item's four
   const int tj = r % p.tiles_w; r /= p.tiles_w;
   const int ti = r % p.tiles_h; r /= p.tiles_h;
   n0 = r * p.nb; i0 = ti * p.th; j0 = tj * p.tw;
@@ -200,14 +215,18 @@ __device__ __forceinline__ void epilogue8(const EpiArgs& e, const float* acc, in
   if (e.out_nrm_lp && (e.epi == HPC_EPI_GDN || e.epi == HPC_EPI_IGDN)) store8_bf16(e.out_nrm_lp, o, nrm);
 }
 
-template <int BLOCK_N, int NCTA>
+template <int BLOCK_N, int NCTA, int MT>
 __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const FwdKParams& p) {
-  using Cfg = FwdCfg<BLOCK_N, NCTA>;
+  using Cfg = FwdCfg<BLOCK_N, NCTA, MT>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1 KB aligned; pointer arithmetic keeps the
                                                                                   // shared address space (LDS/STS, not generic LD/ST)
-  uint8_t* smem_a = smem;                                  // STAGES x 16 KB
-  uint8_t* smem_b = smem + Cfg::STAGES * Cfg::A_BYTES;     // STAGES x B_BYTES (multiples of 1 KB)
+  if (Cfg::ALIGN_SLACK == 0 && smem != smem_raw) {         // no slack budgeted: the window itself must be aligned
+    if (threadIdx.x == 0) printf("hpcodec: igemm_fwd (MT=2): dynamic shared memory window not 1 KB aligned\n");
+    __trap();
+  }
+  uint8_t* smem_a = smem;                                  // STAGES x MT x 16 KB
+  uint8_t* smem_b = smem + Cfg::STAGES * MT * Cfg::A_BYTES;   // STAGES x B_BYTES (multiples of 1 KB)
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
   uint64_t* full_bar = bars;                    // [STAGES]  TMA -> MMA     (pair: the leader's collects both CTAs)
   uint64_t* empty_bar = bars + Cfg::STAGES;     // [STAGES]  MMA -> TMA     (pair: commit multicast to both CTAs)
@@ -215,12 +234,12 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
   uint64_t* tempty_bar = tfull_bar + 2;         // [2]       epilogue -> MMA (pair: both CTAs arrive at the leader's)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
   float* bias_s = reinterpret_cast<float*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256);   // bias staged once per CTA
-  uint8_t* stg = smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256 + 1024;                        // output staging (pair kernel)
+  uint8_t* stg = smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256 + Cfg::BIAS_BYTES;             // output staging (pair kernel)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int rank = NCTA == 2 ? (int)cluster_ctarank() : 0;
   const int worker = blockIdx.x / NCTA, nworkers = gridDim.x / NCTA;       // CTA (or CTA pair) index
-  const int per_phase = NCTA == 1 ? p.tiles_per_phase : (p.tiles_per_phase + 1) / 2;
+  const int per_phase = (p.tiles_per_phase + NCTA * MT - 1) / (NCTA * MT);
   const int ksplit = NCTA == 1 ? p.ksplit : 1;              // split-K for grids of a few tiles (single-CTA kernel only)
   const int total_work = p.interleave ? (per_phase + nworkers - 1) / nworkers * nworkers * p.nphases
                                       : per_phase * p.nphases * ksplit;
@@ -248,12 +267,14 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
     // ================================ TMA producer ================================
     // The whole warp runs the loop; lane 0 issues the activation box and lane 1 the weight box of a stage (a TMA
     // instruction costs its issuing thread ~100+ cycles, so the boxes of one stage are issued from different lanes).
-    if (lane < 2) {
+    if (lane < 1 + MT) {
+      constexpr uint32_t kIssuers = (1u << (1 + MT)) - 1;
+      const int mt = lane == 2 ? 1 : 0;          // lane 0: pixels of M tile 0, lane 1: weights, lane 2: pixels of M tile 1
       int stage = 0; uint32_t phase = 0;
       for (int w = worker; w < total_work; w += nworkers) {
         int ph, idx, n0, i0, j0;
         if (!work_item(p, w, worker, nworkers, per_phase, ksplit, ph, idx)) continue;
-        tile_coords<NCTA>(p, ph, idx, rank, n0, i0, j0);
+        tile_coords<NCTA, MT>(p, ph, idx, rank, n0, i0, j0, mt);
         const hpc_igemm_phase P = p.phase[ph];
         const int ksteps = P.ntaps * p.kchunks, sp = w % ksplit;
         const int ks0 = ksteps * sp / ksplit, ks1 = ksteps * (sp + 1) / ksplit;
@@ -264,15 +285,15 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
             mbar_wait(&empty_bar[stage], phase ^ 1);
             if (NCTA == 1) {
               if (lane == 0) mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
-              __syncwarp(3u);
+              __syncwarp(kIssuers);
               if (lane == 0) tma_load_4d(smem_a + stage * Cfg::A_BYTES, &tmA, &full_bar[stage], c * FW_BK, cw, chh, n0);
               else tma_load_2d(smem_b + stage * Cfg::B_BYTES, &tmB, &full_bar[stage], c * FW_BK, t * p.Co);
             } else {
               // each CTA loads its own pixels and its half of the output channels; all bytes complete on the leader
               if (rank == 0 && lane == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::STAGE_BYTES);
-              __syncwarp(3u);
+              __syncwarp(kIssuers);
               const uint32_t lead = mapa_u32(smem_u32(&full_bar[stage]), 0);
-              if (lane == 0) tma_load_4d_pair(smem_a + stage * Cfg::A_BYTES, &tmA, lead, c * FW_BK, cw, chh, n0);
+              if (lane != 1) tma_load_4d_pair(smem_a + (stage * MT + mt) * Cfg::A_BYTES, &tmA, lead, c * FW_BK, cw, chh, n0);
               else tma_load_2d_pair(smem_b + stage * Cfg::B_BYTES, &tmB, lead, c * FW_BK, t * p.Co + rank * (BLOCK_N / 2));
             }
             if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
@@ -296,18 +317,21 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
         const int kall = p.phase[ph].ntaps * p.kchunks, sp = w % ksplit;
         const int ksteps = kall * (sp + 1) / ksplit - kall * sp / ksplit;
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);     // epilogue(s) have drained this accumulator
+        if (MT == 2) mbar_wait(&tempty_bar[1], acc_phase ^ 1);        // (acc == 0 here: both belong to this item)
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * Cfg::ACC_STRIDE;
         for (int ks = 0; ks < ksteps; ++ks) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          const uint64_t ad = adesc0 + (uint64_t)(stage * (Cfg::A_BYTES >> 4));
+          const uint64_t ad = adesc0 + (uint64_t)(stage * (MT * Cfg::A_BYTES >> 4));
           const uint64_t bd = bdesc0 + (uint64_t)(stage * (Cfg::B_BYTES >> 4));
           if (elect_one()) {
 #pragma unroll
             for (int k = 0; k < FW_BK / 16; ++k) {
               if (NCTA == 1) mma_bf16_ss(d_tmem, ad + 2 * k, bd + 2 * k, idesc, (ks | k) != 0);
               else mma_bf16_ss_pair(d_tmem, ad + 2 * k, bd + 2 * k, idesc, (ks | k) != 0);
+              if (MT == 2)                     // second M tile of this CTA pair against the same weight half-tiles
+                mma_bf16_ss_pair(d_tmem + Cfg::ACC_STRIDE, ad + (Cfg::A_BYTES >> 4) + 2 * k, bd + 2 * k, idesc, (ks | k) != 0);
             }
             // frees the smem stage (in both CTAs) when these MMAs retire
             if (NCTA == 1) mma_commit(&empty_bar[stage]); else mma_commit_pair(&empty_bar[stage]);
@@ -317,9 +341,11 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
         }
         if (elect_one()) {
           if (NCTA == 1) mma_commit(&tfull_bar[acc]); else mma_commit_pair(&tfull_bar[acc]);   // accumulator complete
+          if (MT == 2) mma_commit_pair(&tfull_bar[1]);
         }
         __syncwarp();
-        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        if (MT == 2) acc_phase ^= 1;
+        else if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
   } else {
@@ -332,8 +358,10 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
     for (int w = worker; w < total_work; w += nworkers) {
       int ph, idx, n0, i0, j0;
       if (!work_item(p, w, worker, nworkers, per_phase, ksplit, ph, idx)) continue;
-      tile_coords<NCTA>(p, ph, idx, rank, n0, i0, j0);
       const hpc_igemm_phase P = p.phase[ph];
+#pragma unroll 1
+      for (int m = 0; m < MT; ++m) {            // MT == 2: accumulator m holds M tile m of this work item
+      tile_coords<NCTA, MT>(p, ph, idx, rank, n0, i0, j0, m);
       const int jl = row % p.tw, il = (row / p.tw) % p.th, nl = row / (p.tw * p.th);
       const int n = n0 + nl, i = i0 + il, j = j0 + jl;
       const int oh = i * p.os + P.oh_off, ow = j * p.os + P.ow_off;
@@ -396,6 +424,7 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
         else mbar_arrive_cluster(mapa_u32(smem_u32(&tempty_bar[acc]), 0));
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
     }
     if (NCTA == 2 && p.stage_out) bulk_group_wait_all();
   }
@@ -410,7 +439,7 @@ template <int BLOCK_N>
 __global__ void __launch_bounds__(FW_THREADS, 1)
 igemm_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                       const __grid_constant__ FwdKParams p) {
-  igemm_fwd_body<BLOCK_N, 1>(tmA, tmB, p);
+  igemm_fwd_body<BLOCK_N, 1, 1>(tmA, tmB, p);
 }
 
 // CTA-pair version: cluster of two CTAs = the two SMs of a TPC, one tcgen05.mma.cta_group::2 of M = 256 per k-step.
@@ -420,7 +449,15 @@ template <int BLOCK_N>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FW_THREADS, 1)
 igemm_fwd_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                            const __grid_constant__ FwdKParams p) {
-  igemm_fwd_body<BLOCK_N, 2>(tmA, tmB, p);
+  igemm_fwd_body<BLOCK_N, 2, 1>(tmA, tmB, p);
+}
+
+// CTA pair, two M tiles per CTA (FwdCfg): M = 512 pixels per work item against one pass over the weights.
+template <int BLOCK_N>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FW_THREADS, 1)
+igemm_fwd_umma_pair2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                            const __grid_constant__ FwdKParams p) {
+  igemm_fwd_body<BLOCK_N, 2, 2>(tmA, tmB, p);
 }
 
 // Second pass of a split-K launch: sums the K slices of every output pixel in a fixed order and applies the bias /
@@ -448,8 +485,20 @@ splitk_epilogue_kernel(const float* __restrict__ ws, int ksplit, int64_t out_ele
 // ---------------------------------------------------------------------------------------
 
 template <int BLOCK_N>
-static int launch_fwd(const CUtensorMap& tmA, const CUtensorMap& tmB, const FwdKParams& kp, bool pair, cudaStream_t st) {
-  if (pair) {
+static int launch_fwd(const CUtensorMap& tmA, const CUtensorMap& tmB, const FwdKParams& kp, bool pair, int mt, cudaStream_t st) {
+  if (pair && mt == 2) {
+    using Cfg = FwdCfg<BLOCK_N, 2, 2>;
+    static HpcOncePerDevice attr_once;
+    int attr_dev;
+    if (attr_once.need(&attr_dev)) {
+      HPC_CUDA(cudaFuncSetAttribute(igemm_fwd_umma_pair2_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    Cfg::SMEM_BYTES));
+      attr_once.mark(attr_dev);
+    }
+    const int items = (kp.tiles_per_phase + 3) / 4 * kp.nphases, tpcs = hpc_num_sms() / 2;
+    const int grid = 2 * (items < tpcs ? items : tpcs);
+    HPC_CUDA(hpc_launch_pdl(igemm_fwd_umma_pair2_kernel<BLOCK_N>, dim3(grid), dim3(FW_THREADS), Cfg::SMEM_BYTES, st, tmA, tmB, kp));
+  } else if (pair) {
     using Cfg = FwdCfg<BLOCK_N, 2>;
     static HpcOncePerDevice attr_once;
     int attr_dev;
@@ -559,6 +608,13 @@ int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
   }
 
   const bool pair = fwd_use_pair(kp);
+  // two M tiles per CTA (FwdCfg): where every CTA pair gets at least one group of four tiles.  HPC_FWD_MT=1 disables.
+  int mt = 1;
+  {
+    static int mode = -1;
+    if (mode < 0) { const char* e = getenv("HPC_FWD_MT"); mode = e ? atoi(e) : 2; }
+    if (pair && mode == 2 && p->Co == 192 && (kp.tiles_per_phase + 3) / 4 * kp.nphases >= hpc_num_sms() / 2) mt = 2;
+  }
   {  // staged bulk-copy epilogue: plain (bias) epilogue whose only output is the bf16 tensor; HPC_FWD_STAGE_OUT=0 disables
     static int want = -1;
     if (want < 0) { const char* e = getenv("HPC_FWD_STAGE_OUT"); want = (e && e[0] == '0') ? 0 : 1; }
@@ -576,7 +632,7 @@ int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
   {
     static int mode = -1;                        // HPC_FWD_INTERLEAVE=0: phase-major tile order everywhere (A/B measurements)
     if (mode < 0) { const char* e = getenv("HPC_FWD_INTERLEAVE"); mode = e ? atoi(e) : 1; }
-    const int per = pair ? (kp.tiles_per_phase + 1) / 2 : kp.tiles_per_phase;
+    const int per = pair ? (kp.tiles_per_phase + 2 * mt - 1) / (2 * mt) : kp.tiles_per_phase;
     const int workers = pair ? hpc_num_sms() / 2 : hpc_num_sms();
     // whole rounds of (tile x all phases) per worker: only where that padding costs < 4 % (measured: 64x64 -> 128x128
     // transposed conv 463 -> 444 us, but 32x32 -> 64x64 with 3.46 rounds 120 -> 130 us)
@@ -608,10 +664,10 @@ int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
                     2.0 * p->N * p->GH * p->GW * (double)ntaps_total_all(p) * p->Ci * p->Co, stream);
   int rc;
   switch (p->Co) {
-    case 64: rc = launch_fwd<64>(tmA, tmB, kp, pair, st); break;
-    case 128: rc = launch_fwd<128>(tmA, tmB, kp, pair, st); break;
-    case 192: rc = launch_fwd<192>(tmA, tmB, kp, pair, st); break;
-    default: rc = launch_fwd<256>(tmA, tmB, kp, pair, st); break;
+    case 64: rc = launch_fwd<64>(tmA, tmB, kp, pair, 1, st); break;
+    case 128: rc = launch_fwd<128>(tmA, tmB, kp, pair, 1, st); break;
+    case 192: rc = launch_fwd<192>(tmA, tmB, kp, pair, mt, st); break;
+    default: rc = launch_fwd<256>(tmA, tmB, kp, pair, 1, st); break;
   }
   if (rc || kp.ksplit == 1) return rc;
   const int64_t units = kp.out_elems / 8;

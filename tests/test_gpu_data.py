@@ -87,7 +87,8 @@ def test_c_abi_strides_guards_and_baseline_batch():
     g = torch.from_numpy(rng.randint(0, 256, size=(2, 5, 6, 1)).astype(np.uint8)).to(DEV)
     o1 = torch.empty(2, 1, 5, 6, dtype=torch.float32, device=DEV)
     _lib.check(call(ptr(g), 30, 6, 2, 5, 6, None, None, 2, 1, 5, 6, None, None, ptr(o1)))
-    assert torch.equal(o1, g.permute(0, 3, 1, 2).float() / 255.0)
+    # (computed on the CPU like the reference's transforms: torch's CUDA division by a scalar multiplies by 1/255 instead)
+    assert torch.equal(o1.cpu(), g.cpu().permute(0, 3, 1, 2).float() / 255.0)
     for args in ((ptr(g), 30, 6, 2, 5, 6, None, None, 2, 1, 6, 6, None, None, ptr(o1)),        # output taller than source
                  (ptr(g), 30, 5, 2, 5, 6, None, None, 2, 1, 5, 6, None, None, ptr(o1)),        # row stride < row
                  (ptr(g), 30, 6, 1, 5, 6, None, None, 2, 1, 5, 6, None, None, ptr(o1)),        # 1 source, 2 outputs, no index

@@ -15,7 +15,7 @@ pytestmark = pytest.mark.gpu
 @pytest.mark.parametrize("recipe", ["psnr_256", "ssim_64"])
 def test_training_step_on_a_second_device_matches_the_first(recipe):
     out = []
-    x0 = torch.rand(2, 3, 128, 128, generator=torch.Generator().manual_seed(1))
+    x0 = torch.rand(2, 3, 192, 192, generator=torch.Generator().manual_seed(1))
     for dev in ("cuda:0", "cuda:1"):
         with torch.cuda.device(dev):
             model, params, _ = make_pair(recipe, 192, device=dev)

@@ -46,10 +46,14 @@ def test_forward_and_dgrad(transposed, k, s, N, H, W, C):
     _cmp(out, ref)
 
 
-@pytest.mark.parametrize("transposed,N,H,W", [(False, 5, 128, 96), (True, 3, 56, 72), (False, 3, 130, 66)])
+@pytest.mark.parametrize("transposed,N,H,W", [(False, 5, 128, 96), (True, 3, 56, 72), (False, 3, 130, 66),
+                                              (False, 10, 128, 128), (True, 5, 64, 64), (False, 7, 136, 168)])
 def test_forward_large_grids_use_cta_pairs(transposed, N, H, W):
     """>= 148 tiles: the cta_group::2 kernel (CTA pairs, half of the weight tile per CTA).  The odd tile counts
-    exercise the phantom tile at the end of a phase / of the grid; the SIMT engine is the checker."""
+    exercise the phantom tile at the end of a phase / of the grid; the SIMT engine is the checker.
+    >= 74 groups of four tiles (cases 2, 4, 5, 6): two M tiles per CTA (igemm_fwd_umma_pair2_kernel), with 1-3 phantom
+    tiles at the end of a phase in cases 2 and 6; both the direct (fp32 output) and the staged bulk-copy (bf16 output
+    only) epilogues."""
     torch.manual_seed(4)
     C = 192
     spec = hp.ConvSpec(transposed, C, C, 5, 2)
@@ -57,6 +61,12 @@ def test_forward_large_grids_use_cta_pairs(transposed, N, H, W):
     w = (torch.randn(C, C, 5, 5, device=DEV) / (C * 25) ** 0.5)
     b = torch.randn(C, device=DEV)
     out, ref = _both(lambda: spec.forward(x, w, b, _lib.EPI_LINEAR, want_f32=True))
+    _cmp(out, ref)
+    out, ref = _both(lambda: spec.forward(x, w, b, _lib.EPI_LINEAR))
+    _cmp(out, ref)
+    OH, OW = spec.out_hw(H, W)
+    g = torch.randn(N, OH, OW, C, device=DEV).to(torch.bfloat16)
+    out, ref = _both(lambda: spec.dgrad(g, w, (H, W)))
     _cmp(out, ref)
 
 
@@ -83,7 +93,8 @@ def test_forced_engine_variants_in_a_subprocess():
     both variants must agree with the SIMT checker on the whole forward/dgrad/epilogue test set."""
     import os, subprocess, sys
     here = os.path.dirname(os.path.abspath(__file__))
-    for env in ({"HPC_FWD_PAIR": "1"}, {"HPC_FWD_PAIR": "0", "HPC_FWD_KSPLIT": "0", "HPC_FWD_INTERLEAVE": "0"}):
+    for env in ({"HPC_FWD_PAIR": "1"}, {"HPC_FWD_PAIR": "0", "HPC_FWD_KSPLIT": "0", "HPC_FWD_INTERLEAVE": "0"},
+                {"HPC_FWD_MT": "1"}):
         r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(here, "test_gpu_umma.py"), "-x", "-q", "-k",
                             "forward_and_dgrad or epilogues or large_grids"], env=dict(os.environ, **env),
                            capture_output=True, text=True, timeout=900)
