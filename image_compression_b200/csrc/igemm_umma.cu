@@ -690,16 +690,30 @@ int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
 constexpr int WG_THREADS = 192;
 constexpr int WG_P = 64;                       // pixels per stage (K block)
 constexpr int WG_ATOM_BYTES = WG_P * 128;      // 8 KB: 64 pixels x 64 bf16
-constexpr int WG_MAX_STAGES = 4;               // 4 x 56 KB for C = 192 (the kernel is bound by bytes in flight x latency)
+constexpr int WG_MAX_STAGES = 6;               // C = 192: 5 x 42 KB with shared `lo` boxes, 4 x 56 KB without
 constexpr int WG_MAX_UNITS = 32;
 
-struct WgUnit { int phase, atom_begin, natoms; };   // atoms index the phase's (tap, r-chunk) list
+// A unit = up to 4 atoms = up to four (tap, 64-row r-chunk) blocks of the result = two 128-row accumulators.
+// Its `lo` operand arrives in up to 4 TMA boxes.  ncu (r02p, 64x64x64-pixel layer): 4.53 GB cross the L2 -> SM
+// crossbar in 400 us = 11.3 TB/s, the chip's L2 output cap, with the tensor pipe 68 % busy: the kernel is bound by
+// operand bytes.  Taps of one phase that differ only in dh read the SAME pixels of `lo` one 8-pixel row apart, and
+// one row of an 8 x 8 K block is exactly one 1 KB swizzle group of the MN-major operand: atoms of the same
+// (dw, r-chunk) therefore share ONE box of 8 + (dh_max - dh_min) rows and their descriptors start 1 KB apart.
+// 4 atoms = 18 KB of `lo` instead of 32 KB per stage (42 KB instead of 56 KB with the 24 KB of `hi`).
+struct WgUnit {
+  uint8_t phase, natoms, nloads, pad;
+  uint8_t tap[4], rc[4];          // atom a: result block (tap[a], rows rc[a]*64 ..)
+  uint8_t aoff[4];                // atom a starts aoff[a] KB into the stage's `lo` area
+  uint8_t lrc[4], lrows[4], loff[4];   // box l: r-chunk, pixel rows (th .. th+2), KB offset in the `lo` area
+  int8_t ldw[4], ldh[4];          // box l: its tap shift (dw, smallest dh)
+};
 
 struct WgKParams {
   int N, GH, GW, R, HH, HW, Cc, hs;
   int tw, th, nb, tiles_w, tiles_h, tiles_n, kblocks;
   int nunits, nsplits, rchunks, cchunks, ntaps;
   int stages;
+  int a_bytes;                                 // `lo` area of a stage (largest unit)
   int epi_smem;                                // stage the accumulators in shared memory and bulk-copy whole rows out
   hpc_igemm_phase phase[HPC_MAX_PHASES];
   int dh[HPC_MAX_TAPS], dw[HPC_MAX_TAPS];
@@ -708,12 +722,13 @@ struct WgKParams {
 };
 
 __global__ void __launch_bounds__(WG_THREADS, 1)
-igemm_wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmLo, const __grid_constant__ CUtensorMap tmHi,
+igemm_wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmLo, const __grid_constant__ CUtensorMap tmLo1,
+                        const __grid_constant__ CUtensorMap tmLo2, const __grid_constant__ CUtensorMap tmHi,
                         const __grid_constant__ WgKParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1 KB aligned; pointer arithmetic keeps the
                                                                                   // shared address space (LDS/STS, not generic LD/ST)
-  const int stage_bytes = (4 + p.cchunks) * WG_ATOM_BYTES;
+  const int stage_bytes = p.a_bytes + p.cchunks * WG_ATOM_BYTES;
   const int nstages = p.stages;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + nstages * stage_bytes);
   uint64_t* full_bar = bars;
@@ -730,7 +745,7 @@ igemm_wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmLo, const __grid_c
   const int nkb = kb1 - kb0;
 
   if (warp == 0 && lane == 0) {
-    prefetch_tmap(&tmLo);
+    prefetch_tmap(&tmLo); prefetch_tmap(&tmLo1); prefetch_tmap(&tmLo2);
     prefetch_tmap(&tmHi);
     for (int s = 0; s < nstages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     mbar_init(done_bar, 1);
@@ -745,17 +760,16 @@ igemm_wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmLo, const __grid_c
   pdl_launch_dependents();
 
   if (warp == 0) {
-    // Producer: the whole warp runs the loop and lane l issues box l of the stage (up to 4 `lo` atoms + Cc/64 `hi`
+    // Producer: the whole warp runs the loop and lane l issues box l of the stage (up to 4 `lo` boxes + Cc/64 `hi`
     // atoms), so the TMA instructions of a stage are issued in parallel instead of one after another by one thread.
     int stage = 0; uint32_t phase = 0;
-    const uint32_t tx = (uint32_t)(U.natoms + p.cchunks) * WG_ATOM_BYTES;
-    const bool is_lo = lane < U.natoms, is_hi = lane >= 4 && lane < 4 + p.cchunks;
-    int t = 0, rc = 0;
-    if (is_lo) {
-      const int atom = U.atom_begin + lane;
-      t = P.tap_begin + atom / p.rchunks; rc = atom % p.rchunks;
-    }
-    const int dwt = p.dw[t], dht = p.dh[t];
+    const bool is_lo = lane < U.nloads, is_hi = lane >= 4 && lane < 4 + p.cchunks;
+    uint32_t tx = (uint32_t)p.cchunks * WG_ATOM_BYTES;
+    for (int l = 0; l < U.nloads; ++l) tx += (uint32_t)U.lrows[l] * (uint32_t)(p.tw * p.nb) * 128u;
+    const int ll = is_lo ? lane : 0;
+    const int rc = U.lrc[ll], dwt = U.ldw[ll], dht = U.ldh[ll], extra = U.lrows[ll] - p.th;
+    const CUtensorMap* tml = extra == 0 ? &tmLo : (extra == 1 ? &tmLo1 : &tmLo2);
+    const int lo_off = U.loff[ll] * 1024;
     for (int kb = kb0; kb < kb1; ++kb) {
       int r = kb;
       const int tj = r % p.tiles_w; r /= p.tiles_w;
@@ -766,28 +780,39 @@ igemm_wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmLo, const __grid_c
       __syncwarp();
       uint8_t* sa = smem + stage * stage_bytes;
       if (is_lo)
-        tma_load_4d(sa + lane * WG_ATOM_BYTES, &tmLo, &full_bar[stage], rc * 64, j0 + dwt, i0 + dht, n0);
+        tma_load_4d(sa + lo_off, tml, &full_bar[stage], rc * 64, j0 + dwt, i0 + dht, n0);
       else if (is_hi)
-        tma_load_4d(sa + lane * WG_ATOM_BYTES, &tmHi, &full_bar[stage], (lane - 4) * 64, j0 * p.hs + P.ow_off,
-                    i0 * p.hs + P.oh_off, n0);
+        tma_load_4d(sa + p.a_bytes + (lane - 4) * WG_ATOM_BYTES, &tmHi, &full_bar[stage], (lane - 4) * 64,
+                    j0 * p.hs + P.ow_off, i0 * p.hs + P.oh_off, n0);
       if (++stage == nstages) { stage = 0; phase ^= 1; }
     }
   } else if (warp == 1) {
     if (lane == 0) {
       const uint32_t idesc = make_idesc_bf16(128, p.Cc, 1, 1);   // both operands MN-major
       const int nmma = (U.natoms + 1) / 2;
+      uint32_t a0off[2], a1off[2];
+#pragma unroll
+      for (int m = 0; m < 2; ++m) {
+        a0off[m] = (uint32_t)U.aoff[2 * m] * 1024u;
+        a1off[m] = 2 * m + 1 < U.natoms ? (uint32_t)(U.aoff[2 * m + 1] - U.aoff[2 * m]) * 1024u : 1024u;
+      }
       int stage = 0; uint32_t phase = 0;
       for (int kb = 0; kb < nkb; ++kb) {
         mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
         const uint32_t a_addr = smem_u32(smem + stage * stage_bytes);
-        const uint32_t b_addr = a_addr + 4 * WG_ATOM_BYTES;
+        const uint32_t b_addr = a_addr + p.a_bytes;
 #pragma unroll
         for (int ks = 0; ks < WG_P / 16; ++ks) {
           const uint64_t bd = make_smem_desc_sw128(b_addr + ks * 2048, WG_ATOM_BYTES, 1024);
-          for (int m = 0; m < nmma; ++m) {
-            const uint64_t ad = make_smem_desc_sw128(a_addr + m * 2 * WG_ATOM_BYTES + ks * 2048, WG_ATOM_BYTES, 1024);
-            mma_bf16_ss(tmem_base + m * 256, ad, bd, idesc, (kb | ks) != 0);
+#pragma unroll
+          for (int m = 0; m < 2; ++m) {
+            // rows 0..63 of the accumulator = atom 2m, rows 64..127 = atom 2m+1 (leading byte offset = their distance;
+            // an odd unit's missing atom reads one row group further: its rows are never stored)
+            if (m < nmma) {
+              const uint64_t ad = make_smem_desc_sw128(a_addr + a0off[m] + ks * 2048, a1off[m], 1024);
+              mma_bf16_ss(tmem_base + m * 256, ad, bd, idesc, (kb | ks) != 0);
+            }
           }
         }
         mma_commit(&empty_bar[stage]);
@@ -828,8 +853,7 @@ igemm_wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmLo, const __grid_c
     for (int m = 0; m < nmma; ++m) {
       const int a = 2 * m + row / 64;
       if (a < U.natoms) {
-        const int atom = U.atom_begin + a;
-        const int t = P.tap_begin + atom / p.rchunks, r = (atom % p.rchunks) * 64 + (row & 63);
+        const int t = U.tap[a], r = U.rc[a] * 64 + (row & 63);
         float* dst = p.ws + (((int64_t)split * p.ntaps + t) * p.R + r) * p.Cc;
         bulk_store_row(dst, smem + (size_t)(m * 128 + row) * pitch, (uint32_t)(p.Cc * 4));
       }
@@ -845,8 +869,7 @@ igemm_wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmLo, const __grid_c
     for (int m = 0; m < nmma; ++m) {
       const int a = 2 * m + row / 64;
       const bool valid = a < U.natoms;
-      const int atom = U.atom_begin + a;
-      const int t = P.tap_begin + atom / p.rchunks, r = (atom % p.rchunks) * 64 + (row & 63);
+      const int t = valid ? U.tap[a] : 0, r = (valid ? U.rc[a] : 0) * 64 + (row & 63);
       float* dst = p.ws + (((int64_t)split * p.ntaps + t) * p.R + r) * p.Cc;
       const uint32_t taddr = tmem_base + m * 256 + ((uint32_t)(q * 32) << 16);
       for (int c0 = 0; c0 < p.Cc; c0 += 16) {
@@ -971,16 +994,63 @@ static int wgrad_plan(const hpc_igemm_wgrad_params* p, WgKParams* kp) {
   memcpy(kp->phase, p->phase, sizeof(kp->phase));
   memcpy(kp->dh, p->dh, sizeof(kp->dh));
   memcpy(kp->dw, p->dw, sizeof(kp->dw));
-  int nu = 0, nt = 0;
+  // `lo` boxes shared between the taps of one (dw, r-chunk) that differ in dh (WgUnit): needs one 8-pixel row of the
+  // K block per 1 KB swizzle group.  HPC_WG_SHARE=0 keeps one box per atom (A/B measurements).
+  static int share_mode = -1;
+  if (share_mode < 0) { const char* e = getenv("HPC_WG_SHARE"); share_mode = (e && e[0] == '0') ? 0 : 1; }
+  const bool share = share_mode && kp->nb == 1 && kp->tw == 8 && kp->th == 8;
+  const int box_kb = kp->tw * kp->th * kp->nb * 128 / 1024;        // 8: a 64-pixel box
+  int nu = 0, nt = 0, amax = 0;
   for (int ph = 0; ph < p->nphases; ++ph) {
-    const int natoms = p->phase[ph].ntaps * kp->rchunks;
-    for (int a = 0; a < natoms; a += 4) {
-      HPC_REQUIRE(nu < WG_MAX_UNITS, HPC_ERR_UNSUPPORTED, "umma wgrad: too many work units");
-      kp->unit[nu].phase = ph; kp->unit[nu].atom_begin = a; kp->unit[nu].natoms = natoms - a < 4 ? natoms - a : 4;
-      ++nu;
+    const hpc_igemm_phase& P = p->phase[ph];
+    HPC_REQUIRE(P.ntaps >= 1 && P.tap_begin >= 0 && P.tap_begin + P.ntaps <= HPC_MAX_TAPS, HPC_ERR_BAD_SHAPE,
+                "umma wgrad: phase %d taps [%d, %d)", ph, P.tap_begin, P.tap_begin + P.ntaps);
+    int order[HPC_MAX_TAPS];                      // taps of the phase sorted by (dw, dh)
+    for (int k = 0; k < P.ntaps; ++k) {
+      const int t = P.tap_begin + k;
+      int q = k;
+      while (q > 0 && (p->dw[order[q - 1]] > p->dw[t] || (p->dw[order[q - 1]] == p->dw[t] && p->dh[order[q - 1]] > p->dh[t]))) {
+        order[q] = order[q - 1];
+        --q;
+      }
+      order[q] = t;
     }
-    nt += p->phase[ph].ntaps;
+    // atoms in (dw, r-chunk, dh) order, four per unit
+    int cur = -1, used = 0;                        // unit being filled, KB of its `lo` area in use
+    for (int g0 = 0; g0 < P.ntaps;) {
+      int g1 = g0;
+      while (g1 < P.ntaps && p->dw[order[g1]] == p->dw[order[g0]]) ++g1;
+      for (int rc = 0; rc < kp->rchunks; ++rc)
+        for (int k = g0; k < g1; ++k) {
+          const int t = order[k];
+          if (cur < 0 || kp->unit[cur].natoms == 4) {
+            HPC_REQUIRE(nu < WG_MAX_UNITS, HPC_ERR_UNSUPPORTED, "umma wgrad: too many work units");
+            cur = nu++;
+            kp->unit[cur].phase = (uint8_t)ph;
+            used = 0;
+          }
+          WgUnit& U = kp->unit[cur];
+          const int a = U.natoms++;
+          U.tap[a] = (uint8_t)t; U.rc[a] = (uint8_t)rc;
+          const int l = U.nloads - 1;
+          if (share && l >= 0 && U.lrc[l] == rc && U.ldw[l] == p->dw[t] && U.lrows[l] < kp->th + 2 &&
+              p->dh[t] == U.ldh[l] + (U.lrows[l] - kp->th) + 1) {
+            U.aoff[a] = (uint8_t)(U.loff[l] + (p->dh[t] - U.ldh[l]));      // one pixel row = 1 KB further into the same box
+            ++U.lrows[l];
+            used += 1;
+          } else {
+            const int n = U.nloads++;
+            U.lrc[n] = (uint8_t)rc; U.ldw[n] = (int8_t)p->dw[t]; U.ldh[n] = (int8_t)p->dh[t];
+            U.lrows[n] = (uint8_t)kp->th; U.loff[n] = (uint8_t)used; U.aoff[a] = (uint8_t)used;
+            used += box_kb;
+          }
+          if (used > amax) amax = used;
+        }
+      g0 = g1;
+    }
+    nt += P.ntaps;
   }
+  kp->a_bytes = amax * 1024;
   kp->nunits = nu; kp->ntaps = nt;
   int ns = hpc_num_sms() / nu;
   if (ns < 1) ns = 1;
@@ -1018,14 +1088,17 @@ int hpc_igemm_wgrad_umma(const hpc_igemm_wgrad_params* p, hpc_stream_t stream) {
               "umma wgrad: workspace too small (%zu < %zu)", p->workspace_bytes, need);
   HPC_REQUIRE(hpc_aligned16(p->workspace), HPC_ERR_BAD_ALIGNMENT, "umma wgrad: workspace must be 16B aligned");
   local.ws = (float*)p->workspace;
-  CUtensorMap tmLo, tmHi;
+  CUtensorMap tmLo, tmLo1, tmLo2, tmHi;
   {
     uint64_t dims[4] = {(uint64_t)p->R, (uint64_t)p->GW, (uint64_t)p->GH, (uint64_t)p->N};
     uint64_t strides[3] = {(uint64_t)p->R * 2, (uint64_t)p->GW * p->R * 2, (uint64_t)p->GH * p->GW * p->R * 2};
-    uint32_t box[4] = {64, (uint32_t)local.tw, (uint32_t)local.th, (uint32_t)local.nb};
     uint32_t estr[4] = {1, 1, 1, 1};
-    rc = make_tmap(&tmLo, p->lo, 4, dims, strides, box, estr);
-    if (rc) return rc;
+    CUtensorMap* maps[3] = {&tmLo, &tmLo1, &tmLo2};
+    for (int e = 0; e < 3; ++e) {               // boxes of th, th + 1, th + 2 pixel rows (shared by 1, 2, 3 taps)
+      uint32_t box[4] = {64, (uint32_t)local.tw, (uint32_t)(local.th + e), (uint32_t)local.nb};
+      rc = make_tmap(maps[e], p->lo, 4, dims, strides, box, estr);
+      if (rc) return rc;
+    }
   }
   {
     uint64_t dims[4] = {(uint64_t)p->Cc, (uint64_t)p->HW, (uint64_t)p->HH, (uint64_t)p->N};
@@ -1035,25 +1108,27 @@ int hpc_igemm_wgrad_umma(const hpc_igemm_wgrad_params* p, hpc_stream_t stream) {
     rc = make_tmap(&tmHi, p->hi, 4, dims, strides, box, estr);
     if (rc) return rc;
   }
-  local.stages = local.cchunks <= 3 ? WG_MAX_STAGES : 3;       // 224 KB for C = 192, 192 KB for C = 256
+  const int stage_bytes = local.a_bytes + local.cchunks * WG_ATOM_BYTES;
+  local.stages = (232448 - 1024 - 256) / stage_bytes;          // C = 192: 5 x 42 KB (shared boxes) or 4 x 56 KB
+  if (local.stages > WG_MAX_STAGES) local.stages = WG_MAX_STAGES;
+  HPC_REQUIRE(local.stages >= 2, HPC_ERR_UNSUPPORTED, "umma wgrad: a stage of %d bytes does not fit twice", stage_bytes);
   { const char* e = getenv("HPC_WG_STAGES"); if (e && atoi(e) >= 2 && atoi(e) <= local.stages) local.stages = atoi(e); }
-  const int smem_bytes = local.stages * (4 + local.cchunks) * WG_ATOM_BYTES + 1024 + 256;
+  const int smem_bytes = local.stages * stage_bytes + 1024 + 256;
   {  // staged epilogue when 256 padded rows fit in the operand stages (C <= 192); HPC_WG_EPI_SMEM=0 keeps direct stores
     static int want = -1;
     if (want < 0) { const char* e = getenv("HPC_WG_EPI_SMEM"); want = (e && e[0] == '0') ? 0 : 1; }
-    local.epi_smem = want && 256 * (p->Cc * 4 + 16) <= local.stages * (4 + local.cchunks) * WG_ATOM_BYTES;
+    local.epi_smem = want && 256 * (p->Cc * 4 + 16) <= local.stages * stage_bytes;
   }
   static HpcOncePerDevice attr_once;
   int attr_dev;
   if (attr_once.need(&attr_dev)) {
-    HPC_CUDA(cudaFuncSetAttribute(igemm_wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  WG_MAX_STAGES * 7 * WG_ATOM_BYTES + 1024 + 256));
+    HPC_CUDA(cudaFuncSetAttribute(igemm_wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
     attr_once.mark(attr_dev);
   }
   auto st = (cudaStream_t)stream;
   HpcProfScope prof(HPC_PROF_IGEMM_WGRAD, 2.0 * p->N * p->GH * p->GW * (double)local.ntaps * p->R * p->Cc, stream);
   HPC_CUDA(hpc_launch_pdl(igemm_wgrad_umma_kernel, dim3(local.nunits * local.nsplits), dim3(WG_THREADS), smem_bytes, st, tmLo,
-                          tmHi, local));
+                          tmLo1, tmLo2, tmHi, local));
   HPC_LAUNCH_CHECK();
   const int64_t n = (int64_t)local.ntaps * p->R * p->Cc;
   WgOut o;
