@@ -845,26 +845,30 @@ gdn_bwd_dual_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
   pdl_launch_dependents();
 
   if (warp == 0) {
-    // lane l: set l / (NT KC), tensor (l % (NT KC)) / KC, chunk l % KC.  The lanes run independently (a complete_tx may
-    // precede the expect_tx of its phase: the phase cannot complete before the expecting arrival).
+    // The whole warp walks the half-tiles of this CTA in order (k = 0, 1, 2, ...: the sets alternate) and waits
+    // CONVERGED for the buffers of half-tile k; lane l then issues tensor l / KC, chunk l % KC of it.  (Independent
+    // per-lane loops made 18 diverged threads spin on their own: ncu r02p, 1.6 M try_wait executions in this warp.)
     if (lane == 0) {
       mbar_arrive_expect_tx(g_full, Cfg::GAMMA);
       for (int c = 0; c < KC; ++c) tma_load_2d(gam + c * (C * 128), &tmG, g_full, c * 64, 0);
     }
-    if (lane < 2 * NT * KC) {
-      const int s = lane / (NT * KC), rem = lane % (NT * KC), which = rem / KC, c = rem % KC;
-      uint8_t* dst = (which == 0 ? bg : (which == 1 ? bx : bn)) + c * G_CHUNK + s * HBYTES;
-      const CUtensorMap* tm = which == 0 ? &tmGr : (which == 1 ? &tmX : &tmR);
-      // L2 prefetch one half-tile of this set ahead: the load that follows the buffer release then pays L2 latency
-      // instead of HBM latency (the buffers, not the bandwidth, bound the bytes in flight: HPC_GDN_PREFETCH=0 disables)
-      if (p.prefetch && s < mine) tma_prefetch_2d(tm, c * 64, (blockIdx.x + s * gridDim.x) * HROWS);
-      for (int k = s, j = 0; k < mine; k += 2, ++j) {
-        const int h = blockIdx.x + k * gridDim.x;
-        if (p.prefetch && k + 2 < mine) tma_prefetch_2d(tm, c * 64, (h + 2 * (int)gridDim.x) * HROWS);
-        mbar_wait(&in_empty[s], (j & 1) ^ 1);
-        if (rem == 0) mbar_arrive_expect_tx(&in_full[s], NT * Cfg::TILE / 2);
-        tma_load_2d(dst, tm, &in_full[s], c * 64, h * HROWS);
-      }
+    __syncwarp();
+    const bool active = lane < NT * KC;
+    const int which = active ? lane / KC : 0, c = lane % KC;
+    uint8_t* dst0 = (which == 0 ? bg : (which == 1 ? bx : bn)) + c * G_CHUNK;
+    const CUtensorMap* tm = which == 0 ? &tmGr : (which == 1 ? &tmX : &tmR);
+    // L2 prefetch two half-tiles ahead: the load that follows the buffer release then pays L2 latency instead of HBM
+    // latency (the buffers, not the bandwidth, bound the bytes in flight: HPC_GDN_PREFETCH=0 disables)
+    if (p.prefetch && active)
+      for (int k = 0; k < 2 && k < mine; ++k) tma_prefetch_2d(tm, c * 64, (blockIdx.x + k * gridDim.x) * HROWS);
+    for (int k = 0; k < mine; ++k) {
+      const int s = k & 1, j = k >> 1;
+      const int h = blockIdx.x + k * gridDim.x;
+      if (p.prefetch && active && k + 2 < mine) tma_prefetch_2d(tm, c * 64, (h + 2 * (int)gridDim.x) * HROWS);
+      mbar_wait(&in_empty[s], (j & 1) ^ 1);
+      if (lane == 0) mbar_arrive_expect_tx(&in_full[s], NT * Cfg::TILE / 2);
+      __syncwarp();
+      if (active) tma_load_2d(dst0 + s * HBYTES, tm, &in_full[s], c * 64, h * HROWS);
     }
   } else if (warp == 1) {
     if (lane == 0) {
@@ -943,18 +947,21 @@ gdn_bwd_dual_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
       mma_commit(dg_done);
     }
   } else if (warp == 2) {
-    if (lane < 2 * KC) {            // lane: set lane / KC, chunk lane % KC; every lane arrives for itself
-      const int s = lane / KC, c = lane % KC;
-      for (int k = s, j = 0; k < mine; k += 2, ++j) {
-        const int h = blockIdx.x + k * gridDim.x;
-        mbar_wait(&out_full[s], j & 1);
-        tma_store_2d(&tmDx, bg + c * G_CHUNK + s * HBYTES, c * 64, h * HROWS);
+    // the warp walks the half-tiles in order, converged (see the producer); lane c < KC stores chunk c and arrives for
+    // itself once its store has finished reading shared memory
+    for (int k = 0; k < mine; ++k) {
+      const int s = k & 1, j = k >> 1;
+      const int h = blockIdx.x + k * gridDim.x;
+      mbar_wait(&out_full[s], j & 1);
+      if (lane < KC) {
+        tma_store_2d(&tmDx, bg + lane * G_CHUNK + s * HBYTES, lane * 64, h * HROWS);
         bulk_commit();
         bulk_wait_read0();
         mbar_arrive(&in_empty[s]);
       }
-      bulk_wait0();
+      __syncwarp();
     }
+    if (lane < KC) bulk_wait0();
   } else {
     const int w = warp - 3;
     const int q = warp & 3, half = w >> 2;        // TMEM lane quarter, channel quarter
