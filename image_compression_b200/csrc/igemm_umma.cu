@@ -57,9 +57,25 @@ struct FwdKParams {
 // with the tensor pipe 63 % busy -- the MT == 1 pair kernel is bound by operand bytes, 43 % of them weights.  MT == 2
 // halves the weight bytes per flop (4.40 -> 3.46 GB) at the price of an epilogue that no longer overlaps the next
 // tile's MMAs (TMEM holds 2 x 256 columns: both are in use).
-template <int BLOCK_N, int NCTA, int MT = 1>
+// SHARE (with MT == 2): the taps of one kernel column (equal dw) whose dh are consecutive steps of the input stride read
+// the same pixels one tile ROW apart, and a row of the tile (tw = 8 or 16 pixels x 128 B) is one or two whole 1 KB
+// swizzle groups of the K-major operand: the 2-3 taps of such a group share ONE activation box of th + 1 / th + 2 rows
+// and their descriptors start tw x 128 B apart.  A 5 x 5 stride-2 layer then loads 2 boxes (10 + 9 rows) instead of 5
+// (8 rows each) per kernel column and channel slice: 52 % fewer activation bytes.  The activation boxes and the weight
+// boxes run in separate rings (an activation slot lives for 2-3 weight slots), filled by separate warps.
+constexpr int FS_THREADS = 224;        // SHARE: warp 6 loads the weights
+constexpr int FS_A_SLOTS = 3, FS_B_SLOTS = 4;
+constexpr int FS_A_TILE = (FW_BM + 2 * 16) * 128;     // (th + 2) x tw pixels, tw <= 16: 20 KB per M tile
+struct FwdShareSched {                 // K loop of a phase: tap groups (equal dw, dh in consecutive steps of the stride)
+  uint8_t gbegin[HPC_MAX_PHASES], ngroups[HPC_MAX_PHASES];
+  uint8_t gtap0[HPC_MAX_TAPS], gsize[HPC_MAX_TAPS];   // group g = taps order[gtap0[g]] .. (gsize[g] of them, dh ascending)
+  uint8_t order[HPC_MAX_TAPS];
+};
+
+template <int BLOCK_N, int NCTA, int MT = 1, bool SHARE = false>
 struct FwdCfg {
   static_assert(MT == 1 || NCTA == 2, "two M tiles per CTA: CTA-pair kernel only");
+  static_assert(!SHARE || MT == 2, "shared activation boxes: MT == 2 kernel only");
   static constexpr int A_BYTES = FW_BM * FW_BK * 2;        // 16 KB per M tile
   static constexpr int B_BYTES = (BLOCK_N / NCTA) * FW_BK * 2;   // a CTA of a pair holds half of the weight tile
   static constexpr int STAGE_BYTES = MT * A_BYTES + B_BYTES;
@@ -74,11 +90,12 @@ struct FwdCfg {
   static constexpr int FIXED_BYTES = ALIGN_SLACK + 256 /*barriers*/ + BIAS_BYTES;
   static constexpr int BUDGET = NCTA == 2 ? (232448 - FIXED_BYTES - STG_BYTES) : 200 * 1024;
   static constexpr int STAGES = (BUDGET / STAGE_BYTES) > 8 ? 8 : (BUDGET / STAGE_BYTES);
+  static constexpr int OPERAND_BYTES = SHARE ? FS_A_SLOTS * MT * FS_A_TILE + FS_B_SLOTS * B_BYTES : STAGES * STAGE_BYTES;
   static constexpr int ACC_STRIDE = BLOCK_N <= 32 ? 32 : (BLOCK_N <= 64 ? 64 : (BLOCK_N <= 128 ? 128 : 256));
   static constexpr int TMEM_COLS = 2 * ACC_STRIDE;          // 64..512, power of two
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + FIXED_BYTES + STG_BYTES;
+  static constexpr int SMEM_BYTES = OPERAND_BYTES + FIXED_BYTES + STG_BYTES;
   static_assert(SMEM_BYTES <= 232448, "shared memory budget");
-  static_assert((2 * STAGES + 4) * 8 + 4 <= 256, "barrier area");
+  static_assert((2 * STAGES + 4) * 8 + 4 <= 256 && (2 * (FS_A_SLOTS + FS_B_SLOTS) + 4) * 8 + 4 <= 256, "barrier area");
 };
 
 // Work item `w` of the persistent loop -> (phase, tile origin).  NCTA == 1: w is a tile.  NCTA == 2: w is a PAIR of
@@ -215,9 +232,11 @@ __device__ __forceinline__ void epilogue8(const EpiArgs& e, const float* acc, in
   if (e.out_nrm_lp && (e.epi == HPC_EPI_GDN || e.epi == HPC_EPI_IGDN)) store8_bf16(e.out_nrm_lp, o, nrm);
 }
 
-template <int BLOCK_N, int NCTA, int MT>
-__device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const FwdKParams& p) {
-  using Cfg = FwdCfg<BLOCK_N, NCTA, MT>;
+template <int BLOCK_N, int NCTA, int MT, bool SHARE = false>
+__device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const FwdKParams& p,
+                                               const CUtensorMap* tmA1 = nullptr, const CUtensorMap* tmA2 = nullptr,
+                                               const FwdShareSched* sch = nullptr) {
+  using Cfg = FwdCfg<BLOCK_N, NCTA, MT, SHARE>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1 KB aligned; pointer arithmetic keeps the
                                                                                   // shared address space (LDS/STS, not generic LD/ST)
@@ -225,16 +244,21 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
     if (threadIdx.x == 0) printf("hpcodec: igemm_fwd (MT=2): dynamic shared memory window not 1 KB aligned\n");
     __trap();
   }
-  uint8_t* smem_a = smem;                                  // STAGES x MT x 16 KB
-  uint8_t* smem_b = smem + Cfg::STAGES * MT * Cfg::A_BYTES;   // STAGES x B_BYTES (multiples of 1 KB)
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
-  uint64_t* full_bar = bars;                    // [STAGES]  TMA -> MMA     (pair: the leader's collects both CTAs)
-  uint64_t* empty_bar = bars + Cfg::STAGES;     // [STAGES]  MMA -> TMA     (pair: commit multicast to both CTAs)
-  uint64_t* tfull_bar = bars + 2 * Cfg::STAGES; // [2]       MMA -> epilogue (pair: multicast)
+  // operand rings.  !SHARE: STAGES x (MT x 16 KB pixels | B_BYTES weights), one full/empty pair per stage.
+  // SHARE: FS_A_SLOTS x MT x 20 KB pixels with their own barriers, then FS_B_SLOTS x B_BYTES weights with theirs.
+  constexpr int NBAR_A = SHARE ? FS_A_SLOTS : Cfg::STAGES;          // "full_bar/empty_bar" = the activation ring when SHARE
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + (SHARE ? FS_A_SLOTS * MT * FS_A_TILE : Cfg::STAGES * MT * Cfg::A_BYTES);   // multiples of 1 KB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::OPERAND_BYTES);
+  uint64_t* full_bar = bars;                    // [NBAR_A]  TMA -> MMA     (pair: the leader's collects both CTAs)
+  uint64_t* empty_bar = bars + NBAR_A;          // [NBAR_A]  MMA -> TMA     (pair: commit multicast to both CTAs)
+  uint64_t* tfull_bar = bars + 2 * NBAR_A;      // [2]       MMA -> epilogue (pair: multicast)
   uint64_t* tempty_bar = tfull_bar + 2;         // [2]       epilogue -> MMA (pair: both CTAs arrive at the leader's)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
-  float* bias_s = reinterpret_cast<float*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256);   // bias staged once per CTA
-  uint8_t* stg = smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256 + Cfg::BIAS_BYTES;             // output staging (pair kernel)
+  uint64_t* bfull_bar = tempty_bar + 2;         // [FS_B_SLOTS] SHARE: weight ring
+  uint64_t* bempty_bar = bfull_bar + FS_B_SLOTS;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bempty_bar + FS_B_SLOTS);
+  float* bias_s = reinterpret_cast<float*>(smem + Cfg::OPERAND_BYTES + 256);   // bias staged once per CTA
+  uint8_t* stg = smem + Cfg::OPERAND_BYTES + 256 + Cfg::BIAS_BYTES;             // output staging (pair kernel)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int rank = NCTA == 2 ? (int)cluster_ctarank() : 0;
@@ -246,8 +270,12 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
-    for (int s = 0; s < Cfg::STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < NBAR_A; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(&tfull_bar[s], 1); mbar_init(&tempty_bar[s], 4 * NCTA); }
+    if (SHARE) {
+      prefetch_tmap(tmA1); prefetch_tmap(tmA2);
+      for (int s = 0; s < FS_B_SLOTS; ++s) { mbar_init(&bfull_bar[s], 1); mbar_init(&bempty_bar[s], 1); }
+    }
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -256,14 +284,100 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
   // everything above overlaps the tail of the previous kernel in the stream (programmatic dependent launch)
   pdl_wait();
   if (p.epi.bias)
-    for (int i = threadIdx.x; i < BLOCK_N; i += FW_THREADS) bias_s[i] = p.epi.bias[i];
+    for (int i = threadIdx.x; i < BLOCK_N; i += blockDim.x) bias_s[i] = p.epi.bias[i];
   tc_fence_before();
   if (NCTA == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   pdl_launch_dependents();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 0) {
+  if (SHARE && (warp == 0 || warp == 6)) {
+    // ================================ TMA producers, shared activation boxes ================================
+    // warp 0, lanes 0 / 1: the activation box of M tile 0 / 1, one per (tap group, channel slice);
+    // warp 6, lane 0: the weight box of every (tap, channel slice), in the order the MMA warp consumes them
+    const int nl = warp == 0 ? MT : 1;
+    if (lane < nl) {
+      int slot = 0; uint32_t phase = 0;
+      const int box_row = p.tw * 128;
+      for (int w = worker; w < total_work; w += nworkers) {
+        int ph, idx, n0, i0, j0;
+        if (!work_item(p, w, worker, nworkers, per_phase, ksplit, ph, idx)) continue;
+        tile_coords<NCTA, MT>(p, ph, idx, rank, n0, i0, j0, lane);
+        for (int g = sch->gbegin[ph]; g < sch->gbegin[ph] + sch->ngroups[ph]; ++g) {
+          const int gs = sch->gsize[g], t0 = sch->order[sch->gtap0[g]];
+          const CUtensorMap* tm = gs == 1 ? &tmA : (gs == 2 ? tmA1 : tmA2);
+          const uint32_t a_bytes = (uint32_t)((p.th + gs - 1) * box_row);
+          const int cw = j0 * p.is + p.dw[t0], chh = i0 * p.is + p.dh[t0];
+          for (int c = 0; c < p.kchunks; ++c) {
+            if (warp == 0) {
+              mbar_wait(&empty_bar[slot], phase ^ 1);
+              if (rank == 0 && lane == 0) mbar_arrive_expect_tx(&full_bar[slot], 2 * MT * a_bytes);
+              __syncwarp((1u << MT) - 1);
+              tma_load_4d_pair(smem_a + (slot * MT + lane) * FS_A_TILE, tm, mapa_u32(smem_u32(&full_bar[slot]), 0), c * FW_BK,
+                               cw, chh, n0);
+              if (++slot == FS_A_SLOTS) { slot = 0; phase ^= 1; }
+            } else {
+              for (int d = 0; d < gs; ++d) {
+                const int t = sch->order[sch->gtap0[g] + d];
+                mbar_wait(&bempty_bar[slot], phase ^ 1);
+                if (rank == 0) mbar_arrive_expect_tx(&bfull_bar[slot], 2 * Cfg::B_BYTES);
+                tma_load_2d_pair(smem_b + slot * Cfg::B_BYTES, &tmB, mapa_u32(smem_u32(&bfull_bar[slot]), 0), c * FW_BK,
+                                 t * p.Co + rank * (BLOCK_N / 2));
+                if (++slot == FS_B_SLOTS) { slot = 0; phase ^= 1; }
+              }
+            }
+          }
+        }
+      }
+    }
+  } else if (SHARE && warp == 1) {
+    // ================================ MMA issuer, shared activation boxes (leader CTA) ================================
+    if (rank == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(FW_BM * NCTA, BLOCK_N, 0, 0);
+      const uint64_t adesc0 = make_smem_desc_sw128(smem_u32(smem_a), 16, 1024);
+      const uint64_t bdesc0 = make_smem_desc_sw128(smem_u32(smem_b), 16, 1024);
+      const uint32_t row16 = (uint32_t)(p.tw * 128) >> 4;              // one tile row further into the box (16-byte units)
+      int sa = 0, sb = 0; uint32_t pa = 0, pb = 0, acc_phase = 0;
+      for (int w = worker; w < total_work; w += nworkers) {
+        int ph, idx;
+        if (!work_item(p, w, worker, nworkers, per_phase, ksplit, ph, idx)) continue;
+        mbar_wait(&tempty_bar[0], acc_phase ^ 1);       // both accumulators belong to this work item
+        mbar_wait(&tempty_bar[1], acc_phase ^ 1);
+        tc_fence_after();
+        uint32_t started = 0;
+        for (int g = sch->gbegin[ph]; g < sch->gbegin[ph] + sch->ngroups[ph]; ++g) {
+          const int gs = sch->gsize[g];
+          for (int c = 0; c < p.kchunks; ++c) {
+            mbar_wait(&full_bar[sa], pa);
+            const uint64_t ad = adesc0 + (uint64_t)(sa * (MT * FS_A_TILE >> 4));
+            for (int d = 0; d < gs; ++d) {
+              mbar_wait(&bfull_bar[sb], pb);
+              tc_fence_after();
+              const uint64_t bd = bdesc0 + (uint64_t)(sb * (Cfg::B_BYTES >> 4));
+              const uint64_t a0 = ad + (uint64_t)(d * row16);
+              if (elect_one()) {
+#pragma unroll
+                for (int k = 0; k < FW_BK / 16; ++k) {
+                  mma_bf16_ss_pair(tmem_base, a0 + 2 * k, bd + 2 * k, idesc, started | (uint32_t)k);
+                  mma_bf16_ss_pair(tmem_base + Cfg::ACC_STRIDE, a0 + (FS_A_TILE >> 4) + 2 * k, bd + 2 * k, idesc,
+                                   started | (uint32_t)k);
+                }
+                mma_commit_pair(&bempty_bar[sb]);                      // frees the weight slot (in both CTAs)
+                if (d == gs - 1) mma_commit_pair(&empty_bar[sa]);      // ... and after the group's last tap the pixels
+              }
+              __syncwarp();
+              started = 1;
+              if (++sb == FS_B_SLOTS) { sb = 0; pb ^= 1; }
+            }
+            if (++sa == FS_A_SLOTS) { sa = 0; pa ^= 1; }
+          }
+        }
+        if (elect_one()) { mma_commit_pair(&tfull_bar[0]); mma_commit_pair(&tfull_bar[1]); }
+        __syncwarp();
+        acc_phase ^= 1;
+      }
+    }
+  } else if (warp == 0) {
     // ================================ TMA producer ================================
     // The whole warp runs the loop; lane 0 issues the activation box and lane 1 the weight box of a stage (a TMA
     // instruction costs its issuing thread ~100+ cycles, so the boxes of one stage are issued from different lanes).
@@ -348,7 +462,7 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
         else if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
-  } else {
+  } else if (warp < 6) {
     // ================================ epilogue (4 warps) ==========================
     const int q = warp & 3;                 // TMEM lane quarter this warp may access
     const int row = q * 32 + lane;          // tile row == TMEM lane
@@ -460,6 +574,16 @@ igemm_fwd_umma_pair2_kernel(const __grid_constant__ CUtensorMap tmA, const __gri
   igemm_fwd_body<BLOCK_N, 2, 2>(tmA, tmB, p);
 }
 
+// ... and activation boxes shared between the taps of a kernel column (FwdCfg SHARE): tmA / tmA1 / tmA2 = boxes of
+// th, th + 1, th + 2 tile rows.
+template <int BLOCK_N>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FS_THREADS, 1)
+igemm_fwd_umma_pair2s_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA1,
+                             const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB,
+                             const __grid_constant__ FwdKParams p, const __grid_constant__ FwdShareSched sch) {
+  igemm_fwd_body<BLOCK_N, 2, 2, true>(tmA, tmB, p, &tmA1, &tmA2, &sch);
+}
+
 // Second pass of a split-K launch: sums the K slices of every output pixel in a fixed order and applies the bias /
 // epilogue exactly like the in-kernel epilogue does (8 channels per thread).
 __global__ void __launch_bounds__(256)
@@ -483,6 +607,58 @@ splitk_epilogue_kernel(const float* __restrict__ ws, int ksplit, int64_t out_ele
 // ---------------------------------------------------------------------------------------
 // host side of the forward kernel
 // ---------------------------------------------------------------------------------------
+
+// tap groups of the shared-box kernel: per phase, taps sorted by (dw, dh); a group = up to 3 taps of one dw whose dh
+// are consecutive steps of the input stride
+static void fwd_share_schedule(const hpc_igemm_fwd_params* p, FwdShareSched* sch) {
+  memset(sch, 0, sizeof(*sch));
+  int ng = 0, no = 0;
+  for (int ph = 0; ph < p->nphases; ++ph) {
+    const hpc_igemm_phase& P = p->phase[ph];
+    sch->gbegin[ph] = (uint8_t)ng;
+    const int o0 = no;
+    for (int k = 0; k < P.ntaps; ++k) {
+      const int t = P.tap_begin + k;
+      int q = no;
+      while (q > o0 && (p->dw[sch->order[q - 1]] > p->dw[t] ||
+                        (p->dw[sch->order[q - 1]] == p->dw[t] && p->dh[sch->order[q - 1]] > p->dh[t]))) {
+        sch->order[q] = sch->order[q - 1];
+        --q;
+      }
+      sch->order[q] = (uint8_t)t;
+      ++no;
+    }
+    for (int k = o0; k < no;) {
+      int e = k + 1;
+      while (e < no && e - k < 3 && p->dw[sch->order[e]] == p->dw[sch->order[k]] &&
+             p->dh[sch->order[e]] == p->dh[sch->order[e - 1]] + p->is)
+        ++e;
+      sch->gtap0[ng] = (uint8_t)k; sch->gsize[ng] = (uint8_t)(e - k);
+      ++ng;
+      k = e;
+    }
+    sch->ngroups[ph] = (uint8_t)(ng - sch->gbegin[ph]);
+  }
+}
+
+template <int BLOCK_N>
+static int launch_fwd_share(const CUtensorMap* tmA, const CUtensorMap& tmB, const FwdKParams& kp, const FwdShareSched& sch,
+                            cudaStream_t st) {
+  using Cfg = FwdCfg<BLOCK_N, 2, 2, true>;
+  static HpcOncePerDevice attr_once;
+  int attr_dev;
+  if (attr_once.need(&attr_dev)) {
+    HPC_CUDA(cudaFuncSetAttribute(igemm_fwd_umma_pair2s_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  Cfg::SMEM_BYTES));
+    attr_once.mark(attr_dev);
+  }
+  const int items = (kp.tiles_per_phase + 3) / 4 * kp.nphases, tpcs = hpc_num_sms() / 2;
+  const int grid = 2 * (items < tpcs ? items : tpcs);
+  HPC_CUDA(hpc_launch_pdl(igemm_fwd_umma_pair2s_kernel<BLOCK_N>, dim3(grid), dim3(FS_THREADS), Cfg::SMEM_BYTES, st, tmA[0],
+                          tmA[1], tmA[2], tmB, kp, sch));
+  HPC_LAUNCH_CHECK();
+  return HPC_OK;
+}
 
 template <int BLOCK_N>
 static int launch_fwd(const CUtensorMap& tmA, const CUtensorMap& tmB, const FwdKParams& kp, bool pair, int mt, cudaStream_t st) {
@@ -640,13 +816,24 @@ int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
     kp.interleave = mode && kp.nphases > 1 && kp.ksplit == 1 && per >= workers &&
                     (int64_t)rounds * workers * 100 <= (int64_t)per * 104;
   }
-  CUtensorMap tmA, tmB;
+  // activation boxes shared between the taps of a kernel column (FwdCfg SHARE): the big Co = 192 grids of whole-image
+  // tiles.  OFF by default, HPC_FWD_SHARE=1 enables: measured (r02t, same box, back to back) 2.310 ms/step for the
+  // forward class with it and 2.271 without -- with two M tiles per CTA the kernel is no longer bound by L2 -> SM bytes
+  // (0.84 of the sustained tensor peak), so 38 % fewer of them buy nothing and the second ring costs a little.
+  bool share = false;
   {
+    static int mode = -1;
+    if (mode < 0) { const char* e = getenv("HPC_FWD_SHARE"); mode = (e && e[0] == '1') ? 1 : 0; }
+    share = mode && mt == 2 && kp.nb == 1 && kp.tw % 8 == 0 && (kp.th + 2) * kp.tw * 128 <= FS_A_TILE;
+  }
+  CUtensorMap tmAs[3], tmB;
+  CUtensorMap& tmA = tmAs[0];
+  for (int e = 0; e < (share ? 3 : 1); ++e) {      // boxes of th (+1, +2) tile rows
     uint64_t dims[4] = {(uint64_t)p->Ci, (uint64_t)p->W, (uint64_t)p->H, (uint64_t)p->N};
     uint64_t strides[3] = {(uint64_t)p->Ci * 2, (uint64_t)p->W * p->Ci * 2, (uint64_t)p->H * p->W * p->Ci * 2};
-    uint32_t box[4] = {(uint32_t)FW_BK, (uint32_t)(kp.tw * p->is), (uint32_t)(kp.th * p->is), (uint32_t)kp.nb};
+    uint32_t box[4] = {(uint32_t)FW_BK, (uint32_t)(kp.tw * p->is), (uint32_t)((kp.th + e) * p->is), (uint32_t)kp.nb};
     uint32_t estr[4] = {1, (uint32_t)p->is, (uint32_t)p->is, 1};
-    int rc = make_tmap(&tmA, p->x, 4, dims, strides, box, estr);
+    int rc = make_tmap(&tmAs[e], p->x, 4, dims, strides, box, estr);
     if (rc) return rc;
   }
   {
@@ -663,6 +850,11 @@ int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
   HpcProfScope prof(HPC_PROF_IGEMM_FWD,
                     2.0 * p->N * p->GH * p->GW * (double)ntaps_total_all(p) * p->Ci * p->Co, stream);
   int rc;
+  if (share) {
+    FwdShareSched sch;
+    fwd_share_schedule(p, &sch);
+    return launch_fwd_share<192>(tmAs, tmB, kp, sch, st);
+  }
   switch (p->Co) {
     case 64: rc = launch_fwd<64>(tmA, tmB, kp, pair, 1, st); break;
     case 128: rc = launch_fwd<128>(tmA, tmB, kp, pair, 1, st); break;

@@ -53,7 +53,9 @@ def test_forward_large_grids_use_cta_pairs(transposed, N, H, W):
     exercise the phantom tile at the end of a phase / of the grid; the SIMT engine is the checker.
     >= 74 groups of four tiles (cases 2, 4, 5, 6): two M tiles per CTA (igemm_fwd_umma_pair2_kernel), with 1-3 phantom
     tiles at the end of a phase in cases 2 and 6; both the direct (fp32 output) and the staged bulk-copy (bf16 output
-    only) epilogues."""
+    only) epilogues.  With HPC_FWD_SHARE=1 (test_forced_engine_variants_in_a_subprocess) those grids also share
+    activation boxes between the taps of a kernel column (igemm_fwd_umma_pair2s_kernel): groups of 3 + 2 taps (stride 2)
+    and of 3 / 2 taps (transposed phases, dgrad)."""
     torch.manual_seed(4)
     C = 192
     spec = hp.ConvSpec(transposed, C, C, 5, 2)
@@ -94,7 +96,7 @@ def test_forced_engine_variants_in_a_subprocess():
     import os, subprocess, sys
     here = os.path.dirname(os.path.abspath(__file__))
     for env in ({"HPC_FWD_PAIR": "1"}, {"HPC_FWD_PAIR": "0", "HPC_FWD_KSPLIT": "0", "HPC_FWD_INTERLEAVE": "0"},
-                {"HPC_FWD_MT": "1"}):
+                {"HPC_FWD_MT": "1"}, {"HPC_FWD_SHARE": "1"}):
         r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(here, "test_gpu_umma.py"), "-x", "-q", "-k",
                             "forward_and_dgrad or epilogues or large_grids"], env=dict(os.environ, **env),
                            capture_output=True, text=True, timeout=900)
