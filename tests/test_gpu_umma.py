@@ -145,8 +145,12 @@ def test_gdn_forward_backward_engines(inverse, C=192, N=2, H=16, W=24):
         a, b = out[k].float(), ref[k].float()
         err = float((a - b).abs().max()) / (float(b.abs().max()) + 1e-20)
         assert err < 2e-2, (k, err)
-    # the in-kernel column sums are those of the bf16 dx the kernel stored
-    assert torch.allclose(out["dxsum"], out["dx"].float().sum((0, 1, 2)), rtol=1e-4, atol=1e-2)
+    # the in-kernel column sums are those of the bf16 dx the kernel stored, added 8 rows at a time in packed bf16 (three
+    # rounding levels, ~2^-8 of a group sum, unbiased) and across groups in fp32: noise ~ 2^-8 sqrt(P) rms(dx)
+    dxf = out["dx"].float()
+    P = dxf.numel() // C
+    noise = 2.0 ** -8 * P ** 0.5 * float(dxf.pow(2).mean().sqrt())
+    assert float((out["dxsum"] - dxf.sum((0, 1, 2))).abs().max()) <= 4 * noise + 1e-3
 
 
 @pytest.mark.parametrize("inverse", [False, True])
