@@ -59,6 +59,14 @@ __device__ __forceinline__ uint4 pack8(const float* f) {
   for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
   return u;
 }
+// rsqrtf() without its denormal-input path (an FSETP, two scaling multiplies and selects per element, a fifth of the
+// forward kernel's instructions): n = beta + gamma . x^2 >= beta >= 1e-6 is never denormal, and for normal inputs this
+// is the same MUFU.RSQ result, bit for bit.
+__device__ __forceinline__ float rsqrt_normal(float x) {
+  float y;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ float rcp_approx(float x) {      // one MUFU.RCP (1 ulp); the results it feeds are rounded to bf16
   float y;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -130,16 +138,17 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
   uint64_t* xs_empty = bars + 3;    // [2]  store warp, after the y store has finished READING smem
   uint64_t* a_full = bars + 5;      // workers: x^2 of the tile is in TMEM (and the accumulator has been drained)
   uint64_t* rs_empty = bars + 6;    // store warp, after the r store has finished reading smem
-  uint64_t* tfull = bars + 7;       // tcgen05.commit
-  uint64_t* out_full = bars + 8;    // workers: y and r written
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+  uint64_t* tfull = bars + 7;       // [2] tcgen05.commit of the two halves of the output channels (see the MMA warp)
+  uint64_t* out_full = bars + 9;    // workers: y and r written
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmX); prefetch_tmap(&tmY); prefetch_tmap(&tmR); prefetch_tmap(&tmG);
     mbar_init(g_full, 1);
     for (int s = 0; s < 2; ++s) { mbar_init(&xs_full[s], 1); mbar_init(&xs_empty[s], 1); }
-    mbar_init(a_full, G_WORKERS); mbar_init(rs_empty, 1); mbar_init(tfull, 1); mbar_init(out_full, G_WORKERS);
+    mbar_init(a_full, G_WORKERS); mbar_init(rs_empty, 1); mbar_init(&tfull[0], 1); mbar_init(&tfull[1], 1);
+    mbar_init(out_full, G_WORKERS);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, Cfg::FWD_TMEM_COLS);
@@ -169,7 +178,12 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(128, C, 0, 0);
+      // The accumulator is single-buffered (TMEM: 192 columns of it + 2 x 96 of x^2), so the workers wait out every
+      // MMA.  It is issued as two halves of the output channels (N = C/2 each, rows C/2.. of gamma^T start 12 KB into
+      // every chunk) with a commit each: the warps of the first two channel quarters start their epilogue after half
+      // of the MMA time, while the second half runs.
+      constexpr uint32_t idesc = make_idesc_bf16(128, C / 2, 0, 0);
+      static_assert((C / 2) % 16 == 0 && ((C / 2) * 128) % 1024 == 0, "N halves");
       mbar_wait(g_full, 0);
       const uint32_t b_addr = smem_u32(gam);
       int it = 0;
@@ -178,10 +192,14 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
         tc_fence_after();
         const uint32_t a_tmem = tmem_base + A_COL + (it & 1) * A_COLS;
 #pragma unroll
-        for (int k = 0; k < C / 16; ++k)
-          mma_bf16_ts(tmem_base, a_tmem + k * 8,
-                      make_smem_desc_sw128(b_addr + (k >> 2) * (C * 128) + (k & 3) * 32, 16, 1024), idesc, k != 0);
-        mma_commit(tfull);
+        for (int nh = 0; nh < 2; ++nh) {
+#pragma unroll
+          for (int k = 0; k < C / 16; ++k)
+            mma_bf16_ts(tmem_base + nh * (C / 2), a_tmem + k * 8,
+                        make_smem_desc_sw128(b_addr + (k >> 2) * (C * 128) + nh * (C / 2) * 128 + (k & 3) * 32, 16, 1024),
+                        idesc, k != 0);
+          mma_commit(&tfull[nh]);
+        }
       }
     }
   } else if (warp == 2) {
@@ -259,7 +277,7 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
       (void)tile;
       const int b = it & 1;
       uint8_t* xt = xs + b * Cfg::TILE;
-      mbar_wait(tfull, it & 1);
+      mbar_wait(&tfull[half >> 1], it & 1);             // this warp's channel quarter lies in half `half >> 1`
       tc_fence_after();
       if (p.store_r) mbar_wait(rs_empty, (it & 1) ^ 1);   // r of the previous tile has left the staging buffer
       const uint32_t taddr = tmem_base + lane_off + half * (C / 4);
@@ -287,7 +305,7 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
               const float n = v[j][hh * 8 + e] + beta_s[c0 + hh * 8 + e];
-              r[e] = rsqrtf(n);
+              r[e] = rsqrt_normal(n);
               y[e] = p.inverse ? x[e] * (n * r[e]) : x[e] * r[e];
             }
             *reinterpret_cast<uint4*>(xt + o) = pack8(y);
@@ -1043,7 +1061,7 @@ gdn_bwd_dual_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
               const float n = v[hh * 8 + e] + beta_s[c0 + hh * 8 + e];
-              const float r = rsqrtf(n);
+              const float r = rsqrt_normal(n);
               t[e] = g[e] * x[e] * (p.inverse ? r : r * r * r);
               u[e] = p.inverse ? g[e] * (n * r) : g[e] * r;        // g / r = g sqrt(n) = g n r
             }
