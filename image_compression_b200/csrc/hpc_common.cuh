@@ -88,6 +88,13 @@ static inline cudaError_t hpc_launch_pdl(void (*kernel)(KArgs...), dim3 grid, di
 static inline bool hpc_aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 // number of SMs of the current device (cached per thread)
+// K axis of the packed conv weights of the 3-channel layers (thin_umma.cu: kmaj): k' = (cs*5 + kh)*8 + kw.  Returns the
+// index into the reference's (cs, kh*5 + kw) axis, or -1 where the packed operand holds a zero (kw >= 5, k' >= 120).
+__host__ __device__ __forceinline__ int c3_kmaj_source(int k) {
+  const int kw = k & 7, r = k >> 3;                                   // r = cs*5 + kh
+  return (kw < 5 && r < 15) ? (r / 5) * 25 + (r % 5) * 5 + kw : -1;
+}
+
 int hpc_num_sms();
 
 // One-time set-up that CUDA keeps PER DEVICE (cudaFuncSetAttribute: the opt-in dynamic shared memory size belongs to the

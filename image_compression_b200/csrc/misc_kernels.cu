@@ -90,12 +90,14 @@ pack_multi_kernel(const __grid_constant__ PackTable t) {
   if (J.kind == HPC_PACK_TAPS) {
     pack_taps_tile<T>(J, b, sm);
   } else if (J.kind == HPC_PACK_C3_K || J.kind == HPC_PACK_C3_N) {
-    // w[cw*stride_r + cs*stride_c + tap] -> kmaj[cw][128] (k = cs*25+tap, zero padded) or nmaj[80][cw]; always bf16
+    // w[cw*stride_r + cs*stride_c + tap] -> kmaj[cw][128] (k' = (cs*5+kh)*8+kw, zeros elsewhere: c3_kmaj_source) or
+    // nmaj[80][cw] (k = cs*25+tap); always bf16
     const int Cw = J.rows, total = J.kind == HPC_PACK_C3_K ? Cw * 128 : 80 * Cw;
     __nv_bfloat16* __restrict__ dst = (__nv_bfloat16*)J.dst;
     for (int i = b * PK_FLAT + threadIdx.x; i < min(total, (b + 1) * PK_FLAT); i += PK_THREADS) {
       const int cw = J.kind == HPC_PACK_C3_K ? i / 128 : i % Cw, k = J.kind == HPC_PACK_C3_K ? i % 128 : i / Cw;
-      dst[i] = __float2bfloat16_rn(k < 75 ? J.src[cw * J.stride_r + (k / 25) * J.stride_c + (k % 25)] : 0.f);
+      const int src = J.kind == HPC_PACK_C3_K ? c3_kmaj_source(k) : (k < 75 ? k : -1);
+      dst[i] = __float2bfloat16_rn(src >= 0 ? J.src[cw * J.stride_r + (src / 25) * J.stride_c + (src % 25)] : 0.f);
     }
   } else {  // HPC_PACK_GDN: gdn.py:59-62 for gamma and beta + both bf16 operand copies of gamma (== gdn_prepare_kernel)
     const int C = J.rows, total = C * C;

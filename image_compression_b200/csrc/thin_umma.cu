@@ -90,15 +90,19 @@ __device__ __forceinline__ void patch_commit(float* patch, const float (&pf)[NPF
 
 // ---------------------------------------------------------------------------------------
 // weight packing: w[cw*w_sr + cs*w_sc + t] (t = kh*5+kw) ->
-//   kmaj [Cw][128] bf16 (k contiguous, zero padded)   : B operand of the conv
-//   nmaj [80][Cw]  bf16 (cw contiguous, rows >= 75 zero): B operand of the transposed conv
+//   kmaj [Cw][128] bf16, k' = (cs*5 + kh)*8 + kw: every (cs, kh) row of the 5x5 window is one 16-byte unit of 8 taps,
+//                  kw = 5..7 and k' >= 120 zero       : B operand of the conv (its im2col rows copy 8 consecutive
+//                  pixels per unit and let the zero weights mask the 3 extra ones)
+//   nmaj [80][Cw]  bf16 (k = cs*25 + t, cw contiguous, rows >= 75 zero): B operand of the transposed conv
 // ---------------------------------------------------------------------------------------
+// (c3_kmaj_source() in hpc_common.cuh maps k' back to the (cs, t) axis)
 __global__ void pack_c3_weight_kernel(const float* __restrict__ w, int64_t w_sr, int64_t w_sc, int Cw,
                                       __nv_bfloat16* __restrict__ kmaj, __nv_bfloat16* __restrict__ nmaj) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (kmaj && i < Cw * 128) {
     const int cw = i / 128, k = i % 128;
-    kmaj[i] = __float2bfloat16_rn(k < 75 ? w[cw * w_sr + (k / 25) * w_sc + (k % 25)] : 0.f);
+    const int src = c3_kmaj_source(k);
+    kmaj[i] = __float2bfloat16_rn(src >= 0 ? w[cw * w_sr + (src / 25) * w_sc + (src % 25)] : 0.f);
   }
   if (nmaj && i < KPAD * Cw) {
     const int k = i / Cw, cw = i % Cw;
@@ -128,13 +132,28 @@ __device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, const void* s
                "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
                : "memory");
 }
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(
+          smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
 __device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void bulk_wait_group_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
 __device__ __forceinline__ void bulk_wait_group_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
 constexpr int T1_TH = 8, T1_TW = 16;                      // 128 output pixels per tile
-constexpr int T1_PH = 2 * T1_TH + 3, T1_PWV = 2 * T1_TW + 3, T1_PW = T1_PWV + 1;   // 19 x 35 (+1 pad)
+constexpr int T1_PH = 2 * T1_TH + 3, T1_PWV = 2 * T1_TW + 3;   // 19 x 35 input pixels per channel
+constexpr int T1_PWF = 40;     // floats per patch row as the TMA box lands it.  The box starts FOUR pixels left of the tile's
+                               // first tap (TMA wants the innermost start coordinate on a 16-byte boundary: x0 = 2 j0 - 4;
+                               // with 2 j0 - 2 the load faults with "illegal instruction"), so pixel (jl, kw) is column
+                               // 2 jl + 2 + kw and a unit's 8 values end at column 39
+constexpr int T1_PX0 = 4;      // image columns left of 2 j0 in the box
+constexpr int T1_NPATCH = 2;   // patch buffers: the box of tile it+2 is in flight while tile it+1 is gathered
+constexpr int T1_PATCH_BYTES = ((TCS * T1_PH * T1_PWF * 4 + 127) / 128) * 128;   // 9216
+constexpr int T1_UNITS = TCS * 5;                         // 16-byte units per im2col row: one per (cs, kh); unit 15 stays zero
 constexpr int T1_THREADS = 416;
 constexpr int T1_EPI = 256;                               // epilogue threads
 constexpr int T1_A_BYTES = 2 * 16384;                     // two 64-wide K chunks of [128 x 128 B]
@@ -154,43 +173,51 @@ struct T1Cfg {
   static constexpr int B_BYTES = 2 * CW * 128;
   static constexpr int ACC_STRIDE = CW <= 64 ? 64 : (CW <= 128 ? 128 : 256);
   static constexpr int TMEM_COLS = 2 * ACC_STRIDE;
-  static constexpr int PATCH_BYTES = ((TCS * T1_PH * T1_PW * 4 + 1023) / 1024) * 1024;     // keeps `stage` 1 KB aligned
-  static constexpr int SMEM = 1024 + 2 * T1_A_BYTES + B_BYTES + PATCH_BYTES + 2 * T1_NSTAGE * T1_ST_BYTES + 1024 /*bias*/ + 256;
+  static constexpr int PATCH_BYTES = T1_NPATCH * T1_PATCH_BYTES;
+  // no alignment slack (CW = 192 fills the 227 KB exactly; the kernel traps if the dynamic window is not 1 KB aligned)
+  static constexpr int SMEM = 2 * T1_A_BYTES + B_BYTES + 2 * T1_NSTAGE * T1_ST_BYTES + PATCH_BYTES + CW * 4 /*bias*/ + 256;
+  static_assert(SMEM <= 232448 || CW > 192, "shared memory budget");
 };
 
 template <int CW>
 __global__ void __launch_bounds__(T1_THREADS, 1)
 conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmOut,
-                    const __grid_constant__ CUtensorMap tmSq, const __grid_constant__ T1Params p) {
+                    const __grid_constant__ CUtensorMap tmSq, const __grid_constant__ CUtensorMap tmX,
+                    const __grid_constant__ T1Params p) {
   using Cfg = T1Cfg<CW>;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1 KB aligned; pointer arithmetic keeps the
-                                                                                  // shared address space (LDS/STS, not generic LD/ST)
+  uint8_t* smem = smem_raw;
+  if (smem_u32(smem_raw) & 1023u) {                         // no slack budgeted (T1Cfg::SMEM)
+    if (threadIdx.x == 0) printf("hpcodec: conv_c3_umma: dynamic shared memory window not 1 KB aligned\n");
+    __trap();
+  }
   uint8_t* smem_a = smem;                                   // 2 x 32 KB
   uint8_t* smem_b = smem_a + 2 * T1_A_BYTES;                // 2 chunks x [CW x 128 B]
-  float* patch = reinterpret_cast<float*>(smem_b + Cfg::B_BYTES);
-  uint8_t* stage = reinterpret_cast<uint8_t*>(patch) + Cfg::PATCH_BYTES;     // [T1_NSTAGE][2 tensors][128 x 128 B]
-  float* bias_s = reinterpret_cast<float*>(stage + 2 * T1_NSTAGE * T1_ST_BYTES);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(bias_s + 256);
+  uint8_t* stage = smem_b + Cfg::B_BYTES;                    // [T1_NSTAGE][2 tensors][128 x 128 B], 1 KB aligned
+  uint8_t* patch = stage + 2 * T1_NSTAGE * T1_ST_BYTES;      // [T1_NPATCH][TCS][T1_PH][T1_PWF] fp32, written by the TMA
+  float* bias_s = reinterpret_cast<float*>(patch + Cfg::PATCH_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(bias_s + CW);
   uint64_t* full_a = bars;          // [2] builders -> MMA   (128 arrivals)
   uint64_t* empty_a = bars + 2;     // [2] MMA -> builders   (tcgen05.commit)
   uint64_t* tfull = bars + 4;       // [2] MMA -> epilogue
   uint64_t* tempty = bars + 6;      // [2] epilogue -> MMA   (4 arrivals)
   uint64_t* b_full = bars + 8;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+  uint64_t* p_full = bars + 9;      // [T1_NPATCH] TMA -> builders: the input patch of a tile has landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9 + T1_NPATCH);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // zero the A buffers once: the padded K columns (k >= 80) are never written again
+  // zero the A buffers once: the last unit (k' >= 120) is never written again
   for (int i = threadIdx.x; i < 2 * T1_A_BYTES / 16; i += T1_THREADS) reinterpret_cast<uint4*>(smem_a)[i] = make_uint4(0, 0, 0, 0);
   if (threadIdx.x == 0) {
-    prefetch_tmap(&tmB); prefetch_tmap(&tmOut); prefetch_tmap(&tmSq);
+    prefetch_tmap(&tmB); prefetch_tmap(&tmOut); prefetch_tmap(&tmSq); prefetch_tmap(&tmX);
+    for (int s = 0; s < T1_NPATCH; ++s) mbar_init(&p_full[s], 1);
     for (int s = 0; s < 2; ++s) { mbar_init(&full_a[s], 128); mbar_init(&empty_a[s], 1); mbar_init(&tfull[s], 1); mbar_init(&tempty[s], T1_EPI / 32); }
     mbar_init(b_full, 1);
     fence_barrier_init();
   }
   if (warp == 0) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
   pdl_wait();                      // the prologue above overlaps the previous kernel's tail
-  for (int i = threadIdx.x; i < 256; i += T1_THREADS) bias_s[i] = (p.bias && i < CW) ? p.bias[i] : 0.f;
+  for (int i = threadIdx.x; i < CW; i += T1_THREADS) bias_s[i] = p.bias ? p.bias[i] : 0.f;
   fence_proxy_async();
   tc_fence_before();
   __syncthreads();
@@ -216,7 +243,7 @@ conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_consta
         const uint32_t a_addr = smem_u32(smem_a + buf * T1_A_BYTES), b_addr = smem_u32(smem_b);
         const uint32_t d = tmem_base + buf * Cfg::ACC_STRIDE;
 #pragma unroll
-        for (int k = 0; k < KPAD / 16; ++k) {
+        for (int k = 0; k < 128 / 16; ++k) {                 // K = 128: 15 units of 8 taps (5 live each) + one zero unit
           const uint32_t ao = (k >> 2) * 16384 + (k & 3) * 32, bo = (k >> 2) * (CW * 128) + (k & 3) * 32;
           mma_bf16_ss(d, make_smem_desc_sw128(a_addr + ao, 16, 1024), make_smem_desc_sw128(b_addr + bo, 16, 1024), idesc,
                       k != 0);
@@ -227,35 +254,45 @@ conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_consta
     }
   } else if (warp <= 4) {
     // ============================ im2col builders (128 threads) ============================
+    // The input patch of a tile ((2 x 8 + 3) x 40 pixels of the 3 channels, the convolution's zero padding included) is
+    // ONE TMA box of the NCHW fp32 image (out-of-bounds = zero fill), two tiles ahead.  (Fetching it with 16 predicated
+    // loads per thread was 2/3 of the builders' instructions and a third of their time was the wait for those loads:
+    // ncu r02u -- and the builders, not the epilogue, bound the kernel.)
     const int t = threadIdx.x - 32;
     const int il = t >> 4, jl = t & 15;
-    constexpr int NPF = (TCS * T1_PH * T1_PWV + 127) / 128;
-    float pf[NPF];
-    if ((int)blockIdx.x < p.total_tiles) {
-      const int n = blockIdx.x / tiles_per_img, r = blockIdx.x % tiles_per_img;
-      patch_fetch<T1_PH, T1_PWV, NPF>(pf, p.x, n, p.H, p.W, (r / p.tiles_w) * T1_TH, (r % p.tiles_w) * T1_TW, t);
-    }
+    auto issue_patch = [&](int tile, int pb) {
+      const int n = tile / tiles_per_img, r = tile % tiles_per_img;
+      mbar_arrive_expect_tx(&p_full[pb], TCS * T1_PH * T1_PWF * 4);
+      tma_load_3d(patch + pb * T1_PATCH_BYTES, &tmX, &p_full[pb], 2 * (r % p.tiles_w) * T1_TW - T1_PX0, 2 * (r / p.tiles_w) * T1_TH - 2,
+                  n * TCS);
+    };
+    if (t == 0)
+      for (int k = 0; k < T1_NPATCH; ++k)
+        if ((int)blockIdx.x + k * (int)gridDim.x < p.total_tiles) issue_patch(blockIdx.x + k * gridDim.x, k);
     int it = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
-      const int buf = it & 1;
+      const int buf = it & 1, pb = it % T1_NPATCH;
       const uint32_t ph = (it >> 1) & 1;
-      named_bar(1, 128);                                   // previous gather finished with `patch`
-      patch_commit<T1_PH, T1_PWV, T1_PW, NPF>(patch, pf, t);
-      named_bar(1, 128);
-      const int nxt = tile + gridDim.x;
-      if (nxt < p.total_tiles) {
-        const int n = nxt / tiles_per_img, r = nxt % tiles_per_img;
-        patch_fetch<T1_PH, T1_PWV, NPF>(pf, p.x, n, p.H, p.W, (r / p.tiles_w) * T1_TH, (r % p.tiles_w) * T1_TW, t);
-      }
+      mbar_wait(&p_full[pb], (it / T1_NPATCH) & 1);
       mbar_wait(&empty_a[buf], ph ^ 1);
       uint8_t* arow = smem_a + buf * T1_A_BYTES + t * 128;
+      // unit u = (cs, kh): the 8 patch values at row 2 il + kh from column 2 jl + 2 (= image column 2 (j0 + jl) - 2; 8-byte
+      // aligned: four 64-bit loads, a half-warp reads 32 consecutive words) -- taps kw = 5..7 meet zero weights (kmaj
+      // layout).  (A non-finite pixel would therefore also reach the outputs up to 1.5 pixels to its left; the
+      // reference's inputs are images.)
+      const float2* prow = reinterpret_cast<const float2*>(patch + pb * T1_PATCH_BYTES) + il * T1_PWF + jl + (T1_PX0 - 2) / 2;
 #pragma unroll
-      for (int u = 0; u < KPAD / 8; ++u) {
-        const uint4 v = im2col_unit<T1_PH, T1_PW>(patch, il, jl, u);
-        *reinterpret_cast<uint4*>(arow + (u >> 3) * 16384 + (((u & 7) ^ (t & 7)) << 4)) = v;
+      for (int u = 0; u < T1_UNITS; ++u) {
+        const float2* src = prow + ((u / 5) * T1_PH + (u % 5)) * (T1_PWF / 2);
+        const float2 a = src[0], b = src[1], c = src[2], d = src[3];
+        *reinterpret_cast<uint4*>(arow + (u >> 3) * 16384 + (((u & 7) ^ (t & 7)) << 4)) =
+            make_uint4(pack2_bf16(a.x, a.y), pack2_bf16(b.x, b.y), pack2_bf16(c.x, c.y), pack2_bf16(d.x, d.y));
       }
       fence_proxy_async();
       mbar_arrive(&full_a[buf]);
+      named_bar(1, 128);                                   // every builder has finished reading patch[pb]
+      const int nxt = tile + T1_NPATCH * gridDim.x;
+      if (t == 0 && nxt < p.total_tiles) issue_patch(nxt, pb);
     }
   } else {
     // ============================ epilogue (256 threads) ===================================
@@ -331,7 +368,8 @@ conv_c3_umma_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_consta
 }
 
 template <int CW>
-int launch_t1(const CUtensorMap& tmB, const CUtensorMap& tmOut, const CUtensorMap& tmSq, const T1Params& kp, cudaStream_t st) {
+int launch_t1(const CUtensorMap& tmB, const CUtensorMap& tmOut, const CUtensorMap& tmSq, const CUtensorMap& tmX,
+              const T1Params& kp, cudaStream_t st) {
   using Cfg = T1Cfg<CW>;
   static HpcOncePerDevice attr_once;
   int attr_dev;
@@ -340,7 +378,7 @@ int launch_t1(const CUtensorMap& tmB, const CUtensorMap& tmOut, const CUtensorMa
     attr_once.mark(attr_dev);
   }
   const int grid = kp.total_tiles < hpc_num_sms() ? kp.total_tiles : hpc_num_sms();
-  HPC_CUDA(hpc_launch_pdl(conv_c3_umma_kernel<CW>, dim3(grid), dim3(T1_THREADS), Cfg::SMEM, st, tmB, tmOut, tmSq, kp));
+  HPC_CUDA(hpc_launch_pdl(conv_c3_umma_kernel<CW>, dim3(grid), dim3(T1_THREADS), Cfg::SMEM, st, tmB, tmOut, tmSq, tmX, kp));
   HPC_LAUNCH_CHECK();
   return HPC_OK;
 }
@@ -353,6 +391,9 @@ int hpc_conv_c3_fwd_umma(const float* x_nchw, const void* w_kmaj_bf16, const flo
   HPC_REQUIRE(Cw == 64 || Cw == 128 || Cw == 192 || Cw == 256, HPC_ERR_UNSUPPORTED,
               "hpc_conv_c3_fwd_umma: Cw=%d not in {64,128,192,256}", Cw);
   HPC_REQUIRE(x_nchw && w_kmaj_bf16 && out_lp_bf16, HPC_ERR_BAD_SHAPE, "hpc_conv_c3_fwd_umma: NULL pointer");
+  HPC_REQUIRE(W % 4 == 0 && hpc_aligned16(x_nchw), HPC_ERR_BAD_ALIGNMENT,
+              "hpc_conv_c3_fwd_umma: the image rows are fetched by TMA: W %% 4 == 0 and a 16-byte aligned x (W = %d); use "
+              "hpc_conv_c3_fwd otherwise", W);
   HPC_REQUIRE(hpc_aligned16(w_kmaj_bf16) && hpc_aligned16(out_lp_bf16) && hpc_aligned16(out_sq_bf16), HPC_ERR_BAD_ALIGNMENT,
               "hpc_conv_c3_fwd_umma: pointers must be 16B aligned");
   T1Params kp;
@@ -375,14 +416,20 @@ int hpc_conv_c3_fwd_umma(const float* x_nchw, const void* w_kmaj_bf16, const flo
   uint32_t oestr[4] = {1, 1, 1, 1};
   if ((rc = make_tmap(&tmOut, out_lp_bf16, 4, odims, ostr, obox, oestr))) return rc;
   if ((rc = make_tmap(&tmSq, out_sq_bf16 ? out_sq_bf16 : out_lp_bf16, 4, odims, ostr, obox, oestr))) return rc;
+  // the input as a 3-D fp32 map (W, H, N*3): one box = the patch of a tile, T1_PWF columns x T1_PH rows x 3 channels
+  CUtensorMap tmX;
+  uint64_t xdims[3] = {(uint64_t)W, (uint64_t)H, (uint64_t)N * TCS};
+  uint64_t xstr[2] = {(uint64_t)W * 4, (uint64_t)H * W * 4};
+  uint32_t xbox[3] = {T1_PWF, T1_PH, TCS};
+  if ((rc = make_tmap_f32_plain(&tmX, x_nchw, 3, xdims, xstr, xbox))) return rc;
   const double opix = (double)N * kp.OH * kp.OW * Cw;
   HpcProfScope prof(HPC_PROF_THIN, (double)N * TCS * H * W * 4 + opix * (2 + (out_sq_bf16 ? 2 : 0)), stream);
   auto st = (cudaStream_t)stream;
   switch (Cw) {
-    case 64: return launch_t1<64>(tmB, tmOut, tmSq, kp, st);
-    case 128: return launch_t1<128>(tmB, tmOut, tmSq, kp, st);
-    case 192: return launch_t1<192>(tmB, tmOut, tmSq, kp, st);
-    default: return launch_t1<256>(tmB, tmOut, tmSq, kp, st);
+    case 64: return launch_t1<64>(tmB, tmOut, tmSq, tmX, kp, st);
+    case 128: return launch_t1<128>(tmB, tmOut, tmSq, tmX, kp, st);
+    case 192: return launch_t1<192>(tmB, tmOut, tmSq, tmX, kp, st);
+    default: return launch_t1<256>(tmB, tmOut, tmSq, tmX, kp, st);
   }
 }
 

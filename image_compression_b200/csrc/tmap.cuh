@@ -34,3 +34,16 @@ static inline int make_tmap(CUtensorMap* m, const void* base, int rank, const ui
   return HPC_OK;
 }
 
+
+// fp32 tensor map without swizzle (dense box rows in shared memory), zero OOB fill: image patches with their padding
+static inline int make_tmap_f32_plain(CUtensorMap* m, const void* base, int rank, const uint64_t* dims,
+                                      const uint64_t* strides_bytes, const uint32_t* box) {
+  EncodeTiledFn fn = get_encode_fn();
+  HPC_REQUIRE(fn, HPC_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
+  const uint32_t estr[5] = {1, 1, 1, 1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<void*>(base), dims, strides_bytes, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  HPC_REQUIRE(r == CUDA_SUCCESS, HPC_ERR_CUDA, "cuTensorMapEncodeTiled (fp32) failed with CUresult %d", (int)r);
+  return HPC_OK;
+}

@@ -541,8 +541,9 @@ int hpc_gdn_bwd_umma(const void* g_bf16, const void* x_bf16, const void* rnorm_b
 
 /* tcgen05 (sm_100a, bf16 operands, fp32 accumulate) versions of the three thin-channel kernels above; same
  * arithmetic, same reference call sites (analysis.py:55, synthesis.py:55-57 and their autograd).
- *   pack_c3_weight:  w[cw*w_sr + cs*w_sc + kh*5+kw] -> kmaj [Cw][128] bf16 (k = cs*25+kh*5+kw contiguous, zero padded;
- *                    operand of conv_c3_fwd_umma) and/or nmaj [80][Cw] bf16 (operand of deconv_c3_fwd_umma)
+ *   pack_c3_weight:  w[cw*w_sr + cs*w_sc + kh*5+kw] -> kmaj [Cw][128] bf16 (k' = (cs*5+kh)*8 + kw: one 16-byte unit of 8
+ *                    taps per window row, zero for kw >= 5 and k' >= 120; operand of conv_c3_fwd_umma, an opaque
+ *                    format) and/or nmaj [80][Cw] bf16 (k = cs*25+kh*5+kw; operand of deconv_c3_fwd_umma)
  *   conv_c3_fwd_umma:   x NCHW float (N,3,H,W) -> out NHWC bf16 (N,H/2,W/2,Cw) (+ squares, may be NULL)
  *   deconv_c3_fwd_umma: x NHWC bf16 (N,H,W,Cw) -> out NCHW float (N,3,2H,2W)
  *   wgrad_c3_umma:      as wgrad_c3 with wide bf16; workspace from hpc_wgrad_c3_umma_workspace_bytes */
