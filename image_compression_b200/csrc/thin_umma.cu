@@ -30,62 +30,6 @@ __device__ __forceinline__ uint32_t pack2_bf16(float a, float b) {
   return *reinterpret_cast<uint32_t*>(&h);
 }
 
-// One 16-byte unit (8 consecutive k) of the im2col row of pixel (il, jl) of a stride-2, 5x5, pad-2 conv:
-// value(k) = patch[cs][2*il + kh][2*jl + kw], k = cs*25 + kh*5 + kw; k >= 75 -> 0.  PW = patch row pitch.
-template <int PH, int PW>
-__device__ __forceinline__ uint4 im2col_unit(const float* patch, int il, int jl, int unit) {
-  float v[8];
-#pragma unroll
-  for (int e = 0; e < 8; ++e) {
-    const int k = unit * 8 + e;
-    if (k < 75) {
-      const int cs = k / 25, kh = (k % 25) / 5, kw = k % 5;
-      v[e] = patch[(cs * PH + 2 * il + kh) * PW + 2 * jl + kw];
-    } else {
-      v[e] = 0.f;
-    }
-  }
-  return make_uint4(pack2_bf16(v[0], v[1]), pack2_bf16(v[2], v[3]), pack2_bf16(v[4], v[5]), pack2_bf16(v[6], v[7]));
-}
-
-// thin patch (TCS x PH x PW floats, zero outside the image) for the tile whose first output pixel is (i0, j0)
-template <int PH, int PWV, int PW>
-__device__ __forceinline__ void load_patch(float* patch, const float* __restrict__ x, int n, int H, int W, int i0, int j0,
-                                           int tid, int nthreads) {
-  for (int e = tid; e < TCS * PH * PWV; e += nthreads) {
-    const int c = e % PWV, r = (e / PWV) % PH, cs = e / (PWV * PH);
-    const int gy = 2 * i0 - 2 + r, gx = 2 * j0 - 2 + c;
-    patch[(cs * PH + r) * PW + c] =
-        (gy >= 0 && gy < H && gx >= 0 && gx < W) ? __ldg(&x[(((int64_t)n * TCS + cs) * H + gy) * W + gx]) : 0.f;
-  }
-}
-
-
-// Register-prefetched variant: `patch_fetch` issues all global loads of the NEXT tile's patch (independent, so
-// their latencies overlap each other and the current tile's gather), `patch_commit` writes them to smem later.
-template <int PH, int PWV, int NPF>
-__device__ __forceinline__ void patch_fetch(float (&pf)[NPF], const float* __restrict__ x, int n, int H, int W, int i0,
-                                            int j0, int tid) {
-#pragma unroll
-  for (int k = 0; k < NPF; ++k) {
-    const int e = tid + k * 128;
-    const int c = e % PWV, r = (e / PWV) % PH, cs = e / (PWV * PH);
-    const int gy = 2 * i0 - 2 + r, gx = 2 * j0 - 2 + c;
-    pf[k] = (cs < TCS && gy >= 0 && gy < H && gx >= 0 && gx < W) ? __ldg(&x[(((int64_t)n * TCS + cs) * H + gy) * W + gx]) : 0.f;
-  }
-}
-template <int PH, int PWV, int PW, int NPF>
-__device__ __forceinline__ void patch_commit(float* patch, const float (&pf)[NPF], int tid) {
-#pragma unroll
-  for (int k = 0; k < NPF; ++k) {
-    const int e = tid + k * 128;
-    if (e < TCS * PH * PWV) {
-      const int c = e % PWV, r = (e / PWV) % PH, cs = e / (PWV * PH);
-      patch[(cs * PH + r) * PW + c] = pf[k];
-    }
-  }
-}
-
 }  // namespace
 
 // ---------------------------------------------------------------------------------------
@@ -676,7 +620,10 @@ int hpc_deconv_c3_fwd_umma(const void* x_nhwc_bf16, const void* w_nmaj_bf16, con
 // ---------------------------------------------------------------------------------------
 namespace {
 constexpr int T3_TH = 4, T3_TW = 16;                      // 64 pixels per K block
-constexpr int T3_PH = 2 * T3_TH + 3, T3_PWV = 2 * T3_TW + 3, T3_PW = T3_PWV + 1;   // 11 x 35 (+1)
+constexpr int T3_PH = 2 * T3_TH + 3;                      // 11 input rows per K block
+constexpr int T3_PWF = T1_PWF, T3_PX0 = T1_PX0;           // the patch box of the conv kernel (T1), 11 rows high
+constexpr int T3_PATCH_BYTES = ((TCS * T3_PH * T3_PWF * 4 + 127) / 128) * 128;       // 5376
+constexpr int T3_KROWS = 120;                             // live rows of the result in the k' = (cs*5+kh)*8 + kw order
 constexpr int T3_GROUPS = 2;                              // independent im2col builder groups (128 threads each): the
                                                           // kernel is bound by the builders, not by TMA or the MMAs
 constexpr int T3_THREADS = 64 + 128 * T3_GROUPS;
@@ -691,23 +638,25 @@ struct T3Params {
 template <int CW>
 struct T3Cfg {
   static constexpr int STAGE_BYTES = (2 + CW / 64) * ATOM_BYTES;
-  static constexpr int PATCH_BYTES = ((TCS * T3_PH * T3_PW * 4 + 127) / 128) * 128;
+  static constexpr int PATCH_BYTES = 2 * T3_PATCH_BYTES;                 // per builder group: two boxes in flight
   static constexpr int SMEM = 1024 + T3_STAGES * STAGE_BYTES + T3_GROUPS * PATCH_BYTES + 256;
 };
 
 template <int CW>
 __global__ void __launch_bounds__(T3_THREADS, 1)
-wgrad_c3_umma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ T3Params p) {
+wgrad_c3_umma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX,
+                     const __grid_constant__ T3Params p) {
   using Cfg = T3Cfg<CW>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1 KB aligned; pointer arithmetic keeps the
                                                                                   // shared address space (LDS/STS, not generic LD/ST)
-  float* patch = reinterpret_cast<float*>(smem + T3_STAGES * Cfg::STAGE_BYTES);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(patch) + T3_GROUPS * Cfg::PATCH_BYTES);
+  uint8_t* patch = smem + T3_STAGES * Cfg::STAGE_BYTES;         // [T3_GROUPS][2][TCS][T3_PH][T3_PWF] fp32, written by the TMA
+  uint64_t* bars = reinterpret_cast<uint64_t*>(patch + T3_GROUPS * Cfg::PATCH_BYTES);
   uint64_t* full_bar = bars;                    // [STAGES] 1 TMA arrival (+tx) + 128 builder arrivals
   uint64_t* empty_bar = bars + T3_STAGES;       // [STAGES] tcgen05.commit
   uint64_t* done_bar = bars + 2 * T3_STAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done_bar + 1);
+  uint64_t* p_full = done_bar + 1;              // [T3_GROUPS][2] TMA -> builders: an input patch has landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(p_full + 2 * T3_GROUPS);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int split = blockIdx.x;
@@ -715,13 +664,14 @@ wgrad_c3_umma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
   const int kb1 = (int)(((int64_t)(split + 1) * p.kblocks) / p.nsplits);
   const int tiles_per_img = p.tiles_w * p.tiles_h;
 
-  // zero all im2col atoms once: rows k >= 80 of the second atom are never written again
+  // zero all im2col atoms once: the last unit (k' >= 120) of the second atom is never written again
   for (int s = 0; s < T3_STAGES; ++s)
     for (int i = threadIdx.x; i < 2 * ATOM_BYTES / 16; i += T3_THREADS)
       reinterpret_cast<uint4*>(smem + s * Cfg::STAGE_BYTES)[i] = make_uint4(0, 0, 0, 0);
   if (threadIdx.x == 0) {
-    prefetch_tmap(&tmW);
+    prefetch_tmap(&tmW); prefetch_tmap(&tmX);
     for (int s = 0; s < T3_STAGES; ++s) { mbar_init(&full_bar[s], 129); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < 2 * T3_GROUPS; ++s) mbar_init(&p_full[s], 1);
     mbar_init(done_bar, 1);
     fence_barrier_init();
   }
@@ -772,48 +722,53 @@ wgrad_c3_umma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
     // the pipeline stage of a block follows from its index, so TMA, MMA and both groups agree without talking.
     const int grp = (threadIdx.x - 64) >> 7;
     const int t = (threadIdx.x - 64) & 127;
-    const int px = t & 63, half = t >> 6;                  // pixel of the K block, which half of its 10 units
+    const int px = t & 63, half = t >> 6;                  // pixel of the K block, which atom (8 units) of its row
     const int il = px >> 4, jl = px & 15;
-    float* mypatch = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(patch) + grp * Cfg::PATCH_BYTES);
-    constexpr int NPF = (TCS * T3_PH * T3_PWV + 127) / 128;
-    float pf[NPF];
-    if (kb0 + grp < kb1) {
-      const int n = (kb0 + grp) / tiles_per_img, r = (kb0 + grp) % tiles_per_img;
-      patch_fetch<T3_PH, T3_PWV, NPF>(pf, p.thin, n, 2 * p.H, 2 * p.W, (r / p.tiles_w) * T3_TH, (r % p.tiles_w) * T3_TW, t);
-    }
-    for (int kb = kb0 + grp; kb < kb1; kb += T3_GROUPS) {
-      const int seq = kb - kb0, stage = seq % T3_STAGES;
+    uint8_t* mypatch = patch + grp * Cfg::PATCH_BYTES;
+    // the input patch of a K block is ONE TMA box, fetched two of the group's blocks ahead (see the conv kernel, T1)
+    auto issue_patch = [&](int kb, int pb) {
+      const int n = kb / tiles_per_img, r = kb % tiles_per_img;
+      mbar_arrive_expect_tx(&p_full[grp * 2 + pb], TCS * T3_PH * T3_PWF * 4);
+      tma_load_3d(mypatch + pb * T3_PATCH_BYTES, &tmX, &p_full[grp * 2 + pb], 2 * (r % p.tiles_w) * T3_TW - T3_PX0,
+                  2 * (r / p.tiles_w) * T3_TH - 2, n * TCS);
+    };
+    if (t == 0)
+      for (int k = 0; k < 2; ++k)
+        if (kb0 + grp + k * T3_GROUPS < kb1) issue_patch(kb0 + grp + k * T3_GROUPS, k);
+    int m = 0;
+    for (int kb = kb0 + grp; kb < kb1; kb += T3_GROUPS, ++m) {
+      const int seq = kb - kb0, stage = seq % T3_STAGES, pb = m & 1;
       const uint32_t phase = (uint32_t)(seq / T3_STAGES) & 1;
-      named_bar(1 + grp, 128);
-      patch_commit<T3_PH, T3_PWV, T3_PW, NPF>(mypatch, pf, t);
-      named_bar(1 + grp, 128);
-      if (kb + T3_GROUPS < kb1) {
-        const int n = (kb + T3_GROUPS) / tiles_per_img, r = (kb + T3_GROUPS) % tiles_per_img;
-        patch_fetch<T3_PH, T3_PWV, NPF>(pf, p.thin, n, 2 * p.H, 2 * p.W, (r / p.tiles_w) * T3_TH, (r % p.tiles_w) * T3_TW, t);
-      }
+      mbar_wait(&p_full[grp * 2 + pb], (m >> 1) & 1);
       mbar_wait(&empty_bar[stage], phase ^ 1);
-      uint8_t* arow = smem + stage * Cfg::STAGE_BYTES + px * 128;
-      if (half == 0) {                                    // units 0..4 | 5..9 of the 80-long row (compile-time k)
+      // unit u = (cs, kh): 8 consecutive pixels of patch row 2 il + kh from column 2 jl + 2 (the conv kernel's im2col;
+      // the result rows of taps kw = 5..7 are never read).  Thread `half` writes atom `half` of the pixel's row: units
+      // 0..7 | 8..14 (unit 15 stays zero).
+      uint8_t* arow = smem + stage * Cfg::STAGE_BYTES + half * ATOM_BYTES + px * 128;
+      const float2* prow = reinterpret_cast<const float2*>(mypatch + pb * T3_PATCH_BYTES) + il * T3_PWF + jl + (T3_PX0 - 2) / 2;
 #pragma unroll
-        for (int u = 0; u < 5; ++u)
-          *reinterpret_cast<uint4*>(arow + (((u & 7) ^ (px & 7)) << 4)) = im2col_unit<T3_PH, T3_PW>(mypatch, il, jl, u);
-      } else {
-#pragma unroll
-        for (int u = 5; u < 10; ++u)
-          *reinterpret_cast<uint4*>(arow + (u >> 3) * ATOM_BYTES + (((u & 7) ^ (px & 7)) << 4)) =
-              im2col_unit<T3_PH, T3_PW>(mypatch, il, jl, u);
+      for (int uu = 0; uu < 8; ++uu) {
+        const int u = half * 8 + uu;
+        if (u < TCS * 5) {
+          const float2* src = prow + ((u / 5) * T3_PH + (u % 5)) * (T3_PWF / 2);
+          const float2 a = src[0], b = src[1], c = src[2], d = src[3];
+          *reinterpret_cast<uint4*>(arow + ((uu ^ (px & 7)) << 4)) =
+              make_uint4(pack2_bf16(a.x, a.y), pack2_bf16(b.x, b.y), pack2_bf16(c.x, c.y), pack2_bf16(d.x, d.y));
+        }
       }
       fence_proxy_async();
       mbar_arrive(&full_bar[stage]);
+      named_bar(1 + grp, 128);                             // the group has finished reading patch buffer pb
+      if (t == 0 && kb + 2 * T3_GROUPS < kb1) issue_patch(kb + 2 * T3_GROUPS, pb);
     }
     if (grp == 0) {
-    // epilogue: row = k (TMEM lane); rows >= 80 are padding
+    // epilogue: row = k' (TMEM lane); rows >= 120 are padding
     const int q = warp & 3;
     const int row = q * 32 + lane;
     mbar_wait(done_bar, 0);
     tc_fence_after();
-    if (q * 32 < KPAD) {
-      float* dst = p.ws + ((int64_t)split * KPAD + row) * CW;
+    if (q * 32 < T3_KROWS) {
+      float* dst = p.ws + ((int64_t)split * T3_KROWS + row) * CW;
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
       for (int c0 = 0; c0 < CW; c0 += 16) {
         float v[16];
@@ -824,7 +779,7 @@ wgrad_c3_umma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
 #pragma unroll
           for (int e = 0; e < 16; ++e) v[e] = 0.f;
         }
-        if (row < KPAD) {
+        if (row < T3_KROWS) {
 #pragma unroll
           for (int e = 0; e < 16; e += 4) *reinterpret_cast<float4*>(dst + c0 + e) = make_float4(v[e], v[e + 1], v[e + 2], v[e + 3]);
         }
@@ -837,7 +792,7 @@ wgrad_c3_umma_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
   if (warp == 1) tmem_dealloc(tmem_base, 256);
 }
 
-// gw[cw*w_sr + cs*w_sc + t] = sum_s ws[s][cs*25+t][cw]
+// gw[cw*w_sr + cs*w_sc + kh*5 + kw] = sum_s ws[s][(cs*5+kh)*8 + kw][cw]
 __global__ void wgrad_c3_umma_reduce(const float* __restrict__ ws, int nsplits, int Cw, float* __restrict__ gw, int64_t w_sr,
                                      int64_t w_sc) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -845,8 +800,9 @@ __global__ void wgrad_c3_umma_reduce(const float* __restrict__ ws, int nsplits, 
   pdl_launch_dependents();
   if (i >= 75 * Cw) return;
   const int k = i / Cw, cw = i % Cw;
+  const int kp = ((k / 25) * 5 + (k % 25) / 5) * 8 + k % 5;
   float a = 0.f;
-  for (int s = 0; s < nsplits; ++s) a += ws[((int64_t)s * KPAD + k) * Cw + cw];
+  for (int s = 0; s < nsplits; ++s) a += ws[((int64_t)s * T3_KROWS + kp) * Cw + cw];
   gw[cw * w_sr + (k / 25) * w_sc + (k % 25)] = a;
 }
 
@@ -858,7 +814,7 @@ int t3_splits(int kblocks) {
 
 size_t hpc_wgrad_c3_umma_workspace_bytes(int N, int Cw, int H, int W) {
   const int kblocks = N * ((H + T3_TH - 1) / T3_TH) * ((W + T3_TW - 1) / T3_TW);
-  return (size_t)t3_splits(kblocks) * KPAD * Cw * sizeof(float);
+  return (size_t)t3_splits(kblocks) * T3_KROWS * Cw * sizeof(float);
 }
 
 int hpc_wgrad_c3_umma(const void* wide_nhwc_bf16, const float* thin_nchw, int N, int Cw, int H, int W, float* gw,
@@ -874,9 +830,20 @@ int hpc_wgrad_c3_umma(const void* wide_nhwc_bf16, const float* thin_nchw, int N,
   kp.tiles_w = (W + T3_TW - 1) / T3_TW; kp.tiles_h = (H + T3_TH - 1) / T3_TH;
   kp.kblocks = N * kp.tiles_w * kp.tiles_h;
   kp.nsplits = t3_splits(kp.kblocks);
-  const size_t need = (size_t)kp.nsplits * KPAD * Cw * sizeof(float);
+  const size_t need = (size_t)kp.nsplits * T3_KROWS * Cw * sizeof(float);
   HPC_REQUIRE(workspace && workspace_bytes >= need, HPC_ERR_BAD_SHAPE, "hpc_wgrad_c3_umma: workspace too small (%zu < %zu)",
               workspace_bytes, need);
+  HPC_REQUIRE(W % 2 == 0 && hpc_aligned16(thin_nchw), HPC_ERR_BAD_ALIGNMENT,
+              "hpc_wgrad_c3_umma: the image rows are fetched by TMA: an even W (rows of 2W floats in whole 16-byte units) and "
+              "a 16-byte aligned image (W = %d); use hpc_wgrad_c3 otherwise", W);
+  CUtensorMap tmX;      // the thin tensor as a 3-D fp32 map (2W, 2H, N*3): one box = the patch of a K block
+  {
+    uint64_t xdims[3] = {(uint64_t)2 * W, (uint64_t)2 * H, (uint64_t)N * TCS};
+    uint64_t xstr[2] = {(uint64_t)2 * W * 4, (uint64_t)4 * H * W * 4};
+    uint32_t xbox[3] = {T3_PWF, T3_PH, TCS};
+    int rcx = make_tmap_f32_plain(&tmX, thin_nchw, 3, xdims, xstr, xbox);
+    if (rcx) return rcx;
+  }
   CUtensorMap tmW;
   uint64_t dims[4] = {(uint64_t)Cw, (uint64_t)W, (uint64_t)H, (uint64_t)N};
   uint64_t strides[3] = {(uint64_t)Cw * 2, (uint64_t)W * Cw * 2, (uint64_t)H * W * Cw * 2};
@@ -895,7 +862,7 @@ int hpc_wgrad_c3_umma(const void* wide_nhwc_bf16, const float* thin_nchw, int N,
                                     T3Cfg<CW_>::SMEM));                                                              \
       attr_once.mark(attr_dev);                                                                                               \
     }                                                                                                                \
-    HPC_CUDA(hpc_launch_pdl(wgrad_c3_umma_kernel<CW_>, dim3(kp.nsplits), dim3(T3_THREADS), T3Cfg<CW_>::SMEM, st, tmW, kp)); \
+    HPC_CUDA(hpc_launch_pdl(wgrad_c3_umma_kernel<CW_>, dim3(kp.nsplits), dim3(T3_THREADS), T3Cfg<CW_>::SMEM, st, tmW, tmX, kp)); \
   } while (0)
   switch (Cw) {
     case 64: LAUNCH_T3(64); break;

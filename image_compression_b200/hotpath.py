@@ -840,7 +840,8 @@ def wgrad_c3(wide_nhwc, thin_nchw, Cw, Cs, weight=None):
         gw = grad_buffer(weight)
     else:
         gw = torch.empty((Cw, Cs, 5, 5), dtype=torch.float32, device=wide_nhwc.device)
-    if _thin_umma_ok(Cw, Cs, wide_nhwc.dtype):
+    # (the tcgen05 kernel fetches the image patches by TMA: rows of 2W floats in whole 16-byte units, aligned base)
+    if _thin_umma_ok(Cw, Cs, wide_nhwc.dtype) and W % 2 == 0 and thin_nchw.data_ptr() % 16 == 0:
         nb = lib().hpc_wgrad_c3_umma_workspace_bytes(N, Cw, H, W)
         sc = torch.empty(nb, dtype=torch.uint8, device=wide_nhwc.device)
         check(lib().hpc_wgrad_c3_umma(ptr(wide_nhwc), ptr(thin_nchw), N, Cw, H, W, ptr(gw), Cs * 25, 25, ptr(sc), nb,
