@@ -120,7 +120,7 @@ struct T1Cfg {
   static constexpr int PATCH_BYTES = T1_NPATCH * T1_PATCH_BYTES;
   // no alignment slack (CW = 192 fills the 227 KB exactly; the kernel traps if the dynamic window is not 1 KB aligned)
   static constexpr int SMEM = 2 * T1_A_BYTES + B_BYTES + 2 * T1_NSTAGE * T1_ST_BYTES + PATCH_BYTES + CW * 4 /*bias*/ + 256;
-  static_assert(SMEM <= 232448 || CW > 192, "shared memory budget");
+  static_assert(SMEM <= 232448, "shared memory budget");
 };
 
 template <int CW>
@@ -332,8 +332,9 @@ int hpc_conv_c3_fwd_umma(const float* x_nchw, const void* w_kmaj_bf16, const flo
                          void* out_lp_bf16, void* out_sq_bf16, hpc_stream_t stream) {
   HPC_REQUIRE(N > 0 && H > 0 && W > 0, HPC_ERR_BAD_SHAPE, "hpc_conv_c3_fwd_umma: empty tensor");
   HPC_REQUIRE(H % 2 == 0 && W % 2 == 0, HPC_ERR_BAD_SHAPE, "hpc_conv_c3_fwd_umma: H, W must be even (got %dx%d)", H, W);
-  HPC_REQUIRE(Cw == 64 || Cw == 128 || Cw == 192 || Cw == 256, HPC_ERR_UNSUPPORTED,
-              "hpc_conv_c3_fwd_umma: Cw=%d not in {64,128,192,256}", Cw);
+  HPC_REQUIRE(Cw == 64 || Cw == 128 || Cw == 192, HPC_ERR_UNSUPPORTED,
+              "hpc_conv_c3_fwd_umma: Cw=%d not in {64,128,192} (256 channels do not fit the 227 KB of shared memory beside the "
+              "staging tiles: use hpc_conv_c3_fwd)", Cw);
   HPC_REQUIRE(x_nchw && w_kmaj_bf16 && out_lp_bf16, HPC_ERR_BAD_SHAPE, "hpc_conv_c3_fwd_umma: NULL pointer");
   HPC_REQUIRE(W % 4 == 0 && hpc_aligned16(x_nchw), HPC_ERR_BAD_ALIGNMENT,
               "hpc_conv_c3_fwd_umma: the image rows are fetched by TMA: W %% 4 == 0 and a 16-byte aligned x (W = %d); use "
@@ -372,8 +373,7 @@ int hpc_conv_c3_fwd_umma(const float* x_nchw, const void* w_kmaj_bf16, const flo
   switch (Cw) {
     case 64: return launch_t1<64>(tmB, tmOut, tmSq, tmX, kp, st);
     case 128: return launch_t1<128>(tmB, tmOut, tmSq, tmX, kp, st);
-    case 192: return launch_t1<192>(tmB, tmOut, tmSq, tmX, kp, st);
-    default: return launch_t1<256>(tmB, tmOut, tmSq, tmX, kp, st);
+    default: return launch_t1<192>(tmB, tmOut, tmSq, tmX, kp, st);
   }
 }
 

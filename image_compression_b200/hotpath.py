@@ -822,7 +822,7 @@ def conv_c3_forward(x_nchw, weight, bias, want_sq=True, want_f32=False):
     out = torch.empty(shape, dtype=dt, device=x_nchw.device)
     sq = torch.empty(shape, dtype=dt, device=x_nchw.device) if want_sq else None
     # (the tcgen05 kernel fetches its input patches by TMA: rows of whole 16-byte units, 16-byte aligned base)
-    if _thin_umma_ok(Cw, Cs, dt) and not want_f32 and W % 4 == 0 and x_nchw.data_ptr() % 16 == 0:
+    if _thin_umma_ok(Cw, Cs, dt) and Cw <= 192 and not want_f32 and W % 4 == 0 and x_nchw.data_ptr() % 16 == 0:
         check(lib().hpc_conv_c3_fwd_umma(ptr(x_nchw), ptr(pack_c3_weight(weight, "k")), ptr(bias), N, H, W, Cw, ptr(out),
                                          ptr(sq), stream()))
         return out, sq, None
@@ -876,7 +876,7 @@ def deconv_c3_backward(g_nchw, x_nhwc, weight, need_dx=True, bias=None):
     dx = None
     if need_dx:
         dx = torch.empty((N, H2 // 2, W2 // 2, Cw), dtype=dt, device=g_nchw.device)
-        if _thin_umma_ok(Cw, Cs, dt) and W2 % 4 == 0 and g_nchw.data_ptr() % 16 == 0:
+        if _thin_umma_ok(Cw, Cs, dt) and Cw <= 192 and W2 % 4 == 0 and g_nchw.data_ptr() % 16 == 0:
             check(lib().hpc_conv_c3_fwd_umma(ptr(g_nchw), ptr(pack_c3_weight(weight, "k")), None, N, H2, W2, Cw, ptr(dx),
                                              None, stream()))
         else:
