@@ -655,10 +655,11 @@ def record_of(r, peaks, args, headline=False):
     if n:
         ach = flops / (ms * 1e-3) / 1e12
         peak = peaks["bf16_tflops_sustained"]   # kernel timed inside a long step -> sustained figure
-        roofline = {"bound": "tensor", "kernel": "igemm_fwd_umma_pair_kernel + igemm_fwd_umma_kernel (one class: the "
-                    "CTA-pair and single-CTA builds of the implicit-GEMM forward engine)", "achieved": ach, "peak": peak,
+        roofline = {"bound": "tensor", "kernel": "igemm_fwd_umma_pair2_kernel + igemm_fwd_umma_pair_kernel + igemm_fwd_umma_kernel "
+                    "(one class: the CTA-pair (one or two M tiles per CTA) and single-CTA builds of the implicit-GEMM "
+                    "forward engine)", "achieved": ach, "peak": peak,
                     "unit": "TFLOP/s", "frac": ach / peak,
-                    "traffic": ncu_traffic("igemm_fwd_umma_pair_kernel", "igemm_fwd_umma_kernel") if wl == "train" else None,
+                    "traffic": ncu_traffic("igemm_fwd_umma_pair2_kernel", "igemm_fwd_umma_pair_kernel", "igemm_fwd_umma_kernel") if wl == "train" else None,
                     "peak_source": f"{peaks['source']} (bf16 sustained)", "launches": n,
                     "avg_launch_ms": ms / n, "share_of_step": ms / r["ms_events"],
                     "algorithmic_flops_per_launch": flops / n}
