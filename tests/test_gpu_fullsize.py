@@ -32,6 +32,40 @@ def _grads(model, x, nz, ny):
     return fg.flat.clone(), {k: float(v) for k, v in losses.items()}
 
 
+def test_train_step_at_the_shipped_crop_size_engines_agree():
+    """192 x 192 = DATA.SIZE of every shipped recipe (configs/*.yaml:10): grids of 96, 48, 24, 12 pixels, i.e. ragged tiles
+    (24 = 16 + 8, 12 = 8 + 4), groups of four tiles with phantom tiles, shared `lo` boxes on 48- and 24-pixel grids, TMA patch
+    boxes that cross the right and bottom image edges.  The tcgen05 path against its CUDA-core twin on identical bf16
+    operands and noise: fp32 accumulation on both sides, so the whole step agrees to summation-order round-off."""
+    model, params, _ = make_pair("psnr_256", 192)
+    model.load_state_dict(perturb(params))
+    model.train()
+    g = torch.Generator(device=DEV).manual_seed(11)
+    N, H, W = 24, 192, 192
+    x = torch.rand(N, 3, H, W, device=DEV, generator=g)
+    nz = torch.rand(N, 192, H // 64, W // 64, device=DEV, generator=g)
+    ny = torch.rand(N, 192, H // 16, W // 16, device=DEV, generator=g)
+    with pkg.compute_mode("bf16"):
+        got, lg = _grads(model, x, nz, ny)
+    with pkg.compute_mode("bf16_simt"):
+        want, lw = _grads(model, x, nz, ny)
+    for k in lw:
+        assert abs(lg[k] - lw[k]) <= 2e-4 * abs(lw[k]) + 1e-6, (k, lg[k], lw[k])
+    fg = sharding.FlatGradients(model.parameters(), x.device, overlap=False)
+    worst = ("", 1.0, 0.0)
+    for (n, p), o in zip(model.named_parameters(), fg.offsets):
+        a, b = got[o:o + p.numel()], want[o:o + p.numel()]
+        c, r = cosine(a, b), rel_l2(a, b)
+        if r > worst[2]:
+            worst = (n, c, r)
+        # bf16 intermediates are rounded on both sides from fp32 sums that differ in the last bits (and the tcgen05 GDN
+        # backward adds its column sums in packed bf16): rounding boundaries crossed here and there give per-tensor
+        # differences of 1e-3 .. 2e-2 (largest in the first hyper-analysis layer, whose input is |y| behind the noise:
+        # measured 0.018), inside the bf16 bound of the oracle tests and far below a wrong tap or tile (O(1))
+        assert c >= 0.999 and r <= 0.03, (n, c, r)
+    record_parity("train_24x192x192_umma_vs_simt_worst", {"tensor": worst[0], "cosine": worst[1], "rel_l2": worst[2]})
+
+
 def test_train_step_full_size_properties():
     model, params, _ = make_pair("psnr_256", 192)
     model.load_state_dict(perturb(params))
