@@ -534,6 +534,7 @@ struct GdnFusedParams {
   int tiles;
   int inverse;
   int prefetch;            // dual kernel: L2 prefetch of the next half-tile of each set
+  int packed;              // dual kernel: the t / u phase in packed bf16 arithmetic (see the kernel)
   const float* beta;       // recompute form (RC): effective beta[C]; r = rsqrt(beta + x^2 . gamma^T) is rebuilt in the kernel
 };
 
@@ -1083,6 +1084,35 @@ gdn_bwd_dual_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
 #pragma unroll
         for (int jj = 0; jj < UB; ++jj) {
           const uint32_t o = unit_off(row, half * UH + ub + jj);
+          if (p.packed) {
+            // Packed bf16 arithmetic: g, x, r ARE bf16 values and t, u are stored as bf16, so the phase can run on
+            // pairs without widening: 4 HMUL2 per pair instead of 3 unpacks, 4 multiplies and a pack per element
+            // (this phase was 41 % of the kernel's instructions, ncu r02u).  Price: t carries three bf16 roundings
+            // (~2^-8 relative) instead of one; u one, as before.  t only enters sums (a = t . gamma over 192 channels,
+            // d(gamma) and d(beta) over all pixels), where the extra rounding noise averages out.
+            const __nv_bfloat162* g2 = reinterpret_cast<const __nv_bfloat162*>(&rg[jj]);
+            const __nv_bfloat162* x2 = reinterpret_cast<const __nv_bfloat162*>(&rx[jj]);
+            const __nv_bfloat162* r2 = reinterpret_cast<const __nv_bfloat162*>(&rr[jj]);
+            uint4 tq, uq;
+            __nv_bfloat162* t2 = reinterpret_cast<__nv_bfloat162*>(&tq);
+            __nv_bfloat162* u2 = reinterpret_cast<__nv_bfloat162*>(&uq);
+            if (p.inverse) {            // t = g x r, u = g / r
+#pragma unroll
+              for (int w2 = 0; w2 < 4; ++w2) {
+                t2[w2] = __hmul2(__hmul2(g2[w2], x2[w2]), r2[w2]);
+                u2[w2] = __hmul2(g2[w2], h2rcp(r2[w2]));
+              }
+            } else {                    // u = g r, t = u (x r^2)
+#pragma unroll
+              for (int w2 = 0; w2 < 4; ++w2) {
+                u2[w2] = __hmul2(g2[w2], r2[w2]);
+                t2[w2] = __hmul2(u2[w2], __hmul2(x2[w2], __hmul2(r2[w2], r2[w2])));
+              }
+            }
+            *reinterpret_cast<uint4*>(bn + o) = tq;
+            *reinterpret_cast<uint4*>(bg + o) = uq;
+            continue;
+          }
           float g[8], x[8], r[8], t[8], u[8];
           unpack8(rg[jj], g);
           unpack8(rx[jj], x);
@@ -1140,12 +1170,15 @@ gdn_bwd_dual_kernel(const __grid_constant__ CUtensorMap tmGr, const __grid_const
           unpack8(ur[hh], u);
           unpack8(xr[hh], x);
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            d[e] = p.inverse ? u[e] + x[e] * v[hh * 8 + e] : u[e] - x[e] * v[hh * 8 + e];
-            x[e] *= x[e];
-          }
+          for (int e = 0; e < 8; ++e) d[e] = p.inverse ? u[e] + x[e] * v[hh * 8 + e] : u[e] - x[e] * v[hh * 8 + e];
+          // x^2 on the packed pairs: the product of two bf16 values is exact in fp32, so one HMUL2 gives the same bits as
+          // two fp32 multiplies and a pack
+          uint4 sq = xr[hh];
+          __nv_bfloat162* s2 = reinterpret_cast<__nv_bfloat162*>(&sq);
+#pragma unroll
+          for (int w2 = 0; w2 < 4; ++w2) s2[w2] = __hmul2(s2[w2], s2[w2]);
           *reinterpret_cast<uint4*>(bg + o) = pack8(d);
-          *reinterpret_cast<uint4*>(bx + o) = pack8(x);
+          *reinterpret_cast<uint4*>(bx + o) = sq;
         }
       }
       tc_fence_before();
@@ -1411,6 +1444,9 @@ static int gdn_bwd_fused_launch(const void* g_bf16, const void* x_bf16, const vo
   static int prefetch = -1;
   if (prefetch < 0) { const char* e = getenv("HPC_GDN_PREFETCH"); prefetch = e ? (atoi(e) ? 1 : 0) : 1; }
   kp.prefetch = prefetch;
+  static int packed = -1;                        // HPC_GDN_PACKED=0: fp32 arithmetic in the t / u phase (A/B measurements)
+  if (packed < 0) { const char* e = getenv("HPC_GDN_PACKED"); packed = e ? (atoi(e) ? 1 : 0) : 1; }
+  kp.packed = packed;
   const int box_rows = dual ? 64 : 128;
   CUtensorMap tmGr, tmX, tmR, tmDx, tmG;
   if ((rc = make_rows_tmap(&tmGr, g_bf16, P, C, box_rows))) return rc;
