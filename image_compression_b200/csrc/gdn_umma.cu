@@ -242,18 +242,15 @@ gdn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
       for (int uu = 0; uu < UH; uu += 2) {
         const uint4 raw0 = *reinterpret_cast<const uint4*>(xt + unit_off(row, half * UH + uu));
         const uint4 raw1 = *reinterpret_cast<const uint4*>(xt + unit_off(row, half * UH + uu + 1));
-        uint32_t v[8];
-        float f[8];
-        unpack8(raw0, f);
+        // squares on the packed pairs: the product of two bf16 values is exact in fp32, so one HMUL2 per pair gives the
+        // bits of two fp32 multiplies and a pack
+        uint32_t v[8] = {raw0.x, raw0.y, raw0.z, raw0.w, raw1.x, raw1.y, raw1.z, raw1.w};
 #pragma unroll
-        for (int e = 0; e < 8; ++e) f[e] *= f[e];
-        uint4 pk = pack8(f);
-        v[0] = pk.x; v[1] = pk.y; v[2] = pk.z; v[3] = pk.w;
-        unpack8(raw1, f);
-#pragma unroll
-        for (int e = 0; e < 8; ++e) f[e] *= f[e];
-        pk = pack8(f);
-        v[4] = pk.x; v[5] = pk.y; v[6] = pk.z; v[7] = pk.w;
+        for (int e = 0; e < 8; ++e) {
+          __nv_bfloat162 h = *reinterpret_cast<__nv_bfloat162*>(&v[e]);
+          h = __hmul2(h, h);
+          v[e] = *reinterpret_cast<uint32_t*>(&h);
+        }
         tmem_st8(abase + uu * 4, v);
       }
       tmem_st_wait();
