@@ -489,21 +489,23 @@ __device__ __forceinline__ void igemm_fwd_body(const CUtensorMap& tmA, const CUt
         // Stage the bf16 row in shared memory (pitch BLOCK_N*2 + 16 B: conflict-free) and write it with ONE bulk copy.
         uint8_t* srow = stg + row * Cfg::STG_PITCH;
         bulk_group_wait_read();                  // the previous tile's copy has finished reading this row
+        static_assert(BLOCK_N % 32 == 0, "two 16-column loads per round");
 #pragma unroll 1
-        for (int c0 = 0; c0 < BLOCK_N; c0 += 16) {
-          float v[16];
+        for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {          // two TMEM loads in flight per wait
+          float v[32];
           tmem_ld16(taddr + c0, v);
+          tmem_ld16(taddr + c0 + 16, v + 16);
           tmem_ld_wait();
           if (epi.bias) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] += epi.bias[c0 + i];
+            for (int i = 0; i < 32; ++i) v[i] += epi.bias[c0 + i];
           }
-          uint4 u[2];
+          uint4 u[4];
           __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(u);
 #pragma unroll
-          for (int i = 0; i < 8; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
-          *reinterpret_cast<uint4*>(srow + c0 * 2) = u[0];
-          *reinterpret_cast<uint4*>(srow + c0 * 2 + 16) = u[1];
+          for (int i = 0; i < 16; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) *reinterpret_cast<uint4*>(srow + c0 * 2 + 16 * i) = u[i];
         }
         tc_fence_before();
         __syncwarp();
