@@ -1265,6 +1265,35 @@ static int wgrad_check(const hpc_igemm_wgrad_params* p) {
   return HPC_OK;
 }
 
+// Host-side introspection of the work-unit plan (no GPU work; used by the CPU tests of the host logic): writes
+// {nunits, nsplits, a_bytes, kblocks} and then, per unit, 35 ints: phase, natoms, nloads, 4 x (tap, r-chunk, offset KB)
+// for the atoms and 4 x (r-chunk, dw, dh, rows, offset KB) for the `lo` boxes (-1 = unused slot).
+int hpc_igemm_wgrad_plan_describe(const hpc_igemm_wgrad_params* p, int* out, int cap) {
+  HPC_REQUIRE(p && out, HPC_ERR_BAD_SHAPE, "hpc_igemm_wgrad_plan_describe: NULL pointer");
+  int rc = wgrad_check(p);
+  if (rc) return -rc;
+  WgKParams kp;
+  if ((rc = wgrad_plan(p, &kp))) return -rc;
+  const int need = 4 + 35 * kp.nunits;
+  HPC_REQUIRE(cap >= need, HPC_ERR_BAD_SHAPE, "hpc_igemm_wgrad_plan_describe: %d ints needed, %d given", need, cap);
+  int* o = out;
+  *o++ = kp.nunits; *o++ = kp.nsplits; *o++ = kp.a_bytes; *o++ = kp.kblocks;
+  for (int u = 0; u < kp.nunits; ++u) {
+    const WgUnit& U = kp.unit[u];
+    *o++ = U.phase; *o++ = U.natoms; *o++ = U.nloads;
+    for (int a = 0; a < 4; ++a) {
+      const bool on = a < U.natoms;
+      *o++ = on ? U.tap[a] : -1; *o++ = on ? U.rc[a] : -1; *o++ = on ? U.aoff[a] : -1;
+    }
+    for (int l = 0; l < 4; ++l) {
+      const bool on = l < U.nloads;
+      *o++ = on ? U.lrc[l] : -1; *o++ = on ? U.ldw[l] : -1; *o++ = on ? U.ldh[l] : -1; *o++ = on ? U.lrows[l] : -1;
+      *o++ = on ? U.loff[l] : -1;
+    }
+  }
+  return need;
+}
+
 size_t hpc_igemm_wgrad_umma_workspace_bytes(const hpc_igemm_wgrad_params* p) {
   WgKParams kp;
   if (wgrad_check(p) || wgrad_plan(p, &kp)) return 0;

@@ -54,6 +54,8 @@ __global__ void pack_c3_weight_kernel(const float* __restrict__ w, int64_t w_sr,
   }
 }
 
+int hpc_c3_kmaj_source(int k) { return c3_kmaj_source(k); }
+
 int hpc_pack_c3_weight(const float* w, int64_t w_sr, int64_t w_sc, int Cw, void* kmaj_bf16, void* nmaj_bf16,
                        hpc_stream_t stream) {
   HPC_REQUIRE(w && Cw > 0 && (kmaj_bf16 || nmaj_bf16), HPC_ERR_BAD_SHAPE, "hpc_pack_c3_weight: bad arguments");

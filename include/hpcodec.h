@@ -348,6 +348,11 @@ typedef struct {
 
 int hpc_igemm_wgrad(const hpc_igemm_wgrad_params* p, hpc_stream_t stream);
 size_t hpc_igemm_wgrad_workspace_bytes(const hpc_igemm_wgrad_params* p);
+/* Host-side introspection of the tcgen05 engine's work-unit plan for `p` (no GPU work; the CPU tests of the host logic
+ * use it): out = {nunits, nsplits, lo_area_bytes, kblocks} then per unit 35 ints: phase, natoms, nboxes,
+ * 4 x (tap, r-chunk, offset KB) for the atoms, 4 x (r-chunk, dw, dh, rows, offset KB) for the `lo` TMA boxes (-1 = unused).
+ * Returns the number of ints written, or -HPC_ERR_*. */
+int hpc_igemm_wgrad_plan_describe(const hpc_igemm_wgrad_params* p, int* out, int cap);
 
 /* Weight (un)packing between the reference layouts and the packed (tap, row, col) layout.
  * src element (r, c, k) of a weight with K taps (k = kh*KW+kw) sits at r*stride_r + c*stride_c + k:
@@ -549,6 +554,8 @@ int hpc_gdn_bwd_umma(const void* g_bf16, const void* x_bf16, const void* rnorm_b
  *   wgrad_c3_umma:      as wgrad_c3 with wide bf16; workspace from hpc_wgrad_c3_umma_workspace_bytes */
 int hpc_pack_c3_weight(const float* w, int64_t w_sr, int64_t w_sc, int Cw, void* kmaj_bf16, void* nmaj_bf16,
                        hpc_stream_t stream);
+/* index into the reference's (cs, kh*5+kw) axis held at position k' of a kmaj row, or -1 where it holds a zero */
+int hpc_c3_kmaj_source(int k);
 int hpc_conv_c3_fwd_umma(const float* x_nchw, const void* w_kmaj_bf16, const float* bias, int N, int H, int W, int Cw,
                          void* out_lp_bf16, void* out_sq_bf16, hpc_stream_t stream);
 int hpc_deconv_c3_fwd_umma(const void* x_nhwc_bf16, const void* w_nmaj_bf16, const float* bias, int N, int Cw, int H,

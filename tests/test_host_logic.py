@@ -4,6 +4,7 @@ import torch
 import torch.nn.functional as F
 
 import igemm_emulator as E
+from image_compression_b200 import _lib
 from image_compression_b200 import hotpath as hp
 
 torch.manual_seed(0)
@@ -151,3 +152,72 @@ def test_early_all_reduce_slot_range(monkeypatch):
     calls.clear()
     fg._reduce_early([views[0]], flush=True)                   # a flush starts the reduce of whatever is contiguous
     assert calls == [(0, fg.offsets[1])] and fg._frontier == 1
+
+@pytest.mark.parametrize("transposed,k,s,grid", [(False, 5, 2, (64, 64)), (True, 5, 2, (64, 64)), (False, 3, 1, (16, 16)),
+                                                 (False, 5, 2, (4, 4)), (True, 5, 2, (12, 12))])
+def test_wgrad_unit_plan_covers_every_block_once_and_shares_boxes(transposed, k, s, grid):
+    """Host logic of the tcgen05 weight-gradient engine (igemm_umma.cu::wgrad_plan, no GPU needed): every (tap, r-chunk)
+    block of the result is owned by exactly one unit; an atom lies inside one of its unit's `lo` boxes at the row that
+    matches its dh; boxes do not overlap in the stage; on 8x8 K blocks the taps of one (dw, r-chunk) share a box
+    (18 KB of `lo` per full unit instead of 32 KB), on smaller grids (several images per K block) they do not."""
+    import ctypes
+    spec = hp.ConvSpec(transposed, 192, 192, k, s)
+    taps, phases = spec.deconv_taps
+    GH, GW = grid
+    P = _lib.IgemmWgradParams()
+    P.engine, P.dtype = _lib.ENGINE_UMMA, _lib.BF16
+    P.lo, P.hi, P.gw_f32 = 1 << 20, 2 << 20, 3 << 20                  # never dereferenced by the planner
+    P.N, P.GH, P.GW, P.R = 64, GH, GW, 192
+    P.HH, P.HW, P.Cc, P.hs = GH * s, GW * s, 192, s
+    hp._fill_taps(P, taps, phases)
+    P.scale = 1.0
+    buf = (ctypes.c_int * (4 + 35 * 32))()
+    n = _lib.lib().hpc_igemm_wgrad_plan_describe(ctypes.byref(P), buf, len(buf))
+    assert n > 0, _lib.lib().hpc_last_error()
+    nunits, nsplits, a_bytes, kblocks = buf[0], buf[1], buf[2], buf[3]
+    assert n == 4 + 35 * nunits and 1 <= nsplits and nunits * nsplits <= 148 and kblocks >= nsplits
+    share = GH >= 8 and GW >= 8
+    th = 8 if share else min(GH, 8)
+    seen, per_unit_kb = set(), []
+    for u in range(nunits):
+        r = list(buf[4 + 35 * u: 4 + 35 * (u + 1)])
+        ph, natoms, nloads = r[:3]
+        atoms = [tuple(r[3 + 3 * a: 6 + 3 * a]) for a in range(4)]
+        loads = [tuple(r[15 + 5 * l: 20 + 5 * l]) for l in range(4)]
+        assert 1 <= natoms <= 4 and 1 <= nloads <= natoms
+        assert all(x == (-1, -1, -1) for x in atoms[natoms:]) and all(x == (-1,) * 5 for x in loads[nloads:])
+        nt, begin = phases[ph][0], phases[ph][1]
+        ends = []
+        for rc, dw, dh0, rows, off in loads[:nloads]:
+            assert th <= rows <= th + 2
+            assert all(off >= e for e in ends)                         # boxes in ascending, non-overlapping order
+            ends.append(off + (rows if share else 8))                  # KB: one 8-pixel row per KB | a whole 64-pixel box
+        offs = []
+        for tap, rc, off in atoms[:natoms]:
+            assert begin <= tap < begin + nt and (tap, rc) not in seen
+            seen.add((tap, rc))
+            dh, dw = taps[tap][0], taps[tap][1]
+            home = [(lrc, ldw, ldh, rows, loff) for lrc, ldw, ldh, rows, loff in loads[:nloads]
+                    if lrc == rc and ldw == dw and ldh <= dh < ldh + (rows - th) + 1 and off == loff + (dh - ldh) * (1 if share else 0)]
+            assert len(home) == 1, (u, tap, rc, off, loads)
+            offs.append(off)
+        assert offs == sorted(offs)                                    # the second atom of an MMA lies at a higher address
+        per_unit_kb.append(max(ends))
+        assert max(ends) * 1024 <= a_bytes
+    assert seen == {(t, rc) for t in range(len(taps)) for rc in range(3)}
+    full = [kb for u, kb in enumerate(per_unit_kb) if buf[4 + 35 * u + 1] == 4]
+    assert max(full) == (18 if share else 32), (share, full)
+
+
+def test_c3_kmaj_axis_is_a_zero_padded_permutation():
+    """k' = (cs*5 + kh)*8 + kw of the packed 3-channel conv weights (thin_umma.cu): the 75 live positions map onto the
+    reference's (cs, kh*5+kw) axis one to one, the other 53 hold zeros."""
+    src = [_lib.lib().hpc_c3_kmaj_source(k) for k in range(128)]
+    live = [v for v in src if v >= 0]
+    assert sorted(live) == list(range(75)) and src.count(-1) == 53
+    for cs in range(3):
+        for kh in range(5):
+            for kw in range(8):
+                want = cs * 25 + kh * 5 + kw if kw < 5 else -1
+                assert src[(cs * 5 + kh) * 8 + kw] == want
+    assert all(v == -1 for v in src[120:])
