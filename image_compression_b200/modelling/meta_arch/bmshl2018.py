@@ -93,6 +93,13 @@ class Compressor2018(nn.Module):
     def forward(self, x, noise_z=None, noise_y=None):
         """noise_z / noise_y: optional U[0,1) tensors shaped like z / y (NCHW) replacing the in-kernel
         Philox noise of training mode (parity tests inject the reference's draws here)."""
+        if getattr(self, "_is_replica", False):
+            # nn.DataParallel with several visible GPUs (engine/trainer.py:256-259) runs replicas of this module on
+            # threads of ONE process.  The operand cache, the gradient sink and the CUDA-graph state of the hot path are
+            # per process, not per replica thread: refuse loudly instead of racing (ADVICE r01).
+            raise RuntimeError("image_compression_b200: this model ran as an nn.DataParallel replica (several GPUs visible to "
+                               "one process). Use one process per GPU: CUDA_VISIBLE_DEVICES=$LOCAL_RANK under torchrun, where "
+                               "the reference's DataParallel wrap is a one-device pass-through (INTEGRATION.md section 5).")
         reducer = None
         if self.flat_gradients and self.training and torch.is_grad_enabled() and x.is_cuda:
             reducer = self.gradient_reducer()

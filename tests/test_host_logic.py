@@ -221,3 +221,13 @@ def test_c3_kmaj_axis_is_a_zero_padded_permutation():
                 want = cs * 25 + kh * 5 + kw if kw < 5 else -1
                 assert src[(cs * 5 + kh) * 8 + kw] == want
     assert all(v == -1 for v in src[120:])
+
+
+def test_data_parallel_replicas_are_refused_loudly():
+    """nn.DataParallel over several GPUs replicates the module onto threads of one process (torch marks replicas with
+    `_is_replica`); the hot path's caches are per process, so the model refuses instead of racing."""
+    import image_compression_b200 as pkg
+    model = pkg.build_model(pkg.get_recipe_cfg("psnr_256"))
+    model._is_replica = True
+    with pytest.raises(RuntimeError, match="one process per GPU"):
+        model(torch.zeros(1, 3, 64, 64))
