@@ -97,3 +97,39 @@ def test_sampler_stream_is_the_references_and_shards_disjointly(key):
     assert isinstance(first, torch.Tensor) and first.dim() == 0    # 0-d tensors, like the reference yields
     with pytest.raises(ValueError):
         DU.TrainingSampler(5, True, 1, rank=2, world_size=2)
+
+
+class _ToyDataset(torch.utils.data.Dataset):
+    """the shape of the reference's datasets (imagenet_dataset.py:41-49): __getitem__ -> (image_id, transforms(img))"""
+
+    def __init__(self, images, tf):
+        self.images, self.tf = images, tf
+
+    def __len__(self):
+        return len(self.images)
+
+    def __getitem__(self, idx):
+        return f"img{int(idx)}", self.tf(self.images[int(idx)])
+
+
+@pytest.mark.parametrize("workers", [0, 2])
+def test_reference_dataloader_wiring_yields_uint8_batches(workers):
+    """data_utils/dataloader.py:52-59 with this package's names: TrainingSampler -> BatchSampler -> DataLoader with
+    collate_fn = Batch.  The items cross the worker boundary (pickle) as uint8 windows; the batch is uint8 (N,H,W,3)."""
+    from torch.utils.data import BatchSampler, DataLoader
+    c = case("train_default")
+    cfg = cfg_of(c)
+    ds = _ToyDataset(c["imgs"], DU.get_transforms(cfg, "train"))
+    sampler = DU.TrainingSampler(len(ds), True, 7, rank=0, world_size=1)
+    loader = DataLoader(ds, batch_sampler=BatchSampler(sampler, 3, drop_last=True), num_workers=workers,
+                        collate_fn=lambda x: DU.Batch(x, cfg))
+    it = iter(loader)
+    want_ids = [int(i) for i in itertools.islice(iter(DU.TrainingSampler(len(ds), True, 7, 0, 1)), 6)]
+    for step in range(2):
+        b = next(it)
+        assert b.image_ids == tuple(f"img{i}" for i in want_ids[3 * step: 3 * step + 3])
+        assert b.pixels.dtype == torch.uint8 and tuple(b.pixels.shape) == (3, c["size"], c["size"], 3)
+        for k, (y, x) in enumerate(b.offsets_yx):                      # every window is a crop of its own image
+            src = c["imgs"][want_ids[3 * step + k]]
+            assert np.array_equal(b.pixels[k].numpy(), src[y:y + c["size"], x:x + c["size"]])
+    del it
