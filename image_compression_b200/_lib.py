@@ -189,6 +189,7 @@ _SIGNATURES = {
     "hpc_igemm_fwd": (c_int, [POINTER(IgemmFwdParams), c_void_p]),
     "hpc_igemm_wgrad": (c_int, [POINTER(IgemmWgradParams), c_void_p]),
     "hpc_igemm_wgrad_workspace_bytes": (c_size_t, [POINTER(IgemmWgradParams)]),
+    "hpc_igemm_fwd_plan_describe": (c_int, [POINTER(IgemmFwdParams), POINTER(c_int), c_int]),
     "hpc_igemm_wgrad_plan_describe": (c_int, [POINTER(IgemmWgradParams), POINTER(c_int), c_int]),
     "hpc_c3_kmaj_source": (c_int, [c_int]),
     "hpc_pack_weight": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int64, c_int64,

@@ -750,18 +750,13 @@ static int ntaps_total_all(const hpc_igemm_fwd_params* p) {
   return n;
 }
 
-int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
-  HPC_REQUIRE(p->dtype == HPC_BF16, HPC_ERR_UNSUPPORTED, "umma engine: operands must be bf16");
-  HPC_REQUIRE(p->Ci % FW_BK == 0, HPC_ERR_UNSUPPORTED, "umma engine: Ci=%d must be a multiple of 64", p->Ci);
-  HPC_REQUIRE(p->Co == 64 || p->Co == 128 || p->Co == 192 || p->Co == 256, HPC_ERR_UNSUPPORTED,
-              "umma engine: Co=%d not in {64,128,192,256}", p->Co);
-  HPC_REQUIRE(p->is >= 1 && p->is <= 8, HPC_ERR_UNSUPPORTED, "umma engine: input stride %d not in [1,8]", p->is);
-  HPC_REQUIRE(hpc_aligned16(p->x) && hpc_aligned16(p->w), HPC_ERR_BAD_ALIGNMENT, "umma engine: x/w must be 16B aligned");
-  const void* outs[] = {p->out_f32, p->out_lp, p->out_sq_lp, p->out_abs_lp, p->out_nrm_lp, p->aux0, p->aux1, p->aux2,
-                        p->bias};
-  for (const void* q : outs) HPC_REQUIRE(hpc_aligned16(q), HPC_ERR_BAD_ALIGNMENT, "umma engine: epilogue pointers must be 16B aligned");
+// Everything the host decides about a forward launch: tile shape, engine build (single CTA / CTA pair / two M tiles per
+// CTA / shared activation boxes), split-K, phase interleave, staged epilogue.  Shared by the launcher and by
+// hpc_igemm_fwd_plan_describe (the CPU tests of the host logic).
+struct FwdPlan { FwdKParams kp; bool pair, share; int mt, ntaps_total; };
 
-  FwdKParams kp;
+static void fwd_plan(const hpc_igemm_fwd_params* p, FwdPlan* plan) {
+  FwdKParams& kp = plan->kp;
   memset(&kp, 0, sizeof(kp));
   kp.N = p->N; kp.GH = p->GH; kp.GW = p->GW; kp.is = p->is; kp.os = p->os; kp.OH = p->OH; kp.OW = p->OW;
   kp.Co = p->Co; kp.Ci = p->Ci;
@@ -828,6 +823,25 @@ int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
     if (mode < 0) { const char* e = getenv("HPC_FWD_SHARE"); mode = (e && e[0] == '1') ? 1 : 0; }
     share = mode && mt == 2 && kp.nb == 1 && kp.tw % 8 == 0 && (kp.th + 2) * kp.tw * 128 <= FS_A_TILE;
   }
+  plan->pair = pair; plan->mt = mt; plan->share = share; plan->ntaps_total = ntaps_total;
+}
+
+int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
+  HPC_REQUIRE(p->dtype == HPC_BF16, HPC_ERR_UNSUPPORTED, "umma engine: operands must be bf16");
+  HPC_REQUIRE(p->Ci % FW_BK == 0, HPC_ERR_UNSUPPORTED, "umma engine: Ci=%d must be a multiple of 64", p->Ci);
+  HPC_REQUIRE(p->Co == 64 || p->Co == 128 || p->Co == 192 || p->Co == 256, HPC_ERR_UNSUPPORTED,
+              "umma engine: Co=%d not in {64,128,192,256}", p->Co);
+  HPC_REQUIRE(p->is >= 1 && p->is <= 8, HPC_ERR_UNSUPPORTED, "umma engine: input stride %d not in [1,8]", p->is);
+  HPC_REQUIRE(hpc_aligned16(p->x) && hpc_aligned16(p->w), HPC_ERR_BAD_ALIGNMENT, "umma engine: x/w must be 16B aligned");
+  const void* outs[] = {p->out_f32, p->out_lp, p->out_sq_lp, p->out_abs_lp, p->out_nrm_lp, p->aux0, p->aux1, p->aux2,
+                        p->bias};
+  for (const void* q : outs) HPC_REQUIRE(hpc_aligned16(q), HPC_ERR_BAD_ALIGNMENT, "umma engine: epilogue pointers must be 16B aligned");
+
+  FwdPlan plan;
+  fwd_plan(p, &plan);
+  FwdKParams& kp = plan.kp;
+  const bool pair = plan.pair, share = plan.share;
+  const int mt = plan.mt, ntaps_total = plan.ntaps_total;
   CUtensorMap tmAs[3], tmB;
   CUtensorMap& tmA = tmAs[0];
   for (int e = 0; e < (share ? 3 : 1); ++e) {      // boxes of th (+1, +2) tile rows
@@ -869,6 +883,28 @@ int hpc_igemm_fwd_umma(const hpc_igemm_fwd_params* p, hpc_stream_t stream) {
                           kp.ksplit, kp.out_elems, p->Co, kp.epi));
   HPC_LAUNCH_CHECK();
   return HPC_OK;
+}
+
+// Host-side introspection of the forward engine's plan for `p` (no GPU work): out = {pair, M tiles per CTA, shared boxes,
+// ksplit, interleave, staged epilogue, tw, th, nb, tiles_per_phase, total_tiles, grid}.  Returns 12 or -HPC_ERR_*.
+int hpc_igemm_fwd_plan_describe(const hpc_igemm_fwd_params* p, int* out, int cap) {
+  HPC_REQUIRE(p && out && cap >= 12, HPC_ERR_BAD_SHAPE, "hpc_igemm_fwd_plan_describe: needs room for 12 ints");
+  if (p->dtype != HPC_BF16 || p->Ci % FW_BK != 0 || !(p->Co == 64 || p->Co == 128 || p->Co == 192 || p->Co == 256)) return -HPC_ERR_UNSUPPORTED;
+  FwdPlan plan;
+  fwd_plan(p, &plan);
+  const FwdKParams& kp = plan.kp;
+  int grid;
+  if (plan.pair) {
+    const int items = (kp.tiles_per_phase + 2 * plan.mt - 1) / (2 * plan.mt) * kp.nphases, tpcs = hpc_num_sms() / 2;
+    grid = 2 * (items < tpcs ? items : tpcs);
+  } else {
+    const int work = kp.total_tiles * kp.ksplit;
+    grid = work < hpc_num_sms() ? work : hpc_num_sms();
+  }
+  const int v[12] = {plan.pair, plan.mt, plan.share, kp.ksplit, kp.interleave, kp.stage_out, kp.tw, kp.th, kp.nb,
+                     kp.tiles_per_phase, kp.total_tiles, grid};
+  memcpy(out, v, sizeof(v));
+  return 12;
 }
 
 // ---------------------------------------------------------------------------------------

@@ -313,6 +313,10 @@ typedef struct {
 
 int hpc_igemm_fwd(const hpc_igemm_fwd_params* p, hpc_stream_t stream);
 size_t hpc_igemm_fwd_workspace_bytes(const hpc_igemm_fwd_params* p);
+/* Host-side introspection of the tcgen05 engine's plan for `p` (no GPU work; the CPU tests of the host logic use it):
+ * out = {CTA pairs, M tiles per CTA, shared activation boxes, split-K slices, phase interleave, staged epilogue,
+ * tw, th, nb (tile = nb x th x tw = 128 pixels), tiles per phase, tiles, grid}.  Returns 12, or -HPC_ERR_*. */
+int hpc_igemm_fwd_plan_describe(const hpc_igemm_fwd_params* p, int* out, int cap);
 
 /* Weight gradient as implicit GEMM over pixels:
  * gw[t][r][c] = scale * sum_{n,i,j} lo[n, i+dh[t], j+dw[t], r] * hi[n, i*hs+oh_off, j*hs+ow_off, c]

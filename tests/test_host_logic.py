@@ -231,3 +231,58 @@ def test_data_parallel_replicas_are_refused_loudly():
     model._is_replica = True
     with pytest.raises(RuntimeError, match="one process per GPU"):
         model(torch.zeros(1, 3, 64, 64))
+
+
+def _fwd_plan(transposed, k, s, grid, N=64, C=192, dgrad=False):
+    import ctypes
+    spec = hp.ConvSpec(transposed, C, C, k, s)
+    GH, GW = grid
+    # forward of a conv / dgrad of a transposed conv: strided input, one phase; forward of a transposed conv / dgrad of a
+    # conv: unit input stride, s*s output phases (hotpath.ConvSpec.forward / dgrad)
+    conv_like = (not transposed) != dgrad
+    taps, phases = spec.conv_taps if conv_like else spec.deconv_taps
+    is_, os_ = (s, 1) if conv_like else (1, s)
+    P = _lib.IgemmFwdParams()
+    P.engine, P.dtype = _lib.ENGINE_UMMA, _lib.BF16
+    P.x, P.w, P.out_lp = 1 << 20, 2 << 20, 3 << 20                    # never dereferenced by the planner
+    P.N, P.H, P.W, P.Ci = N, GH * is_, GW * is_, C
+    P.GH, P.GW, P.is_, P.os = GH, GW, is_, os_
+    P.OH, P.OW, P.Co = GH * os_, GW * os_, C
+    hp._fill_taps(P, taps, phases)
+    P.epi = _lib.EPI_LINEAR
+    wsb = _lib.lib().hpc_igemm_fwd_workspace_bytes(ctypes.byref(P))
+    if wsb:
+        P.workspace, P.workspace_bytes = 4 << 20, wsb
+    buf = (ctypes.c_int * 12)()
+    assert _lib.lib().hpc_igemm_fwd_plan_describe(ctypes.byref(P), buf, 12) == 12, _lib.lib().hpc_last_error()
+    keys = ("pair", "mt", "share", "ksplit", "interleave", "stage_out", "tw", "th", "nb", "tiles_per_phase", "tiles", "grid")
+    return dict(zip(keys, list(buf)))
+
+
+def test_forward_engine_plan_for_the_model_layers_at_the_benchmark_size():
+    """Which build of the tcgen05 forward engine each 192 -> 192 layer of a 64 x 256x256 step gets (igemm_umma.cu::fwd_plan,
+    no GPU needed): DESIGN 3.1's table.  grid = the layer's iteration grid (output pixels of a conv, input pixels of a
+    transposed conv)."""
+    big = dict(pair=1, mt=2, ksplit=1, stage_out=1, tw=16, th=8, nb=1)
+    for grid, tiles in (((64, 64), 2048), ((32, 32), 512)):            # g_a conv2, conv3: groups of four tiles per CTA pair
+        pl = _fwd_plan(False, 5, 2, grid)
+        assert {k: pl[k] for k in big} == big and pl["tiles"] == tiles and pl["grid"] == 148 and pl["interleave"] == 0
+    pl = _fwd_plan(False, 5, 2, (16, 16))                              # g_a conv4: 128 tiles, one per SM, no pairs
+    assert (pl["pair"], pl["mt"], pl["ksplit"], pl["tiles"], pl["grid"]) == (0, 1, 1, 128, 128)
+    pl = _fwd_plan(False, 3, 1, (16, 16))                              # h_a conv1 (3x3, stride 1)
+    assert (pl["pair"], pl["tiles"], pl["grid"]) == (0, 128, 128)
+    pl = _fwd_plan(False, 5, 2, (8, 8))                                # h_a conv2: 32 tiles of two images, K split 4 ways
+    assert (pl["pair"], pl["nb"], pl["tiles"], pl["ksplit"], pl["grid"]) == (0, 2, 32, 4, 128)
+    pl = _fwd_plan(False, 5, 2, (4, 4))                                # h_a conv3: 8 tiles of eight images, K split 16 ways
+    assert (pl["pair"], pl["tw"], pl["th"], pl["nb"], pl["tiles"], pl["ksplit"], pl["grid"]) == (0, 4, 4, 8, 8, 16, 128)
+    # transposed convs: four output phases over the INPUT grid
+    pl = _fwd_plan(True, 5, 2, (16, 16))                               # g_s deconv1: 4 x 128 tiles -> pairs, 32 groups per phase
+    assert (pl["pair"], pl["mt"], pl["tiles_per_phase"], pl["tiles"], pl["interleave"]) == (1, 2, 128, 512, 0)
+    pl = _fwd_plan(True, 5, 2, (32, 32))                               # deconv2: 1.73 rounds per phase: phase-major
+    assert (pl["pair"], pl["mt"], pl["tiles_per_phase"], pl["interleave"], pl["grid"]) == (1, 2, 512, 0, 148)
+    pl = _fwd_plan(True, 5, 2, (64, 64))                               # deconv3: 6.9 rounds: phases interleaved per tile group
+    assert (pl["pair"], pl["mt"], pl["tiles_per_phase"], pl["interleave"]) == (1, 2, 2048, 1)
+    # dgrads mirror them: dgrad of a strided conv is phase-structured, dgrad of a transposed conv is conv-like
+    assert _fwd_plan(False, 5, 2, (64, 64), dgrad=True)["interleave"] == 1
+    assert _fwd_plan(True, 5, 2, (64, 64), dgrad=True) == _fwd_plan(False, 5, 2, (64, 64))
+    assert all(_fwd_plan(t, 5, 2, g)["share"] == 0 for t in (False, True) for g in ((64, 64), (4, 4)))   # off by default
