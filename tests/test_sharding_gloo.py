@@ -122,3 +122,27 @@ def test_flat_gradients_single_process_noop():
     assert float(fg.flat.abs().sum()) > 0
     fg.zero()
     assert float(net.weight.grad.abs().sum()) == 0.0
+
+
+def _sampler_worker(rank, world, port, results):
+    import itertools
+    from image_compression_b200 import data_utils as DU
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        # the reference's call, unchanged: TrainingSampler(len(dataset), True, cfg.SEED) -- rank and world size come from
+        # the initialised process group
+        results[rank] = [int(i) for i in itertools.islice(iter(DU.TrainingSampler(11, True, 3)), 9)]
+    finally:
+        dist.destroy_process_group()
+
+
+def test_training_sampler_shards_the_reference_stream_under_a_process_group():
+    import itertools
+    from image_compression_b200 import data_utils as DU
+    world = 2
+    mgr = mp.Manager()
+    results = mgr.dict()
+    mp.spawn(_sampler_worker, args=(world, _free_port(), results), nprocs=world, join=True)
+    whole = [int(i) for i in itertools.islice(iter(DU.TrainingSampler(11, True, 3, rank=0, world_size=1)), 18)]
+    assert [results[k % 2][k // 2] for k in range(18)] == whole        # disjoint, nothing skipped, the reference's order
