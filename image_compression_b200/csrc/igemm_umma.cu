@@ -8,6 +8,12 @@
 //   as a canonical K-major SWIZZLE_128B [128 x 64] bf16 operand, plus a [BLOCK_N x 64] weight box.
 //   Accumulators (128 lanes x BLOCK_N fp32 columns) are double-buffered in TMEM so the epilogue of
 //   tile i overlaps the MMAs of tile i+1.
+//   Builds of the same body (igemm_fwd_body), chosen per launch by fwd_plan():
+//     igemm_fwd_umma_kernel          one CTA per tile (grids below 148 tiles; split-K below 74)
+//     igemm_fwd_umma_pair_kernel     CTA pairs, tcgen05.mma.cta_group::2, each CTA holds half of the weight tile
+//     igemm_fwd_umma_pair2_kernel    ... and TWO M tiles per CTA: the pair kernel was bound by L2 -> SM operand bytes
+//     igemm_fwd_umma_pair2s_kernel   ... and one activation box per kernel column (off by default: no faster)
+// Weight-gradient kernel (igemm_wgrad_umma_kernel): see its own header further down.
 #include <cuda.h>
 
 #include <cstdlib>
